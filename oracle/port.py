@@ -1,0 +1,269 @@
+"""ctypes bindings for oracle/libsa_oracle.so (the CPU restatement, oracle/sa_oracle.c) — TEST INFRASTRUCTURE ONLY.
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline leg may import this module.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libsa_oracle.so")
+
+EMIT_GAUSS_MEANONLY_DESCALE = 0
+EMIT_HDP = 1
+EMIT_GAUSS_NOISE_SCALED = 2
+EMIT_GAUSS_NOISE_DESCALE = 3
+
+c_i64p = C.POINTER(C.c_int64)
+c_f64p = C.POINTER(C.c_double)
+c_i32p = C.POINTER(C.c_int32)
+
+
+class SaoModel(C.Structure):
+    _fields_ = [("kind", C.c_int32), ("alphabetSize", C.c_int32), ("kmerLength", C.c_int32), ("pad", C.c_int32),
+                ("K", C.c_int64), ("alphabet", C.c_char * 64), ("trans", C.c_double * 9),
+                ("matchTable", c_f64p), ("gapYTable", c_f64p), ("gapXTable", c_f64p),
+                ("scale", C.c_double), ("shift", C.c_double), ("var", C.c_double),
+                ("gridLength", C.c_int64), ("grid", c_f64p), ("kmerToRow", c_i32p),
+                ("postPred", c_f64p), ("slopes", c_f64p)]
+
+
+class SaoParams(C.Structure):
+    _fields_ = [("threshold", C.c_double), ("minDiagsBetweenTraceBack", C.c_int64),
+                ("traceBackDiagonals", C.c_int64), ("diagonalExpansion", C.c_int64),
+                ("splitMatrixBiggerThanThis", C.c_int64)]
+
+
+class SaoAmbig(C.Structure):
+    _fields_ = [("opts", (C.c_char * 16) * 256)]
+
+
+_lib = None
+
+
+def build():
+    subprocess.check_call(["make", "-s", "-C", HERE, "port"])
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            build()
+        L = C.CDLL(LIB_PATH)
+        L.sao_logAdd.restype = C.c_double
+        L.sao_logAdd.argtypes = [C.c_double, C.c_double]
+        L.sao_kmer_id.restype = C.c_int64
+        L.sao_kmer_id.argtypes = [C.c_char_p, C.c_char_p, C.c_int64, C.c_int64]
+        L.sao_emission.restype = C.c_double
+        L.sao_emission.argtypes = [C.POINTER(SaoModel), C.c_int64, C.c_double, C.c_double, C.c_int]
+        L.sao_band.argtypes = [c_i64p, C.c_int64, C.c_int64, C.c_int64, C.c_int64, c_i64p]
+        L.sao_split_points.restype = C.c_int64
+        L.sao_split_points.argtypes = [c_i64p, C.c_int64, C.c_int64, C.c_int64, C.c_int64, C.c_int, C.c_int,
+                                       c_i64p, C.c_int64]
+        L.sao_paths.restype = C.c_int64
+        L.sao_paths.argtypes = [C.c_char_p, C.POINTER(SaoModel), C.POINTER(SaoAmbig), c_i32p, C.c_int64]
+        L.sao_ambig_default.argtypes = [C.POINTER(SaoAmbig)]
+        L.sao_ambig_from_file.argtypes = [C.POINTER(SaoAmbig), C.c_char_p]
+        L.sao_align.restype = C.c_int64
+        L.sao_align.argtypes = [C.POINTER(SaoModel), C.c_char_p, C.c_int64, c_f64p, C.c_int64, c_i64p, C.c_int64,
+                                C.POINTER(SaoParams), C.c_int, C.c_int, C.POINTER(SaoAmbig), c_i64p, C.c_int64,
+                                c_f64p]
+        L.sao_expectations.restype = C.c_int64
+        L.sao_expectations.argtypes = [C.POINTER(SaoModel), C.c_char_p, C.c_int64, c_f64p, C.c_int64, c_i64p,
+                                       C.c_int64, C.POINTER(SaoParams), C.c_int, C.c_int, C.POINTER(SaoAmbig),
+                                       c_f64p, c_f64p, c_i64p, c_i64p, C.c_int64]
+        L.sao_align_noband.restype = C.c_int64
+        L.sao_align_noband.argtypes = [C.POINTER(SaoModel), C.c_char_p, C.c_int64, c_f64p, C.c_int64,
+                                       C.POINTER(SaoParams), C.c_int, C.c_int, C.POINTER(SaoAmbig), c_i64p,
+                                       C.c_int64]
+        _lib = L
+    return _lib
+
+
+def _i64(a):
+    return a.ctypes.data_as(c_i64p)
+
+
+def _f64(a):
+    return a.ctypes.data_as(c_f64p)
+
+
+def params(threshold=0.01, min_diags=1000, trace_back=40, expansion=20, split_bigger=3000 * 3000):
+    """Library defaults of pairwiseAlignmentBandingParameters_construct (pairwiseAligner.c:2022-2037)."""
+    return SaoParams(threshold, min_diags, trace_back, expansion, split_bigger)
+
+
+class PortModel:
+    """Flat model for the oracle port. Tables are numpy arrays kept alive by this object."""
+
+    def __init__(self, alphabet, k, trans_log, match, gap_y=None, gap_x=None, kind=EMIT_GAUSS_MEANONLY_DESCALE,
+                 scale=1.0, shift=0.0, var=1.0, grid=None, kmer_to_row=None, post_pred=None, slopes=None):
+        self.alphabet = "".join(sorted(alphabet))
+        self.k = k
+        self.K = len(alphabet) ** k
+        self.match = np.ascontiguousarray(match, np.float64).reshape(self.K, 5).copy()
+        if gap_y is None:
+            gap_y = self.match.copy()
+            gap_y[:, 1] *= 1.75  # EXTRA_EVENT_NOISE_MULTIPLIER, stateMachine.c:1528-1532
+        self.gap_y = np.ascontiguousarray(gap_y, np.float64).reshape(self.K, 5).copy()
+        if gap_x is None:
+            gap_x = np.full(self.K, -2.3025850929940455)
+        self.gap_x = np.ascontiguousarray(gap_x, np.float64)
+        self.trans = np.ascontiguousarray(trans_log, np.float64)
+        self.kind = kind
+        self.scale, self.shift, self.var = scale, shift, var
+        self.grid = None if grid is None else np.ascontiguousarray(grid, np.float64)
+        self.kmer_to_row = None if kmer_to_row is None else np.ascontiguousarray(kmer_to_row, np.int32)
+        self.post_pred = None if post_pred is None else np.ascontiguousarray(post_pred, np.float64)
+        self.slopes = None if slopes is None else np.ascontiguousarray(slopes, np.float64)
+
+    def cstruct(self):
+        m = SaoModel()
+        m.kind = self.kind
+        m.alphabetSize = len(self.alphabet)
+        m.kmerLength = self.k
+        m.K = self.K
+        m.alphabet = self.alphabet.encode()
+        for i in range(9):
+            m.trans[i] = self.trans[i]
+        m.matchTable = _f64(self.match)
+        m.gapYTable = _f64(self.gap_y)
+        m.gapXTable = _f64(self.gap_x)
+        m.scale, m.shift, m.var = self.scale, self.shift, self.var
+        if self.grid is not None:
+            m.gridLength = len(self.grid)
+            m.grid = _f64(self.grid)
+            m.kmerToRow = self.kmer_to_row.ctypes.data_as(c_i32p)
+            m.postPred = _f64(self.post_pred)
+            m.slopes = _f64(self.slopes)
+        return m
+
+    def kmer_string(self, idx):
+        a = len(self.alphabet)
+        s = []
+        for _ in range(self.k):
+            s.append(self.alphabet[idx % a])
+            idx //= a
+        return "".join(reversed(s))
+
+
+def load_model_file(path, kind=EMIT_GAUSS_MEANONLY_DESCALE):
+    """Parse a signalAlign .model file (format: stateMachine.c:1445-1452; transitions mapping :1202-1258)."""
+    with open(path) as f:
+        l0 = f.readline().split()
+        l1 = f.readline().split()
+        l2 = f.readline().split()
+    n_states, a_size, alphabet, k = int(l0[0]), int(l0[1]), l0[2], int(l0[3])
+    assert n_states == 3 and len(alphabet) == a_size
+    t = [float(v) for v in l1]
+    assert len(t) == 10
+    with np.errstate(divide="ignore"):
+        lg = np.log(np.array(t[:9]))
+    # order: MATCH_CONTINUE, MATCH_FROM_GAP_X, MATCH_FROM_GAP_Y, GAP_OPEN_X, GAP_OPEN_Y, GAP_EXTEND_X, GAP_EXTEND_Y,
+    #        GAP_SWITCH_TO_X (never loaded: stays LOG_ZERO), GAP_SWITCH_TO_Y (file token 7)
+    trans = np.array([lg[0], lg[3], lg[6], lg[1], lg[2], lg[4], lg[8], -np.inf, lg[7]])
+    table = np.array([float(v) for v in l2]).reshape(-1, 5)
+    assert table.shape[0] == a_size ** k
+    return PortModel(alphabet, k, trans, table, kind=kind)
+
+
+def make_ambig(path=None):
+    a = SaoAmbig()
+    if path:
+        if lib().sao_ambig_from_file(C.byref(a), path.encode()) != 0:
+            raise IOError(path)
+    else:
+        lib().sao_ambig_default(C.byref(a))
+    return a
+
+
+def align(model, target, events, anchors, p=None, ragged_left=True, ragged_right=True, ambig=None):
+    """Returns (pairs[n,4] int64 (p1e7, x, y, kmerIdx), stats[4])."""
+    p = p or params()
+    events = np.ascontiguousarray(events, np.float64).reshape(-1, 4)
+    anchors = np.ascontiguousarray(anchors, np.int64).reshape(-1, 2)
+    lY = events.shape[0]
+    lX = max(0, len(target) - (model.k - 1))
+    m = model.cstruct()
+    amb = ambig or make_ambig()
+    cap = 64 * (lX + lY) + 1024
+    stats = np.zeros(4)
+    while True:
+        out = np.zeros((cap, 4), np.int64)
+        n = lib().sao_align(C.byref(m), target.encode(), lX, _f64(events), lY, _i64(anchors), anchors.shape[0],
+                            C.byref(p), int(ragged_left), int(ragged_right), C.byref(amb), _i64(out), cap,
+                            _f64(stats))
+        if n < 0:
+            raise ValueError("kmer contains a character outside the alphabet")
+        if n <= cap:
+            return out[:n].copy(), stats
+        cap = n
+
+
+def align_noband(model, target, events, p=None, ragged_left=False, ragged_right=False, ambig=None):
+    p = p or params()
+    events = np.ascontiguousarray(events, np.float64).reshape(-1, 4)
+    lY = events.shape[0]
+    lX = len(target) - (model.k - 1)
+    m = model.cstruct()
+    amb = ambig or make_ambig()
+    cap = 64 * (lX + lY) + 1024
+    out = np.zeros((cap, 4), np.int64)
+    n = lib().sao_align_noband(C.byref(m), target.encode(), lX, _f64(events), lY, C.byref(p), int(ragged_left),
+                               int(ragged_right), C.byref(amb), _i64(out), cap)
+    return out[:n].copy()
+
+
+def expectations(model, target, events, anchors, p=None, ragged_left=True, ragged_right=True, ambig=None,
+                 pseudo_t=0.001):
+    """Returns (transitions9 incl. pseudocount, likelihood, assignKmerOff, assignEvent)."""
+    p = p or params()
+    events = np.ascontiguousarray(events, np.float64).reshape(-1, 4)
+    anchors = np.ascontiguousarray(anchors, np.int64).reshape(-1, 2)
+    lY = events.shape[0]
+    lX = len(target) - (model.k - 1)
+    m = model.cstruct()
+    amb = ambig or make_ambig()
+    tr = np.full(9, pseudo_t)
+    lik = np.zeros(1)
+    cap = 8 * (lX + lY) + 1024
+    ak = np.zeros(cap, np.int64)
+    ae = np.zeros(cap, np.int64)
+    n = lib().sao_expectations(C.byref(m), target.encode(), lX, _f64(events), lY, _i64(anchors), anchors.shape[0],
+                               C.byref(p), int(ragged_left), int(ragged_right), C.byref(amb), _f64(tr), _f64(lik),
+                               _i64(ak), _i64(ae), cap)
+    if n < 0:
+        raise ValueError("kmer contains a character outside the alphabet")
+    return tr, float(lik[0]), ak[:n].copy(), ae[:n].copy()
+
+
+def band(anchors, lX, lY, expansion):
+    anchors = np.ascontiguousarray(anchors, np.int64).reshape(-1, 2)
+    out = np.zeros((lX + lY + 1, 3), np.int64)
+    lib().sao_band(_i64(anchors), anchors.shape[0], lX, lY, expansion, _i64(out))
+    return out
+
+
+def split_points(anchors, lX, lY, split_bigger, ragged_left, ragged_right):
+    anchors = np.ascontiguousarray(anchors, np.int64).reshape(-1, 2)
+    cap = anchors.shape[0] + 4
+    out = np.zeros((cap, 4), np.int64)
+    n = lib().sao_split_points(_i64(anchors), anchors.shape[0], lX, lY, split_bigger, int(ragged_left),
+                               int(ragged_right), _i64(out), cap)
+    return out[:n].copy()
+
+
+def log_add(x, y):
+    return lib().sao_logAdd(x, y)
+
+
+def kmer_id(kmer, alphabet):
+    return lib().sao_kmer_id(kmer.encode(), alphabet.encode(), len(alphabet), len(kmer))
+
+
+def emission(model, kmer_idx, mean, noise=1.0, match=True):
+    m = model.cstruct()
+    return lib().sao_emission(C.byref(m), kmer_idx, mean, noise, 1 if match else 0)
