@@ -1,0 +1,163 @@
+/*
+ * signalalign_b200.h — C-ABI of the B200-native signalAlign hot path (libsagpu.so).
+ *
+ * One data-parallel path is exported: the anchor-banded forward/backward posterior-match DP of
+ * signalAlign's 3-state pair-HMM with its Gaussian-table / HDP emissions.  Every entry point is
+ * `extern "C"`, takes plain pointers and sizes, and names the reference interface it replaces
+ * (paths relative to the signalAlign source tree).
+ *
+ * There is NO CPU fallback: every compute entry point fails (non-zero return + sa_last_error())
+ * when no CUDA device is usable.
+ */
+#ifndef SIGNALALIGN_B200_H
+#define SIGNALALIGN_B200_H
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SA_OK 0
+#define SA_ERR_CUDA 1      /* CUDA runtime failure (message in sa_last_error) */
+#define SA_ERR_INPUT 2     /* malformed input (bad kmer character, anchors out of range, ...) — the reference st_errAbort()s */
+#define SA_ERR_IO 3        /* model file unreadable */
+
+/* ---------------------------------------------------------------------------------------------- models
+ * Replaces: stateMachine3_loadFromFile (impl/stateMachine.c:1440-1538), deserialize_nhdp
+ * (impl/nanopore_hdp.c:1088-1115) -> deserialize_hdp (impl/hdp.c:3052-3322),
+ * stateMachine3_setModelToHdpExpectedValues (impl/stateMachine.c:1275-1304).
+ */
+typedef struct sa_model sa_model_t;
+
+/* which reference emission function the model evaluates (inc/stateMachine.h:303-309) */
+#define SA_EMIT_GAUSS_MEANONLY_DESCALE 0 /* emissions_signal_strawManGetKmerEventMatchProbWithDescaling_MeanOnly (signalMachine production) */
+#define SA_EMIT_HDP 1                    /* emissions_signal_getHdpKmerDensity (production with an .nhdp) */
+#define SA_EMIT_GAUSS_NOISE_SCALED 2     /* emissions_signal_strawManGetKmerEventMatchProb (getStateMachine3) */
+#define SA_EMIT_GAUSS_NOISE_DESCALE 3    /* emissions_signal_strawManGetKmerEventMatchProbWithDescaling (getStateMachine3_descaled) */
+
+/* .model (3 lines) [+ .nhdp]; nhdpFile may be NULL.  With an .nhdp the kind is forced to SA_EMIT_HDP. */
+sa_model_t *sa_model_load(const char *modelFile, const char *nhdpFile, int emissionKind);
+
+/* From the raw tables of an existing `StateMachine` (inc/stateMachine.h:85-118):
+ *   alphabet (any order; sorted internally as sequence_prepareAlphabet, impl/pairwiseAligner.c:366),
+ *   logTransitions[9] in `struct _StateMachine3` order (inc/stateMachine.h:154-162),
+ *   matchTable / gapYTable = EMISSION_MATCH_MATRIX / EMISSION_GAP_Y_MATRIX (K*5 doubles),
+ *   gapXTable = EMISSION_GAP_X_PROBS (K doubles, may be NULL = log 0.1). */
+sa_model_t *sa_model_from_tables(const char *alphabet, int32_t kmerLength, const double *logTransitions,
+                                 const double *matchTable, const double *gapYTable, const double *gapXTable,
+                                 int emissionKind);
+/* attach HDP spline tables (kmerToRow: K entries, parent walk of dir_proc_density already resolved) */
+int sa_model_set_hdp(sa_model_t *m, int64_t gridLength, const double *grid, const int32_t *kmerToRow,
+                     int64_t nRows, const double *postPred, const double *slopes);
+int sa_model_set_hdp_expected_values(sa_model_t *m);
+/* emissions_signal_scaleNoise (impl/stateMachine.c:721-741) / emissions_signal_scaleModel (:743-779) */
+int sa_model_scale_noise(sa_model_t *m, double scale_sd, double var_sd);
+int sa_model_scale_model(sa_model_t *m, double scale, double shift, double var, double scale_sd, double var_sd);
+void sa_model_free(sa_model_t *m);
+
+/* introspection (tests, drop-in shim) */
+int64_t sa_model_num_kmers(const sa_model_t *m);
+int32_t sa_model_kmer_length(const sa_model_t *m);
+const char *sa_model_alphabet(const sa_model_t *m);               /* sorted */
+void sa_model_get_tables(const sa_model_t *m, double *logTransitions9, double *matchTable, double *gapYTable);
+/* host evaluation of the .nhdp spline density the device uses (get_nanopore_kmer_density, nanopore_hdp.c:420) */
+double sa_model_hdp_density(const sa_model_t *m, int64_t kmerIdx, double x);
+
+/* ---------------------------------------------------------------------------------------------- inputs
+ * One sa_read_t = the arguments of one getAlignedPairsUsingAnchors call
+ * (inc/pairwiseAligner.h:406-414; call site impl/signalMachine.c:436-437).
+ */
+typedef struct {
+    const char *target;      /* nucleotides, lX + k - 1 chars (need not be NUL terminated); Sequence sX->elements */
+    int64_t targetLength;    /* number of nucleotides */
+    const double *events;    /* nEvents * 4 doubles: mean, sd, duration, start (NB_EVENT_PARAMS, inc/nanopore.h:5) */
+    int64_t nEvents;         /* lY */
+    const int64_t *anchors;  /* nAnchors (x, y) pairs, 0-based, strictly increasing in both (stList of stIntTuple) */
+    int64_t nAnchors;
+    double scale, shift, var; /* sM->scale / shift / var (inc/stateMachine.h:92-94) */
+    int32_t raggedLeft, raggedRight;
+} sa_read_t;
+
+/* PairwiseAlignmentParameters fields the path reads (inc/pairwiseAligner.h:143-154) */
+typedef struct {
+    double threshold;
+    int64_t minDiagsBetweenTraceBack;
+    int64_t traceBackDiagonals;
+    int64_t diagonalExpansion;
+    int64_t splitMatrixBiggerThanThis;
+} sa_params_t;
+/* pairwiseAlignmentBandingParameters_construct defaults (impl/pairwiseAligner.c:2022-2037) */
+void sa_params_default(sa_params_t *p);
+
+/* ambiguity table: create_ambig_bases / create_ambig_bases2 (impl/pairwiseAligner.c:32-92); file may be NULL */
+typedef struct sa_ambig sa_ambig_t;
+sa_ambig_t *sa_ambig_load(const char *file);
+void sa_ambig_free(sa_ambig_t *a);
+
+/* ---------------------------------------------------------------------------------------------- outputs */
+/* one aligned pair = stIntTuple4(floor(p*1e7), x, y, kmer*) (impl/pairwiseAligner.c:1405-1408);
+ * the kmer pointer becomes the kmer's index (sa_kmer_string turns it back into text) */
+typedef struct {
+    int32_t p;        /* floor(posterior * 1e7) */
+    int32_t x;        /* reference kmer index (0-based) */
+    int32_t y;        /* event index (0-based) */
+    int32_t kmerIdx;  /* path kmer */
+} sa_pair_t;
+
+typedef struct {
+    int64_t nReads;
+    int64_t *pairOffsets;    /* nReads + 1 */
+    sa_pair_t *pairs;        /* pairOffsets[nReads] pairs, per read in the reference's list order */
+    /* expectations (getExpectationsUsingAnchors): per read 9 transition sums (from*3+to) + likelihood */
+    double *transitions;     /* nReads * 9, NULL for alignment runs */
+    double *likelihood;      /* nReads */
+    int64_t *assignOffsets;  /* nReads + 1 (HDP assignments), NULL unless HDP expectations */
+    int32_t *assignKmerPos;  /* offset of the assigned kmer in the read's target */
+    int32_t *assignEvent;    /* event index */
+    /* accounting (same integer band logic as the reference): */
+    int64_t totalBandCells;  /* sum over diagonals of band width */
+    int64_t totalPathCells;  /* band cells weighted by the number of paths */
+    int64_t totalEvents;
+} sa_result_t;
+void sa_result_free(sa_result_t *r);
+void sa_kmer_string(const sa_model_t *m, int64_t kmerIdx, char *out /* k+1 bytes */);
+
+/* ---------------------------------------------------------------------------------------------- device */
+int sa_gpu_init(int device);                 /* select device for this process/thread; SA_ERR_CUDA if none */
+const char *sa_last_error(void);
+int sa_gpu_device_count(void);
+
+/* One-shot drop-in for a batch of getAlignedPairsUsingAnchors calls (host buffers in, host result out). */
+int sa_gpu_align_batch(const sa_model_t *m, const sa_read_t *reads, int64_t nReads, const sa_params_t *p,
+                       const sa_ambig_t *ambig, sa_result_t **out);
+/* ... and of getExpectationsUsingAnchors (inc/pairwiseAligner.h:417-429; call site signalMachine.c:479).
+ * Results are the per-read expectation sums WITHOUT pseudocounts. */
+int sa_gpu_expectations_batch(const sa_model_t *m, const sa_read_t *reads, int64_t nReads, const sa_params_t *p,
+                              const sa_ambig_t *ambig, sa_result_t **out);
+
+/* Staged form of the same call, so that callers (and bench.py) can keep a batch resident in HBM:
+ *   prepare  = host packing + H2D of inputs (+ device geometry pass + scratch allocation)
+ *   run      = kernels only, inputs and outputs resident in HBM; may be called repeatedly
+ *   fetch    = D2H of the compacted results
+ */
+typedef struct sa_batch sa_batch_t;
+int sa_batch_prepare(const sa_model_t *m, const sa_read_t *reads, int64_t nReads, const sa_params_t *p,
+                     const sa_ambig_t *ambig, int expectations, sa_batch_t **out);
+int sa_batch_run(sa_batch_t *b);
+int sa_batch_fetch(sa_batch_t *b, sa_result_t **out);
+/* device time of the last sa_batch_run measured with CUDA events on the batch's stream (ms);
+ * kernelMs[0] = geometry/setup kernels, [1] = DP kernel(s), [2] = compaction; launches = #kernel launches */
+int sa_batch_last_timing(const sa_batch_t *b, float *kernelMs3, int64_t *launches);
+int64_t sa_batch_band_cells(const sa_batch_t *b);
+int64_t sa_batch_h2d_bytes(const sa_batch_t *b);
+int64_t sa_batch_d2h_bytes(const sa_batch_t *b);
+void sa_batch_free(sa_batch_t *b);
+
+/* expectation-table reduction across reads of one GPU (the per-GPU table NCCL then all-reduces):
+ * out[0..8] = sum of transitions, out[9] = sum of likelihood */
+void sa_result_sum_expectations(const sa_result_t *r, double *out10);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,351 @@
+"""signalalign_b200 — B200-native hot path of signalAlign (banded forward/backward posterior-match DP).
+
+This module is a thin ctypes binding over the C-ABI of ``libsagpu.so`` (include/signalalign_b200.h).  All compute is
+in the CUDA library; there is no CPU fallback and nothing here touches ``oracle/``: if the library or a CUDA device is
+missing, calls raise.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libsagpu.so")
+
+EMIT_GAUSS_MEANONLY_DESCALE = 0
+EMIT_HDP = 1
+EMIT_GAUSS_NOISE_SCALED = 2
+EMIT_GAUSS_NOISE_DESCALE = 3
+
+c_i64p = C.POINTER(C.c_int64)
+c_i32p = C.POINTER(C.c_int32)
+c_f64p = C.POINTER(C.c_double)
+
+
+class SaRead(C.Structure):
+    _fields_ = [("target", C.c_char_p), ("targetLength", C.c_int64), ("events", c_f64p), ("nEvents", C.c_int64),
+                ("anchors", c_i64p), ("nAnchors", C.c_int64), ("scale", C.c_double), ("shift", C.c_double),
+                ("var", C.c_double), ("raggedLeft", C.c_int32), ("raggedRight", C.c_int32)]
+
+
+class SaParams(C.Structure):
+    _fields_ = [("threshold", C.c_double), ("minDiagsBetweenTraceBack", C.c_int64),
+                ("traceBackDiagonals", C.c_int64), ("diagonalExpansion", C.c_int64),
+                ("splitMatrixBiggerThanThis", C.c_int64)]
+
+
+class SaPair(C.Structure):
+    _fields_ = [("p", C.c_int32), ("x", C.c_int32), ("y", C.c_int32), ("kmerIdx", C.c_int32)]
+
+
+class SaResult(C.Structure):
+    _fields_ = [("nReads", C.c_int64), ("pairOffsets", c_i64p), ("pairs", C.POINTER(SaPair)),
+                ("transitions", c_f64p), ("likelihood", c_f64p), ("assignOffsets", c_i64p),
+                ("assignKmerPos", c_i32p), ("assignEvent", c_i32p), ("totalBandCells", C.c_int64),
+                ("totalPathCells", C.c_int64), ("totalEvents", C.c_int64)]
+
+
+EXPORTS = [
+    "sa_model_load", "sa_model_from_tables", "sa_model_set_hdp", "sa_model_set_hdp_expected_values",
+    "sa_model_scale_noise", "sa_model_scale_model", "sa_model_free", "sa_model_num_kmers", "sa_model_kmer_length",
+    "sa_model_alphabet", "sa_model_get_tables", "sa_model_hdp_density", "sa_params_default", "sa_ambig_load",
+    "sa_ambig_free", "sa_result_free", "sa_kmer_string", "sa_gpu_init", "sa_last_error", "sa_gpu_device_count",
+    "sa_gpu_align_batch", "sa_gpu_expectations_batch", "sa_batch_prepare", "sa_batch_run", "sa_batch_fetch",
+    "sa_batch_last_timing", "sa_batch_band_cells", "sa_batch_h2d_bytes", "sa_batch_d2h_bytes", "sa_batch_free",
+    "sa_result_sum_expectations",
+]
+
+_lib = None
+
+
+def build(verbose=False):
+    """Compile libsagpu.so in-tree for sm_100a (nvcc cross-compiles without a GPU)."""
+    cmd = ["make", "-C", os.path.join(HERE, "csrc")]
+    if not verbose:
+        cmd.insert(1, "-s")
+    subprocess.check_call(cmd)
+
+
+def lib():
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError("libsagpu.so is not built (run `python -c 'import __graft_entry__ as g; g.build()'`); "
+                           "signalalign_b200 has no CPU fallback")
+    L = C.CDLL(LIB_PATH)
+    L.sa_last_error.restype = C.c_char_p
+    L.sa_model_load.restype = C.c_void_p
+    L.sa_model_load.argtypes = [C.c_char_p, C.c_char_p, C.c_int]
+    L.sa_model_from_tables.restype = C.c_void_p
+    L.sa_model_from_tables.argtypes = [C.c_char_p, C.c_int32, c_f64p, c_f64p, c_f64p, c_f64p, C.c_int]
+    L.sa_model_set_hdp.argtypes = [C.c_void_p, C.c_int64, c_f64p, c_i32p, C.c_int64, c_f64p, c_f64p]
+    L.sa_model_set_hdp_expected_values.argtypes = [C.c_void_p]
+    L.sa_model_scale_noise.argtypes = [C.c_void_p, C.c_double, C.c_double]
+    L.sa_model_scale_model.argtypes = [C.c_void_p] + [C.c_double] * 5
+    L.sa_model_free.argtypes = [C.c_void_p]
+    L.sa_model_num_kmers.restype = C.c_int64
+    L.sa_model_num_kmers.argtypes = [C.c_void_p]
+    L.sa_model_kmer_length.restype = C.c_int32
+    L.sa_model_kmer_length.argtypes = [C.c_void_p]
+    L.sa_model_alphabet.restype = C.c_char_p
+    L.sa_model_alphabet.argtypes = [C.c_void_p]
+    L.sa_model_get_tables.argtypes = [C.c_void_p, c_f64p, c_f64p, c_f64p]
+    L.sa_model_hdp_density.restype = C.c_double
+    L.sa_model_hdp_density.argtypes = [C.c_void_p, C.c_int64, C.c_double]
+    L.sa_params_default.argtypes = [C.POINTER(SaParams)]
+    L.sa_ambig_load.restype = C.c_void_p
+    L.sa_ambig_load.argtypes = [C.c_char_p]
+    L.sa_ambig_free.argtypes = [C.c_void_p]
+    L.sa_result_free.argtypes = [C.POINTER(SaResult)]
+    L.sa_kmer_string.argtypes = [C.c_void_p, C.c_int64, C.c_char_p]
+    L.sa_gpu_init.argtypes = [C.c_int]
+    L.sa_gpu_align_batch.argtypes = [C.c_void_p, C.POINTER(SaRead), C.c_int64, C.POINTER(SaParams), C.c_void_p,
+                                     C.POINTER(C.POINTER(SaResult))]
+    L.sa_gpu_expectations_batch.argtypes = L.sa_gpu_align_batch.argtypes
+    L.sa_batch_prepare.argtypes = [C.c_void_p, C.POINTER(SaRead), C.c_int64, C.POINTER(SaParams), C.c_void_p,
+                                   C.c_int, C.POINTER(C.c_void_p)]
+    L.sa_batch_run.argtypes = [C.c_void_p]
+    L.sa_batch_fetch.argtypes = [C.c_void_p, C.POINTER(C.POINTER(SaResult))]
+    L.sa_batch_last_timing.argtypes = [C.c_void_p, C.POINTER(C.c_float), c_i64p]
+    for f in ("sa_batch_band_cells", "sa_batch_h2d_bytes", "sa_batch_d2h_bytes"):
+        getattr(L, f).restype = C.c_int64
+        getattr(L, f).argtypes = [C.c_void_p]
+    L.sa_batch_free.argtypes = [C.c_void_p]
+    L.sa_result_sum_expectations.argtypes = [C.POINTER(SaResult), c_f64p]
+    _lib = L
+    return L
+
+
+class SaError(RuntimeError):
+    pass
+
+
+def _check(rc):
+    if rc != 0:
+        raise SaError(lib().sa_last_error().decode(errors="replace"))
+
+
+def gpu_init(device=0):
+    _check(lib().sa_gpu_init(device))
+
+
+def default_params(**kw):
+    """pairwiseAlignmentBandingParameters_construct defaults (reference impl/pairwiseAligner.c:2022-2037)."""
+    p = SaParams()
+    lib().sa_params_default(C.byref(p))
+    names = {"threshold": "threshold", "min_diags": "minDiagsBetweenTraceBack", "trace_back": "traceBackDiagonals",
+             "expansion": "diagonalExpansion", "split_bigger": "splitMatrixBiggerThanThis"}
+    for k, v in kw.items():
+        setattr(p, names[k], v)
+    return p
+
+
+class Model:
+    """Host mirror of the reference `StateMachine` for the path (reference inc/stateMachine.h:85-191)."""
+
+    def __init__(self, handle):
+        if not handle:
+            raise SaError(lib().sa_last_error().decode(errors="replace"))
+        self.h = handle
+        self.K = lib().sa_model_num_kmers(self.h)
+        self.k = lib().sa_model_kmer_length(self.h)
+        self.alphabet = lib().sa_model_alphabet(self.h).decode()
+
+    @classmethod
+    def load(cls, model_file, nhdp_file=None, kind=EMIT_GAUSS_MEANONLY_DESCALE):
+        return cls(lib().sa_model_load(model_file.encode(), nhdp_file.encode() if nhdp_file else None, kind))
+
+    @classmethod
+    def from_tables(cls, alphabet, k, log_transitions, match, gap_y=None, gap_x=None,
+                    kind=EMIT_GAUSS_MEANONLY_DESCALE):
+        t = np.ascontiguousarray(log_transitions, np.float64)
+        m = np.ascontiguousarray(match, np.float64)
+        gy = None if gap_y is None else np.ascontiguousarray(gap_y, np.float64)
+        gx = None if gap_x is None else np.ascontiguousarray(gap_x, np.float64)
+        f = lambda a: None if a is None else a.ctypes.data_as(c_f64p)
+        return cls(lib().sa_model_from_tables(alphabet.encode(), k, f(t), f(m), f(gy), f(gx), kind))
+
+    def set_hdp(self, grid, kmer_to_row, post_pred, slopes):
+        grid = np.ascontiguousarray(grid, np.float64)
+        k2r = np.ascontiguousarray(kmer_to_row, np.int32)
+        pp = np.ascontiguousarray(post_pred, np.float64)
+        sl = np.ascontiguousarray(slopes, np.float64)
+        _check(lib().sa_model_set_hdp(self.h, len(grid), grid.ctypes.data_as(c_f64p), k2r.ctypes.data_as(c_i32p),
+                                      pp.shape[0], pp.ctypes.data_as(c_f64p), sl.ctypes.data_as(c_f64p)))
+
+    def set_hdp_expected_values(self):
+        _check(lib().sa_model_set_hdp_expected_values(self.h))
+
+    def scale_noise(self, scale_sd, var_sd):
+        _check(lib().sa_model_scale_noise(self.h, scale_sd, var_sd))
+
+    def scale_model(self, scale, shift, var, scale_sd, var_sd):
+        _check(lib().sa_model_scale_model(self.h, scale, shift, var, scale_sd, var_sd))
+
+    def tables(self):
+        t = np.zeros(9)
+        m = np.zeros((self.K, 5))
+        y = np.zeros((self.K, 5))
+        lib().sa_model_get_tables(self.h, t.ctypes.data_as(c_f64p), m.ctypes.data_as(c_f64p),
+                                  y.ctypes.data_as(c_f64p))
+        return t, m, y
+
+    def hdp_density(self, kmer_idx, x):
+        return lib().sa_model_hdp_density(self.h, kmer_idx, x)
+
+    def kmer_string(self, idx):
+        buf = C.create_string_buffer(self.k + 1)
+        lib().sa_kmer_string(self.h, idx, buf)
+        return buf.value.decode()
+
+    def kmer_index(self, kmer):
+        a = len(self.alphabet)
+        idx = 0
+        for ch in kmer:
+            idx = idx * a + self.alphabet.index(ch)
+        return idx
+
+    def __del__(self):
+        try:
+            if self.h:
+                lib().sa_model_free(self.h)
+                self.h = None
+        except Exception:
+            pass
+
+
+class Read:
+    """Arguments of one getAlignedPairsUsingAnchors call (reference inc/pairwiseAligner.h:406-414)."""
+
+    def __init__(self, target, events, anchors, scale=1.0, shift=0.0, var=1.0, ragged_left=True, ragged_right=True):
+        self.target = target.encode() if isinstance(target, str) else bytes(target)
+        self.events = np.ascontiguousarray(events, np.float64).reshape(-1, 4)
+        self.anchors = np.ascontiguousarray(anchors, np.int64).reshape(-1, 2)
+        self.scale, self.shift, self.var = float(scale), float(shift), float(var)
+        self.ragged_left, self.ragged_right = bool(ragged_left), bool(ragged_right)
+
+    def cstruct(self):
+        return SaRead(self.target, len(self.target), self.events.ctypes.data_as(c_f64p), self.events.shape[0],
+                      self.anchors.ctypes.data_as(c_i64p), self.anchors.shape[0], self.scale, self.shift, self.var,
+                      int(self.ragged_left), int(self.ragged_right))
+
+
+def _read_array(reads):
+    arr = (SaRead * max(1, len(reads)))()
+    for i, r in enumerate(reads):
+        arr[i] = r.cstruct()
+    return arr
+
+
+class Ambig:
+    def __init__(self, path=None):
+        self.h = lib().sa_ambig_load(path.encode() if path else None)
+        if not self.h:
+            raise SaError(lib().sa_last_error().decode(errors="replace"))
+
+    def __del__(self):
+        try:
+            lib().sa_ambig_free(self.h)
+        except Exception:
+            pass
+
+
+class Result:
+    """Owns an sa_result_t; exposes numpy copies."""
+
+    def __init__(self, ptr):
+        r = ptr.contents
+        n = r.nReads
+        self.n_reads = n
+        self.band_cells, self.path_cells, self.events = r.totalBandCells, r.totalPathCells, r.totalEvents
+        self.pair_offsets = np.ctypeslib.as_array(r.pairOffsets, shape=(n + 1,)).copy()
+        total = int(self.pair_offsets[-1])
+        self.pairs = np.zeros((total, 4), np.int32)
+        if total and r.pairs:
+            C.memmove(self.pairs.ctypes.data, r.pairs, total * 16)
+        self.transitions = self.likelihood = None
+        self.assign_offsets = self.assign_kmer_pos = self.assign_event = None
+        if r.transitions:
+            self.transitions = np.ctypeslib.as_array(r.transitions, shape=(n, 9)).copy() if n else np.zeros((0, 9))
+            self.likelihood = np.ctypeslib.as_array(r.likelihood, shape=(n,)).copy() if n else np.zeros(0)
+        if r.assignOffsets:
+            self.assign_offsets = np.ctypeslib.as_array(r.assignOffsets, shape=(n + 1,)).copy()
+            ta = int(self.assign_offsets[-1])
+            self.assign_kmer_pos = np.ctypeslib.as_array(r.assignKmerPos, shape=(max(ta, 1),))[:ta].copy()
+            self.assign_event = np.ctypeslib.as_array(r.assignEvent, shape=(max(ta, 1),))[:ta].copy()
+        lib().sa_result_free(ptr)
+
+    def read_pairs(self, i):
+        """pairs of read i as int32 [n, 4] = (floor(p*1e7), x, y, kmerIdx) in the reference's list order"""
+        return self.pairs[self.pair_offsets[i]:self.pair_offsets[i + 1]]
+
+
+def align_batch(model, reads, params=None, ambig=None):
+    """Batch of getAlignedPairsUsingAnchors calls (host buffers in, host result out)."""
+    params = params or default_params()
+    arr = _read_array(reads)
+    out = C.POINTER(SaResult)()
+    _check(lib().sa_gpu_align_batch(model.h, arr, len(reads), C.byref(params), ambig.h if ambig else None,
+                                    C.byref(out)))
+    return Result(out)
+
+
+def expectations_batch(model, reads, params=None, ambig=None):
+    """Batch of getExpectationsUsingAnchors calls; per-read sums WITHOUT pseudocounts."""
+    params = params or default_params()
+    arr = _read_array(reads)
+    out = C.POINTER(SaResult)()
+    _check(lib().sa_gpu_expectations_batch(model.h, arr, len(reads), C.byref(params), ambig.h if ambig else None,
+                                           C.byref(out)))
+    return Result(out)
+
+
+class Batch:
+    """Staged form: prepare (pack + H2D), run (kernels only; repeatable), fetch (D2H)."""
+
+    def __init__(self, model, reads, params=None, ambig=None, expectations=False):
+        self.model, self.reads, self.ambig = model, reads, ambig  # keep host buffers alive
+        self.params = params or default_params()
+        arr = _read_array(reads)
+        self.h = C.c_void_p()
+        _check(lib().sa_batch_prepare(model.h, arr, len(reads), C.byref(self.params), ambig.h if ambig else None,
+                                      int(expectations), C.byref(self.h)))
+
+    def run(self):
+        _check(lib().sa_batch_run(self.h))
+
+    def fetch(self):
+        out = C.POINTER(SaResult)()
+        _check(lib().sa_batch_fetch(self.h, C.byref(out)))
+        return Result(out)
+
+    def timing(self):
+        ms = (C.c_float * 3)()
+        n = C.c_int64(0)
+        lib().sa_batch_last_timing(self.h, ms, C.byref(n))
+        return [ms[0], ms[1], ms[2]], n.value
+
+    @property
+    def band_cells(self):
+        return lib().sa_batch_band_cells(self.h)
+
+    @property
+    def h2d_bytes(self):
+        return lib().sa_batch_h2d_bytes(self.h)
+
+    @property
+    def d2h_bytes(self):
+        return lib().sa_batch_d2h_bytes(self.h)
+
+    def close(self):
+        if self.h:
+            lib().sa_batch_free(self.h)
+            self.h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

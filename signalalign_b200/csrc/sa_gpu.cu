@@ -1,0 +1,626 @@
+// sa_gpu.cu — device side of libsagpu: model upload, batch packing, kernel launches, result assembly.
+//
+// A batch = many getAlignedPairsUsingAnchors / getExpectationsUsingAnchors calls (one per read) executed together.
+// Host work here is integer-only preparation that the reference also does on the host (split points, kmer
+// indices / ambiguity paths, band geometry); all floating-point DP work runs in the kernels.
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <memory>
+#include <numeric>
+#include <vector>
+#include <cuda_runtime.h>
+#include "sa_internal.h"
+#include "sa_general.cuh"
+
+#define CK(call)                                                                                   \
+    do {                                                                                           \
+        cudaError_t e_ = (call);                                                                   \
+        if (e_ != cudaSuccess) {                                                                   \
+            sa_set_error("CUDA error %s at %s:%d: %s", #call, __FILE__, __LINE__, cudaGetErrorString(e_)); \
+            return SA_ERR_CUDA;                                                                    \
+        }                                                                                          \
+    } while (0)
+
+// ------------------------------------------------------------------------------------------------ device model
+struct DeviceModel {
+    double *kt = nullptr, *gapX = nullptr, *grid = nullptr, *pp = nullptr, *slopes = nullptr;
+    int32_t *kmerToRow = nullptr;
+};
+
+void sa_model_drop_device(const sa_model *m) {
+    if (!m->dev) return;
+    cudaFree(m->dev->kt); cudaFree(m->dev->gapX); cudaFree(m->dev->grid); cudaFree(m->dev->pp);
+    cudaFree(m->dev->slopes); cudaFree(m->dev->kmerToRow);
+    delete m->dev;
+    m->dev = nullptr;
+    m->devDevice = -1;
+}
+
+static int uploadModel(const sa_model *m) {
+    int dev;
+    CK(cudaGetDevice(&dev));
+    if (m->dev && m->devDevice == dev) return SA_OK;
+    sa_model_drop_device(m);
+    DeviceModel *d = new DeviceModel;
+    std::vector<double> kt((size_t) m->K * SA_KT_STRIDE);
+    for (int64_t i = 0; i < m->K; i++)
+        for (int t = 0; t < 2; t++) {
+            const double *src = (t == 0 ? m->match.data() : m->gapY.data()) + i * 5;
+            double *dst = kt.data() + i * SA_KT_STRIDE + t * 6;
+            dst[0] = src[0];
+            dst[1] = src[1];
+            dst[2] = log(src[1]);  // l_sigma of emissions_signal_logGaussPdf, evaluated by the host libm like the reference
+            dst[3] = src[2];
+            dst[4] = src[4];
+            dst[5] = log(src[4]);
+        }
+    CK(cudaMalloc(&d->kt, kt.size() * sizeof(double)));
+    CK(cudaMemcpy(d->kt, kt.data(), kt.size() * sizeof(double), cudaMemcpyHostToDevice));
+    CK(cudaMalloc(&d->gapX, m->K * sizeof(double)));
+    CK(cudaMemcpy(d->gapX, m->gapX.data(), m->K * sizeof(double), cudaMemcpyHostToDevice));
+    if (m->G > 0) {
+        CK(cudaMalloc(&d->grid, m->G * sizeof(double)));
+        CK(cudaMemcpy(d->grid, m->grid.data(), m->G * sizeof(double), cudaMemcpyHostToDevice));
+        CK(cudaMalloc(&d->pp, m->postPred.size() * sizeof(double)));
+        CK(cudaMemcpy(d->pp, m->postPred.data(), m->postPred.size() * sizeof(double), cudaMemcpyHostToDevice));
+        CK(cudaMalloc(&d->slopes, m->slopes.size() * sizeof(double)));
+        CK(cudaMemcpy(d->slopes, m->slopes.data(), m->slopes.size() * sizeof(double), cudaMemcpyHostToDevice));
+        CK(cudaMalloc(&d->kmerToRow, m->K * sizeof(int32_t)));
+        CK(cudaMemcpy(d->kmerToRow, m->kmerToRow.data(), m->K * sizeof(int32_t), cudaMemcpyHostToDevice));
+    }
+    m->dev = d;
+    m->devDevice = dev;
+    return SA_OK;
+}
+
+// ------------------------------------------------------------------------------------------------ device init
+extern "C" int sa_gpu_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) return 0;
+    return n;
+}
+
+extern "C" int sa_gpu_init(int device) {
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n == 0) {
+        sa_set_error("sa_gpu_init: no CUDA device available (%s); libsagpu has no CPU fallback",
+                     e == cudaSuccess ? "device count 0" : cudaGetErrorString(e));
+        return SA_ERR_CUDA;
+    }
+    if (device < 0 || device >= n) {
+        sa_set_error("sa_gpu_init: device %d out of range (have %d)", device, n);
+        return SA_ERR_CUDA;
+    }
+    CK(cudaSetDevice(device));
+    CK(cudaFree(0));
+    return SA_OK;
+}
+
+// ------------------------------------------------------------------------------------------------ batch
+template <class T>
+struct DevBuf {
+    T *p = nullptr;
+    size_t n = 0;
+    int alloc(size_t count) {
+        release();
+        n = count;
+        if (count == 0) return SA_OK;
+        CK(cudaMalloc(&p, count * sizeof(T)));
+        return SA_OK;
+    }
+    int upload(const std::vector<T> &v, cudaStream_t s, int64_t *bytes) {
+        int rc = alloc(v.size());
+        if (rc) return rc;
+        if (!v.empty()) {
+            CK(cudaMemcpyAsync(p, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice, s));
+            if (bytes) *bytes += (int64_t) (v.size() * sizeof(T));
+        }
+        return SA_OK;
+    }
+    void release() {
+        if (p) cudaFree(p);
+        p = nullptr;
+        n = 0;
+    }
+    ~DevBuf() { release(); }
+};
+
+struct ItemHost {
+    int64_t read, x1, y1, lX, lY;
+    int64_t work;  // path-cells
+    int32_t region, nRegions;
+};
+
+struct sa_batch {
+    const sa_model *model = nullptr;
+    sa_params_t params;
+    bool expectations = false;
+    int64_t nReads = 0;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+    std::vector<ItemHost> itemsHost;  // in device order (sorted by work, descending)
+    std::vector<GItem> gItems;
+    DevBuf<GItem> dItems;
+    DevBuf<int32_t> dCounter, dPathOff, dPathKmer, dBandL, dBandW, dAssignK, dAssignE;
+    DevBuf<int64_t> dBandOff, dPairCount, dAssignCount;
+    DevBuf<double> dEvMean, dEvNoise, dEvLogNoise, dScratch, dExpOut;
+    DevBuf<sa_pair_t> dPairs;
+    GParams gp;
+    int nCta = 0;
+    int64_t bandCells = 0, pathCells = 0, events = 0;
+    int64_t h2dBytes = 0, d2hBytes = 0;
+    float lastMs[3] = {0, 0, 0};
+    int64_t lastLaunches = 0;
+    std::vector<int64_t> pairCountHost, assignCountHost;
+    ~sa_batch() {
+        for (auto &e : ev)
+            if (e) cudaEventDestroy(e);
+        if (stream) cudaStreamDestroy(stream);
+    }
+};
+
+static int64_t nextPow2(int64_t v) {
+    int64_t p = 1;
+    while (p < v) p <<= 1;
+    return p;
+}
+
+extern "C" int sa_batch_prepare(const sa_model_t *m, const sa_read_t *reads, int64_t nReads, const sa_params_t *p,
+                                const sa_ambig_t *ambigIn, int expectations, sa_batch_t **out) {
+    *out = nullptr;
+    if (sa_gpu_device_count() == 0) {
+        sa_set_error("sa_batch_prepare: no CUDA device available; libsagpu has no CPU fallback");
+        return SA_ERR_CUDA;
+    }
+    if (p->diagonalExpansion % 2 != 0 || p->diagonalExpansion < 0 || p->traceBackDiagonals < 1 ||
+        p->minDiagsBetweenTraceBack < 2 || p->traceBackDiagonals + 1 >= p->minDiagsBetweenTraceBack) {
+        sa_set_error("sa_batch_prepare: parameters violate the prerequisites of getPosteriorProbsWithBanding "
+                     "(pairwiseAligner.c:1460-1464)");
+        return SA_ERR_INPUT;
+    }
+    if (m->kind == SA_EMIT_HDP && m->G == 0) {
+        sa_set_error("sa_batch_prepare: HDP emission requested but the model has no .nhdp tables");
+        return SA_ERR_INPUT;
+    }
+    int rc = uploadModel(m);
+    if (rc) return rc;
+    sa_ambig defAmbig;
+    const sa_ambig *ambig = ambigIn;
+    if (!ambig) {
+        sa_ambig_default_table(defAmbig);
+        ambig = &defAmbig;
+    }
+    std::unique_ptr<sa_batch> b(new sa_batch);
+    b->model = m;
+    b->params = *p;
+    b->expectations = expectations != 0;
+    b->nReads = nReads;
+    CK(cudaStreamCreate(&b->stream));
+    for (auto &e : b->ev) CK(cudaEventCreate(&e));
+
+    const bool needNoise = m->kind == SA_EMIT_GAUSS_NOISE_SCALED || m->kind == SA_EMIT_GAUSS_NOISE_DESCALE;
+    std::vector<int32_t> pathOff, pathKmer, bandL, bandW;
+    std::vector<int64_t> bandOff;
+    std::vector<double> evMean, evNoise, evLogNoise;
+    std::vector<GItem> items;
+    std::vector<ItemHost> itemsHost;
+    std::vector<int64_t> split;
+    std::vector<Diag> band;
+    std::vector<int32_t> paths;
+    int64_t ringNeedMax = 1, maxDiagPC = 1, maxWidth = 1;
+    int64_t pairTotalCap = 0, assignTotalCap = 0;
+
+    // ambiguity / alphabet classification per character for the rolling fast path
+    int charCode[256];
+    bool charAmbig[256];
+    for (int c = 0; c < 256; c++) {
+        size_t j = m->alphabet.find((char) c);
+        charCode[c] = (c != 0 && j != std::string::npos) ? (int) j : -1;
+        charAmbig[c] = ambig->opts[c][0] != 0;
+    }
+
+    for (int64_t r = 0; r < nReads; r++) {
+        const sa_read_t &R = reads[r];
+        int64_t lXt = R.targetLength > 0 ? R.targetLength - (m->k - 1) : 0;  // sequence_correctSeqLength (:523-538)
+        if (lXt < 0) lXt = 0;
+        int64_t lYt = R.nEvents;
+        for (int64_t i = 0; i < R.nAnchors; i++) {
+            int64_t ax = R.anchors[2 * i], ay = R.anchors[2 * i + 1];
+            bool ok = ax >= 0 && ay >= 0 && ax < lXt && ay < lYt;
+            if (ok && i > 0) ok = ax > R.anchors[2 * i - 2] && ay > R.anchors[2 * i - 1];
+            if (!ok) {
+                sa_set_error("read %lld: anchor %lld (%lld, %lld) out of range or not strictly increasing "
+                             "(asserted by band_construct, pairwiseAligner.c:226-231)",
+                             (long long) r, (long long) i, (long long) ax, (long long) ay);
+                return SA_ERR_INPUT;
+            }
+        }
+        sa_split_points(R.anchors, R.nAnchors, lXt, lYt, p->splitMatrixBiggerThanThis, R.raggedLeft != 0,
+                        R.raggedRight != 0, split);
+        int64_t nSplit = (int64_t) split.size() / 4, j = 0;
+        for (int64_t s = 0; s < nSplit; s++) {
+            int64_t x1 = split[4 * s], y1 = split[4 * s + 1], x2 = split[4 * s + 2], y2 = split[4 * s + 3];
+            std::vector<int64_t> sub;
+            while (j < R.nAnchors) {  // pairwiseAligner.c:1984-1997
+                int64_t ax = R.anchors[2 * j], ay = R.anchors[2 * j + 1];
+                if (ax + ay >= x2 + y2) break;
+                sub.push_back(ax - x1);
+                sub.push_back(ay - y1);
+                j++;
+            }
+            GItem it;
+            memset(&it, 0, sizeof(it));
+            ItemHost ih;
+            ih.read = r; ih.x1 = x1; ih.y1 = y1; ih.lX = x2 - x1; ih.lY = y2 - y1;
+            ih.region = (int32_t) s; ih.nRegions = (int32_t) nSplit;
+            it.lX = (int32_t) ih.lX; it.lY = (int32_t) ih.lY;
+            bool rl = R.raggedLeft || s > 0, rr = R.raggedRight || s < nSplit - 1;  // :2001-2002
+            it.flags = (rl ? 1 : 0) | (rr ? 2 : 0);
+            it.scale = R.scale; it.shift = R.shift; it.var = R.var;
+            it.invVar = 1 / R.var;
+            it.logInvVar = log((1 / R.var));
+            // events of the region
+            it.evOff = (int64_t) evMean.size();
+            for (int64_t y = 0; y < ih.lY; y++) {
+                const double *e = R.events + (y1 + y) * 4;
+                evMean.push_back(e[0]);
+                if (needNoise) {
+                    double noise = e[1];
+                    evNoise.push_back(noise);
+                    if (m->kind == SA_EMIT_GAUSS_NOISE_DESCALE && noise == 0) noise = 0.000000001;
+                    evLogNoise.push_back(log(noise));
+                }
+            }
+            // kmer paths per matrix column (column 0 = NULL kmer)
+            it.pathOffOff = (int64_t) pathOff.size();
+            it.pathKmerOff = (int64_t) pathKmer.size();
+            int64_t base = (int64_t) pathKmer.size();
+            pathOff.push_back(0);
+            pathKmer.push_back(-1);
+            pathOff.push_back(1);
+            int64_t roll = -1;  // rolling kmer id of the previous window when it was unambiguous
+            int64_t maxP = 1;
+            for (int64_t x = 1; x <= ih.lX; x++) {
+                const char *km = R.target + x1 + x - 1;
+                bool simple = true;
+                for (int q = 0; q < m->k; q++) {
+                    unsigned char ch = (unsigned char) km[q];
+                    if (charAmbig[ch] || charCode[ch] < 0) { simple = false; break; }
+                }
+                if (simple) {
+                    if (roll >= 0) roll = (roll % (m->K / m->A)) * m->A + charCode[(unsigned char) km[m->k - 1]];
+                    else {
+                        roll = 0;
+                        for (int q = 0; q < m->k; q++) roll = roll * m->A + charCode[(unsigned char) km[q]];
+                    }
+                    pathKmer.push_back((int32_t) roll);
+                } else {
+                    roll = -1;
+                    if (!sa_kmer_paths(km, *m, *ambig, paths)) {
+                        sa_set_error("read %lld: kmer at reference position %lld contains a character outside the "
+                                     "alphabet %s (the reference exits in kmer_to_word, nanopore_hdp.c:393-398)",
+                                     (long long) r, (long long) (x1 + x - 1), m->alphabet.c_str());
+                        return SA_ERR_INPUT;
+                    }
+                    pathKmer.insert(pathKmer.end(), paths.begin(), paths.end());
+                    maxP = std::max<int64_t>(maxP, (int64_t) paths.size());
+                }
+                pathOff.push_back((int32_t) ((int64_t) pathKmer.size() - base));
+            }
+            // band geometry + the traceback schedule's storage needs
+            it.diagOff = (int64_t) bandL.size();
+            sa_build_band(sub.data(), (int64_t) sub.size() / 2, ih.lX, ih.lY, p->diagonalExpansion, band);
+            const int32_t *po = pathOff.data() + it.pathOffOff;
+            int64_t nDiag = ih.lX + ih.lY, off = 0, tracedBackTo = 0, ringNeed = 1;
+            ih.work = 0;
+            for (int64_t d = 0; d <= nDiag; d++) {
+                int64_t w = (band[d].xmyR - band[d].xmyL) / 2 + 1;
+                int64_t x0 = (d + band[d].xmyL) / 2;
+                int64_t pc = po[x0 + w] - po[x0];
+                bandL.push_back((int32_t) band[d].xmyL);
+                bandW.push_back((int32_t) w);
+                bandOff.push_back(off);
+                off += pc;
+                b->bandCells += w;
+                ih.work += pc;
+                maxDiagPC = std::max(maxDiagPC, pc);
+                maxWidth = std::max(maxWidth, w);
+                if (d >= 1) {
+                    bool atEnd = d == nDiag;
+                    bool tb = d >= tracedBackTo + p->minDiagsBetweenTraceBack && w <= p->diagonalExpansion * 2 + 1;
+                    if (atEnd || tb) {
+                        ringNeed = std::max(ringNeed, off - bandOff[it.diagOff + tracedBackTo]);
+                        tracedBackTo = d - (atEnd ? 0 : p->traceBackDiagonals + 1);
+                    }
+                }
+            }
+            if (nDiag == 0) ringNeed = 1;
+            b->pathCells += ih.work;
+            b->events += ih.lY;
+            ringNeedMax = std::max(ringNeedMax, ringNeed);
+            it.pairOff = pairTotalCap;
+            it.pairCap = b->expectations ? 0 : 3 * ih.lY * maxP + 64;
+            pairTotalCap += it.pairCap;
+            it.assignOff = assignTotalCap;
+            it.assignCap = (b->expectations && m->kind == SA_EMIT_HDP) ? 4 * ih.lY * maxP + 64 : 0;
+            assignTotalCap += it.assignCap;
+            items.push_back(it);
+            itemsHost.push_back(ih);
+        }
+    }
+    // longest-processing-time-first order for the persistent CTAs
+    std::vector<int64_t> order(items.size());
+    std::iota(order.begin(), order.end(), 0);
+    std::stable_sort(order.begin(), order.end(),
+                     [&](int64_t a, int64_t c) { return itemsHost[a].work > itemsHost[c].work; });
+    b->gItems.resize(items.size());
+    b->itemsHost.resize(items.size());
+    for (size_t i = 0; i < order.size(); i++) {
+        b->gItems[i] = items[order[i]];
+        b->itemsHost[i] = itemsHost[order[i]];
+    }
+
+    cudaStream_t st = b->stream;
+    if ((rc = b->dItems.upload(b->gItems, st, &b->h2dBytes))) return rc;
+    if ((rc = b->dPathOff.upload(pathOff, st, &b->h2dBytes))) return rc;
+    if ((rc = b->dPathKmer.upload(pathKmer, st, &b->h2dBytes))) return rc;
+    if ((rc = b->dBandL.upload(bandL, st, &b->h2dBytes))) return rc;
+    if ((rc = b->dBandW.upload(bandW, st, &b->h2dBytes))) return rc;
+    if ((rc = b->dBandOff.upload(bandOff, st, &b->h2dBytes))) return rc;
+    if ((rc = b->dEvMean.upload(evMean, st, &b->h2dBytes))) return rc;
+    if ((rc = b->dEvNoise.upload(evNoise, st, &b->h2dBytes))) return rc;
+    if ((rc = b->dEvLogNoise.upload(evLogNoise, st, &b->h2dBytes))) return rc;
+    if ((rc = b->dCounter.alloc(1))) return rc;
+    if ((rc = b->dPairCount.alloc(std::max<size_t>(1, items.size())))) return rc;
+    if ((rc = b->dPairs.alloc(std::max<int64_t>(1, pairTotalCap)))) return rc;
+    if (b->expectations) {
+        if ((rc = b->dExpOut.alloc(std::max<size_t>(1, items.size() * 10)))) return rc;
+        if ((rc = b->dAssignCount.alloc(std::max<size_t>(1, items.size())))) return rc;
+        if ((rc = b->dAssignK.alloc(std::max<int64_t>(1, assignTotalCap)))) return rc;
+        if ((rc = b->dAssignE.alloc(std::max<int64_t>(1, assignTotalCap)))) return rc;
+    }
+
+    // per-CTA scratch slabs
+    int dev, nSM = 148;
+    CK(cudaGetDevice(&dev));
+    CK(cudaDeviceGetAttribute(&nSM, cudaDevAttrMultiProcessorCount, dev));
+    int64_t ring = nextPow2(ringNeedMax);
+    int64_t slab = ring * 3 + 9 * maxDiagPC + 2 * maxWidth;
+    size_t freeB = 0, totalB = 0;
+    CK(cudaMemGetInfo(&freeB, &totalB));
+    int nCta = (int) std::min<int64_t>((int64_t) items.size(), (int64_t) nSM * 8);
+    while (nCta > 1 && (double) nCta * slab * 8.0 > 0.6 * (double) freeB) nCta = nCta / 2;
+    if ((double) nCta * slab * 8.0 > 0.9 * (double) freeB) {
+        sa_set_error("sa_batch_prepare: a single work item needs %.1f GB of forward-matrix scratch (band too wide)",
+                     slab * 8.0 / 1e9);
+        return SA_ERR_INPUT;
+    }
+    b->nCta = std::max(1, nCta);
+    if ((rc = b->dScratch.alloc((size_t) b->nCta * slab))) return rc;
+
+    GParams &g = b->gp;
+    memset(&g, 0, sizeof(g));
+    g.items = b->dItems.p; g.nItems = (int32_t) items.size(); g.counter = b->dCounter.p;
+    g.pathOff = b->dPathOff.p; g.pathKmer = b->dPathKmer.p;
+    g.evMean = b->dEvMean.p; g.evNoise = b->dEvNoise.p; g.evLogNoise = b->dEvLogNoise.p;
+    g.bandL = b->dBandL.p; g.bandW = b->dBandW.p; g.bandOff = b->dBandOff.p;
+    g.kt = m->dev->kt; g.gapX = m->dev->gapX;
+    memcpy(g.trans, m->trans, sizeof(g.trans));
+    g.kind = m->kind; g.A = m->A; g.suffixMod = m->K / m->A;
+    g.G = m->G; g.grid = m->dev->grid; g.pp = m->dev->pp; g.slopes = m->dev->slopes; g.kmerToRow = m->dev->kmerToRow;
+    g.threshold = p->threshold; g.minDiags = p->minDiagsBetweenTraceBack; g.traceBack = p->traceBackDiagonals;
+    g.expansion = p->diagonalExpansion;
+    g.scratch = b->dScratch.p; g.slabDoubles = slab; g.ringSize = ring; g.maxDiagPC = maxDiagPC; g.maxWidth = maxWidth;
+    g.pairs = b->dPairs.p; g.pairCount = b->dPairCount.p; g.expOut = b->dExpOut.p;
+    g.assignK = b->dAssignK.p; g.assignE = b->dAssignE.p; g.assignCount = b->expectations ? b->dAssignCount.p : nullptr;
+    CK(cudaStreamSynchronize(st));
+    *out = b.release();
+    return SA_OK;
+}
+
+extern "C" int sa_batch_run(sa_batch_t *b) {
+    cudaStream_t st = b->stream;
+    b->lastLaunches = 0;
+    CK(cudaEventRecord(b->ev[0], st));
+    CK(cudaMemsetAsync(b->dCounter.p, 0, sizeof(int32_t), st));
+    CK(cudaEventRecord(b->ev[1], st));
+    if (b->gp.nItems > 0) {
+        if (b->expectations) sa_general_kernel<true><<<b->nCta, 128, 0, st>>>(b->gp);
+        else sa_general_kernel<false><<<b->nCta, 128, 0, st>>>(b->gp);
+        b->lastLaunches++;
+        CK(cudaGetLastError());
+    }
+    CK(cudaEventRecord(b->ev[2], st));
+    CK(cudaEventRecord(b->ev[3], st));
+    CK(cudaStreamSynchronize(st));
+    CK(cudaEventElapsedTime(&b->lastMs[0], b->ev[0], b->ev[1]));
+    CK(cudaEventElapsedTime(&b->lastMs[1], b->ev[1], b->ev[2]));
+    CK(cudaEventElapsedTime(&b->lastMs[2], b->ev[2], b->ev[3]));
+    return SA_OK;
+}
+
+static int growAndRerun(sa_batch_t *b) {
+    // some item produced more pairs / assignments than its slot: re-slot with the exact counts and run again
+    int64_t n = (int64_t) b->gItems.size();
+    int64_t pt = 0, at = 0;
+    for (int64_t i = 0; i < n; i++) {
+        GItem &it = b->gItems[i];
+        if (!b->expectations) {
+            it.pairCap = std::max(it.pairCap, b->pairCountHost[i]);
+            it.pairOff = pt;
+            pt += it.pairCap;
+        } else if (!b->assignCountHost.empty()) {
+            it.assignCap = std::max(it.assignCap, b->assignCountHost[i]);
+            it.assignOff = at;
+            at += it.assignCap;
+        }
+    }
+    int rc;
+    if ((rc = b->dItems.upload(b->gItems, b->stream, &b->h2dBytes))) return rc;
+    b->gp.items = b->dItems.p;
+    if (!b->expectations) {
+        if ((rc = b->dPairs.alloc(std::max<int64_t>(1, pt)))) return rc;
+        b->gp.pairs = b->dPairs.p;
+    } else {
+        if ((rc = b->dAssignK.alloc(std::max<int64_t>(1, at)))) return rc;
+        if ((rc = b->dAssignE.alloc(std::max<int64_t>(1, at)))) return rc;
+        b->gp.assignK = b->dAssignK.p;
+        b->gp.assignE = b->dAssignE.p;
+    }
+    return sa_batch_run(b);
+}
+
+extern "C" int sa_batch_fetch(sa_batch_t *b, sa_result_t **out) {
+    *out = nullptr;
+    int64_t n = (int64_t) b->gItems.size();
+    cudaStream_t st = b->stream;
+    b->d2hBytes = 0;
+    for (int attempt = 0; attempt < 3; attempt++) {
+        bool overflow = false;
+        if (!b->expectations) {
+            b->pairCountHost.assign(std::max<int64_t>(1, n), 0);
+            CK(cudaMemcpyAsync(b->pairCountHost.data(), b->dPairCount.p, sizeof(int64_t) * std::max<int64_t>(1, n),
+                               cudaMemcpyDeviceToHost, st));
+            CK(cudaStreamSynchronize(st));
+            b->d2hBytes += sizeof(int64_t) * n;
+            for (int64_t i = 0; i < n; i++) overflow |= b->pairCountHost[i] > b->gItems[i].pairCap;
+        } else if (b->model->kind == SA_EMIT_HDP) {
+            b->assignCountHost.assign(std::max<int64_t>(1, n), 0);
+            CK(cudaMemcpyAsync(b->assignCountHost.data(), b->dAssignCount.p, sizeof(int64_t) * std::max<int64_t>(1, n),
+                               cudaMemcpyDeviceToHost, st));
+            CK(cudaStreamSynchronize(st));
+            b->d2hBytes += sizeof(int64_t) * n;
+            for (int64_t i = 0; i < n; i++) overflow |= b->assignCountHost[i] > b->gItems[i].assignCap;
+        }
+        if (!overflow) break;
+        if (attempt == 2) {
+            sa_set_error("sa_batch_fetch: output slots still overflow after re-run");
+            return SA_ERR_CUDA;
+        }
+        int rc = growAndRerun(b);
+        if (rc) return rc;
+    }
+    sa_result_t *r = (sa_result_t *) calloc(1, sizeof(sa_result_t));
+    r->nReads = b->nReads;
+    r->totalBandCells = b->bandCells;
+    r->totalPathCells = b->pathCells;
+    r->totalEvents = b->events;
+    // items of each read in region order
+    std::vector<std::vector<int64_t>> byRead(b->nReads);
+    for (int64_t i = 0; i < n; i++) byRead[b->itemsHost[i].read].push_back(i);
+    for (auto &v : byRead)
+        std::sort(v.begin(), v.end(), [&](int64_t a, int64_t c) { return b->itemsHost[a].region < b->itemsHost[c].region; });
+    r->pairOffsets = (int64_t *) calloc(b->nReads + 1, sizeof(int64_t));
+    if (!b->expectations) {
+        // one D2H of the used prefix of every slot would need n copies; slots are dense enough to take in one go
+        int64_t totalCap = n ? b->gItems[n - 1].pairOff + b->gItems[n - 1].pairCap : 0;
+        for (int64_t i = 0; i < n; i++) totalCap = std::max(totalCap, b->gItems[i].pairOff + b->gItems[i].pairCap);
+        std::vector<sa_pair_t> raw((size_t) std::max<int64_t>(1, totalCap));
+        if (totalCap > 0) {
+            CK(cudaMemcpyAsync(raw.data(), b->dPairs.p, sizeof(sa_pair_t) * totalCap, cudaMemcpyDeviceToHost, st));
+            CK(cudaStreamSynchronize(st));
+            b->d2hBytes += sizeof(sa_pair_t) * totalCap;
+        }
+        int64_t total = 0;
+        for (int64_t i = 0; i < n; i++) total += b->pairCountHost[i];
+        r->pairs = (sa_pair_t *) malloc(sizeof(sa_pair_t) * std::max<int64_t>(1, total));
+        int64_t w = 0;
+        for (int64_t rd = 0; rd < b->nReads; rd++) {
+            r->pairOffsets[rd] = w;
+            for (int64_t i : byRead[rd]) {
+                const GItem &it = b->gItems[i];
+                const ItemHost &ih = b->itemsHost[i];
+                // alignedPairCoordinateCorrectionFn (pairwiseAligner.c:2043-2050): shift to read coordinates and
+                // pop the region's list from its END
+                for (int64_t q = b->pairCountHost[i] - 1; q >= 0; q--) {
+                    sa_pair_t pr = raw[it.pairOff + q];
+                    pr.x += (int32_t) ih.x1;
+                    pr.y += (int32_t) ih.y1;
+                    r->pairs[w++] = pr;
+                }
+            }
+        }
+        r->pairOffsets[b->nReads] = w;
+    } else {
+        std::vector<double> e((size_t) std::max<int64_t>(1, n * 10));
+        if (n > 0) {
+            CK(cudaMemcpyAsync(e.data(), b->dExpOut.p, sizeof(double) * n * 10, cudaMemcpyDeviceToHost, st));
+            CK(cudaStreamSynchronize(st));
+            b->d2hBytes += sizeof(double) * n * 10;
+        }
+        r->transitions = (double *) calloc(std::max<int64_t>(1, b->nReads * 9), sizeof(double));
+        r->likelihood = (double *) calloc(std::max<int64_t>(1, b->nReads), sizeof(double));
+        for (int64_t rd = 0; rd < b->nReads; rd++)
+            for (int64_t i : byRead[rd]) {
+                for (int j = 0; j < 9; j++) r->transitions[rd * 9 + j] += e[i * 10 + j];
+                r->likelihood[rd] += e[i * 10 + 9];
+            }
+        if (b->model->kind == SA_EMIT_HDP) {
+            int64_t totalCap = 0, total = 0;
+            for (int64_t i = 0; i < n; i++) {
+                totalCap = std::max(totalCap, b->gItems[i].assignOff + b->gItems[i].assignCap);
+                total += b->assignCountHost[i];
+            }
+            std::vector<int32_t> ak((size_t) std::max<int64_t>(1, totalCap)), ae((size_t) std::max<int64_t>(1, totalCap));
+            if (totalCap > 0) {
+                CK(cudaMemcpyAsync(ak.data(), b->dAssignK.p, sizeof(int32_t) * totalCap, cudaMemcpyDeviceToHost, st));
+                CK(cudaMemcpyAsync(ae.data(), b->dAssignE.p, sizeof(int32_t) * totalCap, cudaMemcpyDeviceToHost, st));
+                CK(cudaStreamSynchronize(st));
+                b->d2hBytes += 2 * sizeof(int32_t) * totalCap;
+            }
+            r->assignOffsets = (int64_t *) calloc(b->nReads + 1, sizeof(int64_t));
+            r->assignKmerPos = (int32_t *) malloc(sizeof(int32_t) * std::max<int64_t>(1, total));
+            r->assignEvent = (int32_t *) malloc(sizeof(int32_t) * std::max<int64_t>(1, total));
+            int64_t w = 0;
+            for (int64_t rd = 0; rd < b->nReads; rd++) {
+                r->assignOffsets[rd] = w;
+                for (int64_t i : byRead[rd]) {
+                    const GItem &it = b->gItems[i];
+                    const ItemHost &ih = b->itemsHost[i];
+                    for (int64_t q = 0; q < b->assignCountHost[i]; q++) {
+                        r->assignKmerPos[w] = ak[it.assignOff + q] + (int32_t) ih.x1;
+                        r->assignEvent[w] = ae[it.assignOff + q] + (int32_t) ih.y1;
+                        w++;
+                    }
+                }
+            }
+            r->assignOffsets[b->nReads] = w;
+        }
+    }
+    *out = r;
+    return SA_OK;
+}
+
+extern "C" int sa_batch_last_timing(const sa_batch_t *b, float *ms3, int64_t *launches) {
+    if (ms3) memcpy(ms3, b->lastMs, sizeof(float) * 3);
+    if (launches) *launches = b->lastLaunches;
+    return SA_OK;
+}
+extern "C" int64_t sa_batch_band_cells(const sa_batch_t *b) { return b->bandCells; }
+extern "C" int64_t sa_batch_h2d_bytes(const sa_batch_t *b) { return b->h2dBytes; }
+extern "C" int64_t sa_batch_d2h_bytes(const sa_batch_t *b) { return b->d2hBytes; }
+extern "C" void sa_batch_free(sa_batch_t *b) { delete b; }
+
+static int runBatch(const sa_model_t *m, const sa_read_t *reads, int64_t nReads, const sa_params_t *p,
+                    const sa_ambig_t *ambig, int expectations, sa_result_t **out) {
+    sa_batch_t *b = nullptr;
+    int rc = sa_batch_prepare(m, reads, nReads, p, ambig, expectations, &b);
+    if (rc) return rc;
+    rc = sa_batch_run(b);
+    if (!rc) rc = sa_batch_fetch(b, out);
+    sa_batch_free(b);
+    return rc;
+}
+
+extern "C" int sa_gpu_align_batch(const sa_model_t *m, const sa_read_t *reads, int64_t nReads, const sa_params_t *p,
+                                  const sa_ambig_t *ambig, sa_result_t **out) {
+    return runBatch(m, reads, nReads, p, ambig, 0, out);
+}
+extern "C" int sa_gpu_expectations_batch(const sa_model_t *m, const sa_read_t *reads, int64_t nReads,
+                                         const sa_params_t *p, const sa_ambig_t *ambig, sa_result_t **out) {
+    return runBatch(m, reads, nReads, p, ambig, 1, out);
+}
