@@ -1,0 +1,318 @@
+#!/usr/bin/env python
+"""bench.py — events aligned/s and banded-DP GCUPS of the signalAlign hot path on B200 (BASELINE.json metric).
+
+A "step" = one pass of the hot path (a batch of getAlignedPairsUsingAnchors calls) over one batch of synthetic reads
+of BASELINE config 3's shape: ~10k events per read against a synthetic reference, 6-mer Gaussian table, band
+expansion 100, threshold 0.01 (signalalign_b200/synth.py, seed fixed).  Per-GPU work is fixed (weak scaling): every
+rank aligns its own shard of reads, no data-path collective.
+
+    value   events/s with the batch already resident in HBM (sa_batch_run only), device-timed with CUDA events
+    e2e     the same through the host-buffer C-ABI call (packing + H2D + kernels + D2H inside the timed region)
+    roofline / roofline_compute / cpu_baseline: see DESIGN.md §Measurement
+
+`--impl reference` times the reference's own CPU implementation (oracle/_ref, built from /root/reference by
+oracle/Makefile; else the oracle port) on the box's host cores on a bounded sample of the same workload.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+WORKLOAD = "config3-synthetic: ~10k-event reads vs synthetic reference, ACGT 6-mer Gaussian table, -x 100, threshold 0.01"
+EXPANSION, TRACE_BACK, MIN_DIAGS, THRESHOLD = 100, 50, 1000, 0.01
+# guide anchors: every kmer that owns an event, in runs of ~80 kmers separated by 1-5 dropped kmers
+GEN = dict(trim=0, block_mean=80)
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--reads", type=int, default=int(os.environ.get("SA_BENCH_READS", "1184")),
+                    help="reads per GPU per step (default 8 per SM)")
+    ap.add_argument("--cpu-reads", type=int, default=0, help="reads in the CPU sample (default: one per host core)")
+    ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--seed", type=int, default=20261104)
+    return ap.parse_args()
+
+
+# ------------------------------------------------------------------------------------------------ CPU arms
+def write_model_file(path, table, alphabet="ACGT", k=6):
+    """Synthetic table in the reference's .model text format (stateMachine.c:1445-1452)."""
+    t = [0.79, 0.1965, 0.0133, 0.8035, 0.1965, 0.0, 0.9867, 1e-9, 0.0133]
+    with open(path, "w") as f:
+        f.write(f"3\t{len(alphabet)}\t{alphabet}\t{k}\n")
+        f.write("\t".join(repr(v) for v in t) + "\t0.0\n")
+        f.write("\t".join(repr(float(v)) for v in table.reshape(-1)) + "\n")
+
+
+def _cpu_worker(args):
+    kind, model_path, reads = args
+    cells = 0
+    t0 = time.time()
+    if kind == "reference":
+        from oracle import ref
+        sm = ref.RefStateMachine(model_path, kind=0)
+        for r in reads:
+            sm.set_scaling(r["scale"], r["shift"], r["var"])
+            sm.align(r["target"], r["events"], r["anchors"], threshold=THRESHOLD, min_diags=MIN_DIAGS,
+                     trace_back=TRACE_BACK, expansion=EXPANSION)
+    else:
+        from oracle import port
+        pm = port.load_model_file(model_path)
+        p = port.params(THRESHOLD, MIN_DIAGS, TRACE_BACK, EXPANSION)
+        for r in reads:
+            pm.scale, pm.shift, pm.var = r["scale"], r["shift"], r["var"]
+            _, st = port.align(pm, r["target"], r["events"], r["anchors"], p)
+            cells += st[0]
+    return time.time() - t0, cells
+
+
+def cpu_arm(reads, table, cores):
+    """Time the reference CPU path (process per core, like signalAlign's own per-read process model)."""
+    import multiprocessing as mp
+    from oracle import ref
+    kind = "reference" if ref.available() else "port"
+    tmp = tempfile.mkdtemp(prefix="sa_bench_")
+    model_path = os.path.join(tmp, "synthetic.model")
+    write_model_file(model_path, table)
+    shards = [reads[i::cores] for i in range(cores)]
+    shards = [s for s in shards if s]
+    ctx = mp.get_context("fork")
+    t0 = time.time()
+    with ctx.Pool(len(shards)) as pool:
+        pool.map(_cpu_worker, [(kind, model_path, s) for s in shards])
+    wall = time.time() - t0
+    events = sum(r["events"].shape[0] for r in reads)
+    return kind, wall, events, len(shards)
+
+
+# ------------------------------------------------------------------------------------------------ clocks
+class ClockSampler:
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "200"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc:
+            self.proc.terminate()
+        sm, mx, reasons = [], 0, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0]))
+                mx = max(mx, float(r[1]))
+                for n, v in zip(names, r[2:6]):
+                    if v.lower().startswith("active"):
+                        reasons.add(n)
+            except Exception:
+                pass
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx or None, "reasons": sorted(reasons)}
+
+
+# ------------------------------------------------------------------------------------------------ main
+def main():
+    a = parse()
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    from signalalign_b200 import synth
+
+    if a.impl == "reference":
+        if rank != 0:
+            return
+        cores = os.cpu_count() or 1
+        n = a.cpu_reads or cores
+        reads, table = synth.make_batch(n, seed=a.seed, **GEN)
+        walls = []
+        kind = "reference"
+        for i in range(a.warmup + a.steps):
+            k = 1 if i < a.warmup else None
+            sample = reads[:max(1, min(len(reads), cores))] if k else reads
+            kind, wall, events, used = cpu_arm(sample, table, cores)
+            if i >= a.warmup:
+                walls.append((wall, events, used))
+        wall = sum(w for w, _, _ in walls)
+        events = sum(e for _, e, _ in walls)
+        used = walls[0][2]
+        v = events / wall
+        print(json.dumps({
+            "impl": "reference", "metric": "events_aligned_per_sec", "value": v, "unit": "events/s", "n_gpus": a.gpus,
+            "steps": a.steps, "warmup": a.warmup, "ms_per_step": 1e3 * wall / a.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": WORKLOAD, "reads_per_step": len(reads)},
+            "cpu_baseline": {"value": v, "unit": "events/s", "cores": used, "kind": kind,
+                             "sample": f"{len(reads)} reads per step, one process per core"},
+            "e2e": {"value": v, "unit": "events/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
+        return
+
+    import torch
+    import torch.distributed as dist
+    import signalalign_b200 as sa
+
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    torch.cuda.set_device(local_rank)
+    sa.gpu_init(local_rank)
+
+    reads_d, table = synth.make_batch(a.reads, seed=a.seed + 1000 * rank, **GEN)
+    trans = synth.nanopore_transitions()
+    model = sa.Model.from_tables("ACGT", 6, trans, table)
+    p = sa.default_params(threshold=THRESHOLD, expansion=EXPANSION, trace_back=TRACE_BACK, min_diags=MIN_DIAGS)
+    reads = [sa.Read(r["target"], r["events"], r["anchors"], r["scale"], r["shift"], r["var"]) for r in reads_d]
+    events = sum(r.events.shape[0] for r in reads)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # L2 flush buffer (126 MB L2): written between timed steps; the batch itself is also far larger than L2
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+
+    # ---- resident arm: inputs in HBM before the timed region
+    batch = sa.Batch(model, reads, p)
+    cells = batch.band_cells
+    kernel_items = batch.kernel_items
+    for _ in range(a.warmup):
+        batch.run()
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    dev_ms, kern_ms, all_ms, launches = [], [], [], 0
+    barrier()
+    t0 = time.time()
+    for _ in range(a.steps):
+        flush.fill_(1)
+        torch.cuda.synchronize()
+        batch.run()
+        ms, n = batch.timing()
+        dev_ms.append(sum(ms))
+        kern_ms.append(ms[0])
+        all_ms.append(ms)
+        launches += n
+    barrier()
+    wall_resident = time.time() - t0
+    clocks = sampler.stop() if rank == 0 else None
+    step_ms = float(np.sum(dev_ms)) / a.steps
+    res = batch.fetch()
+    n_pairs = int(res.pair_offsets[-1])
+    batch.close()
+
+    # ---- end-to-end arm: host buffers -> C-ABI call -> host result (pack + H2D + kernels + D2H timed)
+    e2e_t = []
+    h2d = d2h = 0
+    barrier()
+    for i in range(max(1, min(a.steps, 2)) + 1):
+        t1 = time.time()
+        b2 = sa.Batch(model, reads, p)
+        b2.run()
+        r2 = b2.fetch()
+        if i > 0:
+            e2e_t.append(time.time() - t1)
+        h2d, d2h = b2.h2d_bytes, b2.d2h_bytes
+        b2.close()
+    barrier()
+    e2e_s = float(np.mean(e2e_t))
+
+    def reduce_max(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def reduce_sum(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return float(t.item())
+
+    step_ms_max = reduce_max(step_ms)
+    kern_ms_max = reduce_max(float(np.mean(kern_ms)))
+    e2e_max = reduce_max(e2e_s)
+    events_all = reduce_sum(float(events))
+    cells_all = reduce_sum(float(cells))
+
+    if rank == 0:
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except Exception:
+            pass
+        hbm_peak = peaks.get("hbm_gbs", 6650.0)
+        peak_src = "measured (MEASURED_PEAKS.json)" if "hbm_gbs" in peaks else "fallback (B200_PROFILING.md)"
+        # algorithmic bytes per band cell of the DP kernel: forward state written once and read
+        # once by the traceback (3 x f64 each way = 48 B) + ~0.4 B of inputs/outputs per cell
+        alg_bytes_per_cell = 48.4
+        achieved_gbs = cells * alg_bytes_per_cell / (float(np.mean(kern_ms)) * 1e-3) / 1e9
+        sm_mhz = (clocks or {}).get("sm_mhz") or 1965.0
+        # FP64 pipe: 64 lanes/SM/clk on B200; instruction count per cell from DESIGN.md (cuobjdump-counted)
+        fp64_per_cell = 150.0
+        fp64_peak = 148 * 64 * sm_mhz * 1e6
+        out = {
+            "metric": "events_aligned_per_sec", "value": events_all / (step_ms_max * 1e-3), "unit": "events/s",
+            "n_gpus": world, "steps": a.steps, "warmup": a.warmup, "ms_per_step": step_ms_max,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": WORKLOAD, "reads_per_gpu_per_step": a.reads, "events_per_step": events_all,
+                       "band_cells_per_step": cells_all, "l2": "flushed between steps (256 MiB write) and inputs > L2",
+                       "aligned_pairs_rank0": n_pairs,
+                       "kernel_ms_rank0": {"fast_c4": float(np.mean([m[0] for m in all_ms])),
+                                           "fast_c2": float(np.mean([m[1] for m in all_ms])),
+                                           "general": float(np.mean([m[2] for m in all_ms]))},
+                       "work_items_by_kernel_rank0": {"general": kernel_items[0], "fast_c2": kernel_items[1],
+                                                      "fast_c4": kernel_items[2]}},
+            "gcups": cells_all / (step_ms_max * 1e-3) / 1e9,
+            "gpu_launches": launches,
+            "clocks": clocks,
+            "e2e": {"value": events_all / e2e_max, "unit": "events/s", "h2d_bytes_per_step": int(h2d),
+                    "d2h_bytes_per_step": int(d2h), "gcups": cells_all / e2e_max / 1e9},
+            "roofline": {"bound": "hbm", "achieved": achieved_gbs, "peak": hbm_peak, "unit": "GB/s",
+                         "frac": achieved_gbs / hbm_peak, "traffic": None, "peak_source": peak_src,
+                         "note": "kernel is FP64-issue bound, not HBM bound: see roofline_compute"},
+            "roofline_compute": {"bound": "fp64_pipe", "achieved": cells * fp64_per_cell / (float(np.mean(kern_ms)) * 1e-3),
+                                 "peak": fp64_peak, "unit": "FP64 lane-instr/s",
+                                 "frac": cells * fp64_per_cell / (float(np.mean(kern_ms)) * 1e-3) / fp64_peak,
+                                 "per_cell": fp64_per_cell, "clock_mhz": sm_mhz},
+            "wall_s_resident_loop": wall_resident,
+        }
+        if world == 1 and not a.no_cpu:
+            cores = os.cpu_count() or 1
+            n = a.cpu_reads or min(cores, len(reads_d))
+            kind, wall, ev, used = cpu_arm(reads_d[:n], table, cores)
+            out["cpu_baseline"] = {"value": ev / wall, "unit": "events/s", "cores": used, "kind": kind,
+                                   "sample": f"first {n} reads of the step's batch, one process per core, {wall:.1f} s"}
+        print(json.dumps(out))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

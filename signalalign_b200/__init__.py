@@ -52,8 +52,8 @@ EXPORTS = [
     "sa_model_alphabet", "sa_model_get_tables", "sa_model_hdp_density", "sa_params_default", "sa_ambig_load",
     "sa_ambig_free", "sa_result_free", "sa_kmer_string", "sa_gpu_init", "sa_last_error", "sa_gpu_device_count",
     "sa_gpu_align_batch", "sa_gpu_expectations_batch", "sa_batch_prepare", "sa_batch_run", "sa_batch_fetch",
-    "sa_batch_last_timing", "sa_batch_band_cells", "sa_batch_h2d_bytes", "sa_batch_d2h_bytes", "sa_batch_free",
-    "sa_result_sum_expectations",
+    "sa_batch_last_timing", "sa_batch_band_cells", "sa_batch_kernel_items", "sa_batch_h2d_bytes", "sa_batch_d2h_bytes", "sa_batch_free",
+    "sa_result_sum_expectations", "sa_debug_logadd",
 ]
 
 _lib = None
@@ -112,8 +112,10 @@ def lib():
     for f in ("sa_batch_band_cells", "sa_batch_h2d_bytes", "sa_batch_d2h_bytes"):
         getattr(L, f).restype = C.c_int64
         getattr(L, f).argtypes = [C.c_void_p]
+    L.sa_batch_kernel_items.argtypes = [C.c_void_p, c_i64p]
     L.sa_batch_free.argtypes = [C.c_void_p]
     L.sa_result_sum_expectations.argtypes = [C.POINTER(SaResult), c_f64p]
+    L.sa_debug_logadd.argtypes = [c_f64p, c_f64p, c_f64p, C.c_int64]
     _lib = L
     return L
 
@@ -302,6 +304,15 @@ def expectations_batch(model, reads, params=None, ambig=None):
     return Result(out)
 
 
+def debug_logadd(x, y):
+    x = np.ascontiguousarray(x, np.float64)
+    y = np.ascontiguousarray(y, np.float64)
+    out = np.zeros_like(x)
+    _check(lib().sa_debug_logadd(x.ctypes.data_as(c_f64p), y.ctypes.data_as(c_f64p), out.ctypes.data_as(c_f64p),
+                                 x.size))
+    return out
+
+
 class Batch:
     """Staged form: prepare (pack + H2D), run (kernels only; repeatable), fetch (D2H)."""
 
@@ -330,6 +341,13 @@ class Batch:
     @property
     def band_cells(self):
         return lib().sa_batch_band_cells(self.h)
+
+    @property
+    def kernel_items(self):
+        """(general, fast C=2, fast C=4) work-item counts"""
+        o = (C.c_int64 * 3)()
+        lib().sa_batch_kernel_items(self.h, o)
+        return tuple(o)
 
     @property
     def h2d_bytes(self):

@@ -31,7 +31,8 @@ struct GItem {
 };
 
 struct GParams {
-    const GItem *items;
+    const GItem *items;      // indexed by global item id
+    const int32_t *order;    // processing order (heaviest first): nItems global ids
     int32_t nItems;
     int32_t *counter;
     const int32_t *pathOff;
@@ -508,8 +509,8 @@ __global__ void __launch_bounds__(128) sa_general_kernel(const GParams P) {
         __syncthreads();
         if (threadIdx.x == 0) sItem = atomicAdd(P.counter, 1);
         __syncthreads();
-        int it = sItem;
-        if (it >= P.nItems) break;
+        if (sItem >= P.nItems) break;
+        const int it = P.order[sItem];
         const GItem &I = P.items[it];
         GCtx c;
         c.P = &P; c.I = &I;

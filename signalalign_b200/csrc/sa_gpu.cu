@@ -14,6 +14,7 @@
 #include <cuda_runtime.h>
 #include "sa_internal.h"
 #include "sa_general.cuh"
+#include "sa_fast.cuh"
 
 #define CK(call)                                                                                   \
     do {                                                                                           \
@@ -26,13 +27,13 @@
 
 // ------------------------------------------------------------------------------------------------ device model
 struct DeviceModel {
-    double *kt = nullptr, *gapX = nullptr, *grid = nullptr, *pp = nullptr, *slopes = nullptr;
+    double *kt = nullptr, *ft = nullptr, *gapX = nullptr, *grid = nullptr, *pp = nullptr, *slopes = nullptr;
     int32_t *kmerToRow = nullptr;
 };
 
 void sa_model_drop_device(const sa_model *m) {
     if (!m->dev) return;
-    cudaFree(m->dev->kt); cudaFree(m->dev->gapX); cudaFree(m->dev->grid); cudaFree(m->dev->pp);
+    cudaFree(m->dev->kt); cudaFree(m->dev->ft); cudaFree(m->dev->gapX); cudaFree(m->dev->grid); cudaFree(m->dev->pp);
     cudaFree(m->dev->slopes); cudaFree(m->dev->kmerToRow);
     delete m->dev;
     m->dev = nullptr;
@@ -59,6 +60,18 @@ static int uploadModel(const sa_model *m) {
         }
     CK(cudaMalloc(&d->kt, kt.size() * sizeof(double)));
     CK(cudaMemcpy(d->kt, kt.data(), kt.size() * sizeof(double), cudaMemcpyHostToDevice));
+    // fast-kernel table: mu, 1/sd, -0.5*log(2*pi) - log(sd) for the match and gap-Y tables (sd == 0 -> emission -inf)
+    std::vector<double> ft((size_t) m->K * 5);
+    for (int64_t i = 0; i < m->K; i++) {
+        double sdM = m->match[i * 5 + 1], sdY = m->gapY[i * 5 + 1];
+        ft[i * 5 + 0] = m->match[i * 5];
+        ft[i * 5 + 1] = sdM == 0.0 ? 0.0 : 1.0 / sdM;
+        ft[i * 5 + 2] = sdM == 0.0 ? -INFINITY : -0.91893853320467267 - log(sdM);
+        ft[i * 5 + 3] = sdY == 0.0 ? 0.0 : 1.0 / sdY;
+        ft[i * 5 + 4] = sdY == 0.0 ? -INFINITY : -0.91893853320467267 - log(sdY);
+    }
+    CK(cudaMalloc(&d->ft, ft.size() * sizeof(double)));
+    CK(cudaMemcpy(d->ft, ft.data(), ft.size() * sizeof(double), cudaMemcpyHostToDevice));
     CK(cudaMalloc(&d->gapX, m->K * sizeof(double)));
     CK(cudaMemcpy(d->gapX, m->gapX.data(), m->K * sizeof(double), cudaMemcpyHostToDevice));
     if (m->G > 0) {
@@ -129,10 +142,18 @@ struct DevBuf {
     ~DevBuf() { release(); }
 };
 
-struct ItemHost {
+// one work item = one sub-region of one read after getSplitPoints
+struct ItemRec {
     int64_t read, x1, y1, lX, lY;
-    int64_t work;  // path-cells
-    int32_t region, nRegions;
+    int32_t region;
+    int32_t flags;            // bit0 ragged left, bit1 ragged right
+    int64_t evOff, pathOffOff, pathKmerOff, anchorOff, nAnchors;
+    int64_t maxP;
+    int64_t pairOff = 0, pairCap = 0, assignOff = 0, assignCap = 0;
+    int64_t cells = 0;        // band cells (integer band logic, same as the reference's)
+    int64_t work = 0;         // path-cells
+    int kernel = 0;           // 0 general, 2 / 4 fast kernel with C cells per lane
+    double scale, shift, var;
 };
 
 struct sa_batch {
@@ -141,16 +162,35 @@ struct sa_batch {
     bool expectations = false;
     int64_t nReads = 0;
     cudaStream_t stream = nullptr;
-    cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
-    std::vector<ItemHost> itemsHost;  // in device order (sorted by work, descending)
-    std::vector<GItem> gItems;
-    DevBuf<GItem> dItems;
-    DevBuf<int32_t> dCounter, dPathOff, dPathKmer, dBandL, dBandW, dAssignK, dAssignE;
-    DevBuf<int64_t> dBandOff, dPairCount, dAssignCount;
-    DevBuf<double> dEvMean, dEvNoise, dEvLogNoise, dScratch, dExpOut;
+    cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+    std::vector<ItemRec> items;  // global item id = index
+    // shared inputs
+    DevBuf<double> dEvMean, dEvNoise, dEvLogNoise;
+    DevBuf<int32_t> dPathOff, dPathKmer, dAnchors;
+    // outputs (indexed by global item id)
     DevBuf<sa_pair_t> dPairs;
+    DevBuf<int64_t> dPairCount, dAssignCount;
+    DevBuf<double> dExpOut;
+    DevBuf<int32_t> dAssignK, dAssignE;
+    // general kernel
+    std::vector<GItem> gItems;      // indexed by global item id (entries of fast items unused)
+    std::vector<int32_t> gOrder;
+    DevBuf<GItem> dGItems;
+    DevBuf<int32_t> dGOrder, dBandL, dBandW, dCounters;
+    DevBuf<int64_t> dBandOff;
+    DevBuf<double> dGScratch;
     GParams gp;
-    int nCta = 0;
+    int gCta = 0;
+    // fast kernel
+    std::vector<FItem> fItems;      // indexed by global item id
+    std::vector<int32_t> fOrder2, fOrder4;
+    DevBuf<FItem> dFItems;
+    DevBuf<int32_t> dFOrder2, dFOrder4, dTb;
+    DevBuf<FGeo> dGeo;
+    DevBuf<double> dFScratch;
+    FParams fp;
+    int fBlocks2 = 0, fBlocks4 = 0;
+    int32_t fRows2 = 1, fRows4 = 1;
     int64_t bandCells = 0, pathCells = 0, events = 0;
     int64_t h2dBytes = 0, d2hBytes = 0;
     float lastMs[3] = {0, 0, 0};
@@ -167,6 +207,16 @@ static int64_t nextPow2(int64_t v) {
     int64_t p = 1;
     while (p < v) p <<= 1;
     return p;
+}
+
+static bool modelFastEligible(const sa_model *m) {
+    if (m->kind != SA_EMIT_GAUSS_MEANONLY_DESCALE) return false;
+    if (!(m->trans[T_GAP_SWITCH_TO_X] == -INFINITY)) return false;
+    for (int64_t i = 0; i < m->K; i++) {
+        if (m->gapX[i] != m->gapX[0]) return false;
+        if (m->gapY[i * 5] != m->match[i * 5]) return false;  // the fast kernel shares the de-scaled mean
+    }
+    return true;
 }
 
 extern "C" int sa_batch_prepare(const sa_model_t *m, const sa_read_t *reads, int64_t nReads, const sa_params_t *p,
@@ -201,20 +251,17 @@ extern "C" int sa_batch_prepare(const sa_model_t *m, const sa_read_t *reads, int
     b->nReads = nReads;
     CK(cudaStreamCreate(&b->stream));
     for (auto &e : b->ev) CK(cudaEventCreate(&e));
+    cudaStream_t st = b->stream;
 
     const bool needNoise = m->kind == SA_EMIT_GAUSS_NOISE_SCALED || m->kind == SA_EMIT_GAUSS_NOISE_DESCALE;
-    std::vector<int32_t> pathOff, pathKmer, bandL, bandW;
-    std::vector<int64_t> bandOff;
+    const bool fastModel = modelFastEligible(m) && !b->expectations && getenv("SA_FORCE_GENERAL") == nullptr;
+    std::vector<int32_t> pathOff, pathKmer, anchors32;
     std::vector<double> evMean, evNoise, evLogNoise;
-    std::vector<GItem> items;
-    std::vector<ItemHost> itemsHost;
+    std::vector<ItemRec> &items = b->items;
     std::vector<int64_t> split;
-    std::vector<Diag> band;
     std::vector<int32_t> paths;
-    int64_t ringNeedMax = 1, maxDiagPC = 1, maxWidth = 1;
-    int64_t pairTotalCap = 0, assignTotalCap = 0;
 
-    // ambiguity / alphabet classification per character for the rolling fast path
+    // alphabet / ambiguity classification per character for the rolling kmer index
     int charCode[256];
     bool charAmbig[256];
     for (int c = 0; c < 256; c++) {
@@ -223,11 +270,16 @@ extern "C" int sa_batch_prepare(const sa_model_t *m, const sa_read_t *reads, int
         charAmbig[c] = ambig->opts[c][0] != 0;
     }
 
+    // ------------------------------------------------------------------ pass 1: split, events, kmer paths, anchors
     for (int64_t r = 0; r < nReads; r++) {
         const sa_read_t &R = reads[r];
         int64_t lXt = R.targetLength > 0 ? R.targetLength - (m->k - 1) : 0;  // sequence_correctSeqLength (:523-538)
         if (lXt < 0) lXt = 0;
         int64_t lYt = R.nEvents;
+        if (lXt > 0x3fffffff || lYt > 0x3fffffff) {
+            sa_set_error("read %lld: sequences longer than 2^30 are not supported", (long long) r);
+            return SA_ERR_INPUT;
+        }
         for (int64_t i = 0; i < R.nAnchors; i++) {
             int64_t ax = R.anchors[2 * i], ay = R.anchors[2 * i + 1];
             bool ok = ax >= 0 && ay >= 0 && ax < lXt && ay < lYt;
@@ -244,28 +296,22 @@ extern "C" int sa_batch_prepare(const sa_model_t *m, const sa_read_t *reads, int
         int64_t nSplit = (int64_t) split.size() / 4, j = 0;
         for (int64_t s = 0; s < nSplit; s++) {
             int64_t x1 = split[4 * s], y1 = split[4 * s + 1], x2 = split[4 * s + 2], y2 = split[4 * s + 3];
-            std::vector<int64_t> sub;
-            while (j < R.nAnchors) {  // pairwiseAligner.c:1984-1997
-                int64_t ax = R.anchors[2 * j], ay = R.anchors[2 * j + 1];
-                if (ax + ay >= x2 + y2) break;
-                sub.push_back(ax - x1);
-                sub.push_back(ay - y1);
-                j++;
-            }
-            GItem it;
-            memset(&it, 0, sizeof(it));
-            ItemHost ih;
-            ih.read = r; ih.x1 = x1; ih.y1 = y1; ih.lX = x2 - x1; ih.lY = y2 - y1;
-            ih.region = (int32_t) s; ih.nRegions = (int32_t) nSplit;
-            it.lX = (int32_t) ih.lX; it.lY = (int32_t) ih.lY;
+            ItemRec it;
+            it.read = r; it.x1 = x1; it.y1 = y1; it.lX = x2 - x1; it.lY = y2 - y1; it.region = (int32_t) s;
             bool rl = R.raggedLeft || s > 0, rr = R.raggedRight || s < nSplit - 1;  // :2001-2002
             it.flags = (rl ? 1 : 0) | (rr ? 2 : 0);
             it.scale = R.scale; it.shift = R.shift; it.var = R.var;
-            it.invVar = 1 / R.var;
-            it.logInvVar = log((1 / R.var));
-            // events of the region
+            it.anchorOff = (int64_t) anchors32.size() / 2;
+            while (j < R.nAnchors) {  // pairwiseAligner.c:1984-1997
+                int64_t ax = R.anchors[2 * j], ay = R.anchors[2 * j + 1];
+                if (ax + ay >= x2 + y2) break;
+                anchors32.push_back((int32_t) (ax - x1));
+                anchors32.push_back((int32_t) (ay - y1));
+                j++;
+            }
+            it.nAnchors = (int64_t) anchors32.size() / 2 - it.anchorOff;
             it.evOff = (int64_t) evMean.size();
-            for (int64_t y = 0; y < ih.lY; y++) {
+            for (int64_t y = 0; y < it.lY; y++) {
                 const double *e = R.events + (y1 + y) * 4;
                 evMean.push_back(e[0]);
                 if (needNoise) {
@@ -282,9 +328,8 @@ extern "C" int sa_batch_prepare(const sa_model_t *m, const sa_read_t *reads, int
             pathOff.push_back(0);
             pathKmer.push_back(-1);
             pathOff.push_back(1);
-            int64_t roll = -1;  // rolling kmer id of the previous window when it was unambiguous
-            int64_t maxP = 1;
-            for (int64_t x = 1; x <= ih.lX; x++) {
+            int64_t roll = -1, maxP = 1;
+            for (int64_t x = 1; x <= it.lX; x++) {
                 const char *km = R.target + x1 + x - 1;
                 bool simple = true;
                 for (int q = 0; q < m->k; q++) {
@@ -311,112 +356,212 @@ extern "C" int sa_batch_prepare(const sa_model_t *m, const sa_read_t *reads, int
                 }
                 pathOff.push_back((int32_t) ((int64_t) pathKmer.size() - base));
             }
-            // band geometry + the traceback schedule's storage needs
-            it.diagOff = (int64_t) bandL.size();
-            sa_build_band(sub.data(), (int64_t) sub.size() / 2, ih.lX, ih.lY, p->diagonalExpansion, band);
-            const int32_t *po = pathOff.data() + it.pathOffOff;
-            int64_t nDiag = ih.lX + ih.lY, off = 0, tracedBackTo = 0, ringNeed = 1;
-            ih.work = 0;
-            for (int64_t d = 0; d <= nDiag; d++) {
-                int64_t w = (band[d].xmyR - band[d].xmyL) / 2 + 1;
-                int64_t x0 = (d + band[d].xmyL) / 2;
-                int64_t pc = po[x0 + w] - po[x0];
-                bandL.push_back((int32_t) band[d].xmyL);
-                bandW.push_back((int32_t) w);
-                bandOff.push_back(off);
-                off += pc;
-                b->bandCells += w;
-                ih.work += pc;
-                maxDiagPC = std::max(maxDiagPC, pc);
-                maxWidth = std::max(maxWidth, w);
-                if (d >= 1) {
-                    bool atEnd = d == nDiag;
-                    bool tb = d >= tracedBackTo + p->minDiagsBetweenTraceBack && w <= p->diagonalExpansion * 2 + 1;
-                    if (atEnd || tb) {
-                        ringNeed = std::max(ringNeed, off - bandOff[it.diagOff + tracedBackTo]);
-                        tracedBackTo = d - (atEnd ? 0 : p->traceBackDiagonals + 1);
-                    }
-                }
-            }
-            if (nDiag == 0) ringNeed = 1;
-            b->pathCells += ih.work;
-            b->events += ih.lY;
-            ringNeedMax = std::max(ringNeedMax, ringNeed);
-            it.pairOff = pairTotalCap;
-            it.pairCap = b->expectations ? 0 : 3 * ih.lY * maxP + 64;
-            pairTotalCap += it.pairCap;
-            it.assignOff = assignTotalCap;
-            it.assignCap = (b->expectations && m->kind == SA_EMIT_HDP) ? 4 * ih.lY * maxP + 64 : 0;
-            assignTotalCap += it.assignCap;
+            it.maxP = maxP;
+            b->events += it.lY;
             items.push_back(it);
-            itemsHost.push_back(ih);
         }
     }
-    // longest-processing-time-first order for the persistent CTAs
-    std::vector<int64_t> order(items.size());
-    std::iota(order.begin(), order.end(), 0);
-    std::stable_sort(order.begin(), order.end(),
-                     [&](int64_t a, int64_t c) { return itemsHost[a].work > itemsHost[c].work; });
-    b->gItems.resize(items.size());
-    b->itemsHost.resize(items.size());
-    for (size_t i = 0; i < order.size(); i++) {
-        b->gItems[i] = items[order[i]];
-        b->itemsHost[i] = itemsHost[order[i]];
+    const int64_t n = (int64_t) items.size();
+    if (n > 0x7fffffff) {
+        sa_set_error("sa_batch_prepare: too many work items");
+        return SA_ERR_INPUT;
     }
-
-    cudaStream_t st = b->stream;
-    if ((rc = b->dItems.upload(b->gItems, st, &b->h2dBytes))) return rc;
-    if ((rc = b->dPathOff.upload(pathOff, st, &b->h2dBytes))) return rc;
-    if ((rc = b->dPathKmer.upload(pathKmer, st, &b->h2dBytes))) return rc;
-    if ((rc = b->dBandL.upload(bandL, st, &b->h2dBytes))) return rc;
-    if ((rc = b->dBandW.upload(bandW, st, &b->h2dBytes))) return rc;
-    if ((rc = b->dBandOff.upload(bandOff, st, &b->h2dBytes))) return rc;
     if ((rc = b->dEvMean.upload(evMean, st, &b->h2dBytes))) return rc;
     if ((rc = b->dEvNoise.upload(evNoise, st, &b->h2dBytes))) return rc;
     if ((rc = b->dEvLogNoise.upload(evLogNoise, st, &b->h2dBytes))) return rc;
-    if ((rc = b->dCounter.alloc(1))) return rc;
-    if ((rc = b->dPairCount.alloc(std::max<size_t>(1, items.size())))) return rc;
+    if ((rc = b->dPathOff.upload(pathOff, st, &b->h2dBytes))) return rc;
+    if ((rc = b->dPathKmer.upload(pathKmer, st, &b->h2dBytes))) return rc;
+    if ((rc = b->dAnchors.upload(anchors32, st, &b->h2dBytes))) return rc;
+    if ((rc = b->dCounters.alloc(4))) return rc;
+
+    // output slots
+    int64_t pairTotalCap = 0, assignTotalCap = 0;
+    for (auto &it : items) {
+        it.pairOff = pairTotalCap;
+        it.pairCap = b->expectations ? 0 : 3 * it.lY * it.maxP + 64;
+        pairTotalCap += it.pairCap;
+        it.assignOff = assignTotalCap;
+        it.assignCap = (b->expectations && m->kind == SA_EMIT_HDP) ? 4 * it.lY * it.maxP + 64 : 0;
+        assignTotalCap += it.assignCap;
+    }
+    if ((rc = b->dPairCount.alloc(std::max<int64_t>(1, n)))) return rc;
     if ((rc = b->dPairs.alloc(std::max<int64_t>(1, pairTotalCap)))) return rc;
     if (b->expectations) {
-        if ((rc = b->dExpOut.alloc(std::max<size_t>(1, items.size() * 10)))) return rc;
-        if ((rc = b->dAssignCount.alloc(std::max<size_t>(1, items.size())))) return rc;
+        if ((rc = b->dExpOut.alloc(std::max<int64_t>(1, n * 10)))) return rc;
+        if ((rc = b->dAssignCount.alloc(std::max<int64_t>(1, n)))) return rc;
         if ((rc = b->dAssignK.alloc(std::max<int64_t>(1, assignTotalCap)))) return rc;
         if ((rc = b->dAssignE.alloc(std::max<int64_t>(1, assignTotalCap)))) return rc;
     }
 
-    // per-CTA scratch slabs
     int dev, nSM = 148;
     CK(cudaGetDevice(&dev));
     CK(cudaDeviceGetAttribute(&nSM, cudaDevAttrMultiProcessorCount, dev));
-    int64_t ring = nextPow2(ringNeedMax);
-    int64_t slab = ring * 3 + 9 * maxDiagPC + 2 * maxWidth;
-    size_t freeB = 0, totalB = 0;
-    CK(cudaMemGetInfo(&freeB, &totalB));
-    int nCta = (int) std::min<int64_t>((int64_t) items.size(), (int64_t) nSM * 8);
-    while (nCta > 1 && (double) nCta * slab * 8.0 > 0.6 * (double) freeB) nCta = nCta / 2;
-    if ((double) nCta * slab * 8.0 > 0.9 * (double) freeB) {
-        sa_set_error("sa_batch_prepare: a single work item needs %.1f GB of forward-matrix scratch (band too wide)",
-                     slab * 8.0 / 1e9);
-        return SA_ERR_INPUT;
-    }
-    b->nCta = std::max(1, nCta);
-    if ((rc = b->dScratch.alloc((size_t) b->nCta * slab))) return rc;
 
+    // ------------------------------------------------------------------ pass 2: fast-kernel candidates + geometry
+    FParams &f = b->fp;
+    memset(&f, 0, sizeof(f));
+    b->fItems.resize(n);
+    std::vector<FGeo> geo(n);
+    if (fastModel && n > 0) {
+        int64_t tbTotal = 0;
+        for (int64_t i = 0; i < n; i++) {
+            ItemRec &it = items[i];
+            FItem &fi = b->fItems[i];
+            memset(&fi, 0, sizeof(fi));
+            fi.evOff = it.evOff;
+            fi.kmerOff = it.pathKmerOff + 1;   // column x reads pathKmer[.. + x] when every column has one path
+            fi.anchorOff = it.anchorOff;
+            fi.nAnchors = (int32_t) it.nAnchors;
+            fi.tbOff = tbTotal;
+            // consecutive traceback points are >= minDiags - (traceBack + 1) diagonals apart
+            fi.nTbCap = (int32_t) ((it.lX + it.lY) / (p->minDiagsBetweenTraceBack - p->traceBackDiagonals - 1) + 2);
+            tbTotal += fi.nTbCap;
+            fi.pairOff = it.pairOff; fi.pairCap = it.pairCap;
+            fi.lX = (int32_t) it.lX; fi.lY = (int32_t) it.lY;
+            fi.flags = it.flags;
+            fi.scale = it.scale; fi.shift = it.shift;
+            fi.invVar = 1 / it.var;
+            fi.logInvVar = log((1 / it.var));
+        }
+        if ((rc = b->dFItems.upload(b->fItems, st, &b->h2dBytes))) return rc;
+        if ((rc = b->dTb.alloc(std::max<int64_t>(1, tbTotal)))) return rc;
+        if ((rc = b->dGeo.alloc(n))) return rc;
+        f.items = b->dFItems.p; f.nItems = (int32_t) n;
+        f.evMean = b->dEvMean.p; f.kmerIdx = b->dPathKmer.p; f.anchors = b->dAnchors.p;
+        f.tb = b->dTb.p; f.geo = b->dGeo.p; f.ft = m->dev->ft;
+        memcpy(f.trans, m->trans, sizeof(f.trans));
+        f.eX = m->gapX[0];
+        f.threshold = p->threshold;
+        f.minDiags = (int32_t) p->minDiagsBetweenTraceBack; f.traceBack = (int32_t) p->traceBackDiagonals;
+        f.expansion = (int32_t) p->diagonalExpansion;
+        f.pairs = b->dPairs.p; f.pairCount = b->dPairCount.p;
+        sa_geometry_kernel<<<(unsigned) ((n + 127) / 128), 128, 0, st>>>(f);
+        CK(cudaGetLastError());
+        CK(cudaMemcpyAsync(geo.data(), b->dGeo.p, sizeof(FGeo) * n, cudaMemcpyDeviceToHost, st));
+        CK(cudaStreamSynchronize(st));
+    }
+    int32_t rows2 = 1, rows4 = 1;
+    for (int64_t i = 0; i < n; i++) {
+        ItemRec &it = items[i];
+        it.kernel = 0;
+        if (fastModel && it.maxP == 1 && geo[i].monotone) {
+            if (geo[i].maxSpan <= FastK<2>::NS - 2 - 1) it.kernel = 2;
+            else if (geo[i].maxSpan <= FastK<4>::NS - 4 - 1) it.kernel = 4;
+        }
+        if (it.kernel) {
+            it.cells = geo[i].cells;
+            it.work = geo[i].cells;
+            b->bandCells += it.cells;
+            b->pathCells += it.cells;
+            if (it.kernel == 2) { b->fOrder2.push_back((int32_t) i); rows2 = std::max(rows2, geo[i].maxRows); }
+            else { b->fOrder4.push_back((int32_t) i); rows4 = std::max(rows4, geo[i].maxRows); }
+        }
+    }
+    auto byWork = [&](int32_t a, int32_t c) { return items[a].work > items[c].work; };
+    std::stable_sort(b->fOrder2.begin(), b->fOrder2.end(), byWork);
+    std::stable_sort(b->fOrder4.begin(), b->fOrder4.end(), byWork);
+    if ((rc = b->dFOrder2.upload(b->fOrder2, st, &b->h2dBytes))) return rc;
+    if ((rc = b->dFOrder4.upload(b->fOrder4, st, &b->h2dBytes))) return rc;
+    {
+        int bps2 = 1, bps4 = 1;
+        CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps2, sa_fast_kernel<2>, 128, 0));
+        CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps4, sa_fast_kernel<4>, 128, 0));
+        b->fBlocks2 = (int) std::min<int64_t>((int64_t) nSM * std::max(1, bps2), ((int64_t) b->fOrder2.size() + 3) / 4);
+        b->fBlocks4 = (int) std::min<int64_t>((int64_t) nSM * std::max(1, bps4), ((int64_t) b->fOrder4.size() + 3) / 4);
+        int64_t need2 = (int64_t) b->fBlocks2 * 4 * rows2 * FastK<2>::ROW;
+        int64_t need4 = (int64_t) b->fBlocks4 * 4 * rows4 * FastK<4>::ROW;
+        if ((rc = b->dFScratch.alloc((size_t) std::max<int64_t>(1, std::max(need2, need4))))) return rc;
+        f.scratch = b->dFScratch.p;
+        b->fRows2 = rows2;  // rowsCap differs per launch
+        b->fRows4 = rows4;
+    }
+
+    // ------------------------------------------------------------------ pass 3: general kernel for the rest
+    std::vector<int32_t> bandL, bandW;
+    std::vector<int64_t> bandOff;
+    std::vector<Diag> band;
+    int64_t ringNeedMax = 1, maxDiagPC = 1, maxWidth = 1;
+    b->gItems.resize(n);
+    std::vector<int64_t> sub;
+    for (int64_t i = 0; i < n; i++) {
+        ItemRec &it = items[i];
+        if (it.kernel) continue;
+        GItem &g = b->gItems[i];
+        memset(&g, 0, sizeof(g));
+        g.evOff = it.evOff; g.pathOffOff = it.pathOffOff; g.pathKmerOff = it.pathKmerOff;
+        g.pairOff = it.pairOff; g.pairCap = it.pairCap; g.assignOff = it.assignOff; g.assignCap = it.assignCap;
+        g.lX = (int32_t) it.lX; g.lY = (int32_t) it.lY; g.flags = it.flags;
+        g.scale = it.scale; g.shift = it.shift; g.var = it.var;
+        g.invVar = 1 / it.var;
+        g.logInvVar = log((1 / it.var));
+        g.diagOff = (int64_t) bandL.size();
+        sub.resize(it.nAnchors * 2);
+        for (int64_t q = 0; q < it.nAnchors * 2; q++) sub[q] = anchors32[it.anchorOff * 2 + q];
+        sa_build_band(sub.data(), it.nAnchors, it.lX, it.lY, p->diagonalExpansion, band);
+        const int32_t *po = pathOff.data() + it.pathOffOff;
+        int64_t nDiag = it.lX + it.lY, off = 0, tracedBackTo = 0, ringNeed = 1;
+        for (int64_t d = 0; d <= nDiag; d++) {
+            int64_t w = (band[d].xmyR - band[d].xmyL) / 2 + 1;
+            int64_t x0 = (d + band[d].xmyL) / 2;
+            int64_t pc = po[x0 + w] - po[x0];
+            bandL.push_back((int32_t) band[d].xmyL);
+            bandW.push_back((int32_t) w);
+            bandOff.push_back(off);
+            off += pc;
+            it.cells += w;
+            it.work += pc;
+            maxDiagPC = std::max(maxDiagPC, pc);
+            maxWidth = std::max(maxWidth, w);
+            if (d >= 1) {
+                bool atEnd = d == nDiag;
+                bool tb = d >= tracedBackTo + p->minDiagsBetweenTraceBack && w <= p->diagonalExpansion * 2 + 1;
+                if (atEnd || tb) {
+                    ringNeed = std::max(ringNeed, off - bandOff[g.diagOff + tracedBackTo]);
+                    tracedBackTo = d - (atEnd ? 0 : p->traceBackDiagonals + 1);
+                }
+            }
+        }
+        b->bandCells += it.cells;
+        b->pathCells += it.work;
+        ringNeedMax = std::max(ringNeedMax, ringNeed);
+        b->gOrder.push_back((int32_t) i);
+    }
+    std::stable_sort(b->gOrder.begin(), b->gOrder.end(), byWork);
     GParams &g = b->gp;
     memset(&g, 0, sizeof(g));
-    g.items = b->dItems.p; g.nItems = (int32_t) items.size(); g.counter = b->dCounter.p;
-    g.pathOff = b->dPathOff.p; g.pathKmer = b->dPathKmer.p;
-    g.evMean = b->dEvMean.p; g.evNoise = b->dEvNoise.p; g.evLogNoise = b->dEvLogNoise.p;
-    g.bandL = b->dBandL.p; g.bandW = b->dBandW.p; g.bandOff = b->dBandOff.p;
-    g.kt = m->dev->kt; g.gapX = m->dev->gapX;
-    memcpy(g.trans, m->trans, sizeof(g.trans));
-    g.kind = m->kind; g.A = m->A; g.suffixMod = m->K / m->A;
-    g.G = m->G; g.grid = m->dev->grid; g.pp = m->dev->pp; g.slopes = m->dev->slopes; g.kmerToRow = m->dev->kmerToRow;
-    g.threshold = p->threshold; g.minDiags = p->minDiagsBetweenTraceBack; g.traceBack = p->traceBackDiagonals;
-    g.expansion = p->diagonalExpansion;
-    g.scratch = b->dScratch.p; g.slabDoubles = slab; g.ringSize = ring; g.maxDiagPC = maxDiagPC; g.maxWidth = maxWidth;
-    g.pairs = b->dPairs.p; g.pairCount = b->dPairCount.p; g.expOut = b->dExpOut.p;
-    g.assignK = b->dAssignK.p; g.assignE = b->dAssignE.p; g.assignCount = b->expectations ? b->dAssignCount.p : nullptr;
+    if (!b->gOrder.empty()) {
+        if ((rc = b->dGItems.upload(b->gItems, st, &b->h2dBytes))) return rc;
+        if ((rc = b->dGOrder.upload(b->gOrder, st, &b->h2dBytes))) return rc;
+        if ((rc = b->dBandL.upload(bandL, st, &b->h2dBytes))) return rc;
+        if ((rc = b->dBandW.upload(bandW, st, &b->h2dBytes))) return rc;
+        if ((rc = b->dBandOff.upload(bandOff, st, &b->h2dBytes))) return rc;
+        int64_t ring = nextPow2(ringNeedMax);
+        int64_t slab = ring * 3 + 9 * maxDiagPC + 2 * maxWidth;
+        size_t freeB = 0, totalB = 0;
+        CK(cudaMemGetInfo(&freeB, &totalB));
+        int nCta = (int) std::min<int64_t>((int64_t) b->gOrder.size(), (int64_t) nSM * 8);
+        while (nCta > 1 && (double) nCta * slab * 8.0 > 0.6 * (double) freeB) nCta = nCta / 2;
+        if ((double) nCta * slab * 8.0 > 0.9 * (double) freeB) {
+            sa_set_error("sa_batch_prepare: a single work item needs %.1f GB of forward-matrix scratch (band too wide)",
+                         slab * 8.0 / 1e9);
+            return SA_ERR_INPUT;
+        }
+        b->gCta = std::max(1, nCta);
+        if ((rc = b->dGScratch.alloc((size_t) b->gCta * slab))) return rc;
+        g.items = b->dGItems.p; g.order = b->dGOrder.p; g.nItems = (int32_t) b->gOrder.size();
+        g.pathOff = b->dPathOff.p; g.pathKmer = b->dPathKmer.p;
+        g.evMean = b->dEvMean.p; g.evNoise = b->dEvNoise.p; g.evLogNoise = b->dEvLogNoise.p;
+        g.bandL = b->dBandL.p; g.bandW = b->dBandW.p; g.bandOff = b->dBandOff.p;
+        g.kt = m->dev->kt; g.gapX = m->dev->gapX;
+        memcpy(g.trans, m->trans, sizeof(g.trans));
+        g.kind = m->kind; g.A = m->A; g.suffixMod = m->K / m->A;
+        g.G = m->G; g.grid = m->dev->grid; g.pp = m->dev->pp; g.slopes = m->dev->slopes; g.kmerToRow = m->dev->kmerToRow;
+        g.threshold = p->threshold; g.minDiags = p->minDiagsBetweenTraceBack; g.traceBack = p->traceBackDiagonals;
+        g.expansion = p->diagonalExpansion;
+        g.scratch = b->dGScratch.p; g.slabDoubles = slab; g.ringSize = ring; g.maxDiagPC = maxDiagPC; g.maxWidth = maxWidth;
+        g.pairs = b->dPairs.p; g.pairCount = b->dPairCount.p; g.expOut = b->dExpOut.p;
+        g.assignK = b->dAssignK.p; g.assignE = b->dAssignE.p; g.assignCount = b->expectations ? b->dAssignCount.p : nullptr;
+    }
     CK(cudaStreamSynchronize(st));
     *out = b.release();
     return SA_OK;
@@ -425,18 +570,37 @@ extern "C" int sa_batch_prepare(const sa_model_t *m, const sa_read_t *reads, int
 extern "C" int sa_batch_run(sa_batch_t *b) {
     cudaStream_t st = b->stream;
     b->lastLaunches = 0;
+    CK(cudaMemsetAsync(b->dCounters.p, 0, 4 * sizeof(int32_t), st));
     CK(cudaEventRecord(b->ev[0], st));
-    CK(cudaMemsetAsync(b->dCounter.p, 0, sizeof(int32_t), st));
+    if (!b->fOrder4.empty()) {
+        FParams f = b->fp;
+        f.order = b->dFOrder4.p; f.nOrder = (int32_t) b->fOrder4.size(); f.counter = b->dCounters.p + 0;
+        f.rowsCap = b->fRows4;
+        sa_fast_kernel<4><<<b->fBlocks4, 128, 0, st>>>(f);
+        b->lastLaunches++;
+        CK(cudaGetLastError());
+    }
     CK(cudaEventRecord(b->ev[1], st));
-    if (b->gp.nItems > 0) {
-        if (b->expectations) sa_general_kernel<true><<<b->nCta, 128, 0, st>>>(b->gp);
-        else sa_general_kernel<false><<<b->nCta, 128, 0, st>>>(b->gp);
+    if (!b->fOrder2.empty()) {
+        FParams f = b->fp;
+        f.order = b->dFOrder2.p; f.nOrder = (int32_t) b->fOrder2.size(); f.counter = b->dCounters.p + 1;
+        f.rowsCap = b->fRows2;
+        sa_fast_kernel<2><<<b->fBlocks2, 128, 0, st>>>(f);
         b->lastLaunches++;
         CK(cudaGetLastError());
     }
     CK(cudaEventRecord(b->ev[2], st));
+    if (!b->gOrder.empty()) {
+        GParams g = b->gp;
+        g.counter = b->dCounters.p + 2;
+        if (b->expectations) sa_general_kernel<true><<<b->gCta, 128, 0, st>>>(g);
+        else sa_general_kernel<false><<<b->gCta, 128, 0, st>>>(g);
+        b->lastLaunches++;
+        CK(cudaGetLastError());
+    }
     CK(cudaEventRecord(b->ev[3], st));
     CK(cudaStreamSynchronize(st));
+    // lastMs: [0] fast kernel C=4, [1] fast kernel C=2, [2] general kernel
     CK(cudaEventElapsedTime(&b->lastMs[0], b->ev[0], b->ev[1]));
     CK(cudaEventElapsedTime(&b->lastMs[1], b->ev[1], b->ev[2]));
     CK(cudaEventElapsedTime(&b->lastMs[2], b->ev[2], b->ev[3]));
@@ -445,10 +609,10 @@ extern "C" int sa_batch_run(sa_batch_t *b) {
 
 static int growAndRerun(sa_batch_t *b) {
     // some item produced more pairs / assignments than its slot: re-slot with the exact counts and run again
-    int64_t n = (int64_t) b->gItems.size();
+    int64_t n = (int64_t) b->items.size();
     int64_t pt = 0, at = 0;
     for (int64_t i = 0; i < n; i++) {
-        GItem &it = b->gItems[i];
+        ItemRec &it = b->items[i];
         if (!b->expectations) {
             it.pairCap = std::max(it.pairCap, b->pairCountHost[i]);
             it.pairOff = pt;
@@ -458,13 +622,26 @@ static int growAndRerun(sa_batch_t *b) {
             it.assignOff = at;
             at += it.assignCap;
         }
+        if (it.kernel) {
+            b->fItems[i].pairOff = it.pairOff; b->fItems[i].pairCap = it.pairCap;
+        } else {
+            b->gItems[i].pairOff = it.pairOff; b->gItems[i].pairCap = it.pairCap;
+            b->gItems[i].assignOff = it.assignOff; b->gItems[i].assignCap = it.assignCap;
+        }
     }
     int rc;
-    if ((rc = b->dItems.upload(b->gItems, b->stream, &b->h2dBytes))) return rc;
-    b->gp.items = b->dItems.p;
+    if (!b->fOrder2.empty() || !b->fOrder4.empty()) {
+        if ((rc = b->dFItems.upload(b->fItems, b->stream, &b->h2dBytes))) return rc;
+        b->fp.items = b->dFItems.p;
+    }
+    if (!b->gOrder.empty()) {
+        if ((rc = b->dGItems.upload(b->gItems, b->stream, &b->h2dBytes))) return rc;
+        b->gp.items = b->dGItems.p;
+    }
     if (!b->expectations) {
         if ((rc = b->dPairs.alloc(std::max<int64_t>(1, pt)))) return rc;
         b->gp.pairs = b->dPairs.p;
+        b->fp.pairs = b->dPairs.p;
     } else {
         if ((rc = b->dAssignK.alloc(std::max<int64_t>(1, at)))) return rc;
         if ((rc = b->dAssignE.alloc(std::max<int64_t>(1, at)))) return rc;
@@ -476,7 +653,7 @@ static int growAndRerun(sa_batch_t *b) {
 
 extern "C" int sa_batch_fetch(sa_batch_t *b, sa_result_t **out) {
     *out = nullptr;
-    int64_t n = (int64_t) b->gItems.size();
+    int64_t n = (int64_t) b->items.size();
     cudaStream_t st = b->stream;
     b->d2hBytes = 0;
     for (int attempt = 0; attempt < 3; attempt++) {
@@ -487,14 +664,14 @@ extern "C" int sa_batch_fetch(sa_batch_t *b, sa_result_t **out) {
                                cudaMemcpyDeviceToHost, st));
             CK(cudaStreamSynchronize(st));
             b->d2hBytes += sizeof(int64_t) * n;
-            for (int64_t i = 0; i < n; i++) overflow |= b->pairCountHost[i] > b->gItems[i].pairCap;
+            for (int64_t i = 0; i < n; i++) overflow |= b->pairCountHost[i] > b->items[i].pairCap;
         } else if (b->model->kind == SA_EMIT_HDP) {
             b->assignCountHost.assign(std::max<int64_t>(1, n), 0);
             CK(cudaMemcpyAsync(b->assignCountHost.data(), b->dAssignCount.p, sizeof(int64_t) * std::max<int64_t>(1, n),
                                cudaMemcpyDeviceToHost, st));
             CK(cudaStreamSynchronize(st));
             b->d2hBytes += sizeof(int64_t) * n;
-            for (int64_t i = 0; i < n; i++) overflow |= b->assignCountHost[i] > b->gItems[i].assignCap;
+            for (int64_t i = 0; i < n; i++) overflow |= b->assignCountHost[i] > b->items[i].assignCap;
         }
         if (!overflow) break;
         if (attempt == 2) {
@@ -509,37 +686,43 @@ extern "C" int sa_batch_fetch(sa_batch_t *b, sa_result_t **out) {
     r->totalBandCells = b->bandCells;
     r->totalPathCells = b->pathCells;
     r->totalEvents = b->events;
-    // items of each read in region order
-    std::vector<std::vector<int64_t>> byRead(b->nReads);
-    for (int64_t i = 0; i < n; i++) byRead[b->itemsHost[i].read].push_back(i);
-    for (auto &v : byRead)
-        std::sort(v.begin(), v.end(), [&](int64_t a, int64_t c) { return b->itemsHost[a].region < b->itemsHost[c].region; });
+    // items are created read by read, region by region: already in (read, region) order
     r->pairOffsets = (int64_t *) calloc(b->nReads + 1, sizeof(int64_t));
     if (!b->expectations) {
-        // one D2H of the used prefix of every slot would need n copies; slots are dense enough to take in one go
-        int64_t totalCap = n ? b->gItems[n - 1].pairOff + b->gItems[n - 1].pairCap : 0;
-        for (int64_t i = 0; i < n; i++) totalCap = std::max(totalCap, b->gItems[i].pairOff + b->gItems[i].pairCap);
+        int64_t totalCap = 0, total = 0;
+        for (int64_t i = 0; i < n; i++) {
+            totalCap = std::max(totalCap, b->items[i].pairOff + b->items[i].pairCap);
+            total += b->pairCountHost[i];
+        }
+        // pairs come back slot by slot (used prefix only) into one pinned-size host buffer
         std::vector<sa_pair_t> raw((size_t) std::max<int64_t>(1, totalCap));
         if (totalCap > 0) {
-            CK(cudaMemcpyAsync(raw.data(), b->dPairs.p, sizeof(sa_pair_t) * totalCap, cudaMemcpyDeviceToHost, st));
+            // slots are ~3x over-provisioned: copy the used prefixes when that is clearly less traffic
+            if (total * 2 < totalCap && n <= 4096) {
+                for (int64_t i = 0; i < n; i++)
+                    if (b->pairCountHost[i] > 0) {
+                        CK(cudaMemcpyAsync(raw.data() + b->items[i].pairOff, b->dPairs.p + b->items[i].pairOff,
+                                           sizeof(sa_pair_t) * b->pairCountHost[i], cudaMemcpyDeviceToHost, st));
+                        b->d2hBytes += sizeof(sa_pair_t) * b->pairCountHost[i];
+                    }
+            } else {
+                CK(cudaMemcpyAsync(raw.data(), b->dPairs.p, sizeof(sa_pair_t) * totalCap, cudaMemcpyDeviceToHost, st));
+                b->d2hBytes += sizeof(sa_pair_t) * totalCap;
+            }
             CK(cudaStreamSynchronize(st));
-            b->d2hBytes += sizeof(sa_pair_t) * totalCap;
         }
-        int64_t total = 0;
-        for (int64_t i = 0; i < n; i++) total += b->pairCountHost[i];
         r->pairs = (sa_pair_t *) malloc(sizeof(sa_pair_t) * std::max<int64_t>(1, total));
-        int64_t w = 0;
+        int64_t w = 0, i = 0;
         for (int64_t rd = 0; rd < b->nReads; rd++) {
             r->pairOffsets[rd] = w;
-            for (int64_t i : byRead[rd]) {
-                const GItem &it = b->gItems[i];
-                const ItemHost &ih = b->itemsHost[i];
+            for (; i < n && b->items[i].read == rd; i++) {
+                const ItemRec &it = b->items[i];
                 // alignedPairCoordinateCorrectionFn (pairwiseAligner.c:2043-2050): shift to read coordinates and
                 // pop the region's list from its END
                 for (int64_t q = b->pairCountHost[i] - 1; q >= 0; q--) {
                     sa_pair_t pr = raw[it.pairOff + q];
-                    pr.x += (int32_t) ih.x1;
-                    pr.y += (int32_t) ih.y1;
+                    pr.x += (int32_t) it.x1;
+                    pr.y += (int32_t) it.y1;
                     r->pairs[w++] = pr;
                 }
             }
@@ -554,15 +737,15 @@ extern "C" int sa_batch_fetch(sa_batch_t *b, sa_result_t **out) {
         }
         r->transitions = (double *) calloc(std::max<int64_t>(1, b->nReads * 9), sizeof(double));
         r->likelihood = (double *) calloc(std::max<int64_t>(1, b->nReads), sizeof(double));
-        for (int64_t rd = 0; rd < b->nReads; rd++)
-            for (int64_t i : byRead[rd]) {
-                for (int j = 0; j < 9; j++) r->transitions[rd * 9 + j] += e[i * 10 + j];
-                r->likelihood[rd] += e[i * 10 + 9];
-            }
+        for (int64_t i = 0; i < n; i++) {
+            int64_t rd = b->items[i].read;
+            for (int j = 0; j < 9; j++) r->transitions[rd * 9 + j] += e[i * 10 + j];
+            r->likelihood[rd] += e[i * 10 + 9];
+        }
         if (b->model->kind == SA_EMIT_HDP) {
             int64_t totalCap = 0, total = 0;
             for (int64_t i = 0; i < n; i++) {
-                totalCap = std::max(totalCap, b->gItems[i].assignOff + b->gItems[i].assignCap);
+                totalCap = std::max(totalCap, b->items[i].assignOff + b->items[i].assignCap);
                 total += b->assignCountHost[i];
             }
             std::vector<int32_t> ak((size_t) std::max<int64_t>(1, totalCap)), ae((size_t) std::max<int64_t>(1, totalCap));
@@ -575,15 +758,14 @@ extern "C" int sa_batch_fetch(sa_batch_t *b, sa_result_t **out) {
             r->assignOffsets = (int64_t *) calloc(b->nReads + 1, sizeof(int64_t));
             r->assignKmerPos = (int32_t *) malloc(sizeof(int32_t) * std::max<int64_t>(1, total));
             r->assignEvent = (int32_t *) malloc(sizeof(int32_t) * std::max<int64_t>(1, total));
-            int64_t w = 0;
+            int64_t w = 0, i = 0;
             for (int64_t rd = 0; rd < b->nReads; rd++) {
                 r->assignOffsets[rd] = w;
-                for (int64_t i : byRead[rd]) {
-                    const GItem &it = b->gItems[i];
-                    const ItemHost &ih = b->itemsHost[i];
+                for (; i < n && b->items[i].read == rd; i++) {
+                    const ItemRec &it = b->items[i];
                     for (int64_t q = 0; q < b->assignCountHost[i]; q++) {
-                        r->assignKmerPos[w] = ak[it.assignOff + q] + (int32_t) ih.x1;
-                        r->assignEvent[w] = ae[it.assignOff + q] + (int32_t) ih.y1;
+                        r->assignKmerPos[w] = ak[it.assignOff + q] + (int32_t) it.x1;
+                        r->assignEvent[w] = ae[it.assignOff + q] + (int32_t) it.y1;
                         w++;
                     }
                 }
@@ -601,9 +783,30 @@ extern "C" int sa_batch_last_timing(const sa_batch_t *b, float *ms3, int64_t *la
     return SA_OK;
 }
 extern "C" int64_t sa_batch_band_cells(const sa_batch_t *b) { return b->bandCells; }
+extern "C" void sa_batch_kernel_items(const sa_batch_t *b, int64_t *o) {
+    o[0] = (int64_t) b->gOrder.size(); o[1] = (int64_t) b->fOrder2.size(); o[2] = (int64_t) b->fOrder4.size();
+}
 extern "C" int64_t sa_batch_h2d_bytes(const sa_batch_t *b) { return b->h2dBytes; }
 extern "C" int64_t sa_batch_d2h_bytes(const sa_batch_t *b) { return b->d2hBytes; }
 extern "C" void sa_batch_free(sa_batch_t *b) { delete b; }
+
+// ---- test hook: the device logAdd on arrays (mirrors the reference's own logAdd unit test,
+// tests/signalPairwiseAlignerTest.c:115-125, but compared bit-for-bit against the oracle)
+__global__ void sa_logadd_kernel(const double *x, const double *y, double *o, int64_t n) {
+    int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) o[i] = sa_logAdd(x[i], y[i]);
+}
+extern "C" int sa_debug_logadd(const double *x, const double *y, double *out, int64_t n) {
+    double *dx, *dy, *dout;
+    CK(cudaMalloc(&dx, n * 8)); CK(cudaMalloc(&dy, n * 8)); CK(cudaMalloc(&dout, n * 8));
+    CK(cudaMemcpy(dx, x, n * 8, cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(dy, y, n * 8, cudaMemcpyHostToDevice));
+    sa_logadd_kernel<<<(unsigned) ((n + 255) / 256), 256>>>(dx, dy, dout, n);
+    CK(cudaGetLastError());
+    CK(cudaMemcpy(out, dout, n * 8, cudaMemcpyDeviceToHost));
+    cudaFree(dx); cudaFree(dy); cudaFree(dout);
+    return SA_OK;
+}
 
 static int runBatch(const sa_model_t *m, const sa_read_t *reads, int64_t nReads, const sa_params_t *p,
                     const sa_ambig_t *ambig, int expectations, sa_result_t **out) {

@@ -1,4 +1,6 @@
 """-m gpu: the CUDA path, called through the C-ABI, against the oracle on the same seeded inputs."""
+import os
+
 import numpy as np
 import pytest
 
@@ -13,19 +15,93 @@ pytestmark = pytest.mark.gpu
 
 @pytest.fixture(scope="module")
 def small_batch():
-    reads, table = synth.make_batch(6, seed=11, mean_len=500, min_len=200, max_len=900)
+    # dense guide anchors (trim 0): bands stay ~expansion+1 wide -> fast kernel
+    reads, table = synth.make_batch(6, seed=11, mean_len=500, min_len=200, max_len=900, trim=0)
     return reads, table
 
 
-def test_gaussian_meanonly_small(small_batch):
-    reads, table = small_batch
+@pytest.fixture(scope="module")
+def gapped_batch():
+    # anchors trimmed by 14 per block (constraintDiagonalTrim): bands widen in the gaps -> mixed kernels
+    reads, table = synth.make_batch(6, seed=12, mean_len=500, min_len=200, max_len=900, trim=14)
+    return reads, table
+
+
+def _run_and_compare(reads, table, p, max_dp=10, force_general=False, expect_fast=None):
     trans = synth.nanopore_transitions()
     model = sa.Model.from_tables("ACGT", 6, trans, table)
     pm = port_model_from("ACGT", 6, trans, table)
-    p = sa.default_params(threshold=0.01, expansion=50, trace_back=50, min_diags=200)
-    res = sa.align_batch(model, [sa_read(r) for r in reads], p)
+    if force_general:
+        os.environ["SA_FORCE_GENERAL"] = "1"
+    try:
+        b = sa.Batch(model, [sa_read(r) for r in reads], p)
+        kernels = b.kernel_items
+        b.run()
+        res = b.fetch()
+        b.close()
+    finally:
+        os.environ.pop("SA_FORCE_GENERAL", None)
+    if force_general:
+        assert kernels[1] == 0 and kernels[2] == 0
+    elif expect_fast is not None:
+        assert kernels[1] + kernels[2] == len(reads), kernels
     worst = 0
+    cells = 0
     for i, r in enumerate(reads):
         ora, stats = oracle_align(pm, r, port_params(p))
+        cells += stats[0]
         worst = max(worst, compare_pairs(res.read_pairs(i), ora, p.threshold))
-    assert worst <= 10  # FP64 device path: differences only from exp/log last-bit effects
+    assert res.band_cells == cells  # same integer band logic as the reference's band_construct
+    assert worst <= max_dp
+    return worst
+
+
+@pytest.mark.parametrize("force_general", [False, True])
+@pytest.mark.parametrize("expansion,trace_back,min_diags", [(50, 50, 200), (100, 50, 300), (20, 40, 1000), (6, 2, 10)])
+def test_gaussian_meanonly_small(small_batch, expansion, trace_back, min_diags, force_general):
+    reads, table = small_batch
+    p = sa.default_params(threshold=0.01, expansion=expansion, trace_back=trace_back, min_diags=min_diags)
+    expect = {50: 1, 100: 2, 20: 1, 6: 1}[expansion]
+    _run_and_compare(reads, table, p, force_general=force_general, expect_fast=expect)
+
+
+@pytest.mark.parametrize("expansion", [20, 50, 100])
+def test_gapped_anchors_mixed_kernels(gapped_batch, expansion):
+    reads, table = gapped_batch
+    p = sa.default_params(threshold=0.01, expansion=expansion, trace_back=20, min_diags=150)
+    _run_and_compare(reads, table, p)
+
+
+def test_ragged_flags_and_thresholds(small_batch):
+    reads, table = small_batch
+    for rl, rr, thr in [(False, False, 0.01), (True, False, 0.2), (False, True, 0.001)]:
+        rs = [dict(r, ragged_left=rl, ragged_right=rr) for r in reads[:3]]
+        p = sa.default_params(threshold=thr, expansion=50, trace_back=50, min_diags=200)
+        _run_and_compare(rs, table, p)
+
+
+def test_medium_reads_many_blocks():
+    reads, table = synth.make_batch(3, seed=5, mean_len=2500, min_len=2000, max_len=3000, trim=0)
+    p = sa.default_params(threshold=0.01, expansion=100, trace_back=50, min_diags=1000)
+    _run_and_compare(reads, table, p, expect_fast=2)
+
+
+def test_device_logadd_bit_exact():
+    """The device logAdd against the oracle's (itself bit-identical to the compiled reference) on random pairs,
+    the range seams (1.0, 2.5, 4.5), the 7.5 cut-off and -inf operands."""
+    rng = np.random.default_rng(3)
+    n = 200000
+    x = rng.uniform(-50, 5, n)
+    y = x + rng.uniform(-9, 9, n)
+    seams = np.array([0.0, 1.0, 2.5, 4.5, 7.5])
+    eps = np.array([0.0, 1e-15, -1e-15, 2.3e-16, 1e-9, -1e-9, 4.4e-16, 8.9e-16])
+    sx = np.repeat(rng.uniform(-30, 0, len(seams) * len(eps)), 2)
+    d = (seams[:, None] + eps[None, :]).reshape(-1)
+    sy = sx.copy()
+    sy[0::2] = sx[0::2] + d
+    sy[1::2] = sx[1::2] - d
+    x = np.concatenate([x, sx, [-np.inf, -np.inf, 3.0, -np.inf]])
+    y = np.concatenate([y, sy, [-np.inf, 2.0, -np.inf, -1e300]])
+    got = sa.debug_logadd(x, y)
+    exp = np.array([port.log_add(a, b) for a, b in zip(x, y)])
+    assert np.array_equal(got.view(np.int64), exp.view(np.int64))
