@@ -11,13 +11,28 @@
 
 #define SA_NEG_INF (__longlong_as_double(0xfff0000000000000LL))
 
-// The reference's cubic coefficients are FLOAT literals promoted to double (impl/pairwiseAligner.c:305-311): the
-// float bit pattern is selected per range (one 32-bit word per coefficient) and widened exactly with F2F.
-#define SA_FB(f) ((unsigned) __float_as_int(f))
+// The reference's four cubics for log(1 + e^x) on [0,1], (1,2.5], (2.5,4.5], (4.5,7.5): FLOAT literals promoted
+// to double (impl/pairwiseAligner.c:305-311).  They live in a 128-byte shared-memory table (row = range,
+// columns c3 c2 c1 c0) so that a logAdd fetches its coefficients with two conflict-free LDS.128 instead of
+// selecting 16 constants through the ALU; every kernel calls sa_logAdd_init() once per CTA.
+__shared__ __align__(16) double sa_lt[16];
+
+__device__ __forceinline__ void sa_logAdd_init() {
+    const float c[16] = {-0.009350833524763f, 0.130659527668286f, 0.498799810682272f, 0.693203116424741f,
+                         -0.014532321752540f, 0.139942324101744f, 0.495635523139337f, 0.692140569840976f,
+                         -0.004605031767994f, 0.063427417320019f, 0.695956496475118f, 0.514272634594009f,
+                         -0.000458661602210f, 0.009695946122598f, 0.930734667215156f, 0.168037164329057f};
+    if (threadIdx.x < 16) {
+        float v = c[0];
+#pragma unroll
+        for (int i = 1; i < 16; i++) v = threadIdx.x == i ? c[i] : v;
+        sa_lt[threadIdx.x] = (double) v;
+    }
+    __syncthreads();
+}
 
 // logAdd (impl/pairwiseAligner.c:314-318): max when either operand is -inf or |x-y| >= 7.5, else
-// min + lookup(|x-y|) with lookup = the reference's four cubics for log(1 + e^x), Horner without contraction.
-// Branch-free, integer tests on the high word wherever that is exact.
+// min + lookup(|x-y|), Horner without contraction.  Branch-free; integer tests on the high word where exact.
 __device__ __forceinline__ double sa_logAdd(double x, double y) {
     const double diff = __dsub_rn(x, y);
     const int dh = __double2hiint(diff);
@@ -27,21 +42,14 @@ __device__ __forceinline__ double sa_logAdd(double x, double y) {
     const int ah = dh & 0x7fffffff;                // high word of |diff|
     // |diff| >= 7.5, |diff| == inf (one operand -inf) and NaN (both -inf) all have ah >= hi(7.5) = 0x401E0000
     const bool far = ah >= 0x401E0000;
-    const double d = __hiloint2double(far ? 0 : ah, far ? 0 : __double2loint(diff));   // clamped: cubic result unused when far
-    // range index as three nested 0/1 flags; the coefficient bit patterns are picked with integer multiply-adds
-    // (wrap-around arithmetic is exact), which keeps the selection off the branch unit
-    const unsigned i1 = d > 1.0, i2 = d > 2.5, i3 = d > 4.5;
-#define SA_PICK(a0, a1, a2, a3)                                                                                   \
-    ((double) __int_as_float((int) (SA_FB(a0) + i1 * (SA_FB(a1) - SA_FB(a0)) + i2 * (SA_FB(a2) - SA_FB(a1)) +      \
-                                    i3 * (SA_FB(a3) - SA_FB(a2)))))
-    const double c3 = SA_PICK(-0.009350833524763f, -0.014532321752540f, -0.004605031767994f, -0.000458661602210f);
-    const double c2 = SA_PICK(0.130659527668286f, 0.139942324101744f, 0.063427417320019f, 0.009695946122598f);
-    const double c1 = SA_PICK(0.498799810682272f, 0.495635523139337f, 0.695956496475118f, 0.930734667215156f);
-    const double c0 = SA_PICK(0.693203116424741f, 0.692140569840976f, 0.514272634594009f, 0.168037164329057f);
-#undef SA_PICK
-    double r = __dmul_rn(c3, d);
-    r = __dmul_rn(__dadd_rn(r, c2), d);
-    r = __dmul_rn(__dadd_rn(r, c1), d);
-    r = __dadd_rn(__dadd_rn(r, c0), lo);
+    // |diff| itself: when far the cubic's result is discarded (idx stays in 0..3 even for inf / NaN)
+    const double d = __hiloint2double(ah, __double2loint(diff));
+    const int idx = (int) (d > 1.0) + (int) (d > 2.5) + (int) (d > 4.5);
+    const double2 ca = *reinterpret_cast<const double2 *>(sa_lt + 4 * idx);
+    const double2 cb = *reinterpret_cast<const double2 *>(sa_lt + 4 * idx + 2);
+    double r = __dmul_rn(ca.x, d);
+    r = __dmul_rn(__dadd_rn(r, ca.y), d);
+    r = __dmul_rn(__dadd_rn(r, cb.x), d);
+    r = __dadd_rn(__dadd_rn(r, cb.y), lo);
     return far ? hi : r;
 }

@@ -622,6 +622,7 @@ struct FastK {
 
 template <int C>
 __global__ void __launch_bounds__(128) sa_fast_kernel(const FParams P) {
+    sa_logAdd_init();
     const int lane = threadIdx.x & 31;
     const int warp = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     double *ring = P.scratch + (int64_t) warp * P.rowsCap * FastK<C>::ROW;

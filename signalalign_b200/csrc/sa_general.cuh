@@ -505,6 +505,7 @@ __global__ void __launch_bounds__(128) sa_general_kernel(const GParams P) {
     __shared__ double sTotal;
     __shared__ int sWarp[8];
     __shared__ double sAcc[8][9];
+    sa_logAdd_init();
     for (;;) {
         __syncthreads();
         if (threadIdx.x == 0) sItem = atomicAdd(P.counter, 1);

@@ -793,6 +793,7 @@ extern "C" void sa_batch_free(sa_batch_t *b) { delete b; }
 // ---- test hook: the device logAdd on arrays (mirrors the reference's own logAdd unit test,
 // tests/signalPairwiseAlignerTest.c:115-125, but compared bit-for-bit against the oracle)
 __global__ void sa_logadd_kernel(const double *x, const double *y, double *o, int64_t n) {
+    sa_logAdd_init();
     int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) o[i] = sa_logAdd(x[i], y[i]);
 }
