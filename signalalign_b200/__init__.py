@@ -255,33 +255,44 @@ class Ambig:
 
 
 class Result:
-    """Owns an sa_result_t; exposes numpy copies."""
+    """Owns an sa_result_t; the arrays are zero-copy numpy views that stay valid while this object lives."""
 
     def __init__(self, ptr):
+        self._ptr = ptr
         r = ptr.contents
         n = r.nReads
         self.n_reads = n
         self.band_cells, self.path_cells, self.events = r.totalBandCells, r.totalPathCells, r.totalEvents
-        self.pair_offsets = np.ctypeslib.as_array(r.pairOffsets, shape=(n + 1,)).copy()
+        self.pair_offsets = np.ctypeslib.as_array(r.pairOffsets, shape=(n + 1,))
         total = int(self.pair_offsets[-1])
-        self.pairs = np.zeros((total, 4), np.int32)
         if total and r.pairs:
-            C.memmove(self.pairs.ctypes.data, r.pairs, total * 16)
+            self.pairs = np.ctypeslib.as_array(C.cast(r.pairs, c_i32p), shape=(total, 4))
+        else:
+            self.pairs = np.zeros((0, 4), np.int32)
         self.transitions = self.likelihood = None
         self.assign_offsets = self.assign_kmer_pos = self.assign_event = None
         if r.transitions:
-            self.transitions = np.ctypeslib.as_array(r.transitions, shape=(n, 9)).copy() if n else np.zeros((0, 9))
-            self.likelihood = np.ctypeslib.as_array(r.likelihood, shape=(n,)).copy() if n else np.zeros(0)
+            self.transitions = np.ctypeslib.as_array(r.transitions, shape=(n, 9)) if n else np.zeros((0, 9))
+            self.likelihood = np.ctypeslib.as_array(r.likelihood, shape=(n,)) if n else np.zeros(0)
         if r.assignOffsets:
-            self.assign_offsets = np.ctypeslib.as_array(r.assignOffsets, shape=(n + 1,)).copy()
+            self.assign_offsets = np.ctypeslib.as_array(r.assignOffsets, shape=(n + 1,))
             ta = int(self.assign_offsets[-1])
-            self.assign_kmer_pos = np.ctypeslib.as_array(r.assignKmerPos, shape=(max(ta, 1),))[:ta].copy()
-            self.assign_event = np.ctypeslib.as_array(r.assignEvent, shape=(max(ta, 1),))[:ta].copy()
-        lib().sa_result_free(ptr)
+            self.assign_kmer_pos = np.ctypeslib.as_array(r.assignKmerPos, shape=(max(ta, 1),))[:ta]
+            self.assign_event = np.ctypeslib.as_array(r.assignEvent, shape=(max(ta, 1),))[:ta]
 
     def read_pairs(self, i):
         """pairs of read i as int32 [n, 4] = (floor(p*1e7), x, y, kmerIdx) in the reference's list order"""
         return self.pairs[self.pair_offsets[i]:self.pair_offsets[i + 1]]
+
+    def __del__(self):
+        try:
+            if self._ptr is not None:
+                self.pairs = self.pair_offsets = self.transitions = self.likelihood = None
+                self.assign_offsets = self.assign_kmer_pos = self.assign_event = None
+                lib().sa_result_free(self._ptr)
+                self._ptr = None
+        except Exception:
+            pass
 
 
 def align_batch(model, reads, params=None, ambig=None):

@@ -114,6 +114,73 @@ extern "C" int sa_gpu_init(int device) {
 }
 
 // ------------------------------------------------------------------------------------------------ batch
+#include <chrono>
+struct PhaseTimer {  // SA_TIMING=1 prints host-side phase times to stderr
+    bool on;
+    const char *what;
+    std::chrono::steady_clock::time_point t0;
+    explicit PhaseTimer(const char *w) : on(getenv("SA_TIMING") != nullptr), what(w), t0(std::chrono::steady_clock::now()) {}
+    void lap(const char *name) {
+        if (!on) return;
+        auto t1 = std::chrono::steady_clock::now();
+        fprintf(stderr, "[sa timing] %s / %s: %.1f ms\n", what, name, std::chrono::duration<double, std::milli>(t1 - t0).count());
+        t0 = t1;
+    }
+};
+
+// page-locked staging memory, cached for the life of the process (pinning is far slower than the copies it serves)
+#include <mutex>
+struct PinnedSlot { void *p = nullptr; size_t cap = 0; bool busy = false; };
+static std::mutex g_pinMu;
+static std::vector<PinnedSlot> g_pins;
+static void *pinAcquire(size_t bytes) {
+    std::lock_guard<std::mutex> lk(g_pinMu);
+    int best = -1, idle = -1;
+    for (int i = 0; i < (int) g_pins.size(); i++) {
+        if (g_pins[i].busy) continue;
+        idle = i;
+        if (g_pins[i].cap >= bytes && (best < 0 || g_pins[i].cap < g_pins[best].cap)) best = i;
+    }
+    if (best < 0) {
+        if (idle < 0) { g_pins.push_back(PinnedSlot()); idle = (int) g_pins.size() - 1; }
+        PinnedSlot &sl = g_pins[idle];
+        if (sl.p) cudaFreeHost(sl.p);
+        sl.p = nullptr; sl.cap = 0;
+        size_t cap = bytes + bytes / 4 + 4096;
+        if (cudaHostAlloc(&sl.p, cap, cudaHostAllocDefault) != cudaSuccess) { sl.p = nullptr; return nullptr; }
+        sl.cap = cap;
+        best = idle;
+    }
+    g_pins[best].busy = true;
+    return g_pins[best].p;
+}
+static void pinRelease(void *p) {
+    if (!p) return;
+    std::lock_guard<std::mutex> lk(g_pinMu);
+    for (auto &sl : g_pins)
+        if (sl.p == p) sl.busy = false;
+}
+template <class T>
+struct PinVec {  // the few vector operations the packer needs, over pinned memory
+    T *p = nullptr;
+    size_t n = 0;
+    bool resize(size_t count) {
+        pinRelease(p);
+        p = nullptr;
+        n = count;
+        if (count == 0) return true;
+        p = (T *) pinAcquire(count * sizeof(T));
+        return p != nullptr;
+    }
+    T *data() { return p; }
+    const T *data() const { return p; }
+    size_t size() const { return n; }
+    bool empty() const { return n == 0; }
+    T &operator[](size_t i) { return p[i]; }
+    const T &operator[](size_t i) const { return p[i]; }
+    ~PinVec() { pinRelease(p); }
+};
+
 template <class T>
 struct DevBuf {
     T *p = nullptr;
@@ -126,6 +193,15 @@ struct DevBuf {
         return SA_OK;
     }
     int upload(const std::vector<T> &v, cudaStream_t s, int64_t *bytes) {
+        int rc = alloc(v.size());
+        if (rc) return rc;
+        if (!v.empty()) {
+            CK(cudaMemcpyAsync(p, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice, s));
+            if (bytes) *bytes += (int64_t) (v.size() * sizeof(T));
+        }
+        return SA_OK;
+    }
+    int upload(const PinVec<T> &v, cudaStream_t s, int64_t *bytes) {
         int rc = alloc(v.size());
         if (rc) return rc;
         if (!v.empty()) {
@@ -255,11 +331,9 @@ extern "C" int sa_batch_prepare(const sa_model_t *m, const sa_read_t *reads, int
 
     const bool needNoise = m->kind == SA_EMIT_GAUSS_NOISE_SCALED || m->kind == SA_EMIT_GAUSS_NOISE_DESCALE;
     const bool fastModel = modelFastEligible(m) && !b->expectations && getenv("SA_FORCE_GENERAL") == nullptr;
-    std::vector<int32_t> pathOff, pathKmer, anchors32;
-    std::vector<double> evMean, evNoise, evLogNoise;
+    PinVec<int32_t> pathOff, pathKmer, anchors32;
+    PinVec<double> evMean, evNoise, evLogNoise;
     std::vector<ItemRec> &items = b->items;
-    std::vector<int64_t> split;
-    std::vector<int32_t> paths;
 
     // alphabet / ambiguity classification per character for the rolling kmer index
     int charCode[256];
@@ -270,97 +344,171 @@ extern "C" int sa_batch_prepare(const sa_model_t *m, const sa_read_t *reads, int
         charAmbig[c] = ambig->opts[c][0] != 0;
     }
 
+    PhaseTimer timer("prepare");
     // ------------------------------------------------------------------ pass 1: split, events, kmer paths, anchors
-    for (int64_t r = 0; r < nReads; r++) {
-        const sa_read_t &R = reads[r];
-        int64_t lXt = R.targetLength > 0 ? R.targetLength - (m->k - 1) : 0;  // sequence_correctSeqLength (:523-538)
-        if (lXt < 0) lXt = 0;
-        int64_t lYt = R.nEvents;
-        if (lXt > 0x3fffffff || lYt > 0x3fffffff) {
-            sa_set_error("read %lld: sequences longer than 2^30 are not supported", (long long) r);
-            return SA_ERR_INPUT;
-        }
-        for (int64_t i = 0; i < R.nAnchors; i++) {
-            int64_t ax = R.anchors[2 * i], ay = R.anchors[2 * i + 1];
-            bool ok = ax >= 0 && ay >= 0 && ax < lXt && ay < lYt;
-            if (ok && i > 0) ok = ax > R.anchors[2 * i - 2] && ay > R.anchors[2 * i - 1];
-            if (!ok) {
-                sa_set_error("read %lld: anchor %lld (%lld, %lld) out of range or not strictly increasing "
-                             "(asserted by band_construct, pairwiseAligner.c:226-231)",
+    // phase A (parallel over reads): validate anchors, split into regions, count paths -> per-read item lists
+    std::vector<std::vector<ItemRec>> perRead((size_t) nReads);
+    std::string firstError;
+    const int64_t suffixK = m->K / m->A;
+#pragma omp parallel
+    {
+        std::vector<int64_t> splitL;
+#pragma omp for schedule(dynamic, 16)
+        for (int64_t r = 0; r < nReads; r++) {
+            const sa_read_t &R = reads[r];
+            int64_t lXt = R.targetLength > 0 ? R.targetLength - (m->k - 1) : 0;  // sequence_correctSeqLength (:523-538)
+            if (lXt < 0) lXt = 0;
+            int64_t lYt = R.nEvents;
+            char err[512];
+            err[0] = 0;
+            if (lXt > 0x3fffffff || lYt > 0x3fffffff)
+                snprintf(err, sizeof(err), "read %lld: sequences longer than 2^30 are not supported", (long long) r);
+            for (int64_t i = 0; i < R.nAnchors && !err[0]; i++) {
+                int64_t ax = R.anchors[2 * i], ay = R.anchors[2 * i + 1];
+                bool ok = ax >= 0 && ay >= 0 && ax < lXt && ay < lYt;
+                if (ok && i > 0) ok = ax > R.anchors[2 * i - 2] && ay > R.anchors[2 * i - 1];
+                if (!ok)
+                    snprintf(err, sizeof(err), "read %lld: anchor %lld (%lld, %lld) out of range or not strictly "
+                             "increasing (asserted by band_construct, pairwiseAligner.c:226-231)",
                              (long long) r, (long long) i, (long long) ax, (long long) ay);
-                return SA_ERR_INPUT;
+            }
+            // every character of the target must be in the alphabet or an ambiguity code whose options are
+            for (int64_t i = 0; i < R.targetLength && lXt > 0 && !err[0]; i++) {
+                unsigned char ch = (unsigned char) R.target[i];
+                bool ok = charCode[ch] >= 0 && !charAmbig[ch];
+                if (!ok && charAmbig[ch]) {
+                    ok = true;
+                    for (const char *o = ambig->opts[ch]; *o; o++) ok = ok && charCode[(unsigned char) *o] >= 0;
+                }
+                if (!ok)
+                    snprintf(err, sizeof(err), "read %lld: kmer at reference position %lld contains a character "
+                             "outside the alphabet %s (the reference exits in kmer_to_word, nanopore_hdp.c:393-398)",
+                             (long long) r, (long long) std::max<int64_t>(0, i - (m->k - 1)), m->alphabet.c_str());
+            }
+            if (err[0]) {
+#pragma omp critical
+                if (firstError.empty()) firstError = err;
+                continue;
+            }
+            sa_split_points(R.anchors, R.nAnchors, lXt, lYt, p->splitMatrixBiggerThanThis, R.raggedLeft != 0,
+                            R.raggedRight != 0, splitL);
+            int64_t nSplit = (int64_t) splitL.size() / 4, j = 0;
+            for (int64_t sI = 0; sI < nSplit; sI++) {
+                int64_t x1 = splitL[4 * sI], y1 = splitL[4 * sI + 1], x2 = splitL[4 * sI + 2], y2 = splitL[4 * sI + 3];
+                ItemRec it;
+                it.read = r; it.x1 = x1; it.y1 = y1; it.lX = x2 - x1; it.lY = y2 - y1; it.region = (int32_t) sI;
+                bool rl = R.raggedLeft || sI > 0, rr = R.raggedRight || sI < nSplit - 1;  // :2001-2002
+                it.flags = (rl ? 1 : 0) | (rr ? 2 : 0);
+                it.scale = R.scale; it.shift = R.shift; it.var = R.var;
+                it.anchorOff = j;   // for now: first anchor of the region inside the read's list
+                while (j < R.nAnchors && R.anchors[2 * j] + R.anchors[2 * j + 1] < x2 + y2) j++;  // :1984-1997
+                it.nAnchors = j - it.anchorOff;
+                // number of paths of the region: 1 (NULL kmer column) + prod of option counts per column
+                int64_t nPaths = 1, maxP = 1;
+                int nAmbInWin = 0;
+                const char *tg = R.target + x1;
+                for (int q = 0; q < m->k - 1 && q < R.targetLength - x1; q++) nAmbInWin += charAmbig[(unsigned char) tg[q]];
+                for (int64_t x = 1; x <= it.lX; x++) {
+                    nAmbInWin += charAmbig[(unsigned char) tg[x - 1 + m->k - 1]];
+                    int64_t pc = 1;
+                    if (nAmbInWin)
+                        for (int q = 0; q < m->k; q++) {
+                            unsigned char ch = (unsigned char) tg[x - 1 + q];
+                            if (charAmbig[ch]) pc *= (int64_t) strlen(ambig->opts[ch]);
+                        }
+                    nPaths += pc;
+                    maxP = std::max(maxP, pc);
+                    nAmbInWin -= charAmbig[(unsigned char) tg[x - 1]];
+                }
+                it.maxP = maxP;
+                it.work = nPaths;  // temporarily: number of paths (re-used as the pathKmer size below)
+                perRead[r].push_back(it);
             }
         }
-        sa_split_points(R.anchors, R.nAnchors, lXt, lYt, p->splitMatrixBiggerThanThis, R.raggedLeft != 0,
-                        R.raggedRight != 0, split);
-        int64_t nSplit = (int64_t) split.size() / 4, j = 0;
-        for (int64_t s = 0; s < nSplit; s++) {
-            int64_t x1 = split[4 * s], y1 = split[4 * s + 1], x2 = split[4 * s + 2], y2 = split[4 * s + 3];
-            ItemRec it;
-            it.read = r; it.x1 = x1; it.y1 = y1; it.lX = x2 - x1; it.lY = y2 - y1; it.region = (int32_t) s;
-            bool rl = R.raggedLeft || s > 0, rr = R.raggedRight || s < nSplit - 1;  // :2001-2002
-            it.flags = (rl ? 1 : 0) | (rr ? 2 : 0);
-            it.scale = R.scale; it.shift = R.shift; it.var = R.var;
-            it.anchorOff = (int64_t) anchors32.size() / 2;
-            while (j < R.nAnchors) {  // pairwiseAligner.c:1984-1997
-                int64_t ax = R.anchors[2 * j], ay = R.anchors[2 * j + 1];
-                if (ax + ay >= x2 + y2) break;
-                anchors32.push_back((int32_t) (ax - x1));
-                anchors32.push_back((int32_t) (ay - y1));
-                j++;
+    }
+    if (!firstError.empty()) {
+        sa_set_error("%s", firstError.c_str());
+        return SA_ERR_INPUT;
+    }
+    // offsets
+    int64_t evTot = 0, poTot = 0, pkTot = 0, anTot = 0;
+    for (int64_t r = 0; r < nReads; r++)
+        for (auto &it : perRead[r]) {
+            int64_t inRead = it.anchorOff;
+            it.evOff = evTot; evTot += it.lY;
+            it.pathOffOff = poTot; poTot += it.lX + 2;
+            it.pathKmerOff = pkTot; pkTot += it.work;
+            it.anchorOff = anTot; anTot += it.nAnchors;
+            it.work = inRead;  // remember where the region's anchors start in the read's list for phase B
+            b->events += it.lY;
+            items.push_back(it);
+        }
+    if (pkTot > 0x7fffffff || poTot > 0x7fffffff) {
+        sa_set_error("sa_batch_prepare: batch too large (more than 2^31 kmer paths); split it");
+        return SA_ERR_INPUT;
+    }
+    bool pinOk = evMean.resize(evTot) && pathOff.resize(poTot) && pathKmer.resize(pkTot) && anchors32.resize(anTot * 2);
+    if (needNoise) pinOk = pinOk && evNoise.resize(evTot) && evLogNoise.resize(evTot);
+    if (!pinOk) {
+        sa_set_error("sa_batch_prepare: cannot allocate pinned staging memory");
+        return SA_ERR_CUDA;
+    }
+    // phase B (parallel over items): fill the packed arrays
+#pragma omp parallel
+    {
+        std::vector<int32_t> pathsL;
+#pragma omp for schedule(dynamic, 8)
+        for (int64_t i = 0; i < (int64_t) items.size(); i++) {
+            ItemRec &it = items[i];
+            const sa_read_t &R = reads[it.read];
+            const int64_t a0 = it.work;
+            it.work = 0;
+            for (int64_t q = 0; q < it.nAnchors; q++) {
+                anchors32[2 * (it.anchorOff + q)] = (int32_t) (R.anchors[2 * (a0 + q)] - it.x1);
+                anchors32[2 * (it.anchorOff + q) + 1] = (int32_t) (R.anchors[2 * (a0 + q) + 1] - it.y1);
             }
-            it.nAnchors = (int64_t) anchors32.size() / 2 - it.anchorOff;
-            it.evOff = (int64_t) evMean.size();
-            for (int64_t y = 0; y < it.lY; y++) {
-                const double *e = R.events + (y1 + y) * 4;
-                evMean.push_back(e[0]);
-                if (needNoise) {
-                    double noise = e[1];
-                    evNoise.push_back(noise);
+            const double *e = R.events + it.y1 * 4;
+            double *em = evMean.data() + it.evOff;
+            for (int64_t y = 0; y < it.lY; y++) em[y] = e[4 * y];
+            if (needNoise)
+                for (int64_t y = 0; y < it.lY; y++) {
+                    double noise = e[4 * y + 1];
+                    evNoise[it.evOff + y] = noise;
                     if (m->kind == SA_EMIT_GAUSS_NOISE_DESCALE && noise == 0) noise = 0.000000001;
-                    evLogNoise.push_back(log(noise));
+                    evLogNoise[it.evOff + y] = log(noise);
                 }
-            }
             // kmer paths per matrix column (column 0 = NULL kmer)
-            it.pathOffOff = (int64_t) pathOff.size();
-            it.pathKmerOff = (int64_t) pathKmer.size();
-            int64_t base = (int64_t) pathKmer.size();
-            pathOff.push_back(0);
-            pathKmer.push_back(-1);
-            pathOff.push_back(1);
-            int64_t roll = -1, maxP = 1;
+            int32_t *po = pathOff.data() + it.pathOffOff;
+            int32_t *pk = pathKmer.data() + it.pathKmerOff;
+            int64_t w = 0;
+            po[0] = 0;
+            pk[w++] = -1;
+            po[1] = 1;
+            int64_t roll = -1;
+            const char *tg = R.target + it.x1;
+            int nAmbInWin = 0;
+            for (int q = 0; q < m->k - 1 && q < R.targetLength - it.x1; q++) nAmbInWin += charAmbig[(unsigned char) tg[q]];
             for (int64_t x = 1; x <= it.lX; x++) {
-                const char *km = R.target + x1 + x - 1;
-                bool simple = true;
-                for (int q = 0; q < m->k; q++) {
-                    unsigned char ch = (unsigned char) km[q];
-                    if (charAmbig[ch] || charCode[ch] < 0) { simple = false; break; }
-                }
-                if (simple) {
-                    if (roll >= 0) roll = (roll % (m->K / m->A)) * m->A + charCode[(unsigned char) km[m->k - 1]];
+                const char *km = tg + x - 1;
+                nAmbInWin += charAmbig[(unsigned char) km[m->k - 1]];
+                if (nAmbInWin == 0) {
+                    if (roll >= 0) roll = (roll % suffixK) * m->A + charCode[(unsigned char) km[m->k - 1]];
                     else {
                         roll = 0;
                         for (int q = 0; q < m->k; q++) roll = roll * m->A + charCode[(unsigned char) km[q]];
                     }
-                    pathKmer.push_back((int32_t) roll);
+                    pk[w++] = (int32_t) roll;
                 } else {
                     roll = -1;
-                    if (!sa_kmer_paths(km, *m, *ambig, paths)) {
-                        sa_set_error("read %lld: kmer at reference position %lld contains a character outside the "
-                                     "alphabet %s (the reference exits in kmer_to_word, nanopore_hdp.c:393-398)",
-                                     (long long) r, (long long) (x1 + x - 1), m->alphabet.c_str());
-                        return SA_ERR_INPUT;
-                    }
-                    pathKmer.insert(pathKmer.end(), paths.begin(), paths.end());
-                    maxP = std::max<int64_t>(maxP, (int64_t) paths.size());
+                    sa_kmer_paths(km, *m, *ambig, pathsL);  // characters were validated in phase A
+                    for (int32_t v : pathsL) pk[w++] = v;
                 }
-                pathOff.push_back((int32_t) ((int64_t) pathKmer.size() - base));
+                po[x + 1] = (int32_t) w;
+                nAmbInWin -= charAmbig[(unsigned char) km[0]];
             }
-            it.maxP = maxP;
-            b->events += it.lY;
-            items.push_back(it);
         }
     }
+    timer.lap("pass1 pack (split, events, kmers, anchors)");
     const int64_t n = (int64_t) items.size();
     if (n > 0x7fffffff) {
         sa_set_error("sa_batch_prepare: too many work items");
@@ -396,6 +544,8 @@ extern "C" int sa_batch_prepare(const sa_model_t *m, const sa_read_t *reads, int
     int dev, nSM = 148;
     CK(cudaGetDevice(&dev));
     CK(cudaDeviceGetAttribute(&nSM, cudaDevAttrMultiProcessorCount, dev));
+    CK(cudaStreamSynchronize(st));
+    timer.lap("uploads + output allocation");
 
     // ------------------------------------------------------------------ pass 2: fast-kernel candidates + geometry
     FParams &f = b->fp;
@@ -476,6 +626,7 @@ extern "C" int sa_batch_prepare(const sa_model_t *m, const sa_read_t *reads, int
         b->fRows4 = rows4;
     }
 
+    timer.lap("geometry pass + fast-kernel scratch");
     // ------------------------------------------------------------------ pass 3: general kernel for the rest
     std::vector<int32_t> bandL, bandW;
     std::vector<int64_t> bandOff;
@@ -563,6 +714,7 @@ extern "C" int sa_batch_prepare(const sa_model_t *m, const sa_read_t *reads, int
         g.assignK = b->dAssignK.p; g.assignE = b->dAssignE.p; g.assignCount = b->expectations ? b->dAssignCount.p : nullptr;
     }
     CK(cudaStreamSynchronize(st));
+    timer.lap("general-kernel packing");
     *out = b.release();
     return SA_OK;
 }
@@ -605,6 +757,20 @@ extern "C" int sa_batch_run(sa_batch_t *b) {
     CK(cudaEventElapsedTime(&b->lastMs[1], b->ev[1], b->ev[2]));
     CK(cudaEventElapsedTime(&b->lastMs[2], b->ev[2], b->ev[3]));
     return SA_OK;
+}
+
+// meta per item: source offset, destination offset, count, (x1 << 32 | y1)
+__global__ void sa_compact_pairs_kernel(const sa_pair_t *src, sa_pair_t *dst, const int64_t *meta, int64_t nItems) {
+    for (int64_t it = blockIdx.x; it < nItems; it += gridDim.x) {
+        const int64_t so = meta[4 * it], dO = meta[4 * it + 1], cnt = meta[4 * it + 2], sh = meta[4 * it + 3];
+        const int32_t x1 = (int32_t) (sh >> 32), y1 = (int32_t) (sh & 0xffffffffLL);
+        for (int64_t q = threadIdx.x; q < cnt; q += blockDim.x) {
+            sa_pair_t pr = src[so + cnt - 1 - q];
+            pr.x += x1;
+            pr.y += y1;
+            dst[dO + q] = pr;
+        }
+    }
 }
 
 static int growAndRerun(sa_batch_t *b) {
@@ -653,6 +819,7 @@ static int growAndRerun(sa_batch_t *b) {
 
 extern "C" int sa_batch_fetch(sa_batch_t *b, sa_result_t **out) {
     *out = nullptr;
+    PhaseTimer timer("fetch");
     int64_t n = (int64_t) b->items.size();
     cudaStream_t st = b->stream;
     b->d2hBytes = 0;
@@ -689,45 +856,48 @@ extern "C" int sa_batch_fetch(sa_batch_t *b, sa_result_t **out) {
     // items are created read by read, region by region: already in (read, region) order
     r->pairOffsets = (int64_t *) calloc(b->nReads + 1, sizeof(int64_t));
     if (!b->expectations) {
-        int64_t totalCap = 0, total = 0;
-        for (int64_t i = 0; i < n; i++) {
-            totalCap = std::max(totalCap, b->items[i].pairOff + b->items[i].pairCap);
-            total += b->pairCountHost[i];
-        }
-        // pairs come back slot by slot (used prefix only) into one pinned-size host buffer
-        std::vector<sa_pair_t> raw((size_t) std::max<int64_t>(1, totalCap));
-        if (totalCap > 0) {
-            // slots are ~3x over-provisioned: copy the used prefixes when that is clearly less traffic
-            if (total * 2 < totalCap && n <= 4096) {
-                for (int64_t i = 0; i < n; i++)
-                    if (b->pairCountHost[i] > 0) {
-                        CK(cudaMemcpyAsync(raw.data() + b->items[i].pairOff, b->dPairs.p + b->items[i].pairOff,
-                                           sizeof(sa_pair_t) * b->pairCountHost[i], cudaMemcpyDeviceToHost, st));
-                        b->d2hBytes += sizeof(sa_pair_t) * b->pairCountHost[i];
-                    }
-            } else {
-                CK(cudaMemcpyAsync(raw.data(), b->dPairs.p, sizeof(sa_pair_t) * totalCap, cudaMemcpyDeviceToHost, st));
-                b->d2hBytes += sizeof(sa_pair_t) * totalCap;
-            }
-            CK(cudaStreamSynchronize(st));
-        }
-        r->pairs = (sa_pair_t *) malloc(sizeof(sa_pair_t) * std::max<int64_t>(1, total));
-        int64_t w = 0, i = 0;
+        // the per-item slots are over-provisioned; a gather kernel packs the used prefixes into the final layout
+        // (items in (read, region) order, each region's list popped from its END and shifted to read coordinates:
+        // alignedPairCoordinateCorrectionFn, pairwiseAligner.c:2043-2050), so one dense D2H is the result.
+        int64_t total = 0;
+        std::vector<int64_t> meta((size_t) std::max<int64_t>(1, n) * 4);
+        int64_t i = 0;
         for (int64_t rd = 0; rd < b->nReads; rd++) {
-            r->pairOffsets[rd] = w;
+            r->pairOffsets[rd] = total;
             for (; i < n && b->items[i].read == rd; i++) {
-                const ItemRec &it = b->items[i];
-                // alignedPairCoordinateCorrectionFn (pairwiseAligner.c:2043-2050): shift to read coordinates and
-                // pop the region's list from its END
-                for (int64_t q = b->pairCountHost[i] - 1; q >= 0; q--) {
-                    sa_pair_t pr = raw[it.pairOff + q];
-                    pr.x += (int32_t) it.x1;
-                    pr.y += (int32_t) it.y1;
-                    r->pairs[w++] = pr;
-                }
+                meta[4 * i] = b->items[i].pairOff;
+                meta[4 * i + 1] = total;
+                meta[4 * i + 2] = b->pairCountHost[i];
+                meta[4 * i + 3] = (b->items[i].x1 << 32) | (b->items[i].y1 & 0xffffffffLL);
+                total += b->pairCountHost[i];
             }
         }
-        r->pairOffsets[b->nReads] = w;
+        r->pairOffsets[b->nReads] = total;
+        r->pairs = (sa_pair_t *) malloc(sizeof(sa_pair_t) * std::max<int64_t>(1, total));
+        if (total > 0) {
+            DevBuf<int64_t> dMeta;
+            DevBuf<sa_pair_t> dDense;
+            int rc;
+            if ((rc = dMeta.upload(meta, st, &b->h2dBytes))) return rc;
+            if ((rc = dDense.alloc(total))) return rc;
+            sa_compact_pairs_kernel<<<(unsigned) std::min<int64_t>(n, 148 * 16), 256, 0, st>>>(b->dPairs.p, dDense.p, dMeta.p, n);
+            CK(cudaGetLastError());
+            sa_pair_t *stage = (sa_pair_t *) pinAcquire(sizeof(sa_pair_t) * total);
+            if (!stage) {
+                sa_set_error("sa_batch_fetch: cannot allocate pinned staging memory");
+                return SA_ERR_CUDA;
+            }
+            CK(cudaMemcpyAsync(stage, dDense.p, sizeof(sa_pair_t) * total, cudaMemcpyDeviceToHost, st));
+            CK(cudaStreamSynchronize(st));
+            b->d2hBytes += sizeof(sa_pair_t) * total;
+            timer.lap("compact + D2H pairs");
+            const int64_t chunk = 1 << 20;
+#pragma omp parallel for schedule(static)
+            for (int64_t c = 0; c < (total + chunk - 1) / chunk; c++)
+                memcpy(r->pairs + c * chunk, stage + c * chunk, sizeof(sa_pair_t) * std::min(chunk, total - c * chunk));
+            pinRelease(stage);
+        }
+        timer.lap("assemble result");
     } else {
         std::vector<double> e((size_t) std::max<int64_t>(1, n * 10));
         if (n > 0) {
