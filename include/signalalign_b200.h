@@ -46,9 +46,11 @@ sa_model_t *sa_model_load(const char *modelFile, const char *nhdpFile, int emiss
 sa_model_t *sa_model_from_tables(const char *alphabet, int32_t kmerLength, const double *logTransitions,
                                  const double *matchTable, const double *gapYTable, const double *gapXTable,
                                  int emissionKind);
-/* attach HDP spline tables (kmerToRow: K entries, parent walk of dir_proc_density already resolved) */
+/* attach HDP spline tables.  kmerToRow: K entries, the parent walk of dir_proc_density (impl/hdp.c:2588-2612) already
+ * resolved; ownRow: K entries, the row of the kmer's OWN Dirichlet process when it is observed, else -1 (decides which
+ * kmers stateMachine3_setModelToHdpExpectedValues replaces); NULL = every kmer's own DP is observed */
 int sa_model_set_hdp(sa_model_t *m, int64_t gridLength, const double *grid, const int32_t *kmerToRow,
-                     int64_t nRows, const double *postPred, const double *slopes);
+                     const int32_t *ownRow, int64_t nRows, const double *postPred, const double *slopes);
 int sa_model_set_hdp_expected_values(sa_model_t *m);
 /* emissions_signal_scaleNoise (impl/stateMachine.c:721-741) / emissions_signal_scaleModel (:743-779) */
 int sa_model_scale_noise(sa_model_t *m, double scale_sd, double var_sd);
@@ -62,6 +64,11 @@ const char *sa_model_alphabet(const sa_model_t *m);               /* sorted */
 void sa_model_get_tables(const sa_model_t *m, double *logTransitions9, double *matchTable, double *gapYTable);
 /* host evaluation of the .nhdp spline density the device uses (get_nanopore_kmer_density, nanopore_hdp.c:420) */
 double sa_model_hdp_density(const sa_model_t *m, int64_t kmerIdx, double x);
+/* the HDP spline tables as loaded from the .nhdp: dims[0] = grid length G, dims[1] = number of observed DPs (rows);
+ * any output pointer may be NULL.  grid: G, kmerToRow / ownRow: K, postPred / slopes: rows * G */
+void sa_model_hdp_dims(const sa_model_t *m, int64_t *dims2);
+void sa_model_get_hdp(const sa_model_t *m, double *grid, int32_t *kmerToRow, int32_t *ownRow, double *postPred,
+                      double *slopes);
 
 /* ---------------------------------------------------------------------------------------------- inputs
  * One sa_read_t = the arguments of one getAlignedPairsUsingAnchors call
@@ -158,6 +165,16 @@ void sa_batch_free(sa_batch_t *b);
 
 /* test hook: element-wise device logAdd (reference logAdd, impl/pairwiseAligner.c:314-318) */
 int sa_debug_logadd(const double *x, const double *y, double *out, int64_t n);
+
+/* test hooks for the host-side integer preparation (no device needed):
+ *   band_construct (impl/pairwiseAligner.c:195-246): out[3*i] = xay, xmyL, xmyR for i in [0, lX+lY]
+ *   getSplitPoints (impl/pairwiseAligner.c:1910-1937): out[4*i] = x1,y1,x2,y2; returns the number of regions
+ *   hdCell_construct2 path enumeration (impl/pairwiseAligner.c:723-801): concrete kmer indices of the k-window
+ *   starting at `kmer`, in the reference's path order; returns the number of paths or -1 (character outside the alphabet) */
+void sa_debug_band(const int64_t *anchors, int64_t nAnchors, int64_t lX, int64_t lY, int64_t expansion, int64_t *out);
+int64_t sa_debug_split_points(const int64_t *anchors, int64_t nAnchors, int64_t lX, int64_t lY, int64_t splitBigger,
+                              int raggedLeft, int raggedRight, int64_t *out, int64_t cap);
+int64_t sa_debug_kmer_paths(const sa_model_t *m, const sa_ambig_t *ambig, const char *kmer, int32_t *out, int64_t cap);
 
 /* expectation-table reduction across reads of one GPU (the per-GPU table NCCL then all-reduces):
  * out[0..8] = sum of transitions, out[9] = sum of likelihood */

@@ -205,9 +205,9 @@ class RefNpRead:
         self.read_length, self.template_read_length, _, self.n_template_events, _ = [int(v) for v in lens]
         self.template_params = dict(zip(["scale", "shift", "var", "shift_sd", "scale_sd", "var_sd", "drift"], tp))
         td = lib().ref_npread_twoD(self.h)
-        self.twoD_read = td.decode() if td else ""
+        self.twoD_read = td.decode(errors="replace") if td and self.read_length > 0 else ""
         tr = lib().ref_npread_template_read(self.h)
-        self.template_read = tr.decode() if tr else ""
+        self.template_read = tr.decode(errors="replace") if tr else ""
 
     def template_events(self):
         p = lib().ref_npread_template_events(self.h)

@@ -53,7 +53,8 @@ EXPORTS = [
     "sa_ambig_free", "sa_result_free", "sa_kmer_string", "sa_gpu_init", "sa_last_error", "sa_gpu_device_count",
     "sa_gpu_align_batch", "sa_gpu_expectations_batch", "sa_batch_prepare", "sa_batch_run", "sa_batch_fetch",
     "sa_batch_last_timing", "sa_batch_band_cells", "sa_batch_kernel_items", "sa_batch_h2d_bytes", "sa_batch_d2h_bytes", "sa_batch_free",
-    "sa_result_sum_expectations", "sa_debug_logadd",
+    "sa_result_sum_expectations", "sa_debug_logadd", "sa_model_hdp_dims", "sa_model_get_hdp", "sa_debug_band",
+    "sa_debug_split_points", "sa_debug_kmer_paths",
 ]
 
 _lib = None
@@ -80,7 +81,7 @@ def lib():
     L.sa_model_load.argtypes = [C.c_char_p, C.c_char_p, C.c_int]
     L.sa_model_from_tables.restype = C.c_void_p
     L.sa_model_from_tables.argtypes = [C.c_char_p, C.c_int32, c_f64p, c_f64p, c_f64p, c_f64p, C.c_int]
-    L.sa_model_set_hdp.argtypes = [C.c_void_p, C.c_int64, c_f64p, c_i32p, C.c_int64, c_f64p, c_f64p]
+    L.sa_model_set_hdp.argtypes = [C.c_void_p, C.c_int64, c_f64p, c_i32p, c_i32p, C.c_int64, c_f64p, c_f64p]
     L.sa_model_set_hdp_expected_values.argtypes = [C.c_void_p]
     L.sa_model_scale_noise.argtypes = [C.c_void_p, C.c_double, C.c_double]
     L.sa_model_scale_model.argtypes = [C.c_void_p] + [C.c_double] * 5
@@ -116,6 +117,14 @@ def lib():
     L.sa_batch_free.argtypes = [C.c_void_p]
     L.sa_result_sum_expectations.argtypes = [C.POINTER(SaResult), c_f64p]
     L.sa_debug_logadd.argtypes = [c_f64p, c_f64p, c_f64p, C.c_int64]
+    L.sa_model_hdp_dims.argtypes = [C.c_void_p, c_i64p]
+    L.sa_model_get_hdp.argtypes = [C.c_void_p, c_f64p, c_i32p, c_i32p, c_f64p, c_f64p]
+    L.sa_debug_band.argtypes = [c_i64p, C.c_int64, C.c_int64, C.c_int64, C.c_int64, c_i64p]
+    L.sa_debug_split_points.restype = C.c_int64
+    L.sa_debug_split_points.argtypes = [c_i64p, C.c_int64, C.c_int64, C.c_int64, C.c_int64, C.c_int, C.c_int, c_i64p,
+                                        C.c_int64]
+    L.sa_debug_kmer_paths.restype = C.c_int64
+    L.sa_debug_kmer_paths.argtypes = [C.c_void_p, C.c_void_p, C.c_char_p, c_i32p, C.c_int64]
     _lib = L
     return L
 
@@ -169,13 +178,14 @@ class Model:
         f = lambda a: None if a is None else a.ctypes.data_as(c_f64p)
         return cls(lib().sa_model_from_tables(alphabet.encode(), k, f(t), f(m), f(gy), f(gx), kind))
 
-    def set_hdp(self, grid, kmer_to_row, post_pred, slopes):
+    def set_hdp(self, grid, kmer_to_row, post_pred, slopes, own_row=None):
         grid = np.ascontiguousarray(grid, np.float64)
         k2r = np.ascontiguousarray(kmer_to_row, np.int32)
+        own = None if own_row is None else np.ascontiguousarray(own_row, np.int32)
         pp = np.ascontiguousarray(post_pred, np.float64)
         sl = np.ascontiguousarray(slopes, np.float64)
         _check(lib().sa_model_set_hdp(self.h, len(grid), grid.ctypes.data_as(c_f64p), k2r.ctypes.data_as(c_i32p),
-                                      pp.shape[0], pp.ctypes.data_as(c_f64p), sl.ctypes.data_as(c_f64p)))
+                                      None if own is None else own.ctypes.data_as(c_i32p), pp.shape[0], pp.ctypes.data_as(c_f64p), sl.ctypes.data_as(c_f64p)))
 
     def set_hdp_expected_values(self):
         _check(lib().sa_model_set_hdp_expected_values(self.h))
@@ -196,6 +206,28 @@ class Model:
 
     def hdp_density(self, kmer_idx, x):
         return lib().sa_model_hdp_density(self.h, kmer_idx, x)
+
+    def hdp_tables(self):
+        """(grid[G], kmer_to_row[K], post_pred[rows, G], slopes[rows, G], own_row[K]) as loaded from the .nhdp"""
+        dims = (C.c_int64 * 2)()
+        lib().sa_model_hdp_dims(self.h, dims)
+        G, rows = dims[0], dims[1]
+        grid = np.zeros(G)
+        k2r = np.zeros(self.K, np.int32)
+        own = np.zeros(self.K, np.int32)
+        pp = np.zeros((rows, G))
+        sl = np.zeros((rows, G))
+        lib().sa_model_get_hdp(self.h, grid.ctypes.data_as(c_f64p), k2r.ctypes.data_as(c_i32p),
+                               own.ctypes.data_as(c_i32p), pp.ctypes.data_as(c_f64p), sl.ctypes.data_as(c_f64p))
+        return grid, k2r, pp, sl, own
+
+    def kmer_paths(self, kmer, ambig=None, cap=4096):
+        """hdCell_construct2 path enumeration of one k-window (host-side; no device needed)"""
+        out = np.zeros(cap, np.int32)
+        n = lib().sa_debug_kmer_paths(self.h, ambig.h if ambig else None, kmer.encode(), out.ctypes.data_as(c_i32p), cap)
+        if n < 0:
+            raise SaError("kmer %r contains a character outside the alphabet %s" % (kmer, self.alphabet))
+        return out[:n].copy()
 
     def kmer_string(self, idx):
         buf = C.create_string_buffer(self.k + 1)
@@ -322,6 +354,24 @@ def debug_logadd(x, y):
     _check(lib().sa_debug_logadd(x.ctypes.data_as(c_f64p), y.ctypes.data_as(c_f64p), out.ctypes.data_as(c_f64p),
                                  x.size))
     return out
+
+
+def debug_band(anchors, lX, lY, expansion):
+    """band_construct on the host (reference impl/pairwiseAligner.c:195-246): int64[lX+lY+1, 3] = xay, xmyL, xmyR"""
+    a = np.ascontiguousarray(anchors, np.int64).reshape(-1, 2)
+    out = np.zeros((lX + lY + 1, 3), np.int64)
+    lib().sa_debug_band(a.ctypes.data_as(c_i64p), a.shape[0], lX, lY, expansion, out.ctypes.data_as(c_i64p))
+    return out
+
+
+def debug_split_points(anchors, lX, lY, split_bigger, ragged_left, ragged_right):
+    """getSplitPoints on the host (reference impl/pairwiseAligner.c:1910-1937): int64[n, 4] = x1, y1, x2, y2"""
+    a = np.ascontiguousarray(anchors, np.int64).reshape(-1, 2)
+    cap = a.shape[0] + 4
+    out = np.zeros((cap, 4), np.int64)
+    n = lib().sa_debug_split_points(a.ctypes.data_as(c_i64p), a.shape[0], lX, lY, split_bigger, int(ragged_left),
+                                    int(ragged_right), out.ctypes.data_as(c_i64p), cap)
+    return out[:n].copy()
 
 
 class Batch:

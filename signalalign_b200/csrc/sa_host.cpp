@@ -422,13 +422,14 @@ static bool loadNhdp(sa_model *m, const char *path) {
     return true;
 }
 
-extern "C" int sa_model_set_hdp(sa_model_t *m, int64_t G, const double *grid, const int32_t *kmerToRow, int64_t nRows,
-                                const double *postPred, const double *slopes) {
+extern "C" int sa_model_set_hdp(sa_model_t *m, int64_t G, const double *grid, const int32_t *kmerToRow,
+                                const int32_t *ownRow, int64_t nRows, const double *postPred, const double *slopes) {
     m->kind = SA_EMIT_HDP;
     m->G = G;
     m->grid.assign(grid, grid + G);
     m->kmerToRow.assign(kmerToRow, kmerToRow + m->K);
-    m->ownRow = m->kmerToRow;
+    if (ownRow) m->ownRow.assign(ownRow, ownRow + m->K);
+    else m->ownRow = m->kmerToRow;
     m->nRows = nRows;
     m->postPred.assign(postPred, postPred + nRows * G);
     m->slopes.assign(slopes, slopes + nRows * G);
@@ -539,4 +540,47 @@ extern "C" void sa_result_sum_expectations(const sa_result_t *r, double *out10) 
         for (int j = 0; j < 9; j++) out10[j] += r->transitions[i * 9 + j];
         out10[9] += r->likelihood[i];
     }
+}
+
+extern "C" void sa_model_hdp_dims(const sa_model_t *m, int64_t *dims2) {
+    dims2[0] = m->G;
+    dims2[1] = m->nRows;
+}
+extern "C" void sa_model_get_hdp(const sa_model_t *m, double *grid, int32_t *kmerToRow, int32_t *ownRow, double *postPred,
+                                 double *slopes) {
+    if (ownRow) memcpy(ownRow, m->ownRow.data(), sizeof(int32_t) * m->ownRow.size());
+    if (grid) memcpy(grid, m->grid.data(), sizeof(double) * m->grid.size());
+    if (kmerToRow) memcpy(kmerToRow, m->kmerToRow.data(), sizeof(int32_t) * m->kmerToRow.size());
+    if (postPred) memcpy(postPred, m->postPred.data(), sizeof(double) * m->postPred.size());
+    if (slopes) memcpy(slopes, m->slopes.data(), sizeof(double) * m->slopes.size());
+}
+
+// ------------------------------------------------------------------------------------------------ test hooks
+extern "C" void sa_debug_band(const int64_t *anchors, int64_t nA, int64_t lX, int64_t lY, int64_t e, int64_t *out) {
+    std::vector<Diag> band;
+    sa_build_band(anchors, nA, lX, lY, e, band);
+    for (size_t i = 0; i < band.size(); i++) {
+        out[3 * i] = band[i].xay; out[3 * i + 1] = band[i].xmyL; out[3 * i + 2] = band[i].xmyR;
+    }
+}
+extern "C" int64_t sa_debug_split_points(const int64_t *anchors, int64_t nA, int64_t lX, int64_t lY, int64_t bigger,
+                                         int rl, int rr, int64_t *out, int64_t cap) {
+    std::vector<int64_t> sp;
+    sa_split_points(anchors, nA, lX, lY, bigger, rl != 0, rr != 0, sp);
+    int64_t n = (int64_t) sp.size() / 4;
+    for (int64_t i = 0; i < n && i < cap; i++)
+        for (int j = 0; j < 4; j++) out[4 * i + j] = sp[4 * i + j];
+    return n;
+}
+extern "C" int64_t sa_debug_kmer_paths(const sa_model_t *m, const sa_ambig_t *ambig, const char *kmer, int32_t *out,
+                                       int64_t cap) {
+    sa_ambig def;
+    if (!ambig) {
+        sa_ambig_default_table(def);
+        ambig = &def;
+    }
+    std::vector<int32_t> paths;
+    if (!sa_kmer_paths(kmer, *m, *ambig, paths)) return -1;
+    for (int64_t i = 0; i < (int64_t) paths.size() && i < cap; i++) out[i] = paths[i];
+    return (int64_t) paths.size();
 }
