@@ -227,14 +227,18 @@ def expectations(model, target, events, anchors, p=None, ragged_left=True, ragge
     lX = len(target) - (model.k - 1)
     m = model.cstruct()
     amb = ambig or make_ambig()
-    tr = np.full(9, pseudo_t)
-    lik = np.zeros(1)
     cap = 8 * (lX + lY) + 1024
-    ak = np.zeros(cap, np.int64)
-    ae = np.zeros(cap, np.int64)
-    n = lib().sao_expectations(C.byref(m), target.encode(), lX, _f64(events), lY, _i64(anchors), anchors.shape[0],
-                               C.byref(p), int(ragged_left), int(ragged_right), C.byref(amb), _f64(tr), _f64(lik),
-                               _i64(ak), _i64(ae), cap)
+    while True:
+        tr = np.full(9, pseudo_t)
+        lik = np.zeros(1)
+        ak = np.zeros(cap, np.int64)
+        ae = np.zeros(cap, np.int64)
+        n = lib().sao_expectations(C.byref(m), target.encode(), lX, _f64(events), lY, _i64(anchors), anchors.shape[0],
+                                   C.byref(p), int(ragged_left), int(ragged_right), C.byref(amb), _f64(tr), _f64(lik),
+                                   _i64(ak), _i64(ae), cap)
+        if n <= cap:
+            break
+        cap = n
     if n < 0:
         raise ValueError("kmer contains a character outside the alphabet")
     return tr, float(lik[0]), ak[:n].copy(), ae[:n].copy()

@@ -178,16 +178,20 @@ class RefStateMachine:
         lY = events.shape[0]
         lX = len(target) - (self.k - 1)
         cap = 8 * (lX + lY) + 1024
-        tr = np.zeros(9)
-        lik = C.c_double(0)
-        ak = np.zeros(cap, np.int64)
-        ae = np.zeros(cap, np.int64)
-        sec = C.c_double(0)
-        n = lib().ref_expectations(self.h, target.encode(), lX, _f64(events), lY, _i64(anchors), anchors.shape[0],
-                                   threshold, min_diags, trace_back, expansion, split_bigger,
-                                   int(ragged_left), int(ragged_right), (ambig_file or "").encode(),
-                                   pseudo_t, pseudo_e, _f64(tr), C.byref(lik), _i64(ak), _i64(ae), cap,
-                                   C.byref(sec))
+        while True:
+            tr = np.zeros(9)
+            lik = C.c_double(0)
+            ak = np.zeros(cap, np.int64)
+            ae = np.zeros(cap, np.int64)
+            sec = C.c_double(0)
+            n = lib().ref_expectations(self.h, target.encode(), lX, _f64(events), lY, _i64(anchors), anchors.shape[0],
+                                       threshold, min_diags, trace_back, expansion, split_bigger,
+                                       int(ragged_left), int(ragged_right), (ambig_file or "").encode(),
+                                       pseudo_t, pseudo_e, _f64(tr), C.byref(lik), _i64(ak), _i64(ae), cap,
+                                       C.byref(sec))
+            if n <= cap:
+                break
+            cap = n
         return tr, lik.value, ak[:min(n, cap)].copy(), ae[:min(n, cap)].copy(), sec.value
 
 

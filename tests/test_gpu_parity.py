@@ -8,7 +8,8 @@ import signalalign_b200 as sa
 from oracle import port
 from signalalign_b200 import synth
 
-from helpers import compare_pairs, oracle_align, port_model_from, port_params, sa_read
+from helpers import (compare_expectations, compare_pairs, oracle_align, oracle_expectations, port_model_from, port_params,
+                     sa_read)
 
 pytestmark = pytest.mark.gpu
 
@@ -105,3 +106,103 @@ def test_device_logadd_bit_exact():
     got = sa.debug_logadd(x, y)
     exp = np.array([port.log_add(a, b) for a, b in zip(x, y)])
     assert np.array_equal(got.view(np.int64), exp.view(np.int64))
+
+
+# ------------------------------------------------------------------------------------------------ every emission kind
+def _synthetic_hdp(table, seed=3, G=120):
+    """single-level HDP tables in the shape of a .nhdp: a two-component mixture around the table mean per kmer row"""
+    rng = np.random.default_rng(seed)
+    K = table.shape[0]
+    rows = 300
+    grid = np.linspace(50.0, 135.0, G)
+    centers = rng.uniform(60, 125, rows)
+    pp = np.zeros((rows, G))
+    for r in range(rows):
+        a, b = centers[r], centers[r] + rng.uniform(-6, 6)
+        pp[r] = 0.7 * np.exp(-0.5 * ((grid - a) / 2.5) ** 2) / (2.5 * np.sqrt(2 * np.pi)) + \
+            0.3 * np.exp(-0.5 * ((grid - b) / 4.0) ** 2) / (4.0 * np.sqrt(2 * np.pi))
+    sl = np.gradient(pp, grid, axis=1)
+    # each kmer uses the row whose centre is nearest to its table mean (some rows shared = unobserved kmers' parents)
+    k2r = np.abs(table[:, 0][:, None] - centers[None, :]).argmin(1).astype(np.int32)
+    return grid, k2r, pp, sl
+
+
+@pytest.mark.parametrize("kind", [port.EMIT_GAUSS_NOISE_SCALED, port.EMIT_GAUSS_NOISE_DESCALE, port.EMIT_HDP])
+def test_other_emission_kinds_alignment_and_expectations(gapped_batch, kind):
+    reads, table = gapped_batch
+    trans = synth.nanopore_transitions()
+    kw = {}
+    model = sa.Model.from_tables("ACGT", 6, trans, table, kind=kind)
+    if kind == port.EMIT_HDP:
+        grid, k2r, pp, sl = _synthetic_hdp(table)
+        model.set_hdp(grid, k2r, pp, sl)
+        kw = dict(grid=grid, kmer_to_row=k2r, post_pred=pp, slopes=sl)
+    pm = port_model_from("ACGT", 6, trans, table, kind=kind, **kw)
+    p = sa.default_params(threshold=0.01, expansion=20, trace_back=20, min_diags=150)
+    rs = [dict(r) for r in reads[:4]]
+    for r in rs:   # realistic event noise for the inverse-Gaussian term
+        r["events"] = r["events"].copy()
+        r["events"][:, 1] = np.random.default_rng(1).uniform(0.5, 2.5, len(r["events"]))
+    res = sa.align_batch(model, [sa_read(r) for r in rs], p)
+    exp = sa.expectations_batch(model, [sa_read(r) for r in rs], p)
+    for i, r in enumerate(rs):
+        ora, _ = oracle_align(pm, r, port_params(p))
+        assert compare_pairs(res.read_pairs(i), ora, p.threshold) <= 20
+        tr, lik, ak, ae = oracle_expectations(pm, r, port_params(p))
+        compare_expectations(exp.transitions[i], exp.likelihood[i], tr, lik)
+        if kind == port.EMIT_HDP:
+            a0, a1 = exp.assign_offsets[i], exp.assign_offsets[i + 1]
+            assert np.array_equal(exp.assign_kmer_pos[a0:a1], ak) and np.array_equal(exp.assign_event[a0:a1], ae)
+
+
+def test_ambiguous_reference_iupac(gapped_batch):
+    reads, table = gapped_batch
+    trans = synth.nanopore_transitions()
+    model = sa.Model.from_tables("ACGT", 6, trans, table)
+    pm = port_model_from("ACGT", 6, trans, table)
+    rng = np.random.default_rng(8)
+    rs = []
+    for r in reads[:3]:
+        t = list(r["target"])
+        for i in rng.choice(len(t), 14, replace=False):
+            t[i] = "RYSWKMBDHVX"[int(rng.integers(0, 11))]
+        rs.append(dict(r, target="".join(t)))
+    p = sa.default_params(threshold=0.01, expansion=20, trace_back=20, min_diags=150)
+    res = sa.align_batch(model, [sa_read(r) for r in rs], p)
+    exp = sa.expectations_batch(model, [sa_read(r) for r in rs], p)
+    assert res.path_cells > res.band_cells
+    for i, r in enumerate(rs):
+        ora, _ = oracle_align(pm, r, port_params(p))
+        assert compare_pairs(res.read_pairs(i), ora, p.threshold) <= 20
+        tr, lik, _, _ = oracle_expectations(pm, r, port_params(p))
+        compare_expectations(exp.transitions[i], exp.likelihood[i], tr, lik)
+
+
+def test_split_regions_large_gaps():
+    """anchor gaps larger than splitMatrixBiggerThanThis cut the read into independently aligned regions with ragged
+    internal ends (reference pairwiseAligner.c:1953-2016); pairs come back in the reference's region order"""
+    reads, table = synth.make_batch(3, seed=21, mean_len=700, min_len=500, max_len=900, trim=14, block_mean=40)
+    trans = synth.nanopore_transitions()
+    model = sa.Model.from_tables("ACGT", 6, trans, table)
+    pm = port_model_from("ACGT", 6, trans, table)
+    p = sa.default_params(threshold=0.01, expansion=20, trace_back=20, min_diags=150, split_bigger=600)
+    res = sa.align_batch(model, [sa_read(r) for r in reads], p)
+    for i, r in enumerate(reads):
+        assert len(port.split_points(r["anchors"], len(r["target"]) - 5, len(r["events"]), 600, True, True)) > 1
+        ora, _ = oracle_align(pm, r, port_params(p))
+        assert compare_pairs(res.read_pairs(i), ora, p.threshold) <= 20
+
+
+def test_rna_5mer_table_long_read():
+    """config 5's table shape (ACGT 5-mer, K = 1024) on a longer read"""
+    table = synth.gaussian_table("ACGT", 5, seed=11)
+    reads, _ = synth.make_batch(2, seed=13, k=5, table=table, mean_len=5000, min_len=4000, max_len=6000, trim=0,
+                                n_probs=(0.15, 0.60, 0.18, 0.07))
+    trans = synth.nanopore_transitions()
+    model = sa.Model.from_tables("ACGT", 5, trans, table)
+    pm = port_model_from("ACGT", 5, trans, table)
+    p = sa.default_params(threshold=0.01, expansion=50, trace_back=50, min_diags=1000)
+    res = sa.align_batch(model, [sa_read(r) for r in reads], p)
+    for i, r in enumerate(reads):
+        ora, _ = oracle_align(pm, r, port_params(p))
+        assert compare_pairs(res.read_pairs(i), ora, p.threshold) <= 20
