@@ -155,7 +155,10 @@ def test_mixed_batch_keeps_read_order_and_sums():
     tab = np.zeros(10)
     import ctypes as C
     sa.lib().sa_result_sum_expectations(e._ptr, tab.ctypes.data_as(sa.c_f64p))
-    assert np.allclose(tab[:9], e.transitions.sum(0)) and np.isclose(tab[9], e.likelihood.sum())
+    # the lX = 0 read has total probability -inf, so (like the reference's exp(-inf - -inf)) its M->Y / Y->Y entries are
+    # NaN and its likelihood -inf: the oracle port returns exactly that, and sums propagate it
+    assert np.allclose(tab[:9], e.transitions.sum(0), equal_nan=True) and tab[9] == e.likelihood.sum()
+    assert np.isnan(e.transitions[3][[2, 8]]).all() and e.likelihood[3] == -np.inf and not np.isnan(e.transitions[[0, 2, 4]]).any()
     assert np.array_equal(e.transitions[0], e.transitions[4]) and e.likelihood[0] == e.likelihood[4]
 
 
