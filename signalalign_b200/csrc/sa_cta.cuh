@@ -1,0 +1,493 @@
+// sa_cta.cuh — the CTA band kernel: one CTA of W warps per work item, ONE band cell per thread.
+//
+// Same eligibility and arithmetic as the warp kernel it replaces (un-ambiguous reference, Gaussian MeanOnly emission,
+// FP64 cubic logAdd in the reference's accumulation order), different mapping:
+//
+//   * thread t owns slot t of NS = 32 W slots; slot = column mod NS inside a sliding window [wlo, wlo + NS), so along a
+//     diagonal the `upper` neighbour (x, y-1) is the thread's own register and `lower` / `middle` (x-1, .) come from
+//     thread t-1: one __shfl_up per value inside a warp, a 4-double shared-memory mailbox between warps, ONE
+//     __syncthreads per diagonal.
+//   * per-thread state is a dozen doubles (f(d-1), f(d-2) of one column), so registers allow ~5 CTAs of 128 threads per
+//     SM (20 warps) instead of the 8 warps the 4-cells-per-lane layout reached: the FP64 dependency chains of the
+//     logAdd are hidden by warp interleaving instead of by compiler-scheduled ILP.
+//   * everything a step needs besides the DP state comes from shared-memory rings filled cooperatively and coalesced:
+//     per-column emission constants (5 doubles, scale/shift/var folded in), event means, and the band of the next NS
+//     diagonals (band_construct in closed form per diagonal from the staged anchors).  No global load sits on the
+//     forward critical path.
+//   * forward rows go to the same HBM ring as before (row = [xlo, xhi | M plane | X plane | Y plane]) for the blocked
+//     traceback; the backward sweep mirrors the forward one (neighbours from thread t+1).
+//   * total probability: the per-cell terms go through shared memory and EVERY warp folds them redundantly in column
+//     order (the fold is sequential and non-associative), so no broadcast is needed.
+//   * posterior pairs: exp() only for cells that can reach the threshold; hits are counted per warp (ballot) and written
+//     one barrier later in the reference's order.
+#pragma once
+#include "sa_fast.cuh"
+
+template <int W>
+struct CtaK {
+    static constexpr int NT = 32 * W;        // threads = slots
+    static constexpr int NS = NT;
+    static constexpr int ROW = 3 * NS + 2;   // doubles per stored forward row
+    static constexpr int RN = 2 * NT;        // entries of the column / event rings
+
+    struct Smem {
+        double cst[5][RN];       // km, iM, cM, iY, cY per column (index = column & (RN - 1))
+        double evs[RN];          // event mean per y (index = y & (RN - 1)); 0 outside [1, lY]
+        double xch[2][W][4];     // warp-boundary mailbox, double buffered by diagonal parity
+        double foldv[2][NS];     // total-probability terms by slot
+        int2 bandTab[NT];        // [xlo, xhi] of forward diagonals bd0 .. bd0 + NT - 1
+        int32_t aX[NT + 1], aY[NT + 1], aD[NT + 1];   // staged anchors (+1 coordinates) and their diagonals
+        unsigned hitM[2][W];     // posterior hits per warp (ballot), double buffered
+        int32_t sItem, sAi;
+    };
+
+    static __device__ __forceinline__ int32_t slotX(int32_t s, int32_t wlo) { return wlo + ((s - wlo) & (NS - 1)); }
+
+    // ------------------------------------------------------------------------------------------ ring refills
+    // constants of columns [c0, c0 + RN): column 0 is the NULL kmer, columns outside [1, lX] never become active
+    static __device__ __forceinline__ void fillConsts(const FParams &P, const FItem &I, Smem &S, int t, int32_t c0) {
+        for (int i = t; i < RN; i += NT) {
+            const int32_t x = c0 + i, s = x & (RN - 1);
+            double km = 0.0, iM = 0.0, iY = 0.0, cM = SA_NEG_INF, cY = SA_NEG_INF;
+            if (x >= 1 && x <= I.lX) {
+                const double *ft = P.ft + (int64_t) P.kmerIdx[I.kmerOff + x - 1] * 5;
+                km = fma(I.scale, ft[0], I.shift);
+                iM = ft[1] * I.invVar;
+                cM = ft[2] + I.logInvVar;
+                iY = ft[3] * I.invVar;
+                cY = ft[4] + I.logInvVar;
+            }
+            S.cst[0][s] = km; S.cst[1][s] = iM; S.cst[2][s] = cM; S.cst[3][s] = iY; S.cst[4][s] = cY;
+        }
+    }
+    static __device__ __forceinline__ void fillEvents(const FParams &P, const FItem &I, Smem &S, int t, int32_t y0) {
+        for (int i = t; i < RN; i += NT) {
+            const int32_t y = y0 + i;
+            S.evs[y & (RN - 1)] = (y >= 1 && y <= I.lY) ? P.evMean[I.evOff + y - 1] : 0.0;
+        }
+    }
+    // make the rings cover the window [wlo, wlo + NS) on diagonal d; uniform decisions, barriers only when refilling
+    static __device__ __forceinline__ void ensureRings(const FParams &P, const FItem &I, Smem &S, int t, int32_t wlo,
+                                                       int32_t d, int32_t &cLo, int32_t &eLo) {
+        const int32_t ymin = d - (wlo + NS - 1);
+        const bool needC = wlo < cLo || wlo + NS > cLo + RN;
+        const bool needE = ymin < eLo || ymin + NS > eLo + RN;
+        if (needC || needE) {
+            __syncthreads();   // nobody still reads the old contents
+            if (needC) { cLo = wlo - NS / 2; fillConsts(P, I, S, t, cLo); }
+            if (needE) { eLo = ymin - NS / 2; fillEvents(P, I, S, t, eLo); }
+        }
+    }
+
+    // band_construct (reference impl/pairwiseAligner.c:195-246) in closed form for diagonals d0 .. d0 + NT - 1:
+    // between two consecutive anchors the band only depends on the diagonal, and the anchor interval of diagonal d is
+    // (number of anchors whose diagonal x + y + 2 is < d).  Anchors are staged in shared memory, then every thread
+    // evaluates its own diagonal.
+    static __device__ __forceinline__ void fillBand(const FParams &P, const FItem &I, Smem &S, int t, int32_t d0) {
+        __syncthreads();
+        const int32_t base = S.sAi;            // anchors with diagonal < d0 - 1 (lower bound of every count below)
+        const int32_t *anch = P.anchors + 2 * I.anchorOff;
+        for (int j = t; j <= NT; j += NT) {
+            const int32_t a = base - 1 + j;
+            int32_t X = 0, Y = 0, D = -0x7fffffff;
+            if (a >= I.nAnchors) { X = I.lX; Y = I.lY; D = 0x7fffffff; }
+            else if (a >= 0) { X = anch[2 * a] + 1; Y = anch[2 * a + 1] + 1; D = X + Y; }
+            S.aX[j] = X; S.aY[j] = Y; S.aD[j] = D;
+        }
+        __syncthreads();
+        const int32_t d = d0 + t, nDiag = I.lX + I.lY;
+        // c = number of staged real anchors (entries 1..NT) with diagonal < d
+        int lo = 0, hi = NT;                   // invariant: entries 1..lo are < d, entries hi+1.. are >= d
+        while (lo < hi) {
+            const int mid = (lo + hi + 1) >> 1;
+            if (S.aD[mid] < d) lo = mid; else hi = mid - 1;
+        }
+        const int c = lo < NT ? lo : NT - 1;   // (c + 1 <= NT always holds: anchor diagonals grow by >= 2)
+        const int32_t pX = S.aX[c], pY = S.aY[c], nX = S.aX[c + 1], nY = S.aY[c + 1];
+        const int32_t pxay = pX + pY, pxmy = pX - pY, nxay = nX + nY, nxmy = nX - nY, e = P.expansion;
+        const int32_t xL = BandIt::clampc((pxay + pxmy - e) / 2, I.lX), yL = BandIt::clampc((nxay - nxmy + e) / 2, I.lY);
+        const int32_t xU = BandIt::clampc((nxay + nxmy + e) / 2, I.lX), yU = BandIt::clampc((pxay - pxmy - e) / 2, I.lY);
+        int32_t l = xL - yL, r = xU - yU, q;
+        if ((d + l) & 1) l++;
+        if ((d + r) & 1) r++;
+        if ((q = xL - (d + l) / 2) > 0) l += 2 * q;
+        if ((q = (d - l) / 2 - yL) > 0) l += 2 * q;
+        if ((q = (d + r) / 2 - xU) > 0) r -= 2 * q;
+        if ((q = yU - (d - r) / 2) > 0) r -= 2 * q;
+        S.bandTab[t] = d <= nDiag ? make_int2((d + l) / 2, (d + r) / 2) : make_int2(0, 0);
+        if (t == NT - 1) S.sAi = base + c;
+        __syncthreads();
+    }
+
+    // ------------------------------------------------------------------------------------------ neighbour exchange
+    template <int N>
+    static __device__ __forceinline__ void publishTop(Smem &S, int buf, int lane, int warp, const double (&v)[N]) {
+        if (W > 1 && lane == 31) {
+#pragma unroll
+            for (int i = 0; i < N; i++) S.xch[buf][warp][i] = v[i];
+        }
+    }
+    template <int N>
+    static __device__ __forceinline__ void fetchUp(const Smem &S, int buf, int lane, int warp, const double (&v)[N],
+                                                   double (&o)[N]) {
+#pragma unroll
+        for (int i = 0; i < N; i++) o[i] = __shfl_sync(0xffffffffu, v[i], (lane + 31) & 31);
+        if (W > 1 && lane == 0) {
+            const int src = (warp + W - 1) % W;
+#pragma unroll
+            for (int i = 0; i < N; i++) o[i] = S.xch[buf][src][i];
+        }
+    }
+    template <int N>
+    static __device__ __forceinline__ void publishBottom(Smem &S, int buf, int lane, int warp, const double (&v)[N]) {
+        if (W > 1 && lane == 0) {
+#pragma unroll
+            for (int i = 0; i < N; i++) S.xch[buf][warp][i] = v[i];
+        }
+    }
+    template <int N>
+    static __device__ __forceinline__ void fetchDown(const Smem &S, int buf, int lane, int warp, const double (&v)[N],
+                                                     double (&o)[N]) {
+#pragma unroll
+        for (int i = 0; i < N; i++) o[i] = __shfl_sync(0xffffffffu, v[i], (lane + 1) & 31);
+        if (W > 1 && lane == 31) {
+            const int src = (warp + 1) % W;
+#pragma unroll
+            for (int i = 0; i < N; i++) o[i] = S.xch[buf][src][i];
+        }
+    }
+
+    static __device__ __forceinline__ void emissions(const Smem &S, int32_t x, int32_t y, double &eM, double &eY) {
+        const int cs = x & (RN - 1);
+        const double d0 = S.evs[y & (RN - 1)] - S.cst[0][cs];
+        const double aM = d0 * S.cst[1][cs], aY = d0 * S.cst[3][cs];
+        eM = fma(-0.5 * aM, aM, S.cst[2][cs]);
+        eY = fma(-0.5 * aY, aY, S.cst[4][cs]);
+    }
+
+    // sequential logAdd fold of S.foldv[which][*] in column order, skipping exact no-ops (see FastK::orderedFold);
+    // every warp computes the same value
+    static __device__ __forceinline__ double orderedFold(const Smem &S, int which, int lane, int32_t wlo) {
+        const int s0 = wlo & (NS - 1);
+        double v[W];
+#pragma unroll
+        for (int j = 0; j < W; j++) v[j] = S.foldv[which][(s0 + lane * W + j) & (NS - 1)];
+        double mx = v[0];
+#pragma unroll
+        for (int j = 1; j < W; j++) mx = fmax(mx, v[j]);
+        double run = mx;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            double q = __shfl_up_sync(0xffffffffu, run, o);
+            if (lane >= o) run = fmax(run, q);
+        }
+        double excl = __shfl_up_sync(0xffffffffu, run, 1);
+        if (lane == 0) excl = SA_NEG_INF;
+        unsigned cand[W];
+        double pm = excl;
+#pragma unroll
+        for (int j = 0; j < W; j++) {
+            const bool c = v[j] > pm - 7.6;   // false for -inf
+            cand[j] = __ballot_sync(0xffffffffu, c);
+            pm = fmax(pm, v[j]);
+        }
+        unsigned any = 0;
+#pragma unroll
+        for (int j = 0; j < W; j++) any |= cand[j];
+        double acc = SA_NEG_INF;
+        while (any) {
+            const int ln = __ffs(any) - 1;
+            any &= any - 1;
+#pragma unroll
+            for (int j = 0; j < W; j++) {
+                const double q = __shfl_sync(0xffffffffu, v[j], ln);
+                if ((cand[j] >> ln) & 1u) acc = sa_logAdd(acc, q);
+            }
+        }
+        return acc;
+    }
+
+    // f(d) of this thread's cell from the own column on d-1 (f1), and the left neighbour on d-1 (n1) and d-2 (n2)
+    static __device__ __forceinline__ void forwardCell(const FParams &P, const Smem &S, int32_t x, int32_t d, bool act,
+                                                       const double (&f1)[3], const double (&n1)[3],
+                                                       const double (&n2)[3], double (&o)[3]) {
+        const double *T = P.trans;
+        double eM, eY;
+        emissions(S, x, d - x, eM, eY);
+        const double cOX = P.eX + T[T_GAP_OPEN_X], cEX = P.eX + T[T_GAP_EXTEND_X];
+        // stateMachine3_cellCalculate order; the first contribution lands on -inf (logAdd(-inf, v) == v exactly)
+        const double X = sa_logAdd(n1[0] + cOX, n1[1] + cEX);
+        const double M = sa_logAdd(sa_logAdd(n2[0] + (eM + T[T_MATCH_CONTINUE]), n2[1] + (eM + T[T_MATCH_FROM_GAP_X])),
+                                   n2[2] + (eM + T[T_MATCH_FROM_GAP_Y]));
+        const double Y = sa_logAdd(f1[0] + (eY + T[T_GAP_OPEN_Y]), f1[2] + (eY + T[T_GAP_EXTEND_Y]));
+        o[0] = act ? M : SA_NEG_INF;
+        o[1] = act ? X : SA_NEG_INF;
+        o[2] = act ? Y : SA_NEG_INF;
+    }
+
+    static __device__ __forceinline__ void storeRow(double *row, int t, int32_t xlo, int32_t xhi, bool full,
+                                                    const double (&f)[3]) {
+        if (t == 0) *reinterpret_cast<int2 *>(row) = make_int2(xlo, xhi);
+        row[2 + t] = f[0];
+        if (full) {
+            row[2 + NS + t] = f[1];
+            row[2 + 2 * NS + t] = f[2];
+        }
+    }
+
+    // number of posterior hits in slots [0, k) from the per-warp ballots
+    static __device__ __forceinline__ int hitsBelow(const unsigned (&m)[W], int k) {
+        int n = 0;
+#pragma unroll
+        for (int w = 0; w < W; w++) {
+            const int lo = w * 32;
+            if (k >= lo + 32) n += __popc(m[w]);
+            else if (k > lo) n += __popc(m[w] & ((1u << (k - lo)) - 1u));
+        }
+        return n;
+    }
+
+    // blocked traceback from diagonal d down to tracedBackTo + 1 (reference impl/pairwiseAligner.c:1500-1570):
+    // backward sweep mirrored on the forward one, posterior pairs for diagonals <= tracedBackFrom
+    static __device__ __forceinline__ void traceback(const FParams &P, const FItem &I, Smem &S, const double *ring, int t,
+                                                     int lane, int warp, int32_t d, int32_t xlo, int32_t xhi, int32_t bw,
+                                                     int32_t &cLo, int32_t &eLo, int32_t tracedBackTo,
+                                                     int32_t tracedBackFrom, bool atEnd, int64_t &nPairs) {
+        const double *T = P.trans;
+        const double cOX = P.eX + T[T_GAP_OPEN_X], cEX = P.eX + T[T_GAP_EXTEND_X];
+        // end / ragged-end state on diagonal d (reference stateMachine.c:1147-1173)
+        const bool rag = atEnd && (I.flags & 2);
+        const double e0 = rag ? (T[T_GAP_OPEN_X] + T[T_GAP_OPEN_Y]) / 2.0 : T[T_MATCH_CONTINUE];
+        const double e1 = rag ? T[T_GAP_EXTEND_X] : T[T_MATCH_FROM_GAP_X];
+        const double e2 = rag ? T[T_GAP_EXTEND_Y] : T[T_MATCH_FROM_GAP_Y];
+        int32_t myx = slotX(t, bw);
+        double curM, curE, qX, qY, qE, nxtM = SA_NEG_INF, nxtE = 0.0;   // own column: d2 (cur, q) and d2 + 1 (nxt)
+        double n1M = SA_NEG_INF, n1E = 0.0;                             // right neighbour's (M, eM) one diagonal up
+        {
+            const bool act = myx >= xlo && myx <= xhi;
+            double eM, eY;
+            emissions(S, myx, d - myx, eM, eY);
+            curM = act ? e0 : SA_NEG_INF; curE = eM;
+            qX = act ? e1 : SA_NEG_INF; qY = act ? e2 : SA_NEG_INF; qE = eY;
+        }
+        __syncthreads();                       // the forward mailbox writes of step d are done with
+        {
+            const double pub[3] = {curM, curE, qX};
+            publishBottom(S, d & 1, lane, warp, pub);
+        }
+        double total = SA_NEG_INF;
+        int32_t nPost = 0, bxlo = xlo, bxhi = xhi;
+        // posterior hit of the previous diagonal, written after the next barrier (needs every warp's ballot)
+        bool pendValid = false, pendHit = false;
+        int32_t pendP = 0, pendX = 0, pendD = 0, pendS0 = 0;
+        auto flush = [&]() {
+            unsigned m[W];
+            int tot = 0;
+#pragma unroll
+            for (int w = 0; w < W; w++) { m[w] = S.hitM[pendD & 1][w]; tot += __popc(m[w]); }
+            if (pendHit) {
+                const int a = hitsBelow(m, pendS0), b = hitsBelow(m, t);
+                const int before = pendS0 <= t ? b - a : tot - a + b;
+                const int64_t w = nPairs + before;
+                if (w < I.pairCap) {
+                    sa_pair_t o;
+                    o.p = pendP; o.x = pendX - 1; o.y = pendD - pendX - 1;
+                    o.kmerIdx = P.kmerIdx[I.kmerOff + pendX - 1];
+                    P.pairs[I.pairOff + w] = o;
+                }
+            }
+            nPairs += tot;
+            pendValid = false;
+        };
+        int2 hdrNext = make_int2(0, 0);
+        if (d - 1 > tracedBackTo) hdrNext = *reinterpret_cast<const int2 *>(ring + (int64_t) ((d - 1) % P.rowsCap) * ROW);
+        for (int32_t d2 = d; d2 > tracedBackTo; d2--) {
+            const double *row = ring + (int64_t) (d2 % P.rowsCap) * ROW;
+            const bool post = d2 <= tracedBackFrom;
+            double fM = 0.0;
+            if (post) fM = row[2 + t];
+            if (d2 < d) {
+                bxlo = hdrNext.x; bxhi = hdrNext.y;
+                if (d2 - 1 > tracedBackTo)
+                    hdrNext = *reinterpret_cast<const int2 *>(ring + (int64_t) ((d2 - 1) % P.rowsCap) * ROW);
+                if (bxlo < bw) bw = bxlo;      // lower the window; recycled slots restart at -inf
+                ensureRings(P, I, S, t, bw, d2, cLo, eLo);
+                __syncthreads();
+                if (pendValid) flush();
+                const int32_t x = slotX(t, bw);
+                if (x != myx) {
+                    myx = x;
+                    curM = SA_NEG_INF; curE = 0.0; nxtM = SA_NEG_INF; nxtE = 0.0;
+                    qX = SA_NEG_INF; qY = SA_NEG_INF; qE = 0.0;
+                }
+                const double own[3] = {curM, curE, qX};
+                double nb[3];
+                fetchDown(S, (d2 + 1) & 1, lane, warp, own, nb);
+                const double aM = n1M, aE = n1E, lX = nb[2];
+                n1M = nb[0]; n1E = nb[1];
+                // gather in the order the reference's scatter delivers (see sa_general.cuh)
+                const double M = sa_logAdd(sa_logAdd(aM + (aE + T[T_MATCH_CONTINUE]), qY + (qE + T[T_GAP_OPEN_Y])), lX + cOX);
+                const double X = sa_logAdd(aM + (aE + T[T_MATCH_FROM_GAP_X]), lX + cEX);
+                const double Y = sa_logAdd(aM + (aE + T[T_MATCH_FROM_GAP_Y]), qY + (qE + T[T_GAP_EXTEND_Y]));
+                double eM, eY;
+                emissions(S, x, d2 - x, eM, eY);
+                const bool act = x >= bxlo && x <= bxhi;
+                nxtM = curM; nxtE = curE;
+                curM = act ? M : SA_NEG_INF; curE = eM;
+                qX = act ? X : SA_NEG_INF; qY = act ? Y : SA_NEG_INF; qE = eY;
+                const double pub[3] = {curM, curE, qX};
+                publishBottom(S, d2 & 1, lane, warp, pub);
+            }
+            if (!post) continue;
+            const int32_t x = myx;
+            if (nPost++ % 10 == 0) {
+                // diagonalCalculationTotalProbability (reference pairwiseAligner.c:1335-1353)
+                const double fX = row[2 + NS + t], fY = row[2 + 2 * NS + t];
+                double v = fM + curM;
+                v = sa_logAdd(v, fX + qX);
+                v = sa_logAdd(v, fY + qY);
+                // matches jumping over d2: middle-only forward step from f(d2 - 1) into the cells of d2 + 1
+                const double *rowm = ring + (int64_t) ((d2 - 1) % P.rowsCap) * ROW + 2;
+                const int sp = (t + NS - 1) & (NS - 1);
+                const double gM = rowm[sp], gX = rowm[NS + sp], gY = rowm[2 * NS + sp];
+                const double m = sa_logAdd(sa_logAdd(gM + (nxtE + T[T_MATCH_CONTINUE]), gX + (nxtE + T[T_MATCH_FROM_GAP_X])),
+                                           gY + (nxtE + T[T_MATCH_FROM_GAP_Y]));
+                S.foldv[0][t] = v;
+                S.foldv[1][t] = m + nxtM;
+                __syncthreads();
+                const double tot = orderedFold(S, 0, lane, bw), tot2 = orderedFold(S, 1, lane, bw);
+                total = sa_logAdd(tot, tot2);
+            }
+            // diagonalCalculationPosteriorMatchProbs (reference pairwiseAligner.c:1355-1421)
+            const double arg = (fM + curM) - total;
+            const bool cand = x >= bxlo && x <= bxhi && x > 0 && d2 - x > 0 && arg >= P.logThrGate;
+            bool hit = false;
+            double pp = 0.0;
+            if (__any_sync(0xffffffffu, cand)) {
+                pp = exp(arg);
+                hit = cand && pp >= P.threshold;
+            }
+            const unsigned mk = __ballot_sync(0xffffffffu, hit);
+            if (lane == 0) S.hitM[d2 & 1][warp] = mk;
+            pendValid = true; pendHit = hit; pendX = x; pendD = d2; pendS0 = bw & (NS - 1);
+            pendP = (int32_t) floor((pp > 1.0 ? 1.0 : pp) * 10000000.0);
+        }
+        if (pendValid) {
+            __syncthreads();
+            flush();
+        }
+    }
+
+    static __device__ void run(const FParams &P, const FItem &I, int it, double *ring, Smem &S) {
+        const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+        const double *T = P.trans;
+        const int32_t nDiag = I.lX + I.lY;
+        int64_t nPairs = 0;
+        if (nDiag == 0) {
+            if (t == 0) P.pairCount[it] = 0;
+            return;
+        }
+        const int32_t *tbList = P.tb + I.tbOff;
+        const int32_t nTb = P.geo[it].nTb;
+        __syncthreads();                       // previous item finished with shared memory
+        if (t == 0) S.sAi = 0;
+        int32_t wlo = 0, cLo = 0, eLo = 0, bd0 = 1;
+        cLo = wlo - NS / 2; fillConsts(P, I, S, t, cLo);
+        eLo = (0 - (wlo + NS - 1)) - NS / 2; fillEvents(P, I, S, t, eLo);
+        fillBand(P, I, S, t, bd0);             // (barriers inside)
+        // diagonal 0: the cell (0, 0) with the start / ragged-start state (reference stateMachine.c:1134-1145)
+        double fa[3], fb[3], nbA[3], nbB[3];   // f(d-1) / f(d-2) by parity and the left neighbour's copies
+        int32_t myx = slotX(t, wlo);
+        {
+            const bool ragged = I.flags & 1, c0 = t == 0;
+            fa[0] = (c0 && !ragged) ? 0.0 : SA_NEG_INF;
+            fa[1] = (c0 && ragged) ? 0.0 : SA_NEG_INF;
+            fa[2] = (c0 && ragged) ? 0.0 : SA_NEG_INF;
+            fb[0] = fb[1] = fb[2] = SA_NEG_INF;
+            nbA[0] = nbA[1] = nbA[2] = SA_NEG_INF;
+            nbB[0] = nbB[1] = nbB[2] = SA_NEG_INF;
+        }
+        storeRow(ring, t, 0, 0, true, fa);
+        publishTop(S, 0, lane, warp, fa);
+        int32_t tracedBackTo = 0;
+        int tbI = 0;
+        int32_t nextT = nTb > 0 ? tbList[0] : nDiag;
+        int32_t curFrom = nextT - (nextT == nDiag ? 0 : P.traceBack + 1);
+        for (int32_t d = 1; d <= nDiag; d++) {
+            if (d >= bd0 + NT) { bd0 = d; fillBand(P, I, S, t, bd0); }
+            const int2 bnd = S.bandTab[d - bd0];
+            const int32_t xlo = bnd.x, xhi = bnd.y;
+            if (xhi > wlo + NS - 1) wlo = xhi - (NS - 1);   // slide the window up; recycled slots restart at -inf
+            ensureRings(P, I, S, t, wlo, d, cLo, eLo);
+            __syncthreads();                   // mailbox of step d-1 and any refill are visible
+            const int32_t x = slotX(t, wlo);
+            if (x != myx) {
+                myx = x;
+                fa[0] = fa[1] = fa[2] = SA_NEG_INF;
+                fb[0] = fb[1] = fb[2] = SA_NEG_INF;
+            }
+            const bool act = x >= xlo && x <= xhi;
+            const int32_t back = curFrom - d;
+            const bool full = back < 0 || (back % 10) <= 1;
+            double *row = ring + (int64_t) (d % P.rowsCap) * ROW;
+            // f(d-1) lives in fa when d is odd, in fb when d is even; the result overwrites f(d-2)
+            if (d & 1) {
+                fetchUp(S, (d - 1) & 1, lane, warp, fa, nbA);
+                forwardCell(P, S, x, d, act, fa, nbA, nbB, fb);
+                storeRow(row, t, xlo, xhi, full, fb);
+                publishTop(S, d & 1, lane, warp, fb);
+            } else {
+                fetchUp(S, (d - 1) & 1, lane, warp, fb, nbB);
+                forwardCell(P, S, x, d, act, fb, nbB, nbA, fa);
+                storeRow(row, t, xlo, xhi, full, fa);
+                publishTop(S, d & 1, lane, warp, fa);
+            }
+            if (d != nextT) continue;
+            // ------------------------------------------------------------------ traceback from diagonal d
+            const bool atEnd = d == nDiag;
+            const int32_t tracedBackFrom = curFrom;
+            traceback(P, I, S, ring, t, lane, warp, d, xlo, xhi, wlo, cLo, eLo, tracedBackTo, tracedBackFrom, atEnd, nPairs);
+            tracedBackTo = tracedBackFrom;
+            tbI++;
+            nextT = tbI < nTb ? tbList[tbI] : nDiag;
+            curFrom = nextT - (nextT == nDiag ? 0 : P.traceBack + 1);
+            if (atEnd) break;
+            // restore the forward sweep: f(d), f(d-1) from the ring (all three planes were kept above tracedBackFrom)
+            __syncthreads();
+            {
+                const double *r0 = ring + (int64_t) (d % P.rowsCap) * ROW + 2 + t;
+                const double *r1 = ring + (int64_t) ((d - 1) % P.rowsCap) * ROW + 2 + t;
+                double cur[3], prv[3], nb[3];
+#pragma unroll
+                for (int s3 = 0; s3 < 3; s3++) { cur[s3] = r0[s3 * NS]; prv[s3] = r1[s3 * NS]; }
+                publishTop(S, (d - 1) & 1, lane, warp, prv);
+                __syncthreads();
+                fetchUp(S, (d - 1) & 1, lane, warp, prv, nb);
+                publishTop(S, d & 1, lane, warp, cur);
+#pragma unroll
+                for (int s3 = 0; s3 < 3; s3++) {
+                    if (d & 1) { fb[s3] = cur[s3]; fa[s3] = prv[s3]; nbA[s3] = nb[s3]; }
+                    else { fa[s3] = cur[s3]; fb[s3] = prv[s3]; nbB[s3] = nb[s3]; }
+                }
+                myx = slotX(t, wlo);
+            }
+        }
+        if (t == 0) P.pairCount[it] = nPairs;
+    }
+};
+
+template <int W>
+__global__ void __launch_bounds__(32 * W) sa_cta_kernel(const FParams P) {
+    __shared__ typename CtaK<W>::Smem S;
+    sa_logAdd_init();
+    double *ring = P.scratch + (int64_t) blockIdx.x * P.rowsCap * CtaK<W>::ROW;
+    for (;;) {
+        __syncthreads();
+        if (threadIdx.x == 0) S.sItem = atomicAdd(P.counter, 1);
+        __syncthreads();
+        const int n = S.sItem;
+        if (n >= P.nOrder) break;
+        const int it = P.order[n];
+        CtaK<W>::run(P, P.items[it], it, ring, S);
+    }
+}

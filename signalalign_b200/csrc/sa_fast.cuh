@@ -57,8 +57,9 @@ struct FParams {
     double trans[9];
     double eX;               // uniform X-gap emission (log 0.1)
     double threshold;
+    double logThrGate;       // log(threshold) - 1e-6: below it exp() cannot reach the threshold (-inf if threshold <= 0)
     int32_t minDiags, traceBack, expansion;
-    int32_t rowsCap;         // rows per warp ring
+    int32_t rowsCap;         // rows per ring
     double *scratch;         // per warp: rowsCap * rowStride doubles
     sa_pair_t *pairs;
     int64_t *pairCount;

@@ -15,6 +15,7 @@
 #include "sa_internal.h"
 #include "sa_general.cuh"
 #include "sa_fast.cuh"
+#include "sa_cta.cuh"
 
 #define CK(call)                                                                                   \
     do {                                                                                           \
@@ -238,7 +239,7 @@ struct sa_batch {
     bool expectations = false;
     int64_t nReads = 0;
     cudaStream_t stream = nullptr;
-    cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+    cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     std::vector<ItemRec> items;  // global item id = index
     // shared inputs
     DevBuf<double> dEvMean, dEvNoise, dEvLogNoise;
@@ -259,14 +260,15 @@ struct sa_batch {
     int gCta = 0;
     // fast kernel
     std::vector<FItem> fItems;      // indexed by global item id
-    std::vector<int32_t> fOrder2, fOrder4;
+    std::vector<int32_t> fOrder[4];   // CTA kernel classes W = 1, 2, 4, 8
     DevBuf<FItem> dFItems;
-    DevBuf<int32_t> dFOrder2, dFOrder4, dTb;
+    DevBuf<int32_t> dFOrder[4], dTb;
     DevBuf<FGeo> dGeo;
     DevBuf<double> dFScratch;
     FParams fp;
-    int fBlocks2 = 0, fBlocks4 = 0;
-    int32_t fRows2 = 1, fRows4 = 1;
+    int fBlocks[4] = {0, 0, 0, 0};
+    int32_t fRows[4] = {1, 1, 1, 1};
+    bool warpKernel = false;
     int64_t bandCells = 0, pathCells = 0, events = 0;
     int64_t h2dBytes = 0, d2hBytes = 0;
     float lastMs[3] = {0, 0, 0};
@@ -520,7 +522,7 @@ extern "C" int sa_batch_prepare(const sa_model_t *m, const sa_read_t *reads, int
     if ((rc = b->dPathOff.upload(pathOff, st, &b->h2dBytes))) return rc;
     if ((rc = b->dPathKmer.upload(pathKmer, st, &b->h2dBytes))) return rc;
     if ((rc = b->dAnchors.upload(anchors32, st, &b->h2dBytes))) return rc;
-    if ((rc = b->dCounters.alloc(4))) return rc;
+    if ((rc = b->dCounters.alloc(8))) return rc;
 
     // output slots
     int64_t pairTotalCap = 0, assignTotalCap = 0;
@@ -582,6 +584,7 @@ extern "C" int sa_batch_prepare(const sa_model_t *m, const sa_read_t *reads, int
         memcpy(f.trans, m->trans, sizeof(f.trans));
         f.eX = m->gapX[0];
         f.threshold = p->threshold;
+        f.logThrGate = p->threshold > 0 ? log(p->threshold) - 1e-6 : -INFINITY;
         f.minDiags = (int32_t) p->minDiagsBetweenTraceBack; f.traceBack = (int32_t) p->traceBackDiagonals;
         f.expansion = (int32_t) p->diagonalExpansion;
         f.pairs = b->dPairs.p; f.pairCount = b->dPairCount.p;
@@ -590,40 +593,55 @@ extern "C" int sa_batch_prepare(const sa_model_t *m, const sa_read_t *reads, int
         CK(cudaMemcpyAsync(geo.data(), b->dGeo.p, sizeof(FGeo) * n, cudaMemcpyDeviceToHost, st));
         CK(cudaStreamSynchronize(st));
     }
-    int32_t rows2 = 1, rows4 = 1;
+    static const int kW[4] = {1, 2, 4, 8};
+    const bool useWarpKernel = getenv("SA_WARP_KERNEL") != nullptr;   // the superseded warp-per-read kernel (A/B runs only)
     for (int64_t i = 0; i < n; i++) {
         ItemRec &it = items[i];
         it.kernel = 0;
         if (fastModel && it.maxP == 1 && geo[i].monotone) {
-            if (geo[i].maxSpan <= FastK<2>::NS - 2 - 1) it.kernel = 2;
-            else if (geo[i].maxSpan <= FastK<4>::NS - 4 - 1) it.kernel = 4;
+            if (useWarpKernel) {
+                if (geo[i].maxSpan <= FastK<4>::NS - 4 - 1) it.kernel = 16;   // class 2 slot, warp kernel C = 4
+            } else {
+                for (int c = 0; c < 4 && !it.kernel; c++)
+                    if (geo[i].maxSpan <= 32 * kW[c] - 2) it.kernel = kW[c];
+            }
         }
         if (it.kernel) {
             it.cells = geo[i].cells;
             it.work = geo[i].cells;
             b->bandCells += it.cells;
             b->pathCells += it.cells;
-            if (it.kernel == 2) { b->fOrder2.push_back((int32_t) i); rows2 = std::max(rows2, geo[i].maxRows); }
-            else { b->fOrder4.push_back((int32_t) i); rows4 = std::max(rows4, geo[i].maxRows); }
+            int c = it.kernel == 16 ? 2 : (it.kernel == 1 ? 0 : it.kernel == 2 ? 1 : it.kernel == 4 ? 2 : 3);
+            b->fOrder[c].push_back((int32_t) i);
+            b->fRows[c] = std::max(b->fRows[c], geo[i].maxRows);
         }
     }
+    b->warpKernel = useWarpKernel;
     auto byWork = [&](int32_t a, int32_t c) { return items[a].work > items[c].work; };
-    std::stable_sort(b->fOrder2.begin(), b->fOrder2.end(), byWork);
-    std::stable_sort(b->fOrder4.begin(), b->fOrder4.end(), byWork);
-    if ((rc = b->dFOrder2.upload(b->fOrder2, st, &b->h2dBytes))) return rc;
-    if ((rc = b->dFOrder4.upload(b->fOrder4, st, &b->h2dBytes))) return rc;
     {
-        int bps2 = 1, bps4 = 1;
-        CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps2, sa_fast_kernel<2>, 128, 0));
-        CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps4, sa_fast_kernel<4>, 128, 0));
-        b->fBlocks2 = (int) std::min<int64_t>((int64_t) nSM * std::max(1, bps2), ((int64_t) b->fOrder2.size() + 3) / 4);
-        b->fBlocks4 = (int) std::min<int64_t>((int64_t) nSM * std::max(1, bps4), ((int64_t) b->fOrder4.size() + 3) / 4);
-        int64_t need2 = (int64_t) b->fBlocks2 * 4 * rows2 * FastK<2>::ROW;
-        int64_t need4 = (int64_t) b->fBlocks4 * 4 * rows4 * FastK<4>::ROW;
-        if ((rc = b->dFScratch.alloc((size_t) std::max<int64_t>(1, std::max(need2, need4))))) return rc;
+        int64_t need = 1;
+        for (int c = 0; c < 4; c++) {
+            std::stable_sort(b->fOrder[c].begin(), b->fOrder[c].end(), byWork);
+            if ((rc = b->dFOrder[c].upload(b->fOrder[c], st, &b->h2dBytes))) return rc;
+            if (b->fOrder[c].empty()) continue;
+            int bps = 1;
+            int64_t rowD = 0, nIt = (int64_t) b->fOrder[c].size();
+            if (useWarpKernel) {
+                CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, sa_fast_kernel<4>, 128, 0));
+                b->fBlocks[c] = (int) std::min<int64_t>((int64_t) nSM * std::max(1, bps), (nIt + 3) / 4);
+                rowD = (int64_t) b->fBlocks[c] * 4 * b->fRows[c] * FastK<4>::ROW;
+            } else {
+                if (c == 0) CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, sa_cta_kernel<1>, 32, 0));
+                if (c == 1) CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, sa_cta_kernel<2>, 64, 0));
+                if (c == 2) CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, sa_cta_kernel<4>, 128, 0));
+                if (c == 3) CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, sa_cta_kernel<8>, 256, 0));
+                b->fBlocks[c] = (int) std::min<int64_t>((int64_t) nSM * std::max(1, bps), nIt);
+                rowD = (int64_t) b->fBlocks[c] * b->fRows[c] * (3 * 32 * kW[c] + 2);
+            }
+            need = std::max(need, rowD);
+        }
+        if ((rc = b->dFScratch.alloc((size_t) need))) return rc;
         f.scratch = b->dFScratch.p;
-        b->fRows2 = rows2;  // rowsCap differs per launch
-        b->fRows4 = rows4;
     }
 
     timer.lap("geometry pass + fast-kernel scratch");
@@ -722,29 +740,26 @@ extern "C" int sa_batch_prepare(const sa_model_t *m, const sa_read_t *reads, int
 extern "C" int sa_batch_run(sa_batch_t *b) {
     cudaStream_t st = b->stream;
     b->lastLaunches = 0;
-    CK(cudaMemsetAsync(b->dCounters.p, 0, 4 * sizeof(int32_t), st));
+    CK(cudaMemsetAsync(b->dCounters.p, 0, 8 * sizeof(int32_t), st));
     CK(cudaEventRecord(b->ev[0], st));
-    if (!b->fOrder4.empty()) {
+    for (int c = 3; c >= 0; c--) {             // widest class first; [ev0, ev1) = W >= 4, [ev1, ev2) = W <= 2
+        if (c == 1) CK(cudaEventRecord(b->ev[1], st));
+        if (b->fOrder[c].empty()) continue;
         FParams f = b->fp;
-        f.order = b->dFOrder4.p; f.nOrder = (int32_t) b->fOrder4.size(); f.counter = b->dCounters.p + 0;
-        f.rowsCap = b->fRows4;
-        sa_fast_kernel<4><<<b->fBlocks4, 128, 0, st>>>(f);
-        b->lastLaunches++;
-        CK(cudaGetLastError());
-    }
-    CK(cudaEventRecord(b->ev[1], st));
-    if (!b->fOrder2.empty()) {
-        FParams f = b->fp;
-        f.order = b->dFOrder2.p; f.nOrder = (int32_t) b->fOrder2.size(); f.counter = b->dCounters.p + 1;
-        f.rowsCap = b->fRows2;
-        sa_fast_kernel<2><<<b->fBlocks2, 128, 0, st>>>(f);
+        f.order = b->dFOrder[c].p; f.nOrder = (int32_t) b->fOrder[c].size(); f.counter = b->dCounters.p + c;
+        f.rowsCap = b->fRows[c];
+        if (b->warpKernel) sa_fast_kernel<4><<<b->fBlocks[c], 128, 0, st>>>(f);
+        else if (c == 0) sa_cta_kernel<1><<<b->fBlocks[c], 32, 0, st>>>(f);
+        else if (c == 1) sa_cta_kernel<2><<<b->fBlocks[c], 64, 0, st>>>(f);
+        else if (c == 2) sa_cta_kernel<4><<<b->fBlocks[c], 128, 0, st>>>(f);
+        else sa_cta_kernel<8><<<b->fBlocks[c], 256, 0, st>>>(f);
         b->lastLaunches++;
         CK(cudaGetLastError());
     }
     CK(cudaEventRecord(b->ev[2], st));
     if (!b->gOrder.empty()) {
         GParams g = b->gp;
-        g.counter = b->dCounters.p + 2;
+        g.counter = b->dCounters.p + 4;
         if (b->expectations) sa_general_kernel<true><<<b->gCta, 128, 0, st>>>(g);
         else sa_general_kernel<false><<<b->gCta, 128, 0, st>>>(g);
         b->lastLaunches++;
@@ -796,7 +811,7 @@ static int growAndRerun(sa_batch_t *b) {
         }
     }
     int rc;
-    if (!b->fOrder2.empty() || !b->fOrder4.empty()) {
+    if (!b->fOrder[0].empty() || !b->fOrder[1].empty() || !b->fOrder[2].empty() || !b->fOrder[3].empty()) {
         if ((rc = b->dFItems.upload(b->fItems, b->stream, &b->h2dBytes))) return rc;
         b->fp.items = b->dFItems.p;
     }
@@ -954,7 +969,9 @@ extern "C" int sa_batch_last_timing(const sa_batch_t *b, float *ms3, int64_t *la
 }
 extern "C" int64_t sa_batch_band_cells(const sa_batch_t *b) { return b->bandCells; }
 extern "C" void sa_batch_kernel_items(const sa_batch_t *b, int64_t *o) {
-    o[0] = (int64_t) b->gOrder.size(); o[1] = (int64_t) b->fOrder2.size(); o[2] = (int64_t) b->fOrder4.size();
+    o[0] = (int64_t) b->gOrder.size();
+    o[1] = (int64_t) (b->fOrder[0].size() + b->fOrder[1].size());
+    o[2] = (int64_t) (b->fOrder[2].size() + b->fOrder[3].size());
 }
 extern "C" int64_t sa_batch_h2d_bytes(const sa_batch_t *b) { return b->h2dBytes; }
 extern "C" int64_t sa_batch_d2h_bytes(const sa_batch_t *b) { return b->d2hBytes; }
