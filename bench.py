@@ -39,8 +39,9 @@ def parse():
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--reads", type=int, default=int(os.environ.get("SA_BENCH_READS", "1184")),
-                    help="reads per GPU per step (default 8 per SM)")
+    ap.add_argument("--reads", type=int, default=int(os.environ.get("SA_BENCH_READS", "4736")),
+                    help="reads per GPU per step (default 32 per SM: ~6 work items per resident CTA, so the tail of the "
+                         "persistent grid is a few % of the step)")
     ap.add_argument("--cpu-reads", type=int, default=0, help="reads in the CPU sample (default: one per host core)")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--seed", type=int, default=20261104)
@@ -269,14 +270,22 @@ def main():
             pass
         hbm_peak = peaks.get("hbm_gbs", 6650.0)
         peak_src = "measured (MEASURED_PEAKS.json)" if "hbm_gbs" in peaks else "fallback (B200_PROFILING.md)"
-        # algorithmic bytes per band cell of the DP kernel: forward state written once and read
-        # once by the traceback (3 x f64 each way = 48 B) + ~0.4 B of inputs/outputs per cell
-        alg_bytes_per_cell = 48.4
+        # algorithmic bytes per band cell of the DP kernel: forward match plane written + read (16 B), X/Y
+        # planes on 2 of 10 rows (6.4 B), inputs / outputs 0.4 B
+        alg_bytes_per_cell = 22.8
         achieved_gbs = cells * alg_bytes_per_cell / (float(np.mean(kern_ms)) * 1e-3) / 1e9
         sm_mhz = (clocks or {}).get("sm_mhz") or 1965.0
-        # FP64 pipe: 64 lanes/SM/clk on B200; instruction count per cell from DESIGN.md (cuobjdump-counted)
-        fp64_per_cell = 150.0
-        fp64_peak = 148 * 64 * sm_mhz * 1e6
+        # FP64 pipe: ~230 algorithmic FP64 lane-instructions per band cell; peak = measured DFMA/DADD/DMUL
+        # issue rate of this pool's B200 (tools/peak_fp.cu -> profiles/r1_peak_fp.jsonl), else 64 lanes/SM/clk nominal
+        fp64_per_cell = 230.0
+        fp64_peak, fp64_src = 148 * 64 * 1.965e9, "nominal 64 lanes/SM/clk at 1965 MHz"
+        try:
+            for line in open(os.path.join(ROOT, "profiles", "r1_peak_fp.jsonl")):
+                rec = json.loads(line)
+                if rec.get("pipe") == "dadd":
+                    fp64_peak, fp64_src = rec["lane_instr_per_s"], "measured (profiles/r1_peak_fp.jsonl, tools/peak_fp.cu)"
+        except Exception:
+            pass
         out = {
             "metric": "events_aligned_per_sec", "value": events_all / (step_ms_max * 1e-3), "unit": "events/s",
             "n_gpus": world, "steps": a.steps, "warmup": a.warmup, "ms_per_step": step_ms_max,
@@ -284,11 +293,11 @@ def main():
             "config": {"workload": WORKLOAD, "reads_per_gpu_per_step": a.reads, "events_per_step": events_all,
                        "band_cells_per_step": cells_all, "l2": "flushed between steps (256 MiB write) and inputs > L2",
                        "aligned_pairs_rank0": n_pairs,
-                       "kernel_ms_rank0": {"fast_c4": float(np.mean([m[0] for m in all_ms])),
-                                           "fast_c2": float(np.mean([m[1] for m in all_ms])),
+                       "kernel_ms_rank0": {"cta_w4_w8": float(np.mean([m[0] for m in all_ms])),
+                                           "cta_w1_w2": float(np.mean([m[1] for m in all_ms])),
                                            "general": float(np.mean([m[2] for m in all_ms]))},
-                       "work_items_by_kernel_rank0": {"general": kernel_items[0], "fast_c2": kernel_items[1],
-                                                      "fast_c4": kernel_items[2]}},
+                       "work_items_by_kernel_rank0": {"general": kernel_items[0], "cta_w1_w2": kernel_items[1],
+                                                      "cta_w4_w8": kernel_items[2]}},
             "gcups": cells_all / (step_ms_max * 1e-3) / 1e9,
             "gpu_launches": launches,
             "clocks": clocks,
@@ -298,14 +307,14 @@ def main():
                          "frac": achieved_gbs / hbm_peak, "traffic": None, "peak_source": peak_src,
                          "note": "kernel is FP64-issue bound, not HBM bound: see roofline_compute"},
             "roofline_compute": {"bound": "fp64_pipe", "achieved": cells * fp64_per_cell / (float(np.mean(kern_ms)) * 1e-3),
-                                 "peak": fp64_peak, "unit": "FP64 lane-instr/s",
+                                 "peak": fp64_peak, "peak_source": fp64_src, "unit": "FP64 lane-instr/s",
                                  "frac": cells * fp64_per_cell / (float(np.mean(kern_ms)) * 1e-3) / fp64_peak,
                                  "per_cell": fp64_per_cell, "clock_mhz": sm_mhz},
             "wall_s_resident_loop": wall_resident,
         }
         if world == 1 and not a.no_cpu:
             cores = os.cpu_count() or 1
-            n = a.cpu_reads or min(cores, len(reads_d))
+            n = a.cpu_reads or min(4 * cores, len(reads_d))
             kind, wall, ev, used = cpu_arm(reads_d[:n], table, cores)
             out["cpu_baseline"] = {"value": ev / wall, "unit": "events/s", "cores": used, "kind": kind,
                                    "sample": f"first {n} reads of the step's batch, one process per core, {wall:.1f} s"}

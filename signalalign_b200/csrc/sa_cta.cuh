@@ -209,12 +209,11 @@ struct CtaK {
 
     // f(d) of this thread's cell from the own column on d-1 (f1), and the left neighbour on d-1 (n1) and d-2 (n2)
     static __device__ __forceinline__ void forwardCell(const FParams &P, const Smem &S, int32_t x, int32_t d, bool act,
-                                                       const double (&f1)[3], const double (&n1)[3],
-                                                       const double (&n2)[3], double (&o)[3]) {
+                                                       double cOX, double cEX, const double (&f1)[3],
+                                                       const double (&n1)[3], const double (&n2)[3], double (&o)[3]) {
         const double *T = P.trans;
         double eM, eY;
         emissions(S, x, d - x, eM, eY);
-        const double cOX = P.eX + T[T_GAP_OPEN_X], cEX = P.eX + T[T_GAP_EXTEND_X];
         // stateMachine3_cellCalculate order; the first contribution lands on -inf (logAdd(-inf, v) == v exactly)
         const double X = sa_logAdd(n1[0] + cOX, n1[1] + cEX);
         const double M = sa_logAdd(sa_logAdd(n2[0] + (eM + T[T_MATCH_CONTINUE]), n2[1] + (eM + T[T_MATCH_FROM_GAP_X])),
@@ -250,11 +249,12 @@ struct CtaK {
     // blocked traceback from diagonal d down to tracedBackTo + 1 (reference impl/pairwiseAligner.c:1500-1570):
     // backward sweep mirrored on the forward one, posterior pairs for diagonals <= tracedBackFrom
     static __device__ __forceinline__ void traceback(const FParams &P, const FItem &I, Smem &S, const double *ring, int t,
-                                                     int lane, int warp, int32_t d, int32_t xlo, int32_t xhi, int32_t bw,
-                                                     int32_t &cLo, int32_t &eLo, int32_t tracedBackTo,
-                                                     int32_t tracedBackFrom, bool atEnd, int64_t &nPairs) {
+                                                     int lane, int warp, int32_t d, int32_t rowI, int32_t xlo, int32_t xhi,
+                                                     int32_t bw, int32_t &cLo, int32_t &eLo, int32_t tracedBackTo,
+                                                     int32_t tracedBackFrom, bool atEnd, double cOX, double cEX,
+                                                     int64_t &nPairs) {
         const double *T = P.trans;
-        const double cOX = P.eX + T[T_GAP_OPEN_X], cEX = P.eX + T[T_GAP_EXTEND_X];
+        const int32_t cap = P.rowsCap;
         // end / ragged-end state on diagonal d (reference stateMachine.c:1147-1173)
         const bool rag = atEnd && (I.flags & 2);
         const double e0 = rag ? (T[T_GAP_OPEN_X] + T[T_GAP_OPEN_Y]) / 2.0 : T[T_MATCH_CONTINUE];
@@ -276,7 +276,7 @@ struct CtaK {
             publishBottom(S, d & 1, lane, warp, pub);
         }
         double total = SA_NEG_INF;
-        int32_t nPost = 0, bxlo = xlo, bxhi = xhi;
+        int32_t postMod = 0, bxlo = xlo, bxhi = xhi;   // postMod: posterior diagonals since the last total, mod 10
         // posterior hit of the previous diagonal, written after the next barrier (needs every warp's ballot)
         bool pendValid = false, pendHit = false;
         int32_t pendP = 0, pendX = 0, pendD = 0, pendS0 = 0;
@@ -300,16 +300,19 @@ struct CtaK {
             pendValid = false;
         };
         int2 hdrNext = make_int2(0, 0);
-        if (d - 1 > tracedBackTo) hdrNext = *reinterpret_cast<const int2 *>(ring + (int64_t) ((d - 1) % P.rowsCap) * ROW);
+        if (d - 1 > tracedBackTo) hdrNext = *reinterpret_cast<const int2 *>(ring + (int64_t) (rowI == 0 ? cap - 1 : rowI - 1) * ROW);
+        rowI = rowI + 1 == cap ? 0 : rowI + 1;
         for (int32_t d2 = d; d2 > tracedBackTo; d2--) {
-            const double *row = ring + (int64_t) (d2 % P.rowsCap) * ROW;
+            rowI = rowI == 0 ? cap - 1 : rowI - 1;             // ring row of d2
+            const int32_t rowP = rowI == 0 ? cap - 1 : rowI - 1;   // ... of d2 - 1
+            const double *row = ring + (int64_t) rowI * ROW;
             const bool post = d2 <= tracedBackFrom;
             double fM = 0.0;
             if (post) fM = row[2 + t];
             if (d2 < d) {
                 bxlo = hdrNext.x; bxhi = hdrNext.y;
                 if (d2 - 1 > tracedBackTo)
-                    hdrNext = *reinterpret_cast<const int2 *>(ring + (int64_t) ((d2 - 1) % P.rowsCap) * ROW);
+                    hdrNext = *reinterpret_cast<const int2 *>(ring + (int64_t) rowP * ROW);
                 if (bxlo < bw) bw = bxlo;      // lower the window; recycled slots restart at -inf
                 ensureRings(P, I, S, t, bw, d2, cLo, eLo);
                 __syncthreads();
@@ -340,14 +343,16 @@ struct CtaK {
             }
             if (!post) continue;
             const int32_t x = myx;
-            if (nPost++ % 10 == 0) {
+            const bool newTotal = postMod == 0;
+            postMod = postMod == 9 ? 0 : postMod + 1;
+            if (newTotal) {
                 // diagonalCalculationTotalProbability (reference pairwiseAligner.c:1335-1353)
                 const double fX = row[2 + NS + t], fY = row[2 + 2 * NS + t];
                 double v = fM + curM;
                 v = sa_logAdd(v, fX + qX);
                 v = sa_logAdd(v, fY + qY);
                 // matches jumping over d2: middle-only forward step from f(d2 - 1) into the cells of d2 + 1
-                const double *rowm = ring + (int64_t) ((d2 - 1) % P.rowsCap) * ROW + 2;
+                const double *rowm = ring + (int64_t) rowP * ROW + 2;
                 const int sp = (t + NS - 1) & (NS - 1);
                 const double gM = rowm[sp], gX = rowm[NS + sp], gY = rowm[2 * NS + sp];
                 const double m = sa_logAdd(sa_logAdd(gM + (nxtE + T[T_MATCH_CONTINUE]), gX + (nxtE + T[T_MATCH_FROM_GAP_X])),
@@ -413,7 +418,12 @@ struct CtaK {
         int tbI = 0;
         int32_t nextT = nTb > 0 ? tbList[0] : nDiag;
         int32_t curFrom = nextT - (nextT == nDiag ? 0 : P.traceBack + 1);
+        const double cOX = P.eX + T[T_GAP_OPEN_X], cEX = P.eX + T[T_GAP_EXTEND_X];
+        const int32_t cap = P.rowsCap;
+        int32_t rowI = 0;                       // ring row of diagonal d (= d mod cap, kept incrementally)
+        int32_t backMod = (curFrom - 1) % 10;   // (curFrom - d) mod 10 while it is >= 0
         for (int32_t d = 1; d <= nDiag; d++) {
+            rowI = rowI + 1 == cap ? 0 : rowI + 1;
             if (d >= bd0 + NT) { bd0 = d; fillBand(P, I, S, t, bd0); }
             const int2 bnd = S.bandTab[d - bd0];
             const int32_t xlo = bnd.x, xhi = bnd.y;
@@ -427,18 +437,18 @@ struct CtaK {
                 fb[0] = fb[1] = fb[2] = SA_NEG_INF;
             }
             const bool act = x >= xlo && x <= xhi;
-            const int32_t back = curFrom - d;
-            const bool full = back < 0 || (back % 10) <= 1;
-            double *row = ring + (int64_t) (d % P.rowsCap) * ROW;
+            const bool full = curFrom - d < 0 || backMod <= 1;
+            backMod = backMod == 0 ? 9 : backMod - 1;
+            double *row = ring + (int64_t) rowI * ROW;
             // f(d-1) lives in fa when d is odd, in fb when d is even; the result overwrites f(d-2)
             if (d & 1) {
                 fetchUp(S, (d - 1) & 1, lane, warp, fa, nbA);
-                forwardCell(P, S, x, d, act, fa, nbA, nbB, fb);
+                forwardCell(P, S, x, d, act, cOX, cEX, fa, nbA, nbB, fb);
                 storeRow(row, t, xlo, xhi, full, fb);
                 publishTop(S, d & 1, lane, warp, fb);
             } else {
                 fetchUp(S, (d - 1) & 1, lane, warp, fb, nbB);
-                forwardCell(P, S, x, d, act, fb, nbB, nbA, fa);
+                forwardCell(P, S, x, d, act, cOX, cEX, fb, nbB, nbA, fa);
                 storeRow(row, t, xlo, xhi, full, fa);
                 publishTop(S, d & 1, lane, warp, fa);
             }
@@ -446,17 +456,19 @@ struct CtaK {
             // ------------------------------------------------------------------ traceback from diagonal d
             const bool atEnd = d == nDiag;
             const int32_t tracedBackFrom = curFrom;
-            traceback(P, I, S, ring, t, lane, warp, d, xlo, xhi, wlo, cLo, eLo, tracedBackTo, tracedBackFrom, atEnd, nPairs);
+            traceback(P, I, S, ring, t, lane, warp, d, rowI, xlo, xhi, wlo, cLo, eLo, tracedBackTo, tracedBackFrom, atEnd,
+                      cOX, cEX, nPairs);
             tracedBackTo = tracedBackFrom;
             tbI++;
             nextT = tbI < nTb ? tbList[tbI] : nDiag;
             curFrom = nextT - (nextT == nDiag ? 0 : P.traceBack + 1);
+            backMod = (curFrom - (d + 1)) % 10;
             if (atEnd) break;
             // restore the forward sweep: f(d), f(d-1) from the ring (all three planes were kept above tracedBackFrom)
             __syncthreads();
             {
-                const double *r0 = ring + (int64_t) (d % P.rowsCap) * ROW + 2 + t;
-                const double *r1 = ring + (int64_t) ((d - 1) % P.rowsCap) * ROW + 2 + t;
+                const double *r0 = ring + (int64_t) rowI * ROW + 2 + t;
+                const double *r1 = ring + (int64_t) (rowI == 0 ? cap - 1 : rowI - 1) * ROW + 2 + t;
                 double cur[3], prv[3], nb[3];
 #pragma unroll
                 for (int s3 = 0; s3 < 3; s3++) { cur[s3] = r0[s3 * NS]; prv[s3] = r1[s3 * NS]; }

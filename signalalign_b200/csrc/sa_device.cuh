@@ -12,41 +12,42 @@
 #define SA_NEG_INF (__longlong_as_double(0xfff0000000000000LL))
 
 // The reference's four cubics for log(1 + e^x) on [0,1], (1,2.5], (2.5,4.5], (4.5,7.5): FLOAT literals promoted
-// to double (impl/pairwiseAligner.c:305-311).  They live in a 128-byte shared-memory table (row = range,
-// columns c3 c2 c1 c0) so that a logAdd fetches its coefficients with two conflict-free LDS.128 instead of
-// selecting 16 constants through the ALU; every kernel calls sa_logAdd_init() once per CTA.
-__shared__ __align__(16) double sa_lt[16];
+// to double (impl/pairwiseAligner.c:305-311).  They live in a 512-byte shared-memory table with one row (c3 c2 c1 c0)
+// per value of n = ceil(2 |x - y|) = 0..15: the range tests d > 1, d > 2.5, d > 4.5 are exactly n >= 3, n >= 6, n >= 10
+// (2 d is exact and the thresholds are half-integers), so ONE F2I.F64.CEIL replaces three DSETP and the predicate
+// arithmetic, and a logAdd fetches its coefficients with two conflict-free LDS.128.  Every kernel calls
+// sa_logAdd_init() once per CTA.
+__shared__ __align__(16) double sa_lt[64];
 
 __device__ __forceinline__ void sa_logAdd_init() {
     const float c[16] = {-0.009350833524763f, 0.130659527668286f, 0.498799810682272f, 0.693203116424741f,
                          -0.014532321752540f, 0.139942324101744f, 0.495635523139337f, 0.692140569840976f,
                          -0.004605031767994f, 0.063427417320019f, 0.695956496475118f, 0.514272634594009f,
                          -0.000458661602210f, 0.009695946122598f, 0.930734667215156f, 0.168037164329057f};
-    if (threadIdx.x < 16) {
+    for (int i = threadIdx.x; i < 64; i += blockDim.x) {
+        const int n = i >> 2, range = (n >= 3) + (n >= 6) + (n >= 10), k = range * 4 + (i & 3);
         float v = c[0];
 #pragma unroll
-        for (int i = 1; i < 16; i++) v = threadIdx.x == i ? c[i] : v;
-        sa_lt[threadIdx.x] = (double) v;
+        for (int q = 1; q < 16; q++) v = k == q ? c[q] : v;
+        sa_lt[i] = (double) v;
     }
     __syncthreads();
 }
 
 // logAdd (impl/pairwiseAligner.c:314-318): max when either operand is -inf or |x-y| >= 7.5, else
-// min + lookup(|x-y|), Horner without contraction.  Branch-free; integer tests on the high word where exact.
+// min + lookup(|x-y|), Horner without contraction.  Branch-free.
 __device__ __forceinline__ double sa_logAdd(double x, double y) {
     const double diff = __dsub_rn(x, y);
-    const int dh = __double2hiint(diff);
-    const bool xlt = dh < 0;                       // x < y  (diff == +0 when equal; NaN only when both are -inf)
+    const bool xlt = __double2hiint(diff) < 0;     // x < y  (diff == +0 when equal; NaN only when both are -inf)
     const double hi = xlt ? y : x;
     const double lo = xlt ? x : y;
-    const int ah = dh & 0x7fffffff;                // high word of |diff|
-    // |diff| >= 7.5, |diff| == inf (one operand -inf) and NaN (both -inf) all have ah >= hi(7.5) = 0x401E0000
-    const bool far = ah >= 0x401E0000;
-    // |diff| itself: when far the cubic's result is discarded (idx stays in 0..3 even for inf / NaN)
-    const double d = __hiloint2double(ah, __double2loint(diff));
-    const int idx = (int) (d > 1.0) + (int) (d > 2.5) + (int) (d > 4.5);
-    const double2 ca = *reinterpret_cast<const double2 *>(sa_lt + 4 * idx);
-    const double2 cb = *reinterpret_cast<const double2 *>(sa_lt + 4 * idx + 2);
+    const double d = fabs(diff);                   // folded into the consumers as an operand modifier
+    // |diff| >= 7.5, |diff| == inf (one operand -inf) and NaN (both -inf): the cubic's result is discarded
+    const bool far = !(d < 7.5);
+    // n = ceil(2 d), clamped into the table (F2I saturates for inf and returns 0 for NaN)
+    const int n = min(__double2int_ru(__dadd_rn(d, d)), 15);
+    const double2 ca = *reinterpret_cast<const double2 *>(sa_lt + 4 * n);
+    const double2 cb = *reinterpret_cast<const double2 *>(sa_lt + 4 * n + 2);
     double r = __dmul_rn(ca.x, d);
     r = __dmul_rn(__dadd_rn(r, ca.y), d);
     r = __dmul_rn(__dadd_rn(r, cb.x), d);

@@ -14,6 +14,6 @@ python bench.py --steps 2 --warmup 1 --no-cpu > gpurun_out/${TAG}_bench_short.js
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/${TAG}_launches.csv \
     python bench.py --steps 2 --warmup 1 --no-cpu > gpurun_out/${TAG}_ncu_launches.log 2>&1
 python bench.py --steps 1 --warmup 1 --reads ${NCU_READS} --no-cpu > gpurun_out/${TAG}_bench_ncu_cfg.json 2>> gpurun_out/${TAG}_bench.err && \
-ncu --set full --clock-control none --import-source on -k regex:sa_fast_kernel -c 1 -f -o gpurun_out/${TAG}_fast_full \
+ncu --set full --clock-control none --import-source on -k regex:sa_cta_kernel -c 1 -f -o gpurun_out/${TAG}_cta_full \
     python bench.py --steps 1 --warmup 0 --reads ${NCU_READS} --no-cpu > gpurun_out/${TAG}_ncu_full.log 2>&1
 tail -3 gpurun_out/${TAG}_pytest.txt; cat gpurun_out/${TAG}_peak_fp.jsonl; cat gpurun_out/${TAG}_bench.json | cut -c1-1500
