@@ -5,8 +5,8 @@
 //
 //   * thread t owns slot t of NS = 32 W slots; slot = column mod NS inside a sliding window [wlo, wlo + NS), so along a
 //     diagonal the `upper` neighbour (x, y-1) is the thread's own register and `lower` / `middle` (x-1, .) come from
-//     thread t-1: one __shfl_up per value inside a warp, a 4-double shared-memory mailbox between warps, ONE
-//     __syncthreads per diagonal.
+//     thread t-1 through a double-buffered shared-memory mailbox (3 doubles per thread), ONE __syncthreads per
+//     diagonal.
 //   * per-thread state is a dozen doubles (f(d-1), f(d-2) of one column), so registers allow ~5 CTAs of 128 threads per
 //     SM (20 warps) instead of the 8 warps the 4-cells-per-lane layout reached: the FP64 dependency chains of the
 //     logAdd are hidden by warp interleaving instead of by compiler-scheduled ILP.
@@ -16,8 +16,8 @@
 //     forward critical path.
 //   * forward rows go to the same HBM ring as before (row = [xlo, xhi | M plane | X plane | Y plane]) for the blocked
 //     traceback; the backward sweep mirrors the forward one (neighbours from thread t+1).
-//   * total probability: the per-cell terms go through shared memory and EVERY warp folds them redundantly in column
-//     order (the fold is sequential and non-associative), so no broadcast is needed.
+//   * total probability: the per-cell terms go through shared memory and warp 0 folds them in column order (the fold
+//     is sequential and non-associative), skipping exact no-ops; the result is broadcast through shared memory.
 //   * posterior pairs: exp() only for cells that can reach the threshold; hits are counted per warp (ballot) and written
 //     one barrier later in the reference's order.
 #pragma once
@@ -33,8 +33,9 @@ struct CtaK {
     struct Smem {
         double cst[5][RN];       // km, iM, cM, iY, cY per column (index = column & (RN - 1))
         double evs[RN];          // event mean per y (index = y & (RN - 1)); 0 outside [1, lY]
-        double xch[2][W][4];     // warp-boundary mailbox, double buffered by diagonal parity
+        double nbx[2][3][NT];    // neighbour mailbox: every thread's 3 newest values, double buffered by diagonal parity
         double foldv[2][NS];     // total-probability terms by slot
+        double sTotal;           // ... and their ordered fold (warp 0 computes, everybody reads)
         int2 bandTab[NT];        // [xlo, xhi] of forward diagonals bd0 .. bd0 + NT - 1
         int32_t aX[NT + 1], aY[NT + 1], aD[NT + 1];   // staged anchors (+1 coordinates) and their diagonals
         unsigned hitM[2][W];     // posterior hits per warp (ballot), double buffered
@@ -70,8 +71,8 @@ struct CtaK {
     static __device__ __forceinline__ void ensureRings(const FParams &P, const FItem &I, Smem &S, int t, int32_t wlo,
                                                        int32_t d, int32_t &cLo, int32_t &eLo) {
         const int32_t ymin = d - (wlo + NS - 1);
-        const bool needC = wlo < cLo || wlo + NS > cLo + RN;
-        const bool needE = ymin < eLo || ymin + NS > eLo + RN;
+        const bool needC = (unsigned) (wlo - cLo) > (unsigned) (RN - NS);    // wlo < cLo || wlo + NS > cLo + RN
+        const bool needE = (unsigned) (ymin - eLo) > (unsigned) (RN - NS);
         if (needC || needE) {
             __syncthreads();   // nobody still reads the old contents
             if (needC) { cLo = wlo - NS / 2; fillConsts(P, I, S, t, cLo); }
@@ -120,41 +121,21 @@ struct CtaK {
     }
 
     // ------------------------------------------------------------------------------------------ neighbour exchange
-    template <int N>
-    static __device__ __forceinline__ void publishTop(Smem &S, int buf, int lane, int warp, const double (&v)[N]) {
-        if (W > 1 && lane == 31) {
+    // every thread posts the three values its neighbours need; one barrier later the neighbour reads them.  (Plain
+    // shared-memory traffic instead of shuffles: no lane-dependent branches at the warp boundaries, 3 STS + 3 LDS.)
+    static __device__ __forceinline__ void publish(Smem &S, int buf, int t, const double (&v)[3]) {
 #pragma unroll
-            for (int i = 0; i < N; i++) S.xch[buf][warp][i] = v[i];
-        }
+        for (int i = 0; i < 3; i++) S.nbx[buf][i][t] = v[i];
     }
-    template <int N>
-    static __device__ __forceinline__ void fetchUp(const Smem &S, int buf, int lane, int warp, const double (&v)[N],
-                                                   double (&o)[N]) {
+    static __device__ __forceinline__ void fetchUp(const Smem &S, int buf, int t, double (&o)[3]) {   // from slot t - 1
+        const int src = (t + NT - 1) & (NT - 1);
 #pragma unroll
-        for (int i = 0; i < N; i++) o[i] = __shfl_sync(0xffffffffu, v[i], (lane + 31) & 31);
-        if (W > 1 && lane == 0) {
-            const int src = (warp + W - 1) % W;
-#pragma unroll
-            for (int i = 0; i < N; i++) o[i] = S.xch[buf][src][i];
-        }
+        for (int i = 0; i < 3; i++) o[i] = S.nbx[buf][i][src];
     }
-    template <int N>
-    static __device__ __forceinline__ void publishBottom(Smem &S, int buf, int lane, int warp, const double (&v)[N]) {
-        if (W > 1 && lane == 0) {
+    static __device__ __forceinline__ void fetchDown(const Smem &S, int buf, int t, double (&o)[3]) {  // from slot t + 1
+        const int src = (t + 1) & (NT - 1);
 #pragma unroll
-            for (int i = 0; i < N; i++) S.xch[buf][warp][i] = v[i];
-        }
-    }
-    template <int N>
-    static __device__ __forceinline__ void fetchDown(const Smem &S, int buf, int lane, int warp, const double (&v)[N],
-                                                     double (&o)[N]) {
-#pragma unroll
-        for (int i = 0; i < N; i++) o[i] = __shfl_sync(0xffffffffu, v[i], (lane + 1) & 31);
-        if (W > 1 && lane == 31) {
-            const int src = (warp + 1) % W;
-#pragma unroll
-            for (int i = 0; i < N; i++) o[i] = S.xch[buf][src][i];
-        }
+        for (int i = 0; i < 3; i++) o[i] = S.nbx[buf][i][src];
     }
 
     static __device__ __forceinline__ void emissions(const Smem &S, int32_t x, int32_t y, double &eM, double &eY) {
@@ -273,7 +254,7 @@ struct CtaK {
         __syncthreads();                       // the forward mailbox writes of step d are done with
         {
             const double pub[3] = {curM, curE, qX};
-            publishBottom(S, d & 1, lane, warp, pub);
+            publish(S, d & 1, t, pub);
         }
         double total = SA_NEG_INF;
         int32_t postMod = 0, bxlo = xlo, bxhi = xhi;   // postMod: posterior diagonals since the last total, mod 10
@@ -323,9 +304,8 @@ struct CtaK {
                     curM = SA_NEG_INF; curE = 0.0; nxtM = SA_NEG_INF; nxtE = 0.0;
                     qX = SA_NEG_INF; qY = SA_NEG_INF; qE = 0.0;
                 }
-                const double own[3] = {curM, curE, qX};
                 double nb[3];
-                fetchDown(S, (d2 + 1) & 1, lane, warp, own, nb);
+                fetchDown(S, (d2 + 1) & 1, t, nb);
                 const double aM = n1M, aE = n1E, lX = nb[2];
                 n1M = nb[0]; n1E = nb[1];
                 // gather in the order the reference's scatter delivers (see sa_general.cuh)
@@ -339,7 +319,7 @@ struct CtaK {
                 curM = act ? M : SA_NEG_INF; curE = eM;
                 qX = act ? X : SA_NEG_INF; qY = act ? Y : SA_NEG_INF; qE = eY;
                 const double pub[3] = {curM, curE, qX};
-                publishBottom(S, d2 & 1, lane, warp, pub);
+                publish(S, d2 & 1, t, pub);
             }
             if (!post) continue;
             const int32_t x = myx;
@@ -360,8 +340,12 @@ struct CtaK {
                 S.foldv[0][t] = v;
                 S.foldv[1][t] = m + nxtM;
                 __syncthreads();
-                const double tot = orderedFold(S, 0, lane, bw), tot2 = orderedFold(S, 1, lane, bw);
-                total = sa_logAdd(tot, tot2);
+                if (warp == 0) {               // the fold is sequential: one warp does it, the others keep their issue slots
+                    const double tot = orderedFold(S, 0, lane, bw), tot2 = orderedFold(S, 1, lane, bw);
+                    if (lane == 0) S.sTotal = sa_logAdd(tot, tot2);
+                }
+                __syncthreads();
+                total = S.sTotal;
             }
             // diagonalCalculationPosteriorMatchProbs (reference pairwiseAligner.c:1355-1421)
             const double arg = (fM + curM) - total;
@@ -413,7 +397,7 @@ struct CtaK {
             nbB[0] = nbB[1] = nbB[2] = SA_NEG_INF;
         }
         storeRow(ring, t, 0, 0, true, fa);
-        publishTop(S, 0, lane, warp, fa);
+        publish(S, 0, t, fa);
         int32_t tracedBackTo = 0;
         int tbI = 0;
         int32_t nextT = nTb > 0 ? tbList[0] : nDiag;
@@ -442,15 +426,15 @@ struct CtaK {
             double *row = ring + (int64_t) rowI * ROW;
             // f(d-1) lives in fa when d is odd, in fb when d is even; the result overwrites f(d-2)
             if (d & 1) {
-                fetchUp(S, (d - 1) & 1, lane, warp, fa, nbA);
+                fetchUp(S, (d - 1) & 1, t, nbA);
                 forwardCell(P, S, x, d, act, cOX, cEX, fa, nbA, nbB, fb);
                 storeRow(row, t, xlo, xhi, full, fb);
-                publishTop(S, d & 1, lane, warp, fb);
+                publish(S, d & 1, t, fb);
             } else {
-                fetchUp(S, (d - 1) & 1, lane, warp, fb, nbB);
+                fetchUp(S, (d - 1) & 1, t, nbB);
                 forwardCell(P, S, x, d, act, cOX, cEX, fb, nbB, nbA, fa);
                 storeRow(row, t, xlo, xhi, full, fa);
-                publishTop(S, d & 1, lane, warp, fa);
+                publish(S, d & 1, t, fa);
             }
             if (d != nextT) continue;
             // ------------------------------------------------------------------ traceback from diagonal d
@@ -472,10 +456,10 @@ struct CtaK {
                 double cur[3], prv[3], nb[3];
 #pragma unroll
                 for (int s3 = 0; s3 < 3; s3++) { cur[s3] = r0[s3 * NS]; prv[s3] = r1[s3 * NS]; }
-                publishTop(S, (d - 1) & 1, lane, warp, prv);
+                publish(S, (d - 1) & 1, t, prv);
                 __syncthreads();
-                fetchUp(S, (d - 1) & 1, lane, warp, prv, nb);
-                publishTop(S, d & 1, lane, warp, cur);
+                fetchUp(S, (d - 1) & 1, t, nb);
+                publish(S, d & 1, t, cur);
 #pragma unroll
                 for (int s3 = 0; s3 < 3; s3++) {
                     if (d & 1) { fb[s3] = cur[s3]; fa[s3] = prv[s3]; nbA[s3] = nb[s3]; }

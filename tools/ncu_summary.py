@@ -71,3 +71,10 @@ for k, v in agg.most_common(40):
 print("\n== by opcode (top 30)")
 for k, v in opagg.most_common(30):
     print("%-12s %14d %5.1f%%" % (k, v, 100.0 * v / tot))
+
+if len(sys.argv) > 4:   # per-line listing of one source file in line order: tools/ncu_summary.py rep so kern file.cuh [unit]
+    want = sys.argv[4]
+    unit = float(sys.argv[5]) if len(sys.argv) > 5 else 1.0
+    print("\n== %s in line order (count / %g)" % (want, unit))
+    for k in sorted(k for k in agg if k and k[0] == want):
+        print("%5d %10.2f" % (k[1], agg[k] / unit))
