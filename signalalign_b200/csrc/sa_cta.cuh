@@ -38,7 +38,7 @@ struct CtaK {
         double sTotal;           // ... and their ordered fold (warp 0 computes, everybody reads)
         int2 bandTab[NT];        // [xlo, xhi] of forward diagonals bd0 .. bd0 + NT - 1
         int32_t aX[NT + 1], aY[NT + 1], aD[NT + 1];   // staged anchors (+1 coordinates) and their diagonals
-        unsigned hitM[2][W];     // posterior hits per warp (ballot), double buffered
+        alignas(16) unsigned hitM[2][W < 4 ? 4 : W];   // posterior hits per warp (ballot), double buffered
         int32_t sItem, sAi;
     };
 
@@ -146,46 +146,51 @@ struct CtaK {
         eY = fma(-0.5 * aY, aY, S.cst[4][cs]);
     }
 
-    // sequential logAdd fold of S.foldv[which][*] in column order, skipping exact no-ops (see FastK::orderedFold);
-    // every warp computes the same value
-    static __device__ __forceinline__ double orderedFold(const Smem &S, int which, int lane, int32_t wlo) {
+    // The two sequential logAdd folds of S.foldv[0][*] and S.foldv[1][*] in column order, run by ONE warp.  Cells that
+    // cannot change an accumulator are skipped exactly: logAdd(acc, v) == acc whenever v <= acc - 7.5, and acc >= every
+    // value folded so far, so v <= prefixMax - 7.6 is an exact no-op (and folding such a cell anyway is harmless, which
+    // lets both folds walk the UNION of their candidate lanes: two independent dependency chains in flight).
+    static __device__ __forceinline__ void orderedFold2(const Smem &S, int lane, int32_t wlo, double &out0, double &out1) {
         const int s0 = wlo & (NS - 1);
-        double v[W];
+        double v[2][W];
+        unsigned cand[2][W], any = 0;
 #pragma unroll
-        for (int j = 0; j < W; j++) v[j] = S.foldv[which][(s0 + lane * W + j) & (NS - 1)];
-        double mx = v[0];
+        for (int f = 0; f < 2; f++) {
 #pragma unroll
-        for (int j = 1; j < W; j++) mx = fmax(mx, v[j]);
-        double run = mx;
+            for (int j = 0; j < W; j++) v[f][j] = S.foldv[f][(s0 + lane * W + j) & (NS - 1)];
+            double mx = v[f][0];
 #pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            double q = __shfl_up_sync(0xffffffffu, run, o);
-            if (lane >= o) run = fmax(run, q);
+            for (int j = 1; j < W; j++) mx = fmax(mx, v[f][j]);
+            double run = mx;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const double q = __shfl_up_sync(0xffffffffu, run, o);
+                if (lane >= o) run = fmax(run, q);
+            }
+            double pm = __shfl_up_sync(0xffffffffu, run, 1);
+            if (lane == 0) pm = SA_NEG_INF;
+#pragma unroll
+            for (int j = 0; j < W; j++) {
+                const bool c = v[f][j] > pm - 7.6;   // false for -inf
+                cand[f][j] = __ballot_sync(0xffffffffu, c);
+                any |= cand[f][j];
+                pm = fmax(pm, v[f][j]);
+            }
         }
-        double excl = __shfl_up_sync(0xffffffffu, run, 1);
-        if (lane == 0) excl = SA_NEG_INF;
-        unsigned cand[W];
-        double pm = excl;
-#pragma unroll
-        for (int j = 0; j < W; j++) {
-            const bool c = v[j] > pm - 7.6;   // false for -inf
-            cand[j] = __ballot_sync(0xffffffffu, c);
-            pm = fmax(pm, v[j]);
-        }
-        unsigned any = 0;
-#pragma unroll
-        for (int j = 0; j < W; j++) any |= cand[j];
-        double acc = SA_NEG_INF;
+        double acc0 = SA_NEG_INF, acc1 = SA_NEG_INF;
         while (any) {
             const int ln = __ffs(any) - 1;
             any &= any - 1;
 #pragma unroll
             for (int j = 0; j < W; j++) {
-                const double q = __shfl_sync(0xffffffffu, v[j], ln);
-                if ((cand[j] >> ln) & 1u) acc = sa_logAdd(acc, q);
+                const double q0 = __shfl_sync(0xffffffffu, v[0][j], ln), q1 = __shfl_sync(0xffffffffu, v[1][j], ln);
+                if (((cand[0][j] | cand[1][j]) >> ln) & 1u) {   // uniform branch
+                    acc0 = sa_logAdd(acc0, q0);
+                    acc1 = sa_logAdd(acc1, q1);
+                }
             }
         }
-        return acc;
+        out0 = acc0; out1 = acc1;
     }
 
     // f(d) of this thread's cell from the own column on d-1 (f1), and the left neighbour on d-1 (n1) and d-2 (n2)
@@ -264,8 +269,17 @@ struct CtaK {
         auto flush = [&]() {
             unsigned m[W];
             int tot = 0;
+            {
+                const uint4 *hp = reinterpret_cast<const uint4 *>(S.hitM[pendD & 1]);
 #pragma unroll
-            for (int w = 0; w < W; w++) { m[w] = S.hitM[pendD & 1][w]; tot += __popc(m[w]); }
+                for (int w4 = 0; w4 < (W + 3) / 4; w4++) {
+                    const uint4 q = hp[w4];
+                    const unsigned qq[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+                    for (int w = 0; w < 4; w++)
+                        if (w4 * 4 + w < W) { m[w4 * 4 + w] = qq[w]; tot += __popc(qq[w]); }
+                }
+            }
             if (pendHit) {
                 const int a = hitsBelow(m, pendS0), b = hitsBelow(m, t);
                 const int before = pendS0 <= t ? b - a : tot - a + b;
@@ -341,7 +355,8 @@ struct CtaK {
                 S.foldv[1][t] = m + nxtM;
                 __syncthreads();
                 if (warp == 0) {               // the fold is sequential: one warp does it, the others keep their issue slots
-                    const double tot = orderedFold(S, 0, lane, bw), tot2 = orderedFold(S, 1, lane, bw);
+                    double tot, tot2;
+                    orderedFold2(S, lane, bw, tot, tot2);
                     if (lane == 0) S.sTotal = sa_logAdd(tot, tot2);
                 }
                 __syncthreads();
@@ -351,15 +366,13 @@ struct CtaK {
             const double arg = (fM + curM) - total;
             const bool cand = x >= bxlo && x <= bxhi && x > 0 && d2 - x > 0 && arg >= P.logThrGate;
             bool hit = false;
-            double pp = 0.0;
             if (__any_sync(0xffffffffu, cand)) {
-                pp = exp(arg);
+                const double pp = exp(arg);
                 hit = cand && pp >= P.threshold;
+                pendP = (int32_t) floor((pp > 1.0 ? 1.0 : pp) * 10000000.0);
             }
-            const unsigned mk = __ballot_sync(0xffffffffu, hit);
-            if (lane == 0) S.hitM[d2 & 1][warp] = mk;
+            S.hitM[d2 & 1][warp] = __ballot_sync(0xffffffffu, hit);   // every lane stores the same word: no branch
             pendValid = true; pendHit = hit; pendX = x; pendD = d2; pendS0 = bw & (NS - 1);
-            pendP = (int32_t) floor((pp > 1.0 ? 1.0 : pp) * 10000000.0);
         }
         if (pendValid) {
             __syncthreads();
@@ -472,8 +485,11 @@ struct CtaK {
     }
 };
 
+// resident CTAs per SM the register allocation is held to: 20 warps for W = 2 and 4, 16 for W = 1 and 8
+template <int W> struct CtaOcc { static constexpr int kMinBlocks = W == 1 ? 16 : W == 2 ? 10 : W == 4 ? 5 : 2; };
+
 template <int W>
-__global__ void __launch_bounds__(32 * W) sa_cta_kernel(const FParams P) {
+__global__ void __launch_bounds__(32 * W, CtaOcc<W>::kMinBlocks) sa_cta_kernel(const FParams P) {
     __shared__ typename CtaK<W>::Smem S;
     sa_logAdd_init();
     double *ring = P.scratch + (int64_t) blockIdx.x * P.rowsCap * CtaK<W>::ROW;
