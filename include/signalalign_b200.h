@@ -134,9 +134,13 @@ int sa_gpu_init(int device);                 /* select device for this process/t
 const char *sa_last_error(void);
 int sa_gpu_device_count(void);
 
-/* One-shot drop-in for a batch of getAlignedPairsUsingAnchors calls (host buffers in, host result out). */
+/* One-shot drop-in for a batch of getAlignedPairsUsingAnchors calls (host buffers in, host result out).
+ * Large batches run as a pipeline of chunks: host packing, H2D, the band kernels and compaction + D2H of consecutive
+ * chunks overlap.  result->pairs is page-locked memory of libsagpu's pool: release it with sa_result_free only. */
 int sa_gpu_align_batch(const sa_model_t *m, const sa_read_t *reads, int64_t nReads, const sa_params_t *p,
                        const sa_ambig_t *ambig, sa_result_t **out);
+/* accounting of the last sa_gpu_align_batch of this process: bytes copied each way and kernels launched */
+void sa_last_call_stats(int64_t *h2dBytes, int64_t *d2hBytes, int64_t *launches);
 /* ... and of getExpectationsUsingAnchors (inc/pairwiseAligner.h:417-429; call site signalMachine.c:479).
  * Results are the per-read expectation sums WITHOUT pseudocounts. */
 int sa_gpu_expectations_batch(const sa_model_t *m, const sa_read_t *reads, int64_t nReads, const sa_params_t *p,

@@ -54,7 +54,7 @@ EXPORTS = [
     "sa_gpu_align_batch", "sa_gpu_expectations_batch", "sa_batch_prepare", "sa_batch_run", "sa_batch_fetch",
     "sa_batch_last_timing", "sa_batch_band_cells", "sa_batch_kernel_items", "sa_batch_h2d_bytes", "sa_batch_d2h_bytes", "sa_batch_free",
     "sa_result_sum_expectations", "sa_debug_logadd", "sa_model_hdp_dims", "sa_model_get_hdp", "sa_debug_band",
-    "sa_debug_split_points", "sa_debug_kmer_paths",
+    "sa_debug_split_points", "sa_debug_kmer_paths", "sa_last_call_stats",
 ]
 
 _lib = None
@@ -93,6 +93,8 @@ def lib():
     L.sa_model_alphabet.restype = C.c_char_p
     L.sa_model_alphabet.argtypes = [C.c_void_p]
     L.sa_model_get_tables.argtypes = [C.c_void_p, c_f64p, c_f64p, c_f64p]
+    L.sa_last_call_stats.restype = None
+    L.sa_last_call_stats.argtypes = [C.POINTER(C.c_int64)] * 3
     L.sa_model_hdp_density.restype = C.c_double
     L.sa_model_hdp_density.argtypes = [C.c_void_p, C.c_int64, C.c_double]
     L.sa_params_default.argtypes = [C.POINTER(SaParams)]
@@ -259,8 +261,15 @@ class Read:
         self.anchors = np.ascontiguousarray(anchors, np.int64).reshape(-1, 2)
         self.scale, self.shift, self.var = float(scale), float(shift), float(var)
         self.ragged_left, self.ragged_right = bool(ragged_left), bool(ragged_right)
+        self._c = None
 
     def cstruct(self):
+        """the sa_read_t over this read's buffers (built once: the arrays are owned by the object and never re-bound)"""
+        if self._c is None:
+            self._c = self._build()
+        return self._c
+
+    def _build(self):
         return SaRead(self.target, len(self.target), self.events.ctypes.data_as(c_f64p), self.events.shape[0],
                       self.anchors.ctypes.data_as(c_i64p), self.anchors.shape[0], self.scale, self.shift, self.var,
                       int(self.ragged_left), int(self.ragged_right))
@@ -345,6 +354,13 @@ def expectations_batch(model, reads, params=None, ambig=None):
     _check(lib().sa_gpu_expectations_batch(model.h, arr, len(reads), C.byref(params), ambig.h if ambig else None,
                                            C.byref(out)))
     return Result(out)
+
+
+def last_call_stats():
+    """(H2D bytes, D2H bytes, kernel launches) of the last align_batch call of this process"""
+    a, b, c = C.c_int64(0), C.c_int64(0), C.c_int64(0)
+    lib().sa_last_call_stats(C.byref(a), C.byref(b), C.byref(c))
+    return a.value, b.value, c.value
 
 
 def debug_logadd(x, y):

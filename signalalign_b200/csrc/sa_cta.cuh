@@ -23,6 +23,25 @@
 #pragma once
 #include "sa_fast.cuh"
 
+// Split CTA barrier (mbarrier in shared memory): a thread ARRIVES right after posting its mailbox values and WAITS only
+// when it needs its neighbour's, so the row store, the loop bookkeeping and the next cell's emissions overlap the wait
+// for the slowest warp.  arrive = release, wait = acquire (CTA scope), so the mailbox writes are visible after the wait.
+__device__ __forceinline__ void sa_mbInit(unsigned long long *bar, int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"((unsigned) __cvta_generic_to_shared(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void sa_mbArrive(unsigned long long *bar) {
+    asm volatile("{\n\t.reg .b64 st;\n\tmbarrier.arrive.shared::cta.b64 st, [%0];\n\t}" ::"r"((unsigned) __cvta_generic_to_shared(bar)) : "memory");
+}
+__device__ __forceinline__ void sa_mbWait(unsigned long long *bar, unsigned &phase) {
+    unsigned ok;
+    const unsigned addr = (unsigned) __cvta_generic_to_shared(bar);
+    do {
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                     : "=r"(ok) : "r"(addr), "r"(phase) : "memory");
+    } while (!ok);
+    phase ^= 1u;
+}
+
 template <int W>
 struct CtaK {
     static constexpr int NT = 32 * W;        // threads = slots
@@ -40,6 +59,7 @@ struct CtaK {
         int32_t aX[NT + 1], aY[NT + 1], aD[NT + 1];   // staged anchors (+1 coordinates) and their diagonals
         alignas(16) unsigned hitM[2][W < 4 ? 4 : W];   // posterior hits per warp (ballot), double buffered
         int32_t sItem, sAi;
+        unsigned long long mbar; // split barrier of the diagonal steps
     };
 
     static __device__ __forceinline__ int32_t slotX(int32_t s, int32_t wlo) { return wlo + ((s - wlo) & (NS - 1)); }
@@ -77,6 +97,7 @@ struct CtaK {
             __syncthreads();   // nobody still reads the old contents
             if (needC) { cLo = wlo - NS / 2; fillConsts(P, I, S, t, cLo); }
             if (needE) { eLo = ymin - NS / 2; fillEvents(P, I, S, t, eLo); }
+            __syncthreads();
         }
     }
 
@@ -195,11 +216,10 @@ struct CtaK {
 
     // f(d) of this thread's cell from the own column on d-1 (f1), and the left neighbour on d-1 (n1) and d-2 (n2)
     static __device__ __forceinline__ void forwardCell(const FParams &P, const Smem &S, int32_t x, int32_t d, bool act,
-                                                       double cOX, double cEX, const double (&f1)[3],
-                                                       const double (&n1)[3], const double (&n2)[3], double (&o)[3]) {
+                                                       double cOX, double cEX, double eM, double eY,
+                                                       const double (&f1)[3], const double (&n1)[3],
+                                                       const double (&n2)[3], double (&o)[3]) {
         const double *T = P.trans;
-        double eM, eY;
-        emissions(S, x, d - x, eM, eY);
         // stateMachine3_cellCalculate order; the first contribution lands on -inf (logAdd(-inf, v) == v exactly)
         const double X = sa_logAdd(n1[0] + cOX, n1[1] + cEX);
         const double M = sa_logAdd(sa_logAdd(n2[0] + (eM + T[T_MATCH_CONTINUE]), n2[1] + (eM + T[T_MATCH_FROM_GAP_X])),
@@ -238,7 +258,7 @@ struct CtaK {
                                                      int lane, int warp, int32_t d, int32_t rowI, int32_t xlo, int32_t xhi,
                                                      int32_t bw, int32_t &cLo, int32_t &eLo, int32_t tracedBackTo,
                                                      int32_t tracedBackFrom, bool atEnd, double cOX, double cEX,
-                                                     int64_t &nPairs) {
+                                                     unsigned &phase, int64_t &nPairs) {
         const double *T = P.trans;
         const int32_t cap = P.rowsCap;
         // end / ragged-end state on diagonal d (reference stateMachine.c:1147-1173)
@@ -256,11 +276,7 @@ struct CtaK {
             curM = act ? e0 : SA_NEG_INF; curE = eM;
             qX = act ? e1 : SA_NEG_INF; qY = act ? e2 : SA_NEG_INF; qE = eY;
         }
-        __syncthreads();                       // the forward mailbox writes of step d are done with
-        {
-            const double pub[3] = {curM, curE, qX};
-            publish(S, d & 1, t, pub);
-        }
+        sa_mbWait(&S.mbar, phase);             // everybody has posted (and finished reading for) forward step d
         double total = SA_NEG_INF;
         int32_t postMod = 0, bxlo = xlo, bxhi = xhi;   // postMod: posterior diagonals since the last total, mod 10
         // posterior hit of the previous diagonal, written after the next barrier (needs every warp's ballot)
@@ -310,14 +326,16 @@ struct CtaK {
                     hdrNext = *reinterpret_cast<const int2 *>(ring + (int64_t) rowP * ROW);
                 if (bxlo < bw) bw = bxlo;      // lower the window; recycled slots restart at -inf
                 ensureRings(P, I, S, t, bw, d2, cLo, eLo);
-                __syncthreads();
-                if (pendValid) flush();
                 const int32_t x = slotX(t, bw);
                 if (x != myx) {
                     myx = x;
                     curM = SA_NEG_INF; curE = 0.0; nxtM = SA_NEG_INF; nxtE = 0.0;
                     qX = SA_NEG_INF; qY = SA_NEG_INF; qE = 0.0;
                 }
+                double eM, eY;
+                emissions(S, x, d2 - x, eM, eY);
+                sa_mbWait(&S.mbar, phase);     // mailbox and hit masks of diagonal d2 + 1 are visible
+                if (pendValid) flush();
                 double nb[3];
                 fetchDown(S, (d2 + 1) & 1, t, nb);
                 const double aM = n1M, aE = n1E, lX = nb[2];
@@ -326,16 +344,16 @@ struct CtaK {
                 const double M = sa_logAdd(sa_logAdd(aM + (aE + T[T_MATCH_CONTINUE]), qY + (qE + T[T_GAP_OPEN_Y])), lX + cOX);
                 const double X = sa_logAdd(aM + (aE + T[T_MATCH_FROM_GAP_X]), lX + cEX);
                 const double Y = sa_logAdd(aM + (aE + T[T_MATCH_FROM_GAP_Y]), qY + (qE + T[T_GAP_EXTEND_Y]));
-                double eM, eY;
-                emissions(S, x, d2 - x, eM, eY);
                 const bool act = x >= bxlo && x <= bxhi;
                 nxtM = curM; nxtE = curE;
                 curM = act ? M : SA_NEG_INF; curE = eM;
                 qX = act ? X : SA_NEG_INF; qY = act ? Y : SA_NEG_INF; qE = eY;
+            }
+            {
                 const double pub[3] = {curM, curE, qX};
                 publish(S, d2 & 1, t, pub);
             }
-            if (!post) continue;
+            if (!post) { sa_mbArrive(&S.mbar); continue; }
             const int32_t x = myx;
             const bool newTotal = postMod == 0;
             postMod = postMod == 9 ? 0 : postMod + 1;
@@ -373,14 +391,13 @@ struct CtaK {
             }
             S.hitM[d2 & 1][warp] = __ballot_sync(0xffffffffu, hit);   // every lane stores the same word: no branch
             pendValid = true; pendHit = hit; pendX = x; pendD = d2; pendS0 = bw & (NS - 1);
+            sa_mbArrive(&S.mbar);
         }
-        if (pendValid) {
-            __syncthreads();
-            flush();
-        }
+        sa_mbWait(&S.mbar, phase);             // the last diagonal's hit masks
+        if (pendValid) flush();
     }
 
-    static __device__ void run(const FParams &P, const FItem &I, int it, double *ring, Smem &S) {
+    static __device__ void run(const FParams &P, const FItem &I, int it, double *ring, Smem &S, unsigned &phase) {
         const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
         const double *T = P.trans;
         const int32_t nDiag = I.lX + I.lY;
@@ -411,6 +428,7 @@ struct CtaK {
         }
         storeRow(ring, t, 0, 0, true, fa);
         publish(S, 0, t, fa);
+        sa_mbArrive(&S.mbar);
         int32_t tracedBackTo = 0;
         int tbI = 0;
         int32_t nextT = nTb > 0 ? tbList[0] : nDiag;
@@ -426,7 +444,6 @@ struct CtaK {
             const int32_t xlo = bnd.x, xhi = bnd.y;
             if (xhi > wlo + NS - 1) wlo = xhi - (NS - 1);   // slide the window up; recycled slots restart at -inf
             ensureRings(P, I, S, t, wlo, d, cLo, eLo);
-            __syncthreads();                   // mailbox of step d-1 and any refill are visible
             const int32_t x = slotX(t, wlo);
             if (x != myx) {
                 myx = x;
@@ -437,24 +454,29 @@ struct CtaK {
             const bool full = curFrom - d < 0 || backMod <= 1;
             backMod = backMod == 0 ? 9 : backMod - 1;
             double *row = ring + (int64_t) rowI * ROW;
+            double eM, eY;
+            emissions(S, x, d - x, eM, eY);
+            sa_mbWait(&S.mbar, phase);         // the mailbox of step d - 1 is visible
             // f(d-1) lives in fa when d is odd, in fb when d is even; the result overwrites f(d-2)
             if (d & 1) {
                 fetchUp(S, (d - 1) & 1, t, nbA);
-                forwardCell(P, S, x, d, act, cOX, cEX, fa, nbA, nbB, fb);
-                storeRow(row, t, xlo, xhi, full, fb);
+                forwardCell(P, S, x, d, act, cOX, cEX, eM, eY, fa, nbA, nbB, fb);
                 publish(S, d & 1, t, fb);
+                sa_mbArrive(&S.mbar);
+                storeRow(row, t, xlo, xhi, full, fb);
             } else {
                 fetchUp(S, (d - 1) & 1, t, nbB);
-                forwardCell(P, S, x, d, act, cOX, cEX, fb, nbB, nbA, fa);
-                storeRow(row, t, xlo, xhi, full, fa);
+                forwardCell(P, S, x, d, act, cOX, cEX, eM, eY, fb, nbB, nbA, fa);
                 publish(S, d & 1, t, fa);
+                sa_mbArrive(&S.mbar);
+                storeRow(row, t, xlo, xhi, full, fa);
             }
             if (d != nextT) continue;
             // ------------------------------------------------------------------ traceback from diagonal d
             const bool atEnd = d == nDiag;
             const int32_t tracedBackFrom = curFrom;
             traceback(P, I, S, ring, t, lane, warp, d, rowI, xlo, xhi, wlo, cLo, eLo, tracedBackTo, tracedBackFrom, atEnd,
-                      cOX, cEX, nPairs);
+                      cOX, cEX, phase, nPairs);
             tracedBackTo = tracedBackFrom;
             tbI++;
             nextT = tbI < nTb ? tbList[tbI] : nDiag;
@@ -473,6 +495,7 @@ struct CtaK {
                 __syncthreads();
                 fetchUp(S, (d - 1) & 1, t, nb);
                 publish(S, d & 1, t, cur);
+                sa_mbArrive(&S.mbar);
 #pragma unroll
                 for (int s3 = 0; s3 < 3; s3++) {
                     if (d & 1) { fb[s3] = cur[s3]; fa[s3] = prv[s3]; nbA[s3] = nb[s3]; }
@@ -491,7 +514,9 @@ template <int W> struct CtaOcc { static constexpr int kMinBlocks = W == 1 ? 16 :
 template <int W>
 __global__ void __launch_bounds__(32 * W, CtaOcc<W>::kMinBlocks) sa_cta_kernel(const FParams P) {
     __shared__ typename CtaK<W>::Smem S;
-    sa_logAdd_init();
+    if (threadIdx.x == 0) sa_mbInit(&S.mbar, 32 * W);
+    sa_logAdd_init();                          // (ends with a barrier: the mbarrier is initialised for everybody)
+    unsigned phase = 0;
     double *ring = P.scratch + (int64_t) blockIdx.x * P.rowsCap * CtaK<W>::ROW;
     for (;;) {
         __syncthreads();
@@ -500,6 +525,6 @@ __global__ void __launch_bounds__(32 * W, CtaOcc<W>::kMinBlocks) sa_cta_kernel(c
         const int n = S.sItem;
         if (n >= P.nOrder) break;
         const int it = P.order[n];
-        CtaK<W>::run(P, P.items[it], it, ring, S);
+        CtaK<W>::run(P, P.items[it], it, ring, S, phase);
     }
 }

@@ -101,35 +101,100 @@ struct BandIt {
         }
         xay++;
     }
+    // position the iterator ON diagonal d0 >= 1, as if next() had been called for 0 .. d0 - 1: diagonal d lies between
+    // the last anchor whose diagonal (x + 1) + (y + 1) is < d and the first one >= d (or the end point (lX, lY))
+    __device__ __forceinline__ void seek(int32_t d0) {
+        int32_t lo = 0, hi = nA;
+        while (lo < hi) {
+            const int32_t mid = (lo + hi) >> 1;
+            if (anch[2 * mid] + anch[2 * mid + 1] + 2 >= d0) hi = mid; else lo = mid + 1;
+        }
+        int32_t px = 0, py = 0, x = lX, y = lY;
+        if (lo > 0) { px = anch[2 * (lo - 1)] + 1; py = anch[2 * (lo - 1) + 1] + 1; }
+        ai = lo;
+        if (ai < nA) { x = anch[2 * ai] + 1; y = anch[2 * ai + 1] + 1; ai++; }
+        pxay = px + py; pxmy = px - py;
+        nxay = x + y; nxmy = x - y;
+        xL = clampc((pxay + pxmy - e) / 2, lX);
+        yL = clampc((nxay - nxmy + e) / 2, lY);
+        xU = clampc((nxay + nxmy + e) / 2, lX);
+        yU = clampc((pxay - pxmy - e) / 2, lY);
+        xay = d0;
+    }
 };
 
-// One thread per item: walks the whole band once and records what the host needs to size buffers and what the
-// fast kernel needs to schedule its tracebacks (getPosteriorProbsWithBanding's traceback condition,
-// reference impl/pairwiseAligner.c:1493-1497, depends on geometry only).
-__global__ void sa_geometry_kernel(const FParams P) {
-    int it = blockIdx.x * blockDim.x + threadIdx.x;
+// One WARP per item: records what the host needs to size buffers and pick the kernel class, and the traceback
+// diagonals the band kernels follow (getPosteriorProbsWithBanding's traceback condition, reference
+// impl/pairwiseAligner.c:1493-1497, depends on geometry only).  The diagonals 0 .. lX+lY are cut into 32 contiguous
+// ranges, one per lane; a lane enters its range with BandIt::seek and walks it incrementally.  The traceback list is
+// periodic when no diagonal is wider than 2 * expansion + 1 (always, for banded nanopore reads); otherwise lane 0
+// walks the band once more for it.
+// (32-thread CTAs held to 32 registers: the pass of the NEXT batch runs next to the persistent band kernel of the one in
+// flight, in the 1024 registers that kernel leaves free in every SM sub-partition.)
+__global__ void __maxnreg__(32) sa_geometry_kernel(const FParams P) {
+    const int it = blockIdx.x, lane = threadIdx.x;
     if (it >= P.nItems) return;
     const FItem &I = P.items[it];
+    const int32_t nDiag = I.lX + I.lY;
     FGeo g;
     g.cells = 0; g.maxWidth = 0; g.nTb = 0; g.maxRows = 1; g.maxSpan = 0; g.monotone = 1; g.pad = 0;
-    int32_t nDiag = I.lX + I.lY;
-    if (nDiag == 0) { P.geo[it] = g; return; }
-    BandIt b;
-    b.init(P.anchors + 2 * I.anchorOff, I.nAnchors, I.lX, I.lY, P.expansion);
-    int32_t tracedBackTo = 0, pxlo = 0, pxhi = 0, ppxlo = 0;
+    if (nDiag == 0) {
+        if (lane == 0) P.geo[it] = g;
+        return;
+    }
+    const int32_t *anch = P.anchors + 2 * I.anchorOff;
+    {
+        const int32_t total = nDiag + 1, len = (total + 31) / 32;
+        const int32_t d0 = lane * len, d1 = min(d0 + len, total);
+        if (d0 < d1) {
+            BandIt b;
+            b.init(anch, I.nAnchors, I.lX, I.lY, P.expansion);
+            const int32_t ds = d0 >= 2 ? d0 - 2 : 0;   // two warm-up diagonals: the predecessors of d0
+            if (ds >= 1) b.seek(ds);
+            int32_t pxlo = 0, pxhi = 0, ppxlo = 0;
+            for (int32_t d = ds; d < d1; d++) {
+                int32_t xlo, xhi;
+                b.next(xlo, xhi);
+                if (d >= d0) {
+                    const int32_t w = xhi - xlo + 1;
+                    g.cells += w;
+                    g.maxWidth = max(g.maxWidth, w);
+                    if (d > 0 && (xlo < pxlo || xhi < pxhi)) g.monotone = 0;
+                    g.maxSpan = max(g.maxSpan, xhi - (d >= 2 ? ppxlo : (d >= 1 ? pxlo : xlo)) + 1);
+                }
+                ppxlo = pxlo; pxlo = xlo; pxhi = xhi;
+            }
+        }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        g.cells += __shfl_xor_sync(0xffffffffu, g.cells, o);
+        g.maxWidth = max(g.maxWidth, __shfl_xor_sync(0xffffffffu, g.maxWidth, o));
+        g.maxSpan = max(g.maxSpan, __shfl_xor_sync(0xffffffffu, g.maxSpan, o));
+        g.monotone &= __shfl_xor_sync(0xffffffffu, g.monotone, o);
+    }
+    if (lane != 0) return;
     int32_t *tb = P.tb + I.tbOff;
-    for (int32_t d = 0; d <= nDiag; d++) {
-        int32_t xlo, xhi;
-        b.next(xlo, xhi);
-        int32_t w = xhi - xlo + 1;
-        g.cells += w;
-        g.maxWidth = max(g.maxWidth, w);
-        if (d > 0 && (xlo < pxlo || xhi < pxhi)) g.monotone = 0;
-        g.maxSpan = max(g.maxSpan, xhi - (d >= 2 ? ppxlo : (d >= 1 ? pxlo : xlo)) + 1);
-        ppxlo = pxlo; pxlo = xlo; pxhi = xhi;
-        if (d >= 1) {
-            bool atEnd = d == nDiag;
-            bool tbp = d >= tracedBackTo + P.minDiags && w <= P.expansion * 2 + 1;
+    int32_t tracedBackTo = 0;
+    if (g.maxWidth <= P.expansion * 2 + 1) {
+        for (;;) {   // the first diagonal >= tracedBackTo + minDiags, or the last one
+            const int32_t d = min(tracedBackTo + P.minDiags, nDiag);
+            const bool atEnd = d == nDiag;
+            g.maxRows = max(g.maxRows, d - tracedBackTo + 1);
+            if (g.nTb < I.nTbCap) tb[g.nTb] = d;
+            g.nTb++;
+            if (atEnd) break;
+            tracedBackTo = d - (P.traceBack + 1);
+        }
+    } else {
+        BandIt b;
+        b.init(anch, I.nAnchors, I.lX, I.lY, P.expansion);
+        for (int32_t d = 0; d <= nDiag; d++) {
+            int32_t xlo, xhi;
+            b.next(xlo, xhi);
+            if (d == 0) continue;
+            const bool atEnd = d == nDiag;
+            const bool tbp = d >= tracedBackTo + P.minDiags && xhi - xlo + 1 <= P.expansion * 2 + 1;
             if (atEnd || tbp) {
                 g.maxRows = max(g.maxRows, d - tracedBackTo + 1);
                 if (g.nTb < I.nTbCap) tb[g.nTb] = d;
@@ -138,7 +203,7 @@ __global__ void sa_geometry_kernel(const FParams P) {
             }
         }
     }
-    if (g.nTb > I.nTbCap) g.monotone = 0;  // cannot happen (capacity is nDiag / minDiags + 2); be safe
+    if (g.nTb > I.nTbCap) g.monotone = 0;  // cannot happen (capacity is nDiag / (minDiags - traceBack - 1) + 2); be safe
     P.geo[it] = g;
 }
 

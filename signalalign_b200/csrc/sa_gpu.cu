@@ -155,12 +155,15 @@ static void *pinAcquire(size_t bytes) {
     g_pins[best].busy = true;
     return g_pins[best].p;
 }
-static void pinRelease(void *p) {
-    if (!p) return;
+static bool pinRelease(void *p) {
+    if (!p) return false;
     std::lock_guard<std::mutex> lk(g_pinMu);
     for (auto &sl : g_pins)
-        if (sl.p == p) sl.busy = false;
+        if (sl.p == p) { sl.busy = false; return true; }
+    return false;
 }
+// sa_result_free (sa_host.cpp): the pairs array of a result is a slab of this pool, D2H'ed into directly
+bool sa_pinned_release(void *p) { return pinRelease(p); }
 template <class T>
 struct PinVec {  // the few vector operations the packer needs, over pinned memory
     T *p = nullptr;
@@ -182,19 +185,37 @@ struct PinVec {  // the few vector operations the packer needs, over pinned memo
     ~PinVec() { pinRelease(p); }
 };
 
+// Device buffers come from the device's default memory pool in stream order (cudaMallocAsync / cudaFreeAsync) with the
+// pool's release threshold lifted, so that a batch neither pays cudaMalloc for its multi-GB slots every call nor stalls
+// the other batches in flight with the device-wide synchronisation of cudaFree.
+static int poolInit() {
+    static bool done[64] = {false};
+    int dev = 0;
+    CK(cudaGetDevice(&dev));
+    if (dev < 64 && done[dev]) return SA_OK;
+    cudaMemPool_t pool;
+    CK(cudaDeviceGetDefaultMemPool(&pool, dev));
+    uint64_t keep = UINT64_MAX;
+    CK(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep));
+    if (dev < 64) done[dev] = true;
+    return SA_OK;
+}
+
 template <class T>
 struct DevBuf {
     T *p = nullptr;
     size_t n = 0;
-    int alloc(size_t count) {
+    cudaStream_t s = nullptr;   // the stream the buffer was allocated on (and is freed on)
+    int alloc(size_t count, cudaStream_t st) {
         release();
         n = count;
+        s = st;
         if (count == 0) return SA_OK;
-        CK(cudaMalloc(&p, count * sizeof(T)));
+        CK(cudaMallocAsync((void **) &p, count * sizeof(T), st));
         return SA_OK;
     }
     int upload(const std::vector<T> &v, cudaStream_t s, int64_t *bytes) {
-        int rc = alloc(v.size());
+        int rc = alloc(v.size(), s);
         if (rc) return rc;
         if (!v.empty()) {
             CK(cudaMemcpyAsync(p, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice, s));
@@ -203,7 +224,7 @@ struct DevBuf {
         return SA_OK;
     }
     int upload(const PinVec<T> &v, cudaStream_t s, int64_t *bytes) {
-        int rc = alloc(v.size());
+        int rc = alloc(v.size(), s);
         if (rc) return rc;
         if (!v.empty()) {
             CK(cudaMemcpyAsync(p, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice, s));
@@ -212,7 +233,7 @@ struct DevBuf {
         return SA_OK;
     }
     void release() {
-        if (p) cudaFree(p);
+        if (p) cudaFreeAsync(p, s);
         p = nullptr;
         n = 0;
     }
@@ -238,7 +259,15 @@ struct sa_batch {
     sa_params_t params;
     bool expectations = false;
     int64_t nReads = 0;
-    cudaStream_t stream = nullptr;
+    struct StreamOwner {         // declared before every DevBuf: destroyed after their stream-ordered frees were queued
+        cudaStream_t s = nullptr;
+        ~StreamOwner() { if (s) cudaStreamDestroy(s); }
+    } streamOwner, auxOwner;
+    cudaStream_t stream = nullptr;  // the band kernels
+    // everything else (H2D, geometry pass, compaction, D2H) on a HIGH-priority stream: when several batches are in
+    // flight, these small kernels must overtake the not yet resident CTAs of another batch's persistent band kernel
+    cudaStream_t aux = nullptr;
+    cudaEvent_t evPrepared = nullptr;
     cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     std::vector<ItemRec> items;  // global item id = index
     // shared inputs
@@ -275,9 +304,10 @@ struct sa_batch {
     int64_t lastLaunches = 0;
     std::vector<int64_t> pairCountHost, assignCountHost;
     ~sa_batch() {
+        if (stream) cudaStreamSynchronize(stream);   // the buffers are freed in the order of the aux stream
         for (auto &e : ev)
             if (e) cudaEventDestroy(e);
-        if (stream) cudaStreamDestroy(stream);
+        if (evPrepared) cudaEventDestroy(evPrepared);
     }
 };
 
@@ -297,8 +327,9 @@ static bool modelFastEligible(const sa_model *m) {
     return true;
 }
 
-extern "C" int sa_batch_prepare(const sa_model_t *m, const sa_read_t *reads, int64_t nReads, const sa_params_t *p,
-                                const sa_ambig_t *ambigIn, int expectations, sa_batch_t **out) {
+// readBase: index of reads[0] in the caller's array (error messages name the caller's read)
+static int prepareBatch(const sa_model_t *m, const sa_read_t *reads, int64_t nReads, const sa_params_t *p,
+                        const sa_ambig_t *ambigIn, int expectations, int64_t readBase, sa_batch_t **out) {
     *out = nullptr;
     if (sa_gpu_device_count() == 0) {
         sa_set_error("sa_batch_prepare: no CUDA device available; libsagpu has no CPU fallback");
@@ -327,9 +358,16 @@ extern "C" int sa_batch_prepare(const sa_model_t *m, const sa_read_t *reads, int
     b->params = *p;
     b->expectations = expectations != 0;
     b->nReads = nReads;
-    CK(cudaStreamCreate(&b->stream));
+    if ((rc = poolInit())) return rc;
+    int prLeast = 0, prGreatest = 0;
+    CK(cudaDeviceGetStreamPriorityRange(&prLeast, &prGreatest));
+    CK(cudaStreamCreateWithPriority(&b->streamOwner.s, cudaStreamNonBlocking, prLeast));
+    CK(cudaStreamCreateWithPriority(&b->auxOwner.s, cudaStreamNonBlocking, prGreatest));
+    b->stream = b->streamOwner.s;
+    b->aux = b->auxOwner.s;
     for (auto &e : b->ev) CK(cudaEventCreate(&e));
-    cudaStream_t st = b->stream;
+    CK(cudaEventCreateWithFlags(&b->evPrepared, cudaEventDisableTiming));
+    cudaStream_t st = b->aux;
 
     const bool needNoise = m->kind == SA_EMIT_GAUSS_NOISE_SCALED || m->kind == SA_EMIT_GAUSS_NOISE_DESCALE;
     const bool fastModel = modelFastEligible(m) && !b->expectations && getenv("SA_FORCE_GENERAL") == nullptr;
@@ -364,7 +402,7 @@ extern "C" int sa_batch_prepare(const sa_model_t *m, const sa_read_t *reads, int
             char err[512];
             err[0] = 0;
             if (lXt > 0x3fffffff || lYt > 0x3fffffff)
-                snprintf(err, sizeof(err), "read %lld: sequences longer than 2^30 are not supported", (long long) r);
+                snprintf(err, sizeof(err), "read %lld: sequences longer than 2^30 are not supported", (long long) (r + readBase));
             for (int64_t i = 0; i < R.nAnchors && !err[0]; i++) {
                 int64_t ax = R.anchors[2 * i], ay = R.anchors[2 * i + 1];
                 bool ok = ax >= 0 && ay >= 0 && ax < lXt && ay < lYt;
@@ -372,7 +410,7 @@ extern "C" int sa_batch_prepare(const sa_model_t *m, const sa_read_t *reads, int
                 if (!ok)
                     snprintf(err, sizeof(err), "read %lld: anchor %lld (%lld, %lld) out of range or not strictly "
                              "increasing (asserted by band_construct, pairwiseAligner.c:226-231)",
-                             (long long) r, (long long) i, (long long) ax, (long long) ay);
+                             (long long) (r + readBase), (long long) i, (long long) ax, (long long) ay);
             }
             // every character of the target must be in the alphabet or an ambiguity code whose options are
             for (int64_t i = 0; i < R.targetLength && lXt > 0 && !err[0]; i++) {
@@ -385,7 +423,7 @@ extern "C" int sa_batch_prepare(const sa_model_t *m, const sa_read_t *reads, int
                 if (!ok)
                     snprintf(err, sizeof(err), "read %lld: kmer at reference position %lld contains a character "
                              "outside the alphabet %s (the reference exits in kmer_to_word, nanopore_hdp.c:393-398)",
-                             (long long) r, (long long) std::max<int64_t>(0, i - (m->k - 1)), m->alphabet.c_str());
+                             (long long) (r + readBase), (long long) std::max<int64_t>(0, i - (m->k - 1)), m->alphabet.c_str());
             }
             if (err[0]) {
 #pragma omp critical
@@ -522,7 +560,7 @@ extern "C" int sa_batch_prepare(const sa_model_t *m, const sa_read_t *reads, int
     if ((rc = b->dPathOff.upload(pathOff, st, &b->h2dBytes))) return rc;
     if ((rc = b->dPathKmer.upload(pathKmer, st, &b->h2dBytes))) return rc;
     if ((rc = b->dAnchors.upload(anchors32, st, &b->h2dBytes))) return rc;
-    if ((rc = b->dCounters.alloc(8))) return rc;
+    if ((rc = b->dCounters.alloc(8, st))) return rc;
 
     // output slots
     int64_t pairTotalCap = 0, assignTotalCap = 0;
@@ -534,13 +572,13 @@ extern "C" int sa_batch_prepare(const sa_model_t *m, const sa_read_t *reads, int
         it.assignCap = (b->expectations && m->kind == SA_EMIT_HDP) ? 4 * it.lY * it.maxP + 64 : 0;
         assignTotalCap += it.assignCap;
     }
-    if ((rc = b->dPairCount.alloc(std::max<int64_t>(1, n)))) return rc;
-    if ((rc = b->dPairs.alloc(std::max<int64_t>(1, pairTotalCap)))) return rc;
+    if ((rc = b->dPairCount.alloc(std::max<int64_t>(1, n), st))) return rc;
+    if ((rc = b->dPairs.alloc(std::max<int64_t>(1, pairTotalCap), st))) return rc;
     if (b->expectations) {
-        if ((rc = b->dExpOut.alloc(std::max<int64_t>(1, n * 10)))) return rc;
-        if ((rc = b->dAssignCount.alloc(std::max<int64_t>(1, n)))) return rc;
-        if ((rc = b->dAssignK.alloc(std::max<int64_t>(1, assignTotalCap)))) return rc;
-        if ((rc = b->dAssignE.alloc(std::max<int64_t>(1, assignTotalCap)))) return rc;
+        if ((rc = b->dExpOut.alloc(std::max<int64_t>(1, n * 10), st))) return rc;
+        if ((rc = b->dAssignCount.alloc(std::max<int64_t>(1, n), st))) return rc;
+        if ((rc = b->dAssignK.alloc(std::max<int64_t>(1, assignTotalCap), st))) return rc;
+        if ((rc = b->dAssignE.alloc(std::max<int64_t>(1, assignTotalCap), st))) return rc;
     }
 
     int dev, nSM = 148;
@@ -576,8 +614,8 @@ extern "C" int sa_batch_prepare(const sa_model_t *m, const sa_read_t *reads, int
             fi.logInvVar = log((1 / it.var));
         }
         if ((rc = b->dFItems.upload(b->fItems, st, &b->h2dBytes))) return rc;
-        if ((rc = b->dTb.alloc(std::max<int64_t>(1, tbTotal)))) return rc;
-        if ((rc = b->dGeo.alloc(n))) return rc;
+        if ((rc = b->dTb.alloc(std::max<int64_t>(1, tbTotal), st))) return rc;
+        if ((rc = b->dGeo.alloc(n, st))) return rc;
         f.items = b->dFItems.p; f.nItems = (int32_t) n;
         f.evMean = b->dEvMean.p; f.kmerIdx = b->dPathKmer.p; f.anchors = b->dAnchors.p;
         f.tb = b->dTb.p; f.geo = b->dGeo.p; f.ft = m->dev->ft;
@@ -588,10 +626,11 @@ extern "C" int sa_batch_prepare(const sa_model_t *m, const sa_read_t *reads, int
         f.minDiags = (int32_t) p->minDiagsBetweenTraceBack; f.traceBack = (int32_t) p->traceBackDiagonals;
         f.expansion = (int32_t) p->diagonalExpansion;
         f.pairs = b->dPairs.p; f.pairCount = b->dPairCount.p;
-        sa_geometry_kernel<<<(unsigned) ((n + 127) / 128), 128, 0, st>>>(f);
+        sa_geometry_kernel<<<(unsigned) n, 32, 0, st>>>(f);
         CK(cudaGetLastError());
         CK(cudaMemcpyAsync(geo.data(), b->dGeo.p, sizeof(FGeo) * n, cudaMemcpyDeviceToHost, st));
         CK(cudaStreamSynchronize(st));
+        timer.lap("geometry kernel + D2H");
     }
     static const int kW[4] = {1, 2, 4, 8};
     const bool useWarpKernel = getenv("SA_WARP_KERNEL") != nullptr;   // the superseded warp-per-read kernel (A/B runs only)
@@ -640,7 +679,7 @@ extern "C" int sa_batch_prepare(const sa_model_t *m, const sa_read_t *reads, int
             }
             need = std::max(need, rowD);
         }
-        if ((rc = b->dFScratch.alloc((size_t) need))) return rc;
+        if ((rc = b->dFScratch.alloc((size_t) need, st))) return rc;
         f.scratch = b->dFScratch.p;
     }
 
@@ -716,7 +755,7 @@ extern "C" int sa_batch_prepare(const sa_model_t *m, const sa_read_t *reads, int
             return SA_ERR_INPUT;
         }
         b->gCta = std::max(1, nCta);
-        if ((rc = b->dGScratch.alloc((size_t) b->gCta * slab))) return rc;
+        if ((rc = b->dGScratch.alloc((size_t) b->gCta * slab, st))) return rc;
         g.items = b->dGItems.p; g.order = b->dGOrder.p; g.nItems = (int32_t) b->gOrder.size();
         g.pathOff = b->dPathOff.p; g.pathKmer = b->dPathKmer.p;
         g.evMean = b->dEvMean.p; g.evNoise = b->dEvNoise.p; g.evLogNoise = b->dEvLogNoise.p;
@@ -731,14 +770,22 @@ extern "C" int sa_batch_prepare(const sa_model_t *m, const sa_read_t *reads, int
         g.pairs = b->dPairs.p; g.pairCount = b->dPairCount.p; g.expOut = b->dExpOut.p;
         g.assignK = b->dAssignK.p; g.assignE = b->dAssignE.p; g.assignCount = b->expectations ? b->dAssignCount.p : nullptr;
     }
+    CK(cudaEventRecord(b->evPrepared, st));
     CK(cudaStreamSynchronize(st));
     timer.lap("general-kernel packing");
     *out = b.release();
     return SA_OK;
 }
 
-extern "C" int sa_batch_run(sa_batch_t *b) {
+extern "C" int sa_batch_prepare(const sa_model_t *m, const sa_read_t *reads, int64_t nReads, const sa_params_t *p,
+                                const sa_ambig_t *ambig, int expectations, sa_batch_t **out) {
+    return prepareBatch(m, reads, nReads, p, ambig, expectations, 0, out);
+}
+
+// queue the batch's kernels on its stream; returns without waiting for them
+static int launchBatch(sa_batch_t *b) {
     cudaStream_t st = b->stream;
+    CK(cudaStreamWaitEvent(st, b->evPrepared, 0));
     b->lastLaunches = 0;
     CK(cudaMemsetAsync(b->dCounters.p, 0, 8 * sizeof(int32_t), st));
     CK(cudaEventRecord(b->ev[0], st));
@@ -766,7 +813,13 @@ extern "C" int sa_batch_run(sa_batch_t *b) {
         CK(cudaGetLastError());
     }
     CK(cudaEventRecord(b->ev[3], st));
-    CK(cudaStreamSynchronize(st));
+    return SA_OK;
+}
+
+extern "C" int sa_batch_run(sa_batch_t *b) {
+    int rc = launchBatch(b);
+    if (rc) return rc;
+    CK(cudaStreamSynchronize(b->stream));
     // lastMs: [0] fast kernel C=4, [1] fast kernel C=2, [2] general kernel
     CK(cudaEventElapsedTime(&b->lastMs[0], b->ev[0], b->ev[1]));
     CK(cudaEventElapsedTime(&b->lastMs[1], b->ev[1], b->ev[2]));
@@ -775,7 +828,7 @@ extern "C" int sa_batch_run(sa_batch_t *b) {
 }
 
 // meta per item: source offset, destination offset, count, (x1 << 32 | y1)
-__global__ void sa_compact_pairs_kernel(const sa_pair_t *src, sa_pair_t *dst, const int64_t *meta, int64_t nItems) {
+__global__ void __launch_bounds__(128) sa_compact_pairs_kernel(const sa_pair_t *src, sa_pair_t *dst, const int64_t *meta, int64_t nItems) {
     for (int64_t it = blockIdx.x; it < nItems; it += gridDim.x) {
         const int64_t so = meta[4 * it], dO = meta[4 * it + 1], cnt = meta[4 * it + 2], sh = meta[4 * it + 3];
         const int32_t x1 = (int32_t) (sh >> 32), y1 = (int32_t) (sh & 0xffffffffLL);
@@ -820,24 +873,43 @@ static int growAndRerun(sa_batch_t *b) {
         b->gp.items = b->dGItems.p;
     }
     if (!b->expectations) {
-        if ((rc = b->dPairs.alloc(std::max<int64_t>(1, pt)))) return rc;
+        if ((rc = b->dPairs.alloc(std::max<int64_t>(1, pt), b->stream))) return rc;
         b->gp.pairs = b->dPairs.p;
         b->fp.pairs = b->dPairs.p;
     } else {
-        if ((rc = b->dAssignK.alloc(std::max<int64_t>(1, at)))) return rc;
-        if ((rc = b->dAssignE.alloc(std::max<int64_t>(1, at)))) return rc;
+        if ((rc = b->dAssignK.alloc(std::max<int64_t>(1, at), b->stream))) return rc;
+        if ((rc = b->dAssignE.alloc(std::max<int64_t>(1, at), b->stream))) return rc;
         b->gp.assignK = b->dAssignK.p;
         b->gp.assignE = b->dAssignE.p;
     }
     return sa_batch_run(b);
 }
 
-extern "C" int sa_batch_fetch(sa_batch_t *b, sa_result_t **out) {
-    *out = nullptr;
-    PhaseTimer timer("fetch");
+// Growing page-locked destination of the compacted pairs: it becomes the result's `pairs` array (sa_result_free hands
+// the slab back to the pool), so the dense D2H is the only copy of the result that is ever made.
+struct PairSink {
+    sa_pair_t *p = nullptr;
+    int64_t cap = 0, used = 0;
+};
+static int sinkReserve(PairSink &k, int64_t need) {
+    if (k.p && need <= k.cap) return SA_OK;
+    int64_t cap = std::max(need, k.cap * 2);
+    sa_pair_t *q = (sa_pair_t *) pinAcquire(sizeof(sa_pair_t) * (size_t) std::max<int64_t>(1, cap));
+    if (!q) {
+        sa_set_error("sa_batch_fetch: cannot allocate pinned memory for the result");
+        return SA_ERR_CUDA;
+    }
+    if (k.used) memcpy(q, k.p, sizeof(sa_pair_t) * (size_t) k.used);
+    pinRelease(k.p);
+    k.p = q;
+    k.cap = cap;
+    return SA_OK;
+}
+
+// wait for the batch's kernels, read the per-item counts, re-run with larger slots if any overflowed
+static int fetchCounts(sa_batch_t *b) {
     int64_t n = (int64_t) b->items.size();
     cudaStream_t st = b->stream;
-    b->d2hBytes = 0;
     for (int attempt = 0; attempt < 3; attempt++) {
         bool overflow = false;
         if (!b->expectations) {
@@ -863,6 +935,57 @@ extern "C" int sa_batch_fetch(sa_batch_t *b, sa_result_t **out) {
         int rc = growAndRerun(b);
         if (rc) return rc;
     }
+    return SA_OK;
+}
+
+// Pairs of the batch, compacted on the device and copied to sink.p[sink.used ...]; pairOffsets[0 .. nReads] receive
+// ABSOLUTE offsets into the sink.  The per-item slots are over-provisioned; a gather kernel packs the used prefixes
+// into the final layout (items in (read, region) order, each region's list popped from its END and shifted to read
+// coordinates: alignedPairCoordinateCorrectionFn, pairwiseAligner.c:2043-2050), so one dense D2H is the result.
+static int fetchPairs(sa_batch_t *b, PairSink &sink, int64_t *pairOffsets) {
+    int64_t n = (int64_t) b->items.size();
+    cudaStream_t st = b->aux;   // (fetchCounts has waited for the band kernels)
+    int64_t total = 0;
+    std::vector<int64_t> meta((size_t) std::max<int64_t>(1, n) * 4);
+    int64_t i = 0;
+    for (int64_t rd = 0; rd < b->nReads; rd++) {
+        pairOffsets[rd] = sink.used + total;
+        for (; i < n && b->items[i].read == rd; i++) {
+            meta[4 * i] = b->items[i].pairOff;
+            meta[4 * i + 1] = total;
+            meta[4 * i + 2] = b->pairCountHost[i];
+            meta[4 * i + 3] = (b->items[i].x1 << 32) | (b->items[i].y1 & 0xffffffffLL);
+            total += b->pairCountHost[i];
+        }
+    }
+    pairOffsets[b->nReads] = sink.used + total;
+    int rc = sinkReserve(sink, sink.used + total);
+    if (rc) return rc;
+    if (total > 0) {
+        DevBuf<int64_t> dMeta;
+        DevBuf<sa_pair_t> dDense;
+        if ((rc = dMeta.upload(meta, st, &b->h2dBytes))) return rc;
+        if ((rc = dDense.alloc(total, st))) return rc;
+        sa_compact_pairs_kernel<<<(unsigned) std::min<int64_t>(n, 148 * 16), 128, 0, st>>>(b->dPairs.p, dDense.p, dMeta.p, n);
+        CK(cudaGetLastError());
+        CK(cudaMemcpyAsync(sink.p + sink.used, dDense.p, sizeof(sa_pair_t) * total, cudaMemcpyDeviceToHost, st));
+        CK(cudaStreamSynchronize(st));
+        b->d2hBytes += sizeof(sa_pair_t) * total;
+        b->lastLaunches++;
+    }
+    sink.used += total;
+    return SA_OK;
+}
+
+extern "C" int sa_batch_fetch(sa_batch_t *b, sa_result_t **out) {
+    *out = nullptr;
+    PhaseTimer timer("fetch");
+    int64_t n = (int64_t) b->items.size();
+    cudaStream_t st = b->stream;
+    b->d2hBytes = 0;
+    int rc = fetchCounts(b);
+    if (rc) return rc;
+    timer.lap("wait for the kernels + counts");
     sa_result_t *r = (sa_result_t *) calloc(1, sizeof(sa_result_t));
     r->nReads = b->nReads;
     r->totalBandCells = b->bandCells;
@@ -871,48 +994,14 @@ extern "C" int sa_batch_fetch(sa_batch_t *b, sa_result_t **out) {
     // items are created read by read, region by region: already in (read, region) order
     r->pairOffsets = (int64_t *) calloc(b->nReads + 1, sizeof(int64_t));
     if (!b->expectations) {
-        // the per-item slots are over-provisioned; a gather kernel packs the used prefixes into the final layout
-        // (items in (read, region) order, each region's list popped from its END and shifted to read coordinates:
-        // alignedPairCoordinateCorrectionFn, pairwiseAligner.c:2043-2050), so one dense D2H is the result.
-        int64_t total = 0;
-        std::vector<int64_t> meta((size_t) std::max<int64_t>(1, n) * 4);
-        int64_t i = 0;
-        for (int64_t rd = 0; rd < b->nReads; rd++) {
-            r->pairOffsets[rd] = total;
-            for (; i < n && b->items[i].read == rd; i++) {
-                meta[4 * i] = b->items[i].pairOff;
-                meta[4 * i + 1] = total;
-                meta[4 * i + 2] = b->pairCountHost[i];
-                meta[4 * i + 3] = (b->items[i].x1 << 32) | (b->items[i].y1 & 0xffffffffLL);
-                total += b->pairCountHost[i];
-            }
+        PairSink sink;
+        if ((rc = fetchPairs(b, sink, r->pairOffsets))) {
+            pinRelease(sink.p);
+            sa_result_free(r);
+            return rc;
         }
-        r->pairOffsets[b->nReads] = total;
-        r->pairs = (sa_pair_t *) malloc(sizeof(sa_pair_t) * std::max<int64_t>(1, total));
-        if (total > 0) {
-            DevBuf<int64_t> dMeta;
-            DevBuf<sa_pair_t> dDense;
-            int rc;
-            if ((rc = dMeta.upload(meta, st, &b->h2dBytes))) return rc;
-            if ((rc = dDense.alloc(total))) return rc;
-            sa_compact_pairs_kernel<<<(unsigned) std::min<int64_t>(n, 148 * 16), 256, 0, st>>>(b->dPairs.p, dDense.p, dMeta.p, n);
-            CK(cudaGetLastError());
-            sa_pair_t *stage = (sa_pair_t *) pinAcquire(sizeof(sa_pair_t) * total);
-            if (!stage) {
-                sa_set_error("sa_batch_fetch: cannot allocate pinned staging memory");
-                return SA_ERR_CUDA;
-            }
-            CK(cudaMemcpyAsync(stage, dDense.p, sizeof(sa_pair_t) * total, cudaMemcpyDeviceToHost, st));
-            CK(cudaStreamSynchronize(st));
-            b->d2hBytes += sizeof(sa_pair_t) * total;
-            timer.lap("compact + D2H pairs");
-            const int64_t chunk = 1 << 20;
-#pragma omp parallel for schedule(static)
-            for (int64_t c = 0; c < (total + chunk - 1) / chunk; c++)
-                memcpy(r->pairs + c * chunk, stage + c * chunk, sizeof(sa_pair_t) * std::min(chunk, total - c * chunk));
-            pinRelease(stage);
-        }
-        timer.lap("assemble result");
+        r->pairs = sink.p;
+        timer.lap("compact + D2H pairs");
     } else {
         std::vector<double> e((size_t) std::max<int64_t>(1, n * 10));
         if (n > 0) {
@@ -1007,9 +1096,76 @@ static int runBatch(const sa_model_t *m, const sa_read_t *reads, int64_t nReads,
     return rc;
 }
 
+static int64_t g_lastH2d = 0, g_lastD2h = 0, g_lastLaunches = 0;
+extern "C" void sa_last_call_stats(int64_t *h2dBytes, int64_t *d2hBytes, int64_t *launches) {
+    if (h2dBytes) *h2dBytes = g_lastH2d;
+    if (d2hBytes) *d2hBytes = g_lastD2h;
+    if (launches) *launches = g_lastLaunches;
+}
+
+// The one-shot alignment call as a pipeline over CHUNKS of the batch (contiguous in read order, each its own
+// sub-batch and stream): while the band kernel of chunk k runs, the host packs chunk k+1 and its H2D / geometry pass go
+// ahead; the persistent CTAs of chunk k+1 take over the SMs as those of chunk k drain; the compaction + D2H of chunk k
+// overlap chunk k+1.  Host work and both copy directions are hidden behind the kernels except for the first chunk's
+// pack and the last chunk's fetch.  SA_CHUNKS overrides the chunk count.
+static int alignPipelined(const sa_model_t *m, const sa_read_t *reads, int64_t nReads, const sa_params_t *p,
+                          const sa_ambig_t *ambig, sa_result_t **out) {
+    *out = nullptr;
+    int64_t nch = nReads >= 2048 ? 4 : (nReads >= 512 ? 2 : 1);
+    if (const char *e = getenv("SA_CHUNKS")) nch = std::max<int64_t>(1, std::min<int64_t>(atoll(e), std::max<int64_t>(1, nReads)));
+    PhaseTimer timer("align");
+    std::vector<std::unique_ptr<sa_batch>> bs;
+    std::vector<int64_t> lo((size_t) nch + 1);
+    for (int64_t k = 0; k <= nch; k++) lo[k] = nReads * k / nch;
+    int rc = SA_OK;
+    for (int64_t k = 0; k < nch; k++) {
+        sa_batch_t *b = nullptr;
+        if ((rc = prepareBatch(m, reads + lo[k], lo[k + 1] - lo[k], p, ambig, 0, lo[k], &b))) break;
+        bs.emplace_back(b);
+        if ((rc = launchBatch(b))) break;
+    }
+    if (rc) {   // the batch is refused as a whole
+        for (auto &b : bs) cudaStreamSynchronize(b->stream);
+        return rc;
+    }
+    timer.lap("chunks packed, uploaded and queued");
+    sa_result_t *r = (sa_result_t *) calloc(1, sizeof(sa_result_t));
+    r->nReads = nReads;
+    r->pairOffsets = (int64_t *) calloc(nReads + 1, sizeof(int64_t));
+    PairSink sink;
+    int64_t capAll = 1;
+    for (auto &b : bs)
+        for (auto &it : b->items) capAll += it.pairCap;
+    g_lastH2d = g_lastD2h = g_lastLaunches = 0;
+    // the upper bound (3 pairs per event) only costs address space of the cached pinned slab; typical use is < 1/3
+    rc = sinkReserve(sink, capAll);
+    for (int64_t k = 0; k < nch && !rc; k++) {
+        sa_batch *b = bs[k].get();
+        b->d2hBytes = 0;
+        if ((rc = fetchCounts(b))) break;
+        if ((rc = fetchPairs(b, sink, r->pairOffsets + lo[k]))) break;
+        r->totalBandCells += b->bandCells;
+        r->totalPathCells += b->pathCells;
+        r->totalEvents += b->events;
+        g_lastH2d += b->h2dBytes;
+        g_lastD2h += b->d2hBytes;
+        g_lastLaunches += b->lastLaunches + 1;   // + the geometry pass
+    }
+    if (rc) {
+        for (auto &b : bs) cudaStreamSynchronize(b->stream);
+        pinRelease(sink.p);
+        sa_result_free(r);
+        return rc;
+    }
+    r->pairs = sink.p;
+    timer.lap("results fetched");
+    *out = r;
+    return SA_OK;
+}
+
 extern "C" int sa_gpu_align_batch(const sa_model_t *m, const sa_read_t *reads, int64_t nReads, const sa_params_t *p,
                                   const sa_ambig_t *ambig, sa_result_t **out) {
-    return runBatch(m, reads, nReads, p, ambig, 0, out);
+    return alignPipelined(m, reads, nReads, p, ambig, out);
 }
 extern "C" int sa_gpu_expectations_batch(const sa_model_t *m, const sa_read_t *reads, int64_t nReads,
                                          const sa_params_t *p, const sa_ambig_t *ambig, sa_result_t **out) {

@@ -526,9 +526,11 @@ extern "C" double sa_model_hdp_density(const sa_model_t *m, int64_t kI, double q
     return v > 0.0 ? v : 0.0;
 }
 
+bool sa_pinned_release(void *p);
 extern "C" void sa_result_free(sa_result_t *r) {
     if (!r) return;
-    free(r->pairOffsets); free(r->pairs); free(r->transitions); free(r->likelihood);
+    if (!sa_pinned_release(r->pairs)) free(r->pairs);   // normally a slab of the pinned pool (sa_gpu.cu)
+    free(r->pairOffsets); free(r->transitions); free(r->likelihood);
     free(r->assignOffsets); free(r->assignKmerPos); free(r->assignEvent);
     free(r);
 }
