@@ -1,12 +1,14 @@
-// sa_cta.cuh — the CTA band kernel: one CTA of W warps per work item, ONE band cell per thread.
+// sa_cta.cuh — the CTA band kernel: one CTA of W warps per work item, C (1 or 2) adjacent band cells per thread.
 //
 // Same eligibility and arithmetic as the warp kernel it replaces (un-ambiguous reference, Gaussian MeanOnly emission,
 // FP64 cubic logAdd in the reference's accumulation order), different mapping:
 //
-//   * thread t owns slot t of NS = 32 W slots; slot = column mod NS inside a sliding window [wlo, wlo + NS), so along a
-//     diagonal the `upper` neighbour (x, y-1) is the thread's own register and `lower` / `middle` (x-1, .) come from
-//     thread t-1 through a double-buffered shared-memory mailbox (3 doubles per thread), ONE __syncthreads per
-//     diagonal.
+//   * thread t owns slots C t .. C t + C - 1 of NS = 32 W C slots; slot = column mod NS inside a sliding window
+//     [wlo, wlo + NS), so along a diagonal the `upper` neighbour (x, y-1) is the thread's own register, `lower` /
+//     `middle` (x-1, .) of the thread's upper cell are its own lower cell, and those of the lower cell come from thread
+//     t-1 through a double-buffered shared-memory mailbox (3 doubles per thread), one split barrier per diagonal.
+//     Two cells per thread halve everything that is per thread and per diagonal (mailbox, barrier, band and ring
+//     bookkeeping) and double the independent logAdd chains in flight.
 //   * per-thread state is a dozen doubles (f(d-1), f(d-2) of one column), so registers allow ~5 CTAs of 128 threads per
 //     SM (20 warps) instead of the 8 warps the 4-cells-per-lane layout reached: the FP64 dependency chains of the
 //     logAdd are hidden by warp interleaving instead of by compiler-scheduled ILP.
@@ -42,12 +44,15 @@ __device__ __forceinline__ void sa_mbWait(unsigned long long *bar, unsigned &pha
     phase ^= 1u;
 }
 
-template <int W>
+template <int W, int C>
 struct CtaK {
-    static constexpr int NT = 32 * W;        // threads = slots
-    static constexpr int NS = NT;
+    static_assert(C == 1 || C == 2, "one or two cells per thread");
+    static constexpr int NT = 32 * W;        // threads
+    static constexpr int NS = NT * C;        // slots
+    static constexpr int NL = NS / 32;       // slots per lane when ONE warp walks all of them (the ordered fold)
+    static constexpr int NH = W * C;         // hit-mask words per diagonal: [warp][cell]
     static constexpr int ROW = 3 * NS + 2;   // doubles per stored forward row
-    static constexpr int RN = 2 * NT;        // entries of the column / event rings
+    static constexpr int RN = 2 * NS;        // entries of the column / event rings
 
     struct Smem {
         double cst[5][RN];       // km, iM, cM, iY, cY per column (index = column & (RN - 1))
@@ -57,7 +62,7 @@ struct CtaK {
         double sTotal;           // ... and their ordered fold (warp 0 computes, everybody reads)
         int2 bandTab[NT];        // [xlo, xhi] of forward diagonals bd0 .. bd0 + NT - 1
         int32_t aX[NT + 1], aY[NT + 1], aD[NT + 1];   // staged anchors (+1 coordinates) and their diagonals
-        alignas(16) unsigned hitM[2][W < 4 ? 4 : W];   // posterior hits per warp (ballot), double buffered
+        alignas(16) unsigned hitM[2][NH < 4 ? 4 : NH];   // posterior hits per warp and cell (ballot), double buffered
         int32_t sItem, sAi;
         unsigned long long mbar; // split barrier of the diagonal steps
     };
@@ -173,15 +178,15 @@ struct CtaK {
     // lets both folds walk the UNION of their candidate lanes: two independent dependency chains in flight).
     static __device__ __forceinline__ void orderedFold2(const Smem &S, int lane, int32_t wlo, double &out0, double &out1) {
         const int s0 = wlo & (NS - 1);
-        double v[2][W];
-        unsigned cand[2][W], any = 0;
+        double v[2][NL];
+        unsigned cand[2][NL], any = 0;
 #pragma unroll
         for (int f = 0; f < 2; f++) {
 #pragma unroll
-            for (int j = 0; j < W; j++) v[f][j] = S.foldv[f][(s0 + lane * W + j) & (NS - 1)];
+            for (int j = 0; j < NL; j++) v[f][j] = S.foldv[f][(s0 + lane * NL + j) & (NS - 1)];
             double mx = v[f][0];
 #pragma unroll
-            for (int j = 1; j < W; j++) mx = fmax(mx, v[f][j]);
+            for (int j = 1; j < NL; j++) mx = fmax(mx, v[f][j]);
             double run = mx;
 #pragma unroll
             for (int o = 1; o < 32; o <<= 1) {
@@ -191,7 +196,7 @@ struct CtaK {
             double pm = __shfl_up_sync(0xffffffffu, run, 1);
             if (lane == 0) pm = SA_NEG_INF;
 #pragma unroll
-            for (int j = 0; j < W; j++) {
+            for (int j = 0; j < NL; j++) {
                 const bool c = v[f][j] > pm - 7.6;   // false for -inf
                 cand[f][j] = __ballot_sync(0xffffffffu, c);
                 any |= cand[f][j];
@@ -203,7 +208,7 @@ struct CtaK {
             const int ln = __ffs(any) - 1;
             any &= any - 1;
 #pragma unroll
-            for (int j = 0; j < W; j++) {
+            for (int j = 0; j < NL; j++) {
                 const double q0 = __shfl_sync(0xffffffffu, v[0][j], ln), q1 = __shfl_sync(0xffffffffu, v[1][j], ln);
                 if (((cand[0][j] | cand[1][j]) >> ln) & 1u) {   // uniform branch
                     acc0 = sa_logAdd(acc0, q0);
@@ -231,23 +236,42 @@ struct CtaK {
     }
 
     static __device__ __forceinline__ void storeRow(double *row, int t, int32_t xlo, int32_t xhi, bool full,
-                                                    const double (&f)[3]) {
+                                                    const double (&f)[C][3]) {
         if (t == 0) *reinterpret_cast<int2 *>(row) = make_int2(xlo, xhi);
-        row[2 + t] = f[0];
-        if (full) {
-            row[2 + NS + t] = f[1];
-            row[2 + 2 * NS + t] = f[2];
+#pragma unroll
+        for (int pl = 0; pl < 3; pl++) {
+            if (pl > 0 && !full) break;
+            double *q = row + 2 + pl * NS + t * C;       // (16-byte aligned for C == 2: ROW and NS are even)
+            if (C == 2) *reinterpret_cast<double2 *>(q) = make_double2(f[0][pl], f[C - 1][pl]);
+            else q[0] = f[0][pl];
         }
     }
+    static __device__ __forceinline__ void loadRow(const double *row, int pl, int t, double (&o)[C]) {
+        const double *q = row + 2 + pl * NS + t * C;
+        if (C == 2) {
+            const double2 v = *reinterpret_cast<const double2 *>(q);
+            o[0] = v.x; o[C - 1] = v.y;
+        } else o[0] = q[0];
+    }
 
-    // number of posterior hits in slots [0, k) from the per-warp ballots
-    static __device__ __forceinline__ int hitsBelow(const unsigned (&m)[W], int k) {
+    // number of posterior hits in slots [0, k) from the ballots m[warp * C + cell]; slot = (32 warp + lane) C + cell
+    static __device__ __forceinline__ int hitsBelow(const unsigned (&m)[NH], int k) {
         int n = 0;
 #pragma unroll
         for (int w = 0; w < W; w++) {
-            const int lo = w * 32;
-            if (k >= lo + 32) n += __popc(m[w]);
-            else if (k > lo) n += __popc(m[w] & ((1u << (k - lo)) - 1u));
+            const int lo = w * 32 * C;
+            if (k >= lo + 32 * C) {
+#pragma unroll
+                for (int j = 0; j < C; j++) n += __popc(m[w * C + j]);
+            } else if (k > lo) {
+                const int r = k - lo, l = r / C, jj = r % C;    // l <= 31
+                const unsigned below = (1u << l) - 1u;
+#pragma unroll
+                for (int j = 0; j < C; j++) {
+                    n += __popc(m[w * C + j] & below);
+                    if (j < jj) n += (m[w * C + j] >> l) & 1u;
+                }
+            }
         }
         return n;
     }
@@ -266,45 +290,59 @@ struct CtaK {
         const double e0 = rag ? (T[T_GAP_OPEN_X] + T[T_GAP_OPEN_Y]) / 2.0 : T[T_MATCH_CONTINUE];
         const double e1 = rag ? T[T_GAP_EXTEND_X] : T[T_MATCH_FROM_GAP_X];
         const double e2 = rag ? T[T_GAP_EXTEND_Y] : T[T_MATCH_FROM_GAP_Y];
-        int32_t myx = slotX(t, bw);
-        double curM, curE, qX, qY, qE, nxtM = SA_NEG_INF, nxtE = 0.0;   // own column: d2 (cur, q) and d2 + 1 (nxt)
-        double n1M = SA_NEG_INF, n1E = 0.0;                             // right neighbour's (M, eM) one diagonal up
-        {
-            const bool act = myx >= xlo && myx <= xhi;
+        // own columns: diagonal d2 (cur, q) and d2 + 1 (nxt)
+        int32_t myx[C];
+        double curM[C], curE[C], qX[C], qY[C], qE[C], nxtM[C], nxtE[C];
+        double n1M = SA_NEG_INF, n1E = 0.0;    // (M, eM) one diagonal up of the column right of the thread's last cell
+#pragma unroll
+        for (int j = 0; j < C; j++) {
+            myx[j] = slotX(t * C + j, bw);
+            const bool act = myx[j] >= xlo && myx[j] <= xhi;
             double eM, eY;
-            emissions(S, myx, d - myx, eM, eY);
-            curM = act ? e0 : SA_NEG_INF; curE = eM;
-            qX = act ? e1 : SA_NEG_INF; qY = act ? e2 : SA_NEG_INF; qE = eY;
+            emissions(S, myx[j], d - myx[j], eM, eY);
+            curM[j] = act ? e0 : SA_NEG_INF; curE[j] = eM;
+            qX[j] = act ? e1 : SA_NEG_INF; qY[j] = act ? e2 : SA_NEG_INF; qE[j] = eY;
+            nxtM[j] = SA_NEG_INF; nxtE[j] = 0.0;
         }
         sa_mbWait(&S.mbar, phase);             // everybody has posted (and finished reading for) forward step d
         double total = SA_NEG_INF;
         int32_t postMod = 0, bxlo = xlo, bxhi = xhi;   // postMod: posterior diagonals since the last total, mod 10
-        // posterior hit of the previous diagonal, written after the next barrier (needs every warp's ballot)
-        bool pendValid = false, pendHit = false;
-        int32_t pendP = 0, pendX = 0, pendD = 0, pendS0 = 0;
+        // posterior hits of the previous diagonal, written after the next barrier (needs every warp's ballot)
+        bool pendValid = false, pendHit[C];
+        int32_t pendP[C], pendX[C], pendD = 0, pendS0 = 0;
+#pragma unroll
+        for (int j = 0; j < C; j++) { pendHit[j] = false; pendP[j] = 0; pendX[j] = 0; }
         auto flush = [&]() {
-            unsigned m[W];
+            unsigned m[NH];
             int tot = 0;
             {
                 const uint4 *hp = reinterpret_cast<const uint4 *>(S.hitM[pendD & 1]);
 #pragma unroll
-                for (int w4 = 0; w4 < (W + 3) / 4; w4++) {
+                for (int w4 = 0; w4 < (NH + 3) / 4; w4++) {
                     const uint4 q = hp[w4];
                     const unsigned qq[4] = {q.x, q.y, q.z, q.w};
 #pragma unroll
                     for (int w = 0; w < 4; w++)
-                        if (w4 * 4 + w < W) { m[w4 * 4 + w] = qq[w]; tot += __popc(qq[w]); }
+                        if (w4 * 4 + w < NH) { m[w4 * 4 + w] = qq[w]; tot += __popc(qq[w]); }
                 }
             }
-            if (pendHit) {
-                const int a = hitsBelow(m, pendS0), b = hitsBelow(m, t);
-                const int before = pendS0 <= t ? b - a : tot - a + b;
-                const int64_t w = nPairs + before;
-                if (w < I.pairCap) {
-                    sa_pair_t o;
-                    o.p = pendP; o.x = pendX - 1; o.y = pendD - pendX - 1;
-                    o.kmerIdx = P.kmerIdx[I.kmerOff + pendX - 1];
-                    P.pairs[I.pairOff + w] = o;
+            bool anyHit = false;
+#pragma unroll
+            for (int j = 0; j < C; j++) anyHit |= pendHit[j];
+            if (anyHit) {
+                const int a = hitsBelow(m, pendS0);
+#pragma unroll
+                for (int j = 0; j < C; j++) {
+                    if (!pendHit[j]) continue;
+                    const int sl = t * C + j, b = hitsBelow(m, sl);
+                    const int before = pendS0 <= sl ? b - a : tot - a + b;
+                    const int64_t w = nPairs + before;
+                    if (w < I.pairCap) {
+                        sa_pair_t o;
+                        o.p = pendP[j]; o.x = pendX[j] - 1; o.y = pendD - pendX[j] - 1;
+                        o.kmerIdx = P.kmerIdx[I.kmerOff + pendX[j] - 1];
+                        P.pairs[I.pairOff + w] = o;
+                    }
                 }
             }
             nPairs += tot;
@@ -318,59 +356,75 @@ struct CtaK {
             const int32_t rowP = rowI == 0 ? cap - 1 : rowI - 1;   // ... of d2 - 1
             const double *row = ring + (int64_t) rowI * ROW;
             const bool post = d2 <= tracedBackFrom;
-            double fM = 0.0;
-            if (post) fM = row[2 + t];
+            double fM[C];
+#pragma unroll
+            for (int j = 0; j < C; j++) fM[j] = 0.0;
+            if (post) loadRow(row, 0, t, fM);
             if (d2 < d) {
                 bxlo = hdrNext.x; bxhi = hdrNext.y;
                 if (d2 - 1 > tracedBackTo)
                     hdrNext = *reinterpret_cast<const int2 *>(ring + (int64_t) rowP * ROW);
                 if (bxlo < bw) bw = bxlo;      // lower the window; recycled slots restart at -inf
                 ensureRings(P, I, S, t, bw, d2, cLo, eLo);
-                const int32_t x = slotX(t, bw);
-                if (x != myx) {
-                    myx = x;
-                    curM = SA_NEG_INF; curE = 0.0; nxtM = SA_NEG_INF; nxtE = 0.0;
-                    qX = SA_NEG_INF; qY = SA_NEG_INF; qE = 0.0;
+                double eM[C], eY[C];
+#pragma unroll
+                for (int j = 0; j < C; j++) {
+                    const int32_t x = slotX(t * C + j, bw);
+                    if (x != myx[j]) {
+                        myx[j] = x;
+                        curM[j] = SA_NEG_INF; curE[j] = 0.0; nxtM[j] = SA_NEG_INF; nxtE[j] = 0.0;
+                        qX[j] = SA_NEG_INF; qY[j] = SA_NEG_INF; qE[j] = 0.0;
+                    }
+                    emissions(S, x, d2 - x, eM[j], eY[j]);
                 }
-                double eM, eY;
-                emissions(S, x, d2 - x, eM, eY);
                 sa_mbWait(&S.mbar, phase);     // mailbox and hit masks of diagonal d2 + 1 are visible
                 if (pendValid) flush();
                 double nb[3];
                 fetchDown(S, (d2 + 1) & 1, t, nb);
-                const double aM = n1M, aE = n1E, lX = nb[2];
+                // ascending j: cell j reads the values cell j + 1 held BEFORE this step
+#pragma unroll
+                for (int j = 0; j < C; j++) {
+                    const bool last = j == C - 1;
+                    const double aM = last ? n1M : nxtM[last ? j : j + 1], aE = last ? n1E : nxtE[last ? j : j + 1];
+                    const double lX = last ? nb[2] : qX[last ? j : j + 1];
+                    // gather in the order the reference's scatter delivers (see sa_general.cuh)
+                    const double M = sa_logAdd(sa_logAdd(aM + (aE + T[T_MATCH_CONTINUE]), qY[j] + (qE[j] + T[T_GAP_OPEN_Y])), lX + cOX);
+                    const double X = sa_logAdd(aM + (aE + T[T_MATCH_FROM_GAP_X]), lX + cEX);
+                    const double Y = sa_logAdd(aM + (aE + T[T_MATCH_FROM_GAP_Y]), qY[j] + (qE[j] + T[T_GAP_EXTEND_Y]));
+                    const bool act = myx[j] >= bxlo && myx[j] <= bxhi;
+                    nxtM[j] = curM[j]; nxtE[j] = curE[j];
+                    curM[j] = act ? M : SA_NEG_INF; curE[j] = eM[j];
+                    qX[j] = act ? X : SA_NEG_INF; qY[j] = act ? Y : SA_NEG_INF; qE[j] = eY[j];
+                }
                 n1M = nb[0]; n1E = nb[1];
-                // gather in the order the reference's scatter delivers (see sa_general.cuh)
-                const double M = sa_logAdd(sa_logAdd(aM + (aE + T[T_MATCH_CONTINUE]), qY + (qE + T[T_GAP_OPEN_Y])), lX + cOX);
-                const double X = sa_logAdd(aM + (aE + T[T_MATCH_FROM_GAP_X]), lX + cEX);
-                const double Y = sa_logAdd(aM + (aE + T[T_MATCH_FROM_GAP_Y]), qY + (qE + T[T_GAP_EXTEND_Y]));
-                const bool act = x >= bxlo && x <= bxhi;
-                nxtM = curM; nxtE = curE;
-                curM = act ? M : SA_NEG_INF; curE = eM;
-                qX = act ? X : SA_NEG_INF; qY = act ? Y : SA_NEG_INF; qE = eY;
             }
             {
-                const double pub[3] = {curM, curE, qX};
+                const double pub[3] = {curM[0], curE[0], qX[0]};   // the left neighbour thread reads the FIRST cell
                 publish(S, d2 & 1, t, pub);
             }
             if (!post) { sa_mbArrive(&S.mbar); continue; }
-            const int32_t x = myx;
             const bool newTotal = postMod == 0;
             postMod = postMod == 9 ? 0 : postMod + 1;
             if (newTotal) {
                 // diagonalCalculationTotalProbability (reference pairwiseAligner.c:1335-1353)
-                const double fX = row[2 + NS + t], fY = row[2 + 2 * NS + t];
-                double v = fM + curM;
-                v = sa_logAdd(v, fX + qX);
-                v = sa_logAdd(v, fY + qY);
-                // matches jumping over d2: middle-only forward step from f(d2 - 1) into the cells of d2 + 1
+                double fX[C], fY[C];
+                loadRow(row, 1, t, fX);
+                loadRow(row, 2, t, fY);
                 const double *rowm = ring + (int64_t) rowP * ROW + 2;
-                const int sp = (t + NS - 1) & (NS - 1);
-                const double gM = rowm[sp], gX = rowm[NS + sp], gY = rowm[2 * NS + sp];
-                const double m = sa_logAdd(sa_logAdd(gM + (nxtE + T[T_MATCH_CONTINUE]), gX + (nxtE + T[T_MATCH_FROM_GAP_X])),
-                                           gY + (nxtE + T[T_MATCH_FROM_GAP_Y]));
-                S.foldv[0][t] = v;
-                S.foldv[1][t] = m + nxtM;
+#pragma unroll
+                for (int j = 0; j < C; j++) {
+                    const int sl = t * C + j;
+                    double v = fM[j] + curM[j];
+                    v = sa_logAdd(v, fX[j] + qX[j]);
+                    v = sa_logAdd(v, fY[j] + qY[j]);
+                    // matches jumping over d2: middle-only forward step from f(d2 - 1) into the cells of d2 + 1
+                    const int sp = (sl + NS - 1) & (NS - 1);
+                    const double gM = rowm[sp], gX = rowm[NS + sp], gY = rowm[2 * NS + sp];
+                    const double m = sa_logAdd(sa_logAdd(gM + (nxtE[j] + T[T_MATCH_CONTINUE]), gX + (nxtE[j] + T[T_MATCH_FROM_GAP_X])),
+                                               gY + (nxtE[j] + T[T_MATCH_FROM_GAP_Y]));
+                    S.foldv[0][sl] = v;
+                    S.foldv[1][sl] = m + nxtM[j];
+                }
                 __syncthreads();
                 if (warp == 0) {               // the fold is sequential: one warp does it, the others keep their issue slots
                     double tot, tot2;
@@ -381,16 +435,21 @@ struct CtaK {
                 total = S.sTotal;
             }
             // diagonalCalculationPosteriorMatchProbs (reference pairwiseAligner.c:1355-1421)
-            const double arg = (fM + curM) - total;
-            const bool cand = x >= bxlo && x <= bxhi && x > 0 && d2 - x > 0 && arg >= P.logThrGate;
-            bool hit = false;
-            if (__any_sync(0xffffffffu, cand)) {
-                const double pp = exp(arg);
-                hit = cand && pp >= P.threshold;
-                pendP = (int32_t) floor((pp > 1.0 ? 1.0 : pp) * 10000000.0);
+#pragma unroll
+            for (int j = 0; j < C; j++) {
+                const int32_t x = myx[j];
+                const double arg = (fM[j] + curM[j]) - total;
+                const bool cand = x >= bxlo && x <= bxhi && x > 0 && d2 - x > 0 && arg >= P.logThrGate;
+                bool hit = false;
+                if (__any_sync(0xffffffffu, cand)) {
+                    const double pp = exp(arg);
+                    hit = cand && pp >= P.threshold;
+                    pendP[j] = (int32_t) floor((pp > 1.0 ? 1.0 : pp) * 10000000.0);
+                }
+                S.hitM[d2 & 1][warp * C + j] = __ballot_sync(0xffffffffu, hit);   // every lane stores the same word
+                pendHit[j] = hit; pendX[j] = x;
             }
-            S.hitM[d2 & 1][warp] = __ballot_sync(0xffffffffu, hit);   // every lane stores the same word: no branch
-            pendValid = true; pendHit = hit; pendX = x; pendD = d2; pendS0 = bw & (NS - 1);
+            pendValid = true; pendD = d2; pendS0 = bw & (NS - 1);
             sa_mbArrive(&S.mbar);
         }
         sa_mbWait(&S.mbar, phase);             // the last diagonal's hit masks
@@ -415,19 +474,25 @@ struct CtaK {
         eLo = (0 - (wlo + NS - 1)) - NS / 2; fillEvents(P, I, S, t, eLo);
         fillBand(P, I, S, t, bd0);             // (barriers inside)
         // diagonal 0: the cell (0, 0) with the start / ragged-start state (reference stateMachine.c:1134-1145)
-        double fa[3], fb[3], nbA[3], nbB[3];   // f(d-1) / f(d-2) by parity and the left neighbour's copies
-        int32_t myx = slotX(t, wlo);
+        // f(d-1) / f(d-2) of the own cells by parity, and the same two of the column left of the thread's first cell
+        double fa[C][3], fb[C][3], nbA[3], nbB[3];
+        int32_t myx[C];
         {
-            const bool ragged = I.flags & 1, c0 = t == 0;
-            fa[0] = (c0 && !ragged) ? 0.0 : SA_NEG_INF;
-            fa[1] = (c0 && ragged) ? 0.0 : SA_NEG_INF;
-            fa[2] = (c0 && ragged) ? 0.0 : SA_NEG_INF;
-            fb[0] = fb[1] = fb[2] = SA_NEG_INF;
+            const bool ragged = I.flags & 1;
+#pragma unroll
+            for (int j = 0; j < C; j++) {
+                const bool c0 = t == 0 && j == 0;
+                myx[j] = slotX(t * C + j, wlo);
+                fa[j][0] = (c0 && !ragged) ? 0.0 : SA_NEG_INF;
+                fa[j][1] = (c0 && ragged) ? 0.0 : SA_NEG_INF;
+                fa[j][2] = (c0 && ragged) ? 0.0 : SA_NEG_INF;
+                fb[j][0] = fb[j][1] = fb[j][2] = SA_NEG_INF;
+            }
             nbA[0] = nbA[1] = nbA[2] = SA_NEG_INF;
             nbB[0] = nbB[1] = nbB[2] = SA_NEG_INF;
         }
         storeRow(ring, t, 0, 0, true, fa);
-        publish(S, 0, t, fa);
+        publish(S, 0, t, fa[C - 1]);           // the right neighbour thread reads the LAST cell
         sa_mbArrive(&S.mbar);
         int32_t tracedBackTo = 0;
         int tbI = 0;
@@ -444,30 +509,43 @@ struct CtaK {
             const int32_t xlo = bnd.x, xhi = bnd.y;
             if (xhi > wlo + NS - 1) wlo = xhi - (NS - 1);   // slide the window up; recycled slots restart at -inf
             ensureRings(P, I, S, t, wlo, d, cLo, eLo);
-            const int32_t x = slotX(t, wlo);
-            if (x != myx) {
-                myx = x;
-                fa[0] = fa[1] = fa[2] = SA_NEG_INF;
-                fb[0] = fb[1] = fb[2] = SA_NEG_INF;
+            bool act[C];
+            double eM[C], eY[C];
+#pragma unroll
+            for (int j = 0; j < C; j++) {
+                const int32_t x = slotX(t * C + j, wlo);
+                if (x != myx[j]) {
+                    myx[j] = x;
+                    fa[j][0] = fa[j][1] = fa[j][2] = SA_NEG_INF;
+                    fb[j][0] = fb[j][1] = fb[j][2] = SA_NEG_INF;
+                }
+                act[j] = x >= xlo && x <= xhi;
+                emissions(S, x, d - x, eM[j], eY[j]);
             }
-            const bool act = x >= xlo && x <= xhi;
             const bool full = curFrom - d < 0 || backMod <= 1;
             backMod = backMod == 0 ? 9 : backMod - 1;
             double *row = ring + (int64_t) rowI * ROW;
-            double eM, eY;
-            emissions(S, x, d - x, eM, eY);
             sa_mbWait(&S.mbar, phase);         // the mailbox of step d - 1 is visible
-            // f(d-1) lives in fa when d is odd, in fb when d is even; the result overwrites f(d-2)
+            // f(d-1) lives in fa when d is odd, in fb when d is even; the result overwrites f(d-2).  Descending j: cell j
+            // reads f(d-2) of cell j - 1 before that cell overwrites it.
             if (d & 1) {
                 fetchUp(S, (d - 1) & 1, t, nbA);
-                forwardCell(P, S, x, d, act, cOX, cEX, eM, eY, fa, nbA, nbB, fb);
-                publish(S, d & 1, t, fb);
+#pragma unroll
+                for (int j = C - 1; j >= 0; j--) {
+                    if (j > 0) forwardCell(P, S, myx[j], d, act[j], cOX, cEX, eM[j], eY[j], fa[j], fa[j > 0 ? j - 1 : 0], fb[j > 0 ? j - 1 : 0], fb[j]);
+                    else forwardCell(P, S, myx[j], d, act[j], cOX, cEX, eM[j], eY[j], fa[j], nbA, nbB, fb[j]);
+                }
+                publish(S, d & 1, t, fb[C - 1]);
                 sa_mbArrive(&S.mbar);
                 storeRow(row, t, xlo, xhi, full, fb);
             } else {
                 fetchUp(S, (d - 1) & 1, t, nbB);
-                forwardCell(P, S, x, d, act, cOX, cEX, eM, eY, fb, nbB, nbA, fa);
-                publish(S, d & 1, t, fa);
+#pragma unroll
+                for (int j = C - 1; j >= 0; j--) {
+                    if (j > 0) forwardCell(P, S, myx[j], d, act[j], cOX, cEX, eM[j], eY[j], fb[j], fb[j > 0 ? j - 1 : 0], fa[j > 0 ? j - 1 : 0], fa[j]);
+                    else forwardCell(P, S, myx[j], d, act[j], cOX, cEX, eM[j], eY[j], fb[j], nbB, nbA, fa[j]);
+                }
+                publish(S, d & 1, t, fa[C - 1]);
                 sa_mbArrive(&S.mbar);
                 storeRow(row, t, xlo, xhi, full, fa);
             }
@@ -486,38 +564,52 @@ struct CtaK {
             // restore the forward sweep: f(d), f(d-1) from the ring (all three planes were kept above tracedBackFrom)
             __syncthreads();
             {
-                const double *r0 = ring + (int64_t) rowI * ROW + 2 + t;
-                const double *r1 = ring + (int64_t) (rowI == 0 ? cap - 1 : rowI - 1) * ROW + 2 + t;
-                double cur[3], prv[3], nb[3];
+                const double *r0 = ring + (int64_t) rowI * ROW;
+                const double *r1 = ring + (int64_t) (rowI == 0 ? cap - 1 : rowI - 1) * ROW;
+                double cur[C][3], prv[C][3], nb[3];
 #pragma unroll
-                for (int s3 = 0; s3 < 3; s3++) { cur[s3] = r0[s3 * NS]; prv[s3] = r1[s3 * NS]; }
-                publish(S, (d - 1) & 1, t, prv);
+                for (int s3 = 0; s3 < 3; s3++) {
+                    double a[C], b[C];
+                    loadRow(r0, s3, t, a);
+                    loadRow(r1, s3, t, b);
+#pragma unroll
+                    for (int j = 0; j < C; j++) { cur[j][s3] = a[j]; prv[j][s3] = b[j]; }
+                }
+                publish(S, (d - 1) & 1, t, prv[C - 1]);
                 __syncthreads();
                 fetchUp(S, (d - 1) & 1, t, nb);
-                publish(S, d & 1, t, cur);
+                publish(S, d & 1, t, cur[C - 1]);
                 sa_mbArrive(&S.mbar);
 #pragma unroll
                 for (int s3 = 0; s3 < 3; s3++) {
-                    if (d & 1) { fb[s3] = cur[s3]; fa[s3] = prv[s3]; nbA[s3] = nb[s3]; }
-                    else { fa[s3] = cur[s3]; fb[s3] = prv[s3]; nbB[s3] = nb[s3]; }
+#pragma unroll
+                    for (int j = 0; j < C; j++) {
+                        if (d & 1) { fb[j][s3] = cur[j][s3]; fa[j][s3] = prv[j][s3]; }
+                        else { fa[j][s3] = cur[j][s3]; fb[j][s3] = prv[j][s3]; }
+                    }
+                    if (d & 1) nbA[s3] = nb[s3]; else nbB[s3] = nb[s3];
                 }
-                myx = slotX(t, wlo);
+#pragma unroll
+                for (int j = 0; j < C; j++) myx[j] = slotX(t * C + j, wlo);
             }
         }
         if (t == 0) P.pairCount[it] = nPairs;
     }
 };
 
-// resident CTAs per SM the register allocation is held to: 20 warps for W = 2 and 4, 16 for W = 1 and 8
-template <int W> struct CtaOcc { static constexpr int kMinBlocks = W == 1 ? 16 : W == 2 ? 10 : W == 4 ? 5 : 2; };
+// resident CTAs per SM the register allocation is held to
+template <int W, int C> struct CtaOcc {
+    static constexpr int kMinBlocks = C == 1 ? (W == 1 ? 16 : W == 2 ? 10 : W == 4 ? 5 : 2)
+                                             : (W == 1 ? 16 : W == 2 ? 8 : 4);
+};
 
-template <int W>
-__global__ void __launch_bounds__(32 * W, CtaOcc<W>::kMinBlocks) sa_cta_kernel(const FParams P) {
-    __shared__ typename CtaK<W>::Smem S;
+template <int W, int C>
+__global__ void __launch_bounds__(32 * W, CtaOcc<W, C>::kMinBlocks) sa_cta_kernel(const FParams P) {
+    __shared__ typename CtaK<W, C>::Smem S;
     if (threadIdx.x == 0) sa_mbInit(&S.mbar, 32 * W);
     sa_logAdd_init();                          // (ends with a barrier: the mbarrier is initialised for everybody)
     unsigned phase = 0;
-    double *ring = P.scratch + (int64_t) blockIdx.x * P.rowsCap * CtaK<W>::ROW;
+    double *ring = P.scratch + (int64_t) blockIdx.x * P.rowsCap * CtaK<W, C>::ROW;
     for (;;) {
         __syncthreads();
         if (threadIdx.x == 0) S.sItem = atomicAdd(P.counter, 1);
@@ -525,6 +617,6 @@ __global__ void __launch_bounds__(32 * W, CtaOcc<W>::kMinBlocks) sa_cta_kernel(c
         const int n = S.sItem;
         if (n >= P.nOrder) break;
         const int it = P.order[n];
-        CtaK<W>::run(P, P.items[it], it, ring, S, phase);
+        CtaK<W, C>::run(P, P.items[it], it, ring, S, phase);
     }
 }

@@ -298,6 +298,7 @@ struct sa_batch {
     int fBlocks[4] = {0, 0, 0, 0};
     int32_t fRows[4] = {1, 1, 1, 1};
     bool warpKernel = false;
+    bool oneCell = false;      // SA_CTA_C1: the 128-slot class with one cell per thread (A/B runs only)
     int64_t bandCells = 0, pathCells = 0, events = 0;
     int64_t h2dBytes = 0, d2hBytes = 0;
     float lastMs[3] = {0, 0, 0};
@@ -325,6 +326,24 @@ static bool modelFastEligible(const sa_model *m) {
         if (m->gapY[i * 5] != m->match[i * 5]) return false;  // the fast kernel shares the de-scaled mean
     }
     return true;
+}
+
+// CTA band kernel classes by slot count NS = 32, 64, 128, 256 (an item goes to the narrowest class its band fits):
+// <warps, cells per thread> = <1,1>, <1,2>, <2,2>, <4,2>
+static int ctaOccupancy(int c, bool oneCell, int *bps) {
+    if (c == 0) CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(bps, sa_cta_kernel<1, 1>, 32, 0));
+    if (c == 1) CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(bps, sa_cta_kernel<1, 2>, 32, 0));
+    if (c == 2 && !oneCell) CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(bps, sa_cta_kernel<2, 2>, 64, 0));
+    if (c == 2 && oneCell) CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(bps, sa_cta_kernel<4, 1>, 128, 0));
+    if (c == 3) CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(bps, sa_cta_kernel<4, 2>, 128, 0));
+    return SA_OK;
+}
+static void ctaLaunch(int c, bool oneCell, int blocks, cudaStream_t st, const FParams &f) {
+    if (c == 0) sa_cta_kernel<1, 1><<<blocks, 32, 0, st>>>(f);
+    else if (c == 1) sa_cta_kernel<1, 2><<<blocks, 32, 0, st>>>(f);
+    else if (c == 2 && !oneCell) sa_cta_kernel<2, 2><<<blocks, 64, 0, st>>>(f);
+    else if (c == 2) sa_cta_kernel<4, 1><<<blocks, 128, 0, st>>>(f);
+    else sa_cta_kernel<4, 2><<<blocks, 128, 0, st>>>(f);
 }
 
 // readBase: index of reads[0] in the caller's array (error messages name the caller's read)
@@ -656,6 +675,7 @@ static int prepareBatch(const sa_model_t *m, const sa_read_t *reads, int64_t nRe
         }
     }
     b->warpKernel = useWarpKernel;
+    b->oneCell = getenv("SA_CTA_C1") != nullptr;
     auto byWork = [&](int32_t a, int32_t c) { return items[a].work > items[c].work; };
     {
         int64_t need = 1;
@@ -670,10 +690,7 @@ static int prepareBatch(const sa_model_t *m, const sa_read_t *reads, int64_t nRe
                 b->fBlocks[c] = (int) std::min<int64_t>((int64_t) nSM * std::max(1, bps), (nIt + 3) / 4);
                 rowD = (int64_t) b->fBlocks[c] * 4 * b->fRows[c] * FastK<4>::ROW;
             } else {
-                if (c == 0) CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, sa_cta_kernel<1>, 32, 0));
-                if (c == 1) CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, sa_cta_kernel<2>, 64, 0));
-                if (c == 2) CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, sa_cta_kernel<4>, 128, 0));
-                if (c == 3) CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, sa_cta_kernel<8>, 256, 0));
+                if ((rc = ctaOccupancy(c, b->oneCell, &bps))) return rc;
                 b->fBlocks[c] = (int) std::min<int64_t>((int64_t) nSM * std::max(1, bps), nIt);
                 rowD = (int64_t) b->fBlocks[c] * b->fRows[c] * (3 * 32 * kW[c] + 2);
             }
@@ -796,10 +813,7 @@ static int launchBatch(sa_batch_t *b) {
         f.order = b->dFOrder[c].p; f.nOrder = (int32_t) b->fOrder[c].size(); f.counter = b->dCounters.p + c;
         f.rowsCap = b->fRows[c];
         if (b->warpKernel) sa_fast_kernel<4><<<b->fBlocks[c], 128, 0, st>>>(f);
-        else if (c == 0) sa_cta_kernel<1><<<b->fBlocks[c], 32, 0, st>>>(f);
-        else if (c == 1) sa_cta_kernel<2><<<b->fBlocks[c], 64, 0, st>>>(f);
-        else if (c == 2) sa_cta_kernel<4><<<b->fBlocks[c], 128, 0, st>>>(f);
-        else sa_cta_kernel<8><<<b->fBlocks[c], 256, 0, st>>>(f);
+        else ctaLaunch(c, b->oneCell, b->fBlocks[c], st, f);
         b->lastLaunches++;
         CK(cudaGetLastError());
     }
