@@ -274,9 +274,9 @@ def main():
         alg_bytes_per_cell = 22.8
         achieved_gbs = cells * alg_bytes_per_cell / (float(np.mean(kern_ms)) * 1e-3) / 1e9
         sm_mhz = (clocks or {}).get("sm_mhz") or 1965.0
-        # FP64 pipe: ~230 algorithmic FP64 lane-instructions per band cell; peak = measured DFMA/DADD/DMUL
+        # FP64 pipe: ~150 algorithmic FP64 lane-instructions per band cell; peak = measured DFMA/DADD/DMUL
         # issue rate of this pool's B200 (tools/peak_fp.cu -> profiles/r1_peak_fp.jsonl), else 64 lanes/SM/clk nominal
-        fp64_per_cell = 230.0
+        fp64_per_cell = 150.0
         fp64_peak, fp64_src = 148 * 64 * 1.965e9, "nominal 64 lanes/SM/clk at 1965 MHz"
         try:
             for line in open(os.path.join(ROOT, "profiles", "r1_peak_fp.jsonl")):
@@ -292,11 +292,11 @@ def main():
             "config": {"workload": WORKLOAD, "reads_per_gpu_per_step": a.reads, "events_per_step": events_all,
                        "band_cells_per_step": cells_all, "l2": "flushed between steps (256 MiB write) and inputs > L2",
                        "aligned_pairs_rank0": n_pairs,
-                       "kernel_ms_rank0": {"cta_w4_w8": float(np.mean([m[0] for m in all_ms])),
-                                           "cta_w1_w2": float(np.mean([m[1] for m in all_ms])),
+                       "kernel_ms_rank0": {"cta_128_256_slots": float(np.mean([m[0] for m in all_ms])),
+                                           "cta_32_64_slots": float(np.mean([m[1] for m in all_ms])),
                                            "general": float(np.mean([m[2] for m in all_ms]))},
-                       "work_items_by_kernel_rank0": {"general": kernel_items[0], "cta_w1_w2": kernel_items[1],
-                                                      "cta_w4_w8": kernel_items[2]}},
+                       "work_items_by_kernel_rank0": {"general": kernel_items[0], "cta_32_64_slots": kernel_items[1],
+                                                      "cta_128_256_slots": kernel_items[2]}},
             "gcups": cells_all / (step_ms_max * 1e-3) / 1e9,
             "gpu_launches": launches,
             "clocks": clocks,

@@ -157,11 +157,11 @@ int sa_batch_prepare(const sa_model_t *m, const sa_read_t *reads, int64_t nReads
 int sa_batch_run(sa_batch_t *b);
 int sa_batch_fetch(sa_batch_t *b, sa_result_t **out);
 /* device time of the last sa_batch_run measured with CUDA events on the batch's stream (ms);
- * kernelMs[0] = CTA band kernel, 4- and 8-warp classes, [1] = CTA band kernel, 1- and 2-warp classes, [2] = general kernel;
+ * kernelMs[0] = CTA band kernel, 128- and 256-slot classes, [1] = CTA band kernel, 32- and 64-slot classes, [2] = general kernel;
  * launches = #kernel launches of the run */
 int sa_batch_last_timing(const sa_batch_t *b, float *kernelMs3, int64_t *launches);
 int64_t sa_batch_band_cells(const sa_batch_t *b);
-/* how many work items each kernel handles: out[0] general kernel, out[1] CTA kernel W <= 2, out[2] CTA kernel W >= 4 */
+/* how many work items each kernel handles: out[0] general kernel, out[1] CTA kernel 32/64 slots, out[2] CTA kernel 128/256 slots */
 void sa_batch_kernel_items(const sa_batch_t *b, int64_t *out3);
 int64_t sa_batch_h2d_bytes(const sa_batch_t *b);
 int64_t sa_batch_d2h_bytes(const sa_batch_t *b);

@@ -72,10 +72,11 @@ def lib():
     global _lib
     if _lib is not None:
         return _lib
-    if not os.path.exists(LIB_PATH):
+    path = os.environ.get("SA_LIBSAGPU", LIB_PATH)   # A/B runs of differently compiled kernels (tools/ab.sh)
+    if not os.path.exists(path):
         raise RuntimeError("libsagpu.so is not built (run `python -c 'import __graft_entry__ as g; g.build()'`); "
                            "signalalign_b200 has no CPU fallback")
-    L = C.CDLL(LIB_PATH)
+    L = C.CDLL(path)
     L.sa_last_error.restype = C.c_char_p
     L.sa_model_load.restype = C.c_void_p
     L.sa_model_load.argtypes = [C.c_char_p, C.c_char_p, C.c_int]

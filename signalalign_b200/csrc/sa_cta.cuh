@@ -44,7 +44,9 @@ __device__ __forceinline__ void sa_mbWait(unsigned long long *bar, unsigned &pha
     phase ^= 1u;
 }
 
-template <int W, int C>
+// EX = false: aligned pairs (diagonalCalculationPosteriorMatchProbs); EX = true: transition expectations + likelihood
+// (diagonalCalculation_Expectations, reference impl/pairwiseAligner.c:1423-1443) on the same sweeps.
+template <int W, int C, bool EX>
 struct CtaK {
     static_assert(C == 1 || C == 2, "one or two cells per thread");
     static constexpr int NT = 32 * W;        // threads
@@ -282,7 +284,8 @@ struct CtaK {
                                                      int lane, int warp, int32_t d, int32_t rowI, int32_t xlo, int32_t xhi,
                                                      int32_t bw, int32_t &cLo, int32_t &eLo, int32_t tracedBackTo,
                                                      int32_t tracedBackFrom, bool atEnd, double cOX, double cEX,
-                                                     unsigned &phase, int64_t &nPairs) {
+                                                     unsigned &phase, int64_t &nPairs, double (&acc)[7], double &lik,
+                                                     bool &yxNaN) {
         const double *T = P.trans;
         const int32_t cap = P.rowsCap;
         // end / ragged-end state on diagonal d (reference stateMachine.c:1147-1173)
@@ -348,8 +351,8 @@ struct CtaK {
             nPairs += tot;
             pendValid = false;
         };
-        int2 hdrNext = make_int2(0, 0);
-        if (d - 1 > tracedBackTo) hdrNext = *reinterpret_cast<const int2 *>(ring + (int64_t) (rowI == 0 ? cap - 1 : rowI - 1) * ROW);
+        int2 hdrNext = make_int2(0, 0);   // band of d2 - 1 (the expectations also need it on the block's lowest diagonal)
+        if (EX || d - 1 > tracedBackTo) hdrNext = *reinterpret_cast<const int2 *>(ring + (int64_t) (rowI == 0 ? cap - 1 : rowI - 1) * ROW);
         rowI = rowI + 1 == cap ? 0 : rowI + 1;
         for (int32_t d2 = d; d2 > tracedBackTo; d2--) {
             rowI = rowI == 0 ? cap - 1 : rowI - 1;             // ring row of d2
@@ -359,10 +362,10 @@ struct CtaK {
             double fM[C];
 #pragma unroll
             for (int j = 0; j < C; j++) fM[j] = 0.0;
-            if (post) loadRow(row, 0, t, fM);
+            if (post && !EX) loadRow(row, 0, t, fM);
             if (d2 < d) {
                 bxlo = hdrNext.x; bxhi = hdrNext.y;
-                if (d2 - 1 > tracedBackTo)
+                if (EX || d2 - 1 > tracedBackTo)
                     hdrNext = *reinterpret_cast<const int2 *>(ring + (int64_t) rowP * ROW);
                 if (bxlo < bw) bw = bxlo;      // lower the window; recycled slots restart at -inf
                 ensureRings(P, I, S, t, bw, d2, cLo, eLo);
@@ -408,6 +411,7 @@ struct CtaK {
             if (newTotal) {
                 // diagonalCalculationTotalProbability (reference pairwiseAligner.c:1335-1353)
                 double fX[C], fY[C];
+                if (EX) loadRow(row, 0, t, fM);
                 loadRow(row, 1, t, fX);
                 loadRow(row, 2, t, fY);
                 const double *rowm = ring + (int64_t) rowP * ROW + 2;
@@ -433,6 +437,52 @@ struct CtaK {
                 }
                 __syncthreads();
                 total = S.sTotal;
+            }
+            if (EX) {
+                // diagonalCalculation_Expectations: current = b(d2), neighbours from f(d2 - 1) and f(d2 - 2); a neighbour
+                // counts when its cell lies inside the band of its diagonal (and the diagonal was not freed:
+                // d2 - 2 >= tracedBackTo).  Every term is exp(((f + b) + (eP + tP)) - total), as the reference adds it.
+                if (t == 0) lik += total;
+                const bool has2 = d2 - 2 >= tracedBackTo;
+                const int32_t rowPP = rowP == 0 ? cap - 1 : rowP - 1;
+                int2 h2 = make_int2(1, 0);
+                if (has2) h2 = *reinterpret_cast<const int2 *>(ring + (int64_t) rowPP * ROW);
+                const double *r1 = ring + (int64_t) rowP * ROW + 2, *r2 = ring + (int64_t) rowPP * ROW + 2;
+                const int2 h1 = hdrNext;
+#pragma unroll
+                for (int j = 0; j < C; j++) {
+                    const int32_t x = myx[j];
+                    const bool here = x >= bxlo && x <= bxhi;
+                    const bool lower = here && x - 1 >= h1.x && x - 1 <= h1.y;
+                    const bool upper = here && x >= h1.x && x <= h1.y;
+                    const bool middle = here && x - 1 >= h2.x && x - 1 <= h2.y;
+                    const int sl = x & (NS - 1), sp = (x - 1) & (NS - 1);
+                    if (__any_sync(0xffffffffu, lower)) {
+                        const double f0 = r1[sp], f1 = r1[NS + sp];
+                        const double a0 = ((f0 + qX[j]) + cOX) - total, a1 = ((f1 + qX[j]) + cEX) - total;
+                        acc[1] += lower ? exp(a0) : 0.0;
+                        acc[3] += lower ? exp(a1) : 0.0;
+                        yxNaN |= lower && !(total > SA_NEG_INF);   // exp(-inf - total): NaN exactly when total is -inf
+                    }
+                    if (__any_sync(0xffffffffu, middle)) {
+                        const double f0 = r2[sp], f1 = r2[NS + sp], f2 = r2[2 * NS + sp];
+                        const double a0 = ((f0 + curM[j]) + (curE[j] + T[T_MATCH_CONTINUE])) - total;
+                        const double a1 = ((f1 + curM[j]) + (curE[j] + T[T_MATCH_FROM_GAP_X])) - total;
+                        const double a2 = ((f2 + curM[j]) + (curE[j] + T[T_MATCH_FROM_GAP_Y])) - total;
+                        acc[0] += middle ? exp(a0) : 0.0;
+                        acc[2] += middle ? exp(a1) : 0.0;
+                        acc[4] += middle ? exp(a2) : 0.0;
+                    }
+                    if (__any_sync(0xffffffffu, upper)) {
+                        const double f0 = r1[sl], f2 = r1[2 * NS + sl];
+                        const double a0 = ((f0 + qY[j]) + (qE[j] + T[T_GAP_OPEN_Y])) - total;
+                        const double a2 = ((f2 + qY[j]) + (qE[j] + T[T_GAP_EXTEND_Y])) - total;
+                        acc[5] += upper ? exp(a0) : 0.0;
+                        acc[6] += upper ? exp(a2) : 0.0;
+                    }
+                }
+                sa_mbArrive(&S.mbar);
+                continue;
             }
             // diagonalCalculationPosteriorMatchProbs (reference pairwiseAligner.c:1355-1421)
 #pragma unroll
@@ -461,8 +511,15 @@ struct CtaK {
         const double *T = P.trans;
         const int32_t nDiag = I.lX + I.lY;
         int64_t nPairs = 0;
+        // expectations: MM, MX, XM, XX, YM, MY, YY sums of this thread's cells; likelihood (thread 0)
+        double acc[7] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0}, lik = 0.0;
+        bool yxNaN = false;
         if (nDiag == 0) {
-            if (t == 0) P.pairCount[it] = 0;
+            if (t == 0) {
+                P.pairCount[it] = 0;
+                if (EX)
+                    for (int i = 0; i < 10; i++) P.expOut[(int64_t) it * 10 + i] = 0.0;
+            }
             return;
         }
         const int32_t *tbList = P.tb + I.tbOff;
@@ -522,7 +579,7 @@ struct CtaK {
                 act[j] = x >= xlo && x <= xhi;
                 emissions(S, x, d - x, eM[j], eY[j]);
             }
-            const bool full = curFrom - d < 0 || backMod <= 1;
+            const bool full = EX || curFrom - d < 0 || backMod <= 1;   // the expectations read all three planes of every row
             backMod = backMod == 0 ? 9 : backMod - 1;
             double *row = ring + (int64_t) rowI * ROW;
             sa_mbWait(&S.mbar, phase);         // the mailbox of step d - 1 is visible
@@ -554,7 +611,7 @@ struct CtaK {
             const bool atEnd = d == nDiag;
             const int32_t tracedBackFrom = curFrom;
             traceback(P, I, S, ring, t, lane, warp, d, rowI, xlo, xhi, wlo, cLo, eLo, tracedBackTo, tracedBackFrom, atEnd,
-                      cOX, cEX, phase, nPairs);
+                      cOX, cEX, phase, nPairs, acc, lik, yxNaN);
             tracedBackTo = tracedBackFrom;
             tbI++;
             nextT = tbI < nTb ? tbList[tbI] : nDiag;
@@ -593,23 +650,51 @@ struct CtaK {
                 for (int j = 0; j < C; j++) myx[j] = slotX(t * C + j, wlo);
             }
         }
+        if (EX) {
+            // CTA reduction of the seven sums (summation order differs from the reference's cell order: ~1e-13 relative)
+            __syncthreads();
+            double *red = &S.foldv[0][0];
+#pragma unroll
+            for (int i = 0; i < 7; i++) {
+                double v = acc[i];
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+                if (lane == 0) red[warp * 8 + i] = v;
+            }
+            const unsigned nanMask = __ballot_sync(0xffffffffu, yxNaN);
+            if (lane == 0) red[warp * 8 + 7] = nanMask ? 1.0 : 0.0;
+            __syncthreads();
+            if (t == 0) {
+                double v[8];
+                for (int i = 0; i < 8; i++) {
+                    v[i] = 0.0;
+                    for (int w = 0; w < W; w++) v[i] += red[w * 8 + i];
+                }
+                double *o = P.expOut + (int64_t) it * 10;   // from * 3 + to, states M, X, Y
+                o[0] = v[0]; o[1] = v[1]; o[2] = v[5];
+                o[3] = v[2]; o[4] = v[3]; o[5] = 0.0;
+                o[6] = v[4]; o[7] = v[7] != 0.0 ? __longlong_as_double(0x7ff8000000000000LL) : 0.0; o[8] = v[6];
+                o[9] = lik;
+            }
+        }
         if (t == 0) P.pairCount[it] = nPairs;
     }
 };
 
 // resident CTAs per SM the register allocation is held to
-template <int W, int C> struct CtaOcc {
-    static constexpr int kMinBlocks = C == 1 ? (W == 1 ? 16 : W == 2 ? 10 : W == 4 ? 5 : 2)
-                                             : (W == 1 ? 16 : W == 2 ? 8 : 4);
+template <int W, int C, bool EX> struct CtaOcc {
+    static constexpr int kMinBlocks = EX ? (W == 1 ? 12 : W == 2 ? 6 : 3)
+                                         : C == 1 ? (W == 1 ? 16 : W == 2 ? 10 : W == 4 ? 5 : 2)
+                                                  : (W == 1 ? 16 : W == 2 ? 8 : 4);
 };
 
-template <int W, int C>
-__global__ void __launch_bounds__(32 * W, CtaOcc<W, C>::kMinBlocks) sa_cta_kernel(const FParams P) {
-    __shared__ typename CtaK<W, C>::Smem S;
+template <int W, int C, bool EX>
+__global__ void __launch_bounds__(32 * W, CtaOcc<W, C, EX>::kMinBlocks) sa_cta_kernel(const FParams P) {
+    __shared__ typename CtaK<W, C, EX>::Smem S;
     if (threadIdx.x == 0) sa_mbInit(&S.mbar, 32 * W);
     sa_logAdd_init();                          // (ends with a barrier: the mbarrier is initialised for everybody)
     unsigned phase = 0;
-    double *ring = P.scratch + (int64_t) blockIdx.x * P.rowsCap * CtaK<W, C>::ROW;
+    double *ring = P.scratch + (int64_t) blockIdx.x * P.rowsCap * CtaK<W, C, EX>::ROW;
     for (;;) {
         __syncthreads();
         if (threadIdx.x == 0) S.sItem = atomicAdd(P.counter, 1);
@@ -617,6 +702,6 @@ __global__ void __launch_bounds__(32 * W, CtaOcc<W, C>::kMinBlocks) sa_cta_kerne
         const int n = S.sItem;
         if (n >= P.nOrder) break;
         const int it = P.order[n];
-        CtaK<W, C>::run(P, P.items[it], it, ring, S, phase);
+        CtaK<W, C, EX>::run(P, P.items[it], it, ring, S, phase);
     }
 }

@@ -63,6 +63,7 @@ struct FParams {
     double *scratch;         // per warp: rowsCap * rowStride doubles
     sa_pair_t *pairs;
     int64_t *pairCount;
+    double *expOut;          // expectations: 9 transition sums (from * 3 + to) + likelihood per item
 };
 
 // ---------------------------------------------------------------------------------------------- band iterator

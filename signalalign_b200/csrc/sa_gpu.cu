@@ -330,20 +330,30 @@ static bool modelFastEligible(const sa_model *m) {
 
 // CTA band kernel classes by slot count NS = 32, 64, 128, 256 (an item goes to the narrowest class its band fits):
 // <warps, cells per thread> = <1,1>, <1,2>, <2,2>, <4,2>
-static int ctaOccupancy(int c, bool oneCell, int *bps) {
-    if (c == 0) CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(bps, sa_cta_kernel<1, 1>, 32, 0));
-    if (c == 1) CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(bps, sa_cta_kernel<1, 2>, 32, 0));
-    if (c == 2 && !oneCell) CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(bps, sa_cta_kernel<2, 2>, 64, 0));
-    if (c == 2 && oneCell) CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(bps, sa_cta_kernel<4, 1>, 128, 0));
-    if (c == 3) CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(bps, sa_cta_kernel<4, 2>, 128, 0));
+template <bool EX>
+static int ctaOccupancyT(int c, bool oneCell, int *bps) {
+    if (c == 0) CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(bps, sa_cta_kernel<1, 1, EX>, 32, 0));
+    if (c == 1) CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(bps, sa_cta_kernel<1, 2, EX>, 32, 0));
+    if (c == 2 && !oneCell) CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(bps, sa_cta_kernel<2, 2, EX>, 64, 0));
+    if (c == 2 && oneCell) CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(bps, sa_cta_kernel<4, 1, false>, 128, 0));
+    if (c == 3) CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(bps, sa_cta_kernel<4, 2, EX>, 128, 0));
     return SA_OK;
 }
-static void ctaLaunch(int c, bool oneCell, int blocks, cudaStream_t st, const FParams &f) {
-    if (c == 0) sa_cta_kernel<1, 1><<<blocks, 32, 0, st>>>(f);
-    else if (c == 1) sa_cta_kernel<1, 2><<<blocks, 32, 0, st>>>(f);
-    else if (c == 2 && !oneCell) sa_cta_kernel<2, 2><<<blocks, 64, 0, st>>>(f);
-    else if (c == 2) sa_cta_kernel<4, 1><<<blocks, 128, 0, st>>>(f);
-    else sa_cta_kernel<4, 2><<<blocks, 128, 0, st>>>(f);
+template <bool EX>
+static void ctaLaunchT(int c, bool oneCell, int blocks, cudaStream_t st, const FParams &f) {
+    if (c == 0) sa_cta_kernel<1, 1, EX><<<blocks, 32, 0, st>>>(f);
+    else if (c == 1) sa_cta_kernel<1, 2, EX><<<blocks, 32, 0, st>>>(f);
+    else if (c == 2 && !oneCell) sa_cta_kernel<2, 2, EX><<<blocks, 64, 0, st>>>(f);
+    else if (c == 2) sa_cta_kernel<4, 1, false><<<blocks, 128, 0, st>>>(f);
+    else sa_cta_kernel<4, 2, EX><<<blocks, 128, 0, st>>>(f);
+}
+// ex: the expectations variant of the kernels (getExpectationsUsingAnchors) instead of the aligned-pairs one
+static int ctaOccupancy(int c, bool oneCell, bool ex, int *bps) {
+    return ex ? ctaOccupancyT<true>(c, false, bps) : ctaOccupancyT<false>(c, oneCell, bps);
+}
+static void ctaLaunch(int c, bool oneCell, bool ex, int blocks, cudaStream_t st, const FParams &f) {
+    if (ex) ctaLaunchT<true>(c, false, blocks, st, f);
+    else ctaLaunchT<false>(c, oneCell, blocks, st, f);
 }
 
 // readBase: index of reads[0] in the caller's array (error messages name the caller's read)
@@ -389,7 +399,8 @@ static int prepareBatch(const sa_model_t *m, const sa_read_t *reads, int64_t nRe
     cudaStream_t st = b->aux;
 
     const bool needNoise = m->kind == SA_EMIT_GAUSS_NOISE_SCALED || m->kind == SA_EMIT_GAUSS_NOISE_DESCALE;
-    const bool fastModel = modelFastEligible(m) && !b->expectations && getenv("SA_FORCE_GENERAL") == nullptr;
+    // (expectations of the HDP machine also collect kmer/event assignments: general kernel)
+    const bool fastModel = modelFastEligible(m) && getenv("SA_FORCE_GENERAL") == nullptr;
     PinVec<int32_t> pathOff, pathKmer, anchors32;
     PinVec<double> evMean, evNoise, evLogNoise;
     std::vector<ItemRec> &items = b->items;
@@ -645,6 +656,7 @@ static int prepareBatch(const sa_model_t *m, const sa_read_t *reads, int64_t nRe
         f.minDiags = (int32_t) p->minDiagsBetweenTraceBack; f.traceBack = (int32_t) p->traceBackDiagonals;
         f.expansion = (int32_t) p->diagonalExpansion;
         f.pairs = b->dPairs.p; f.pairCount = b->dPairCount.p;
+        f.expOut = b->expectations ? b->dExpOut.p : nullptr;
         sa_geometry_kernel<<<(unsigned) n, 32, 0, st>>>(f);
         CK(cudaGetLastError());
         CK(cudaMemcpyAsync(geo.data(), b->dGeo.p, sizeof(FGeo) * n, cudaMemcpyDeviceToHost, st));
@@ -652,7 +664,7 @@ static int prepareBatch(const sa_model_t *m, const sa_read_t *reads, int64_t nRe
         timer.lap("geometry kernel + D2H");
     }
     static const int kW[4] = {1, 2, 4, 8};
-    const bool useWarpKernel = getenv("SA_WARP_KERNEL") != nullptr;   // the superseded warp-per-read kernel (A/B runs only)
+    const bool useWarpKernel = getenv("SA_WARP_KERNEL") != nullptr && !b->expectations;   // the superseded warp-per-read kernel (A/B runs only)
     for (int64_t i = 0; i < n; i++) {
         ItemRec &it = items[i];
         it.kernel = 0;
@@ -690,7 +702,7 @@ static int prepareBatch(const sa_model_t *m, const sa_read_t *reads, int64_t nRe
                 b->fBlocks[c] = (int) std::min<int64_t>((int64_t) nSM * std::max(1, bps), (nIt + 3) / 4);
                 rowD = (int64_t) b->fBlocks[c] * 4 * b->fRows[c] * FastK<4>::ROW;
             } else {
-                if ((rc = ctaOccupancy(c, b->oneCell, &bps))) return rc;
+                if ((rc = ctaOccupancy(c, b->oneCell, b->expectations, &bps))) return rc;
                 b->fBlocks[c] = (int) std::min<int64_t>((int64_t) nSM * std::max(1, bps), nIt);
                 rowD = (int64_t) b->fBlocks[c] * b->fRows[c] * (3 * 32 * kW[c] + 2);
             }
@@ -813,7 +825,7 @@ static int launchBatch(sa_batch_t *b) {
         f.order = b->dFOrder[c].p; f.nOrder = (int32_t) b->fOrder[c].size(); f.counter = b->dCounters.p + c;
         f.rowsCap = b->fRows[c];
         if (b->warpKernel) sa_fast_kernel<4><<<b->fBlocks[c], 128, 0, st>>>(f);
-        else ctaLaunch(c, b->oneCell, b->fBlocks[c], st, f);
+        else ctaLaunch(c, b->oneCell, b->expectations, b->fBlocks[c], st, f);
         b->lastLaunches++;
         CK(cudaGetLastError());
     }

@@ -87,6 +87,34 @@ def test_medium_reads_many_blocks():
     _run_and_compare(reads, table, p, expect_fast=2)
 
 
+@pytest.mark.parametrize("expansion,trace_back,min_diags", [(50, 50, 200), (100, 50, 300), (20, 40, 1000), (6, 2, 10)])
+def test_expectations_band_kernel_vs_oracle_and_general(small_batch, gapped_batch, expansion, trace_back, min_diags):
+    """getExpectationsUsingAnchors on the band kernel (<W, C, EX = true>): transitions and likelihood against the oracle
+    (1e-6 / 1e-5 relative) and against the general kernel on the same batch; ragged flags on and off."""
+    trans = synth.nanopore_transitions()
+    for reads, table in (small_batch, gapped_batch):
+        model = sa.Model.from_tables("ACGT", 6, trans, table)
+        pm = port_model_from("ACGT", 6, trans, table)
+        p = sa.default_params(threshold=0.01, expansion=expansion, trace_back=trace_back, min_diags=min_diags)
+        rs = [dict(r, ragged_left=(i % 2 == 0), ragged_right=(i % 3 != 0)) for i, r in enumerate(reads)]
+        b = sa.Batch(model, [sa_read(r) for r in rs], p, expectations=True)
+        kernels = b.kernel_items
+        b.run()
+        fast = b.fetch()
+        b.close()
+        if reads is small_batch[0]:
+            assert kernels[1] + kernels[2] == len(rs), kernels     # dense anchors: every read on the band kernel
+        os.environ["SA_FORCE_GENERAL"] = "1"
+        try:
+            gen = sa.expectations_batch(model, [sa_read(r) for r in rs], p)
+        finally:
+            os.environ.pop("SA_FORCE_GENERAL", None)
+        for i, r in enumerate(rs):
+            t, lik = oracle_expectations(pm, r, port_params(p))[:2]
+            compare_expectations(fast.transitions[i], fast.likelihood[i], t, lik)
+            compare_expectations(fast.transitions[i], fast.likelihood[i], gen.transitions[i], gen.likelihood[i])
+
+
 def test_device_logadd_bit_exact():
     """The device logAdd against the oracle's (itself bit-identical to the compiled reference) on random pairs,
     the range seams (1.0, 2.5, 4.5), the 7.5 cut-off and -inf operands."""
