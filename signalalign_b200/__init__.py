@@ -54,7 +54,7 @@ EXPORTS = [
     "sa_gpu_align_batch", "sa_gpu_expectations_batch", "sa_batch_prepare", "sa_batch_run", "sa_batch_fetch",
     "sa_batch_last_timing", "sa_batch_band_cells", "sa_batch_kernel_items", "sa_batch_h2d_bytes", "sa_batch_d2h_bytes", "sa_batch_free",
     "sa_result_sum_expectations", "sa_debug_logadd", "sa_model_hdp_dims", "sa_model_get_hdp", "sa_debug_band",
-    "sa_debug_split_points", "sa_debug_kmer_paths", "sa_last_call_stats",
+    "sa_debug_split_points", "sa_debug_kmer_paths", "sa_last_call_stats", "sa_set_host_threads",
 ]
 
 _lib = None
@@ -355,6 +355,11 @@ def expectations_batch(model, reads, params=None, ambig=None):
     _check(lib().sa_gpu_expectations_batch(model.h, arr, len(reads), C.byref(params), ambig.h if ambig else None,
                                            C.byref(out)))
     return Result(out)
+
+
+def set_host_threads(n):
+    """host threads for the packing passes of this process (launchers like torchrun export OMP_NUM_THREADS=1)"""
+    lib().sa_set_host_threads(int(n))
 
 
 def last_call_stats():

@@ -1122,6 +1122,11 @@ static int runBatch(const sa_model_t *m, const sa_read_t *reads, int64_t nReads,
     return rc;
 }
 
+#include <omp.h>
+// host threads of the packing passes (OpenMP); launchers such as torchrun export OMP_NUM_THREADS=1, which would make
+// the host side of a multi-GPU job the bottleneck: the caller hands every rank its share of the cores instead
+extern "C" void sa_set_host_threads(int n) { omp_set_num_threads(n > 0 ? n : 1); }
+
 static int64_t g_lastH2d = 0, g_lastD2h = 0, g_lastLaunches = 0;
 extern "C" void sa_last_call_stats(int64_t *h2dBytes, int64_t *d2hBytes, int64_t *launches) {
     if (h2dBytes) *h2dBytes = g_lastH2d;
