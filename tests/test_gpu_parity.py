@@ -234,3 +234,57 @@ def test_rna_5mer_table_long_read():
     for i, r in enumerate(reads):
         ora, _ = oracle_align(pm, r, port_params(p))
         assert compare_pairs(res.read_pairs(i), ora, p.threshold) <= 20
+
+
+# ------------------------------------------------------------------------------------------------ full-size properties
+def test_config3_size_reads_band_kernel_equals_general_kernel():
+    """BASELINE config 3's shape (~10 k events per read, -x 100): the band kernel and the general kernel are two
+    independent implementations of the same recurrence (thread-per-cell sliding window vs. CTA-wide diagonals over
+    explicit band tables); at full read size they must agree pair for pair (order, coordinates, kmers; posteriors
+    within the FP64 bound), and so must their expectations.  The oracle checks three of the reads in full."""
+    import bench
+    reads, table = synth.make_batch(48, seed=77, **bench.GEN)
+    trans = synth.nanopore_transitions()
+    model = sa.Model.from_tables("ACGT", 6, trans, table)
+    p = sa.default_params(threshold=bench.THRESHOLD, expansion=bench.EXPANSION, trace_back=bench.TRACE_BACK,
+                          min_diags=bench.MIN_DIAGS)
+    rs = [sa_read(r) for r in reads]
+    fast = sa.align_batch(model, rs, p)
+    fe = sa.expectations_batch(model, rs, p)
+    os.environ["SA_FORCE_GENERAL"] = "1"
+    try:
+        gen = sa.align_batch(model, rs, p)
+        ge = sa.expectations_batch(model, rs, p)
+    finally:
+        os.environ.pop("SA_FORCE_GENERAL", None)
+    assert fast.band_cells == gen.band_cells and fast.events == gen.events
+    assert np.array_equal(fast.pair_offsets, gen.pair_offsets)
+    assert np.array_equal(fast.pairs[:, 1:], gen.pairs[:, 1:])
+    assert np.abs(fast.pairs[:, 0].astype(np.int64) - gen.pairs[:, 0]).max() <= 20
+    for i in range(len(rs)):
+        compare_expectations(fe.transitions[i], fe.likelihood[i], ge.transitions[i], ge.likelihood[i])
+    pm = port_model_from("ACGT", 6, trans, table)
+    for i in (0, 17, 47):
+        ora, _ = oracle_align(pm, reads[i], port_params(p))
+        assert compare_pairs(fast.read_pairs(i), ora, p.threshold) <= 20
+
+
+def test_pipelined_call_equals_single_batch():
+    """sa_gpu_align_batch cuts large batches into chunks that overlap on the device; the result must be byte-identical
+    to the un-chunked call for any chunk count (including more chunks than reads and an empty read in the middle)."""
+    reads, table = synth.make_batch(23, seed=31, mean_len=700, min_len=200, max_len=1500, trim=0)
+    model = sa.Model.from_tables("ACGT", 6, synth.nanopore_transitions(), table)
+    p = sa.default_params(threshold=0.01, expansion=50, trace_back=50, min_diags=200)
+    rs = [sa_read(r) for r in reads]
+    rs.insert(11, sa.Read("", np.zeros((0, 4)), np.zeros((0, 2))))
+    outs = []
+    for nch in ("1", "3", "7", "64"):
+        os.environ["SA_CHUNKS"] = nch
+        try:
+            r = sa.align_batch(model, rs, p)
+        finally:
+            os.environ.pop("SA_CHUNKS", None)
+        outs.append((r.pair_offsets.copy(), r.pairs.copy(), r.band_cells, r.events))
+    for o in outs[1:]:
+        assert np.array_equal(o[0], outs[0][0]) and np.array_equal(o[1], outs[0][1]) and o[2:] == outs[0][2:]
+    assert outs[0][0][12] == outs[0][0][11]     # the empty read has no pairs
