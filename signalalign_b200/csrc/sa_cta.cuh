@@ -46,7 +46,9 @@ __device__ __forceinline__ void sa_mbWait(unsigned long long *bar, unsigned &pha
 
 // EX = false: aligned pairs (diagonalCalculationPosteriorMatchProbs); EX = true: transition expectations + likelihood
 // (diagonalCalculation_Expectations, reference impl/pairwiseAligner.c:1423-1443) on the same sweeps.
-template <int W, int C, bool EX>
+// HD = true: HDP emission (stateMachine3HDP: the same kmer density for the match and the gap-Y state) instead of the
+// Gaussian tables; per column the ring then holds var * mu, scale * mu and the kmer's row of the spline tables.
+template <int W, int C, bool EX, bool HD>
 struct CtaK {
     static_assert(C == 1 || C == 2, "one or two cells per thread");
     static constexpr int NT = 32 * W;        // threads
@@ -77,7 +79,18 @@ struct CtaK {
         for (int i = t; i < RN; i += NT) {
             const int32_t x = c0 + i, s = x & (RN - 1);
             double km = 0.0, iM = 0.0, iY = 0.0, cM = SA_NEG_INF, cY = SA_NEG_INF;
-            if (x >= 1 && x <= I.lX) {
+            if (HD) {
+                // (km, iM, cM) = (var * mu, scale * mu, row of the kmer in the spline tables or -1 for the NULL kmer)
+                long long row = -1;
+                if (x >= 1 && x <= I.lX) {
+                    const int32_t k = P.kmerIdx[I.kmerOff + x - 1];
+                    const double mu = P.ft[(int64_t) k * 5];
+                    km = I.var * mu;
+                    iM = I.scale * mu;
+                    row = P.kmerToRow[k];
+                }
+                cM = __longlong_as_double(row);
+            } else if (x >= 1 && x <= I.lX) {
                 const double *ft = P.ft + (int64_t) P.kmerIdx[I.kmerOff + x - 1] * 5;
                 km = fma(I.scale, ft[0], I.shift);
                 iM = ft[1] * I.invVar;
@@ -166,8 +179,41 @@ struct CtaK {
         for (int i = 0; i < 3; i++) o[i] = S.nbx[buf][i][src];
     }
 
-    static __device__ __forceinline__ void emissions(const Smem &S, int32_t x, int32_t y, double &eM, double &eY) {
+    // get_nanopore_kmer_density (reference stateMachine.c:527-554 -> hdp.c:2588-2612 -> hdp_math_utils.c:471-495):
+    // cubic Hermite spline of the kmer's posterior predictive on the uniform grid, linear beyond its ends
+    static __device__ __forceinline__ double hdpLogDensity(const FParams &P, const FItem &I, long long row, double q) {
+        const int32_t n = P.G;
+        const double *yv = P.pp + row * n, *sv = P.slopes + row * n;
+        const double x0 = P.grid[0], xn = P.grid[n - 1];
+        double v;
+        if (q <= x0) v = yv[0] - sv[0] * (x0 - q);
+        else if (q >= xn) v = yv[n - 1] + sv[n - 1] * (q - xn);
+        else {
+            const double dx = P.gridDx;
+            int32_t il = (int32_t) ((q - x0) / dx);
+            il = il > n - 2 ? n - 2 : il;
+            const int32_t ir = il + 1;
+            const double yl = yv[il], yr = yv[ir], dy = yr - yl;
+            const double a = sv[il] * dx - dy, b = dy - sv[ir] * dx;
+            const double tl = (q - P.grid[il]) / dx, tr = 1.0 - tl;
+            v = (tr * yl + tl * yr) + (tl * tr) * (a * tr + b * tl);
+        }
+        const double dens = v > 0.0 ? v : 0.0;
+        return log(I.invVar * dens);
+    }
+
+    static __device__ __forceinline__ void emissions(const FParams &P, const FItem &I, const Smem &S, int32_t x, int32_t y,
+                                                     double &eM, double &eY) {
         const int cs = x & (RN - 1);
+        if (HD) {
+            const long long row = __double_as_longlong(S.cst[2][cs]);
+            // de-scaled event mean (stateMachine.c:344-348): (mean + var mu - scale mu - shift) / var
+            const double q = (((S.evs[y & (RN - 1)] + S.cst[0][cs]) - S.cst[1][cs]) - I.shift) / I.var;
+            double e = SA_NEG_INF;
+            if (row >= 0) e = hdpLogDensity(P, I, row, q);
+            eM = e; eY = e;
+            return;
+        }
         const double d0 = S.evs[y & (RN - 1)] - S.cst[0][cs];
         const double aM = d0 * S.cst[1][cs], aY = d0 * S.cst[3][cs];
         eM = fma(-0.5 * aM, aM, S.cst[2][cs]);
@@ -302,7 +348,7 @@ struct CtaK {
             myx[j] = slotX(t * C + j, bw);
             const bool act = myx[j] >= xlo && myx[j] <= xhi;
             double eM, eY;
-            emissions(S, myx[j], d - myx[j], eM, eY);
+            emissions(P, I, S, myx[j], d - myx[j], eM, eY);
             curM[j] = act ? e0 : SA_NEG_INF; curE[j] = eM;
             qX[j] = act ? e1 : SA_NEG_INF; qY[j] = act ? e2 : SA_NEG_INF; qE[j] = eY;
             nxtM[j] = SA_NEG_INF; nxtE[j] = 0.0;
@@ -378,7 +424,7 @@ struct CtaK {
                         curM[j] = SA_NEG_INF; curE[j] = 0.0; nxtM[j] = SA_NEG_INF; nxtE[j] = 0.0;
                         qX[j] = SA_NEG_INF; qY[j] = SA_NEG_INF; qE[j] = 0.0;
                     }
-                    emissions(S, x, d2 - x, eM[j], eY[j]);
+                    emissions(P, I, S, x, d2 - x, eM[j], eY[j]);
                 }
                 sa_mbWait(&S.mbar, phase);     // mailbox and hit masks of diagonal d2 + 1 are visible
                 if (pendValid) flush();
@@ -577,7 +623,7 @@ struct CtaK {
                     fb[j][0] = fb[j][1] = fb[j][2] = SA_NEG_INF;
                 }
                 act[j] = x >= xlo && x <= xhi;
-                emissions(S, x, d - x, eM[j], eY[j]);
+                emissions(P, I, S, x, d - x, eM[j], eY[j]);
             }
             const bool full = EX || curFrom - d < 0 || backMod <= 1;   // the expectations read all three planes of every row
             backMod = backMod == 0 ? 9 : backMod - 1;
@@ -682,19 +728,19 @@ struct CtaK {
 };
 
 // resident CTAs per SM the register allocation is held to
-template <int W, int C, bool EX> struct CtaOcc {
-    static constexpr int kMinBlocks = EX ? (W == 1 ? 12 : W == 2 ? 6 : 3)
+template <int W, int C, bool EX, bool HD> struct CtaOcc {
+    static constexpr int kMinBlocks = (EX || HD) ? (W == 1 ? 12 : W == 2 ? 6 : 3)
                                          : C == 1 ? (W == 1 ? 16 : W == 2 ? 10 : W == 4 ? 5 : 2)
                                                   : (W == 1 ? 16 : W == 2 ? 8 : 4);
 };
 
-template <int W, int C, bool EX>
-__global__ void __launch_bounds__(32 * W, CtaOcc<W, C, EX>::kMinBlocks) sa_cta_kernel(const FParams P) {
-    __shared__ typename CtaK<W, C, EX>::Smem S;
+template <int W, int C, bool EX, bool HD>
+__global__ void __launch_bounds__(32 * W, CtaOcc<W, C, EX, HD>::kMinBlocks) sa_cta_kernel(const FParams P) {
+    __shared__ typename CtaK<W, C, EX, HD>::Smem S;
     if (threadIdx.x == 0) sa_mbInit(&S.mbar, 32 * W);
     sa_logAdd_init();                          // (ends with a barrier: the mbarrier is initialised for everybody)
     unsigned phase = 0;
-    double *ring = P.scratch + (int64_t) blockIdx.x * P.rowsCap * CtaK<W, C, EX>::ROW;
+    double *ring = P.scratch + (int64_t) blockIdx.x * P.rowsCap * CtaK<W, C, EX, HD>::ROW;
     for (;;) {
         __syncthreads();
         if (threadIdx.x == 0) S.sItem = atomicAdd(P.counter, 1);
@@ -702,6 +748,6 @@ __global__ void __launch_bounds__(32 * W, CtaOcc<W, C, EX>::kMinBlocks) sa_cta_k
         const int n = S.sItem;
         if (n >= P.nOrder) break;
         const int it = P.order[n];
-        CtaK<W, C, EX>::run(P, P.items[it], it, ring, S, phase);
+        CtaK<W, C, EX, HD>::run(P, P.items[it], it, ring, S, phase);
     }
 }

@@ -32,6 +32,7 @@ struct FItem {
     int32_t flags;      // bit0 ragged left, bit1 ragged right
     int32_t pad;
     double scale, shift, invVar, logInvVar;
+    double var;
 };
 
 struct FGeo {            // per item, written by sa_geometry_kernel
@@ -64,6 +65,11 @@ struct FParams {
     sa_pair_t *pairs;
     int64_t *pairCount;
     double *expOut;          // expectations: 9 transition sums (from * 3 + to) + likelihood per item
+    // HDP emission (band kernel <.., HD = true>): uniform grid, posterior predictive and spline slopes per row, kmer -> row
+    const double *grid, *pp, *slopes;
+    const int32_t *kmerToRow;
+    int32_t G;
+    double gridDx;           // grid[1] - grid[0]
 };
 
 // ---------------------------------------------------------------------------------------------- band iterator

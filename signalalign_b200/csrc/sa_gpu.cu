@@ -318,42 +318,49 @@ static int64_t nextPow2(int64_t v) {
     return p;
 }
 
-static bool modelFastEligible(const sa_model *m) {
-    if (m->kind != SA_EMIT_GAUSS_MEANONLY_DESCALE) return false;
+// Models the band kernel handles: the production Gaussian emission, or the HDP emission for alignment runs
+static bool modelFastEligible(const sa_model *m, bool expectations) {
+    const bool hdp = m->kind == SA_EMIT_HDP;
+    if (m->kind != SA_EMIT_GAUSS_MEANONLY_DESCALE && !hdp) return false;
+    if (hdp && (expectations || m->G < 2)) return false;
     if (!(m->trans[T_GAP_SWITCH_TO_X] == -INFINITY)) return false;
+    // the HDP machine's X-gap emission is the literal log(0.1) (stateMachine.c:1394), whatever the table says
     for (int64_t i = 0; i < m->K; i++) {
-        if (m->gapX[i] != m->gapX[0]) return false;
-        if (m->gapY[i * 5] != m->match[i * 5]) return false;  // the fast kernel shares the de-scaled mean
+        if (!hdp && m->gapX[i] != m->gapX[0]) return false;
+        if (!hdp && m->gapY[i * 5] != m->match[i * 5]) return false;  // the fast kernel shares the de-scaled mean
     }
     return true;
 }
 
 // CTA band kernel classes by slot count NS = 32, 64, 128, 256 (an item goes to the narrowest class its band fits):
 // <warps, cells per thread> = <1,1>, <1,2>, <2,2>, <4,2>
-template <bool EX>
+template <bool EX, bool HD>
 static int ctaOccupancyT(int c, bool oneCell, int *bps) {
-    if (c == 0) CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(bps, sa_cta_kernel<1, 1, EX>, 32, 0));
-    if (c == 1) CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(bps, sa_cta_kernel<1, 2, EX>, 32, 0));
-    if (c == 2 && !oneCell) CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(bps, sa_cta_kernel<2, 2, EX>, 64, 0));
-    if (c == 2 && oneCell) CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(bps, sa_cta_kernel<4, 1, false>, 128, 0));
-    if (c == 3) CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(bps, sa_cta_kernel<4, 2, EX>, 128, 0));
+    if (c == 0) CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(bps, sa_cta_kernel<1, 1, EX, HD>, 32, 0));
+    if (c == 1) CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(bps, sa_cta_kernel<1, 2, EX, HD>, 32, 0));
+    if (c == 2 && !oneCell) CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(bps, sa_cta_kernel<2, 2, EX, HD>, 64, 0));
+    if (c == 2 && oneCell) CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(bps, sa_cta_kernel<4, 1, false, false>, 128, 0));
+    if (c == 3) CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(bps, sa_cta_kernel<4, 2, EX, HD>, 128, 0));
     return SA_OK;
 }
-template <bool EX>
+template <bool EX, bool HD>
 static void ctaLaunchT(int c, bool oneCell, int blocks, cudaStream_t st, const FParams &f) {
-    if (c == 0) sa_cta_kernel<1, 1, EX><<<blocks, 32, 0, st>>>(f);
-    else if (c == 1) sa_cta_kernel<1, 2, EX><<<blocks, 32, 0, st>>>(f);
-    else if (c == 2 && !oneCell) sa_cta_kernel<2, 2, EX><<<blocks, 64, 0, st>>>(f);
-    else if (c == 2) sa_cta_kernel<4, 1, false><<<blocks, 128, 0, st>>>(f);
-    else sa_cta_kernel<4, 2, EX><<<blocks, 128, 0, st>>>(f);
+    if (c == 0) sa_cta_kernel<1, 1, EX, HD><<<blocks, 32, 0, st>>>(f);
+    else if (c == 1) sa_cta_kernel<1, 2, EX, HD><<<blocks, 32, 0, st>>>(f);
+    else if (c == 2 && !oneCell) sa_cta_kernel<2, 2, EX, HD><<<blocks, 64, 0, st>>>(f);
+    else if (c == 2) sa_cta_kernel<4, 1, false, false><<<blocks, 128, 0, st>>>(f);
+    else sa_cta_kernel<4, 2, EX, HD><<<blocks, 128, 0, st>>>(f);
 }
-// ex: the expectations variant of the kernels (getExpectationsUsingAnchors) instead of the aligned-pairs one
-static int ctaOccupancy(int c, bool oneCell, bool ex, int *bps) {
-    return ex ? ctaOccupancyT<true>(c, false, bps) : ctaOccupancyT<false>(c, oneCell, bps);
+// ex: the expectations variant of the kernels (getExpectationsUsingAnchors) instead of the aligned-pairs one;
+// hdp: the HDP emission instead of the Gaussian tables (alignment only: HDP expectations collect assignments)
+static int ctaOccupancy(int c, bool oneCell, bool ex, bool hdp, int *bps) {
+    if (hdp) return ctaOccupancyT<false, true>(c, false, bps);
+    return ex ? ctaOccupancyT<true, false>(c, false, bps) : ctaOccupancyT<false, false>(c, oneCell, bps);
 }
-static void ctaLaunch(int c, bool oneCell, bool ex, int blocks, cudaStream_t st, const FParams &f) {
-    if (ex) ctaLaunchT<true>(c, false, blocks, st, f);
-    else ctaLaunchT<false>(c, oneCell, blocks, st, f);
+static void ctaLaunch(int c, bool oneCell, bool ex, bool hdp, int blocks, cudaStream_t st, const FParams &f) {
+    if (hdp) ctaLaunchT<false, true>(c, false, blocks, st, f);
+    else if (ex) ctaLaunchT<true, false>(c, false, blocks, st, f);
+    else ctaLaunchT<false, false>(c, oneCell, blocks, st, f);
 }
 
 // readBase: index of reads[0] in the caller's array (error messages name the caller's read)
@@ -400,7 +407,7 @@ static int prepareBatch(const sa_model_t *m, const sa_read_t *reads, int64_t nRe
 
     const bool needNoise = m->kind == SA_EMIT_GAUSS_NOISE_SCALED || m->kind == SA_EMIT_GAUSS_NOISE_DESCALE;
     // (expectations of the HDP machine also collect kmer/event assignments: general kernel)
-    const bool fastModel = modelFastEligible(m) && getenv("SA_FORCE_GENERAL") == nullptr;
+    const bool fastModel = modelFastEligible(m, b->expectations) && getenv("SA_FORCE_GENERAL") == nullptr;
     PinVec<int32_t> pathOff, pathKmer, anchors32;
     PinVec<double> evMean, evNoise, evLogNoise;
     std::vector<ItemRec> &items = b->items;
@@ -642,6 +649,7 @@ static int prepareBatch(const sa_model_t *m, const sa_read_t *reads, int64_t nRe
             fi.scale = it.scale; fi.shift = it.shift;
             fi.invVar = 1 / it.var;
             fi.logInvVar = log((1 / it.var));
+            fi.var = it.var;
         }
         if ((rc = b->dFItems.upload(b->fItems, st, &b->h2dBytes))) return rc;
         if ((rc = b->dTb.alloc(std::max<int64_t>(1, tbTotal), st))) return rc;
@@ -657,6 +665,12 @@ static int prepareBatch(const sa_model_t *m, const sa_read_t *reads, int64_t nRe
         f.expansion = (int32_t) p->diagonalExpansion;
         f.pairs = b->dPairs.p; f.pairCount = b->dPairCount.p;
         f.expOut = b->expectations ? b->dExpOut.p : nullptr;
+        if (m->kind == SA_EMIT_HDP) {
+            f.grid = m->dev->grid; f.pp = m->dev->pp; f.slopes = m->dev->slopes; f.kmerToRow = m->dev->kmerToRow;
+            f.G = (int32_t) m->G;
+            f.gridDx = m->grid[1] - m->grid[0];
+            f.eX = -2.3025850929940455;     // stateMachine3HDP_cellCalculate's literal X-gap emission
+        }
         sa_geometry_kernel<<<(unsigned) n, 32, 0, st>>>(f);
         CK(cudaGetLastError());
         CK(cudaMemcpyAsync(geo.data(), b->dGeo.p, sizeof(FGeo) * n, cudaMemcpyDeviceToHost, st));
@@ -702,7 +716,7 @@ static int prepareBatch(const sa_model_t *m, const sa_read_t *reads, int64_t nRe
                 b->fBlocks[c] = (int) std::min<int64_t>((int64_t) nSM * std::max(1, bps), (nIt + 3) / 4);
                 rowD = (int64_t) b->fBlocks[c] * 4 * b->fRows[c] * FastK<4>::ROW;
             } else {
-                if ((rc = ctaOccupancy(c, b->oneCell, b->expectations, &bps))) return rc;
+                if ((rc = ctaOccupancy(c, b->oneCell, b->expectations, m->kind == SA_EMIT_HDP, &bps))) return rc;
                 b->fBlocks[c] = (int) std::min<int64_t>((int64_t) nSM * std::max(1, bps), nIt);
                 rowD = (int64_t) b->fBlocks[c] * b->fRows[c] * (3 * 32 * kW[c] + 2);
             }
@@ -825,7 +839,7 @@ static int launchBatch(sa_batch_t *b) {
         f.order = b->dFOrder[c].p; f.nOrder = (int32_t) b->fOrder[c].size(); f.counter = b->dCounters.p + c;
         f.rowsCap = b->fRows[c];
         if (b->warpKernel) sa_fast_kernel<4><<<b->fBlocks[c], 128, 0, st>>>(f);
-        else ctaLaunch(c, b->oneCell, b->expectations, b->fBlocks[c], st, f);
+        else ctaLaunch(c, b->oneCell, b->expectations, b->model->kind == SA_EMIT_HDP, b->fBlocks[c], st, f);
         b->lastLaunches++;
         CK(cudaGetLastError());
     }

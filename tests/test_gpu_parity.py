@@ -183,6 +183,38 @@ def test_other_emission_kinds_alignment_and_expectations(gapped_batch, kind):
             assert np.array_equal(exp.assign_kmer_pos[a0:a1], ak) and np.array_equal(exp.assign_event[a0:a1], ae)
 
 
+@pytest.mark.parametrize("expansion,trace_back,min_diags", [(50, 50, 200), (100, 50, 300), (20, 40, 1000)])
+def test_hdp_emission_on_the_band_kernel(small_batch, expansion, trace_back, min_diags):
+    """Un-ambiguous reference + HDP machine: the band kernel's HDP variant (<W, C, false, HD = true>) against the oracle
+    and against the general kernel; events beyond both ends of the spline grid included (linear extrapolation)."""
+    reads, table = small_batch
+    trans = synth.nanopore_transitions()
+    model = sa.Model.from_tables("ACGT", 6, trans, table, kind=port.EMIT_HDP)
+    grid, k2r, pp, sl = _synthetic_hdp(table)
+    model.set_hdp(grid, k2r, pp, sl)
+    pm = port_model_from("ACGT", 6, trans, table, kind=port.EMIT_HDP, grid=grid, kmer_to_row=k2r, post_pred=pp, slopes=sl)
+    p = sa.default_params(threshold=0.01, expansion=expansion, trace_back=trace_back, min_diags=min_diags)
+    rs = [dict(r) for r in reads]
+    rs[1]["events"] = rs[1]["events"].copy()
+    rs[1]["events"][::37, 0] = 20.0      # far left of the grid
+    rs[1]["events"][5::41, 0] = 190.0    # far right
+    b = sa.Batch(model, [sa_read(r) for r in rs], p)
+    kernels = b.kernel_items
+    b.run()
+    fast = b.fetch()
+    b.close()
+    assert kernels[1] + kernels[2] == len(rs), kernels
+    os.environ["SA_FORCE_GENERAL"] = "1"
+    try:
+        gen = sa.align_batch(model, [sa_read(r) for r in rs], p)
+    finally:
+        os.environ.pop("SA_FORCE_GENERAL", None)
+    for i, r in enumerate(rs):
+        ora, _ = oracle_align(pm, r, port_params(p))
+        assert compare_pairs(fast.read_pairs(i), ora, p.threshold) <= 20
+        assert compare_pairs(fast.read_pairs(i), gen.read_pairs(i), p.threshold) <= 20
+
+
 def test_ambiguous_reference_iupac(gapped_batch):
     reads, table = gapped_batch
     trans = synth.nanopore_transitions()
