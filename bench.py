@@ -258,12 +258,28 @@ def main():
     # ---- config 4 beside it: getExpectationsUsingAnchors on the same reads, end to end (one warm-up, one timed call)
     exp_s = None
     if not a.no_expectations:
+        from signalalign_b200 import shard
+        exp_table = exp_ar_ms = None
         for i in range(2):
             t1 = time.time()
             r3 = sa.expectations_batch(model, reads, p)
             exp_s = time.time() - t1
+            exp_table = shard.expectation_table(r3)
             del r3
         barrier()
+        # the one collective of the path: all-reduce of the per-GPU expectation tables (NCCL over NVLink at N > 1),
+        # checked against the all-gathered per-rank tables
+        if world > 1:
+            shard.allreduce_expectations(exp_table, device=torch.device("cuda", local_rank))     # warm-up (communicator)
+            barrier()
+            t1 = time.time()
+            reduced = shard.allreduce_expectations(exp_table, device=torch.device("cuda", local_rank))
+            exp_ar_ms = 1e3 * (time.time() - t1)
+            parts = [torch.zeros(10, dtype=torch.float64, device="cuda") for _ in range(world)]
+            dist.all_gather(parts, torch.from_numpy(exp_table).to("cuda"))
+            want = torch.stack(parts).sum(0).cpu().numpy()
+            assert np.allclose(reduced, want, rtol=1e-12, atol=0), (reduced, want)
+            exp_table = reduced
 
     def reduce_max(x):
         if world == 1:
@@ -318,7 +334,8 @@ def main():
                        "aligned_pairs_rank0": n_pairs,
                        "expectations_e2e_rank0": None if exp_s is None else {
                            "call": "sa_gpu_expectations_batch (config 4 shape: same reads)", "events_per_s": events / exp_s,
-                           "gcups": cells / exp_s / 1e9, "ms": 1e3 * exp_s},
+                           "gcups": cells / exp_s / 1e9, "ms": 1e3 * exp_s,
+                           "allreduce_ms": exp_ar_ms, "table_all_ranks": [float(v) for v in exp_table]},
                        "kernel_ms_rank0": {"cta_128_256_slots": float(np.mean([m[0] for m in all_ms])),
                                            "cta_32_64_slots": float(np.mean([m[1] for m in all_ms])),
                                            "general": float(np.mean([m[2] for m in all_ms]))},
