@@ -238,6 +238,7 @@ def main():
     step_ms = float(np.sum(dev_ms)) / a.steps
     res = batch.fetch()
     n_pairs = int(res.pair_offsets[-1])
+    pairs_digest = [int(res.pairs[:, c].astype(np.int64).sum()) for c in range(4)]   # p, x, y, kmer column sums
     batch.close()
 
     # ---- end-to-end arm: host buffers -> C-ABI call -> host result (pack + H2D + kernels + D2H timed)
@@ -331,7 +332,7 @@ def main():
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": WORKLOAD, "reads_per_gpu_per_step": a.reads, "host_threads_per_rank": host_threads, "events_per_step": events_all,
                        "band_cells_per_step": cells_all, "l2": "flushed between steps (256 MiB write) and inputs > L2",
-                       "aligned_pairs_rank0": n_pairs,
+                       "aligned_pairs_rank0": n_pairs, "pairs_column_sums_rank0": pairs_digest,
                        "expectations_e2e_rank0": None if exp_s is None else {
                            "call": "sa_gpu_expectations_batch (config 4 shape: same reads)", "events_per_s": events / exp_s,
                            "gcups": cells / exp_s / 1e9, "ms": 1e3 * exp_s,

@@ -220,47 +220,62 @@ struct CtaK {
         eY = fma(-0.5 * aY, aY, S.cst[4][cs]);
     }
 
-    // The two sequential logAdd folds of S.foldv[0][*] and S.foldv[1][*] in column order, run by ONE warp.  Cells that
-    // cannot change an accumulator are skipped exactly: logAdd(acc, v) == acc whenever v <= acc - 7.5, and acc >= every
-    // value folded so far, so v <= prefixMax - 7.6 is an exact no-op (and folding such a cell anyway is harmless, which
-    // lets both folds walk the UNION of their candidate lanes: two independent dependency chains in flight).
+    // The two sequential logAdd folds of S.foldv[0][*] and S.foldv[1][*] in column order, run by ONE warp.  The fold is
+    // a dependent chain of logAdds (non-associative: the order is the reference's), so the work is to make the chain
+    // short, exactly:
+    //   * no-op cells: logAdd(acc, v) == acc whenever v <= acc - 7.5, and acc >= every value folded so far (the cubic
+    //     is positive on [0, 7.5)), so v <= prefixMax - 7.6 never changes the accumulator;
+    //   * reset cells: the cubic overshoots log(1 + e^-d) by < 1.1e-4, hence acc <= prefixMax + ln(NS) + NS * 1.1e-4
+    //     < prefixMax + 5.6, and a cell with v >= prefixMax + 13.2 makes |acc - v| >= 7.5: the result is v itself,
+    //     whatever came before.  The chain starts at the LAST such cell (the first finite cell is one).
+    // On a diagonal the terms rise by tens of nats per cell towards the alignment path and fall off behind it, so a
+    // chain is a handful of cells instead of every cell left of the path.  Candidates are read straight from shared
+    // memory (uniform address), the two folds advance in lockstep: two independent dependency chains in flight.
     static __device__ __forceinline__ void orderedFold2(const Smem &S, int lane, int32_t wlo, double &out0, double &out1) {
         const int s0 = wlo & (NS - 1);
-        double v[2][NL];
-        unsigned cand[2][NL], any = 0;
+        unsigned m[2][NL];
 #pragma unroll
         for (int f = 0; f < 2; f++) {
+            double carry = SA_NEG_INF;      // max over the previous 32-cell blocks
+            int lastReset = 0;
 #pragma unroll
-            for (int j = 0; j < NL; j++) v[f][j] = S.foldv[f][(s0 + lane * NL + j) & (NS - 1)];
-            double mx = v[f][0];
+            for (int k = 0; k < NL; k++) {
+                const double v = S.foldv[f][(s0 + k * 32 + lane) & (NS - 1)];
+                double run = v;
 #pragma unroll
-            for (int j = 1; j < NL; j++) mx = fmax(mx, v[f][j]);
-            double run = mx;
-#pragma unroll
-            for (int o = 1; o < 32; o <<= 1) {
-                const double q = __shfl_up_sync(0xffffffffu, run, o);
-                if (lane >= o) run = fmax(run, q);
+                for (int o = 1; o < 32; o <<= 1) {
+                    const double q = __shfl_up_sync(0xffffffffu, run, o);
+                    if (lane >= o) run = fmax(run, q);
+                }
+                double pm = __shfl_up_sync(0xffffffffu, run, 1);
+                if (lane == 0) pm = SA_NEG_INF;
+                pm = fmax(pm, carry);                       // exclusive prefix max in cell order
+                const unsigned mc = __ballot_sync(0xffffffffu, v > pm - 7.6);     // false for -inf
+                const unsigned mr = __ballot_sync(0xffffffffu, v >= pm + 13.2);
+                m[f][k] = mc;
+                if (mr) lastReset = k * 32 + 31 - __clz(mr);
+                carry = fmax(carry, __shfl_sync(0xffffffffu, run, 31));
             }
-            double pm = __shfl_up_sync(0xffffffffu, run, 1);
-            if (lane == 0) pm = SA_NEG_INF;
 #pragma unroll
-            for (int j = 0; j < NL; j++) {
-                const bool c = v[f][j] > pm - 7.6;   // false for -inf
-                cand[f][j] = __ballot_sync(0xffffffffu, c);
-                any |= cand[f][j];
-                pm = fmax(pm, v[f][j]);
+            for (int k = 0; k < NL; k++) {
+                if (k * 32 + 31 < lastReset) m[f][k] = 0;
+                else if (k * 32 <= lastReset) m[f][k] &= 0xffffffffu << (lastReset - k * 32);
             }
         }
         double acc0 = SA_NEG_INF, acc1 = SA_NEG_INF;
-        while (any) {
-            const int ln = __ffs(any) - 1;
-            any &= any - 1;
 #pragma unroll
-            for (int j = 0; j < NL; j++) {
-                const double q0 = __shfl_sync(0xffffffffu, v[0][j], ln), q1 = __shfl_sync(0xffffffffu, v[1][j], ln);
-                if (((cand[0][j] | cand[1][j]) >> ln) & 1u) {   // uniform branch
-                    acc0 = sa_logAdd(acc0, q0);
-                    acc1 = sa_logAdd(acc1, q1);
+        for (int k = 0; k < NL; k++) {
+            unsigned a = m[0][k], b = m[1][k];
+            while (a | b) {                                  // uniform
+                if (a) {
+                    const int i = __ffs(a) - 1;
+                    a &= a - 1;
+                    acc0 = sa_logAdd(acc0, S.foldv[0][(s0 + k * 32 + i) & (NS - 1)]);
+                }
+                if (b) {
+                    const int i = __ffs(b) - 1;
+                    b &= b - 1;
+                    acc1 = sa_logAdd(acc1, S.foldv[1][(s0 + k * 32 + i) & (NS - 1)]);
                 }
             }
         }

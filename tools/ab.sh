@@ -9,8 +9,7 @@ if [ "$1" = build ]; then
 else
     shift
     for v in "$@"; do
-        SA_LIBSAGPU=$PWD/gpurun_ab/libsagpu_$v.so python bench.py --no-cpu --steps 2 > gpurun_out/ab_$v.json 2> gpurun_out/ab_$v.err || tail -3 gpurun_out/ab_$v.err
-        python -c "
-import json; d=json.load(open('gpurun_out/ab_$v.json')); print('$v', 'gcups %.2f' % d['gcups'], 'ms %.1f' % d['ms_per_step'], 'e2e gcups %.2f' % d['e2e']['gcups'])"
+        SA_LIBSAGPU=$PWD/gpurun_ab/libsagpu_$v.so python bench.py --no-cpu --no-expectations --steps 2 > gpurun_out/ab_$v.json 2> gpurun_out/ab_$v.err || tail -3 gpurun_out/ab_$v.err
+        python tools/ab_line.py $v gpurun_out/ab_$v.json
     done
 fi
