@@ -44,8 +44,10 @@ __device__ __forceinline__ double sa_logAdd(double x, double y) {
     const double d = fabs(diff);                   // folded into the consumers as an operand modifier
     // |diff| >= 7.5, |diff| == inf (one operand -inf) and NaN (both -inf): the cubic's result is discarded
     const bool far = !(d < 7.5);
-    // n = ceil(2 d), clamped into the table (F2I saturates for inf and returns 0 for NaN)
-    const int n = min(__double2int_ru(__dadd_rn(d, d)), 15);
+    // n = ceil(2 d), clamped into the table: 2 d + 2^52 rounded UP leaves ceil(2 d) in the low mantissa word (one DFMA on
+    // the FP64 pipe instead of DADD + F2I on the XU pipe).  For d >= 2^31, inf and NaN the word is arbitrary, but those
+    // are `far` and the cubic is discarded; the unsigned clamp keeps the table index in range.
+    const unsigned n = umin((unsigned) __double2loint(__fma_ru(d, 2.0, 4503599627370496.0)), 15u);
     const double2 ca = *reinterpret_cast<const double2 *>(sa_lt + 4 * n);
     const double2 cb = *reinterpret_cast<const double2 *>(sa_lt + 4 * n + 2);
     double r = __dmul_rn(ca.x, d);
