@@ -428,19 +428,23 @@ struct CtaK {
                 bxlo = hdrNext.x; bxhi = hdrNext.y;
                 if (EX || d2 - 1 > tracedBackTo)
                     hdrNext = *reinterpret_cast<const int2 *>(ring + (int64_t) rowP * ROW);
-                if (bxlo < bw) bw = bxlo;      // lower the window; recycled slots restart at -inf
+                const bool slid = bxlo < bw;
+                if (slid) bw = bxlo;           // lower the window; recycled slots restart at -inf
                 ensureRings(P, I, S, t, bw, d2, cLo, eLo);
+                if (slid) {                    // (uniform branch: the per-slot checks run on slide steps only)
+#pragma unroll
+                    for (int j = 0; j < C; j++) {
+                        const int32_t x = slotX(t * C + j, bw);
+                        if (x != myx[j]) {
+                            myx[j] = x;
+                            curM[j] = SA_NEG_INF; curE[j] = 0.0; nxtM[j] = SA_NEG_INF; nxtE[j] = 0.0;
+                            qX[j] = SA_NEG_INF; qY[j] = SA_NEG_INF; qE[j] = 0.0;
+                        }
+                    }
+                }
                 double eM[C], eY[C];
 #pragma unroll
-                for (int j = 0; j < C; j++) {
-                    const int32_t x = slotX(t * C + j, bw);
-                    if (x != myx[j]) {
-                        myx[j] = x;
-                        curM[j] = SA_NEG_INF; curE[j] = 0.0; nxtM[j] = SA_NEG_INF; nxtE[j] = 0.0;
-                        qX[j] = SA_NEG_INF; qY[j] = SA_NEG_INF; qE[j] = 0.0;
-                    }
-                    emissions(P, I, S, x, d2 - x, eM[j], eY[j]);
-                }
+                for (int j = 0; j < C; j++) emissions(P, I, S, myx[j], d2 - myx[j], eM[j], eY[j]);
                 sa_mbWait(&S.mbar, phase);     // mailbox and hit masks of diagonal d2 + 1 are visible
                 if (pendValid) flush();
                 double nb[3];
@@ -625,18 +629,25 @@ struct CtaK {
             if (d >= bd0 + NT) { bd0 = d; fillBand(P, I, S, t, bd0); }
             const int2 bnd = S.bandTab[d - bd0];
             const int32_t xlo = bnd.x, xhi = bnd.y;
-            if (xhi > wlo + NS - 1) wlo = xhi - (NS - 1);   // slide the window up; recycled slots restart at -inf
+            const bool slid = xhi > wlo + NS - 1;
+            if (slid) wlo = xhi - (NS - 1);    // slide the window up; recycled slots restart at -inf
             ensureRings(P, I, S, t, wlo, d, cLo, eLo);
+            if (slid) {                        // (uniform branch: the per-slot checks run on slide steps only)
+#pragma unroll
+                for (int j = 0; j < C; j++) {
+                    const int32_t x = slotX(t * C + j, wlo);
+                    if (x != myx[j]) {
+                        myx[j] = x;
+                        fa[j][0] = fa[j][1] = fa[j][2] = SA_NEG_INF;
+                        fb[j][0] = fb[j][1] = fb[j][2] = SA_NEG_INF;
+                    }
+                }
+            }
             bool act[C];
             double eM[C], eY[C];
 #pragma unroll
             for (int j = 0; j < C; j++) {
-                const int32_t x = slotX(t * C + j, wlo);
-                if (x != myx[j]) {
-                    myx[j] = x;
-                    fa[j][0] = fa[j][1] = fa[j][2] = SA_NEG_INF;
-                    fb[j][0] = fb[j][1] = fb[j][2] = SA_NEG_INF;
-                }
+                const int32_t x = myx[j];
                 act[j] = x >= xlo && x <= xhi;
                 emissions(P, I, S, x, d - x, eM[j], eY[j]);
             }

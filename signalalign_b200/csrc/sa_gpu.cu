@@ -262,12 +262,19 @@ struct sa_batch {
     struct StreamOwner {         // declared before every DevBuf: destroyed after their stream-ordered frees were queued
         cudaStream_t s = nullptr;
         ~StreamOwner() { if (s) cudaStreamDestroy(s); }
-    } streamOwner, auxOwner;
+    } streamOwner, auxOwner, latOwner;
     cudaStream_t stream = nullptr;  // the band kernels
     // everything else (H2D, geometry pass, compaction, D2H) on a HIGH-priority stream: when several batches are in
     // flight, these small kernels must overtake the not yet resident CTAs of another batch's persistent band kernel
     cudaStream_t aux = nullptr;
     cudaEvent_t evPrepared = nullptr;
+    // latency class: the few reads whose own sweep is long against the whole batch run on the one-cell-per-thread
+    // mapping (<4, 1>: half the instructions per thread and diagonal) next to the throughput kernel, on their own stream
+    cudaStream_t lat = nullptr;
+    cudaEvent_t evFork = nullptr, evJoin = nullptr;
+    std::vector<int32_t> latOrder;
+    int latBlocks = 0;
+    int32_t latRows = 1;
     cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     std::vector<ItemRec> items;  // global item id = index
     // shared inputs
@@ -293,7 +300,8 @@ struct sa_batch {
     DevBuf<FItem> dFItems;
     DevBuf<int32_t> dFOrder[4], dTb;
     DevBuf<FGeo> dGeo;
-    DevBuf<double> dFScratch;
+    DevBuf<double> dFScratch, dLatScratch;
+    DevBuf<int32_t> dLatOrder;
     FParams fp;
     int fBlocks[4] = {0, 0, 0, 0};
     int32_t fRows[4] = {1, 1, 1, 1};
@@ -309,6 +317,8 @@ struct sa_batch {
         for (auto &e : ev)
             if (e) cudaEventDestroy(e);
         if (evPrepared) cudaEventDestroy(evPrepared);
+        if (evFork) cudaEventDestroy(evFork);
+        if (evJoin) cudaEventDestroy(evJoin);
     }
 };
 
@@ -364,8 +374,10 @@ static void ctaLaunch(int c, bool oneCell, bool ex, bool hdp, int blocks, cudaSt
 }
 
 // readBase: index of reads[0] in the caller's array (error messages name the caller's read)
+// chunkCount: how many sub-batches of this size the caller runs back to back (scales the latency-class decision)
 static int prepareBatch(const sa_model_t *m, const sa_read_t *reads, int64_t nReads, const sa_params_t *p,
-                        const sa_ambig_t *ambigIn, int expectations, int64_t readBase, sa_batch_t **out) {
+                        const sa_ambig_t *ambigIn, int expectations, int64_t readBase, int64_t chunkCount,
+                        sa_batch_t **out) {
     *out = nullptr;
     if (sa_gpu_device_count() == 0) {
         sa_set_error("sa_batch_prepare: no CUDA device available; libsagpu has no CPU fallback");
@@ -399,8 +411,12 @@ static int prepareBatch(const sa_model_t *m, const sa_read_t *reads, int64_t nRe
     CK(cudaDeviceGetStreamPriorityRange(&prLeast, &prGreatest));
     CK(cudaStreamCreateWithPriority(&b->streamOwner.s, cudaStreamNonBlocking, prLeast));
     CK(cudaStreamCreateWithPriority(&b->auxOwner.s, cudaStreamNonBlocking, prGreatest));
+    CK(cudaStreamCreateWithPriority(&b->latOwner.s, cudaStreamNonBlocking, prGreatest));
     b->stream = b->streamOwner.s;
     b->aux = b->auxOwner.s;
+    b->lat = b->latOwner.s;
+    CK(cudaEventCreateWithFlags(&b->evFork, cudaEventDisableTiming));
+    CK(cudaEventCreateWithFlags(&b->evJoin, cudaEventDisableTiming));
     for (auto &e : b->ev) CK(cudaEventCreate(&e));
     CK(cudaEventCreateWithFlags(&b->evPrepared, cudaEventDisableTiming));
     cudaStream_t st = b->aux;
@@ -703,10 +719,31 @@ static int prepareBatch(const sa_model_t *m, const sa_read_t *reads, int64_t nRe
     b->warpKernel = useWarpKernel;
     b->oneCell = getenv("SA_CTA_C1") != nullptr;
     auto byWork = [&](int32_t a, int32_t c) { return items[a].work > items[c].work; };
+    for (int c = 0; c < 4; c++) std::stable_sort(b->fOrder[c].begin(), b->fOrder[c].end(), byWork);
+    // Latency class.  A read is one CTA's sequential sweep (~2.3 us per diagonal on the two-cell mapping under load);
+    // when that alone exceeds half of what the whole batch needs at full throughput (~30 GCUPS), the read decides the
+    // makespan (heavy-tailed lengths, BASELINE config 5; batches smaller than the resident grid).  Those reads, at most
+    // two per SM and longest first, go to the one-cell mapping, whose step is about half as long.
+    if (!useWarpKernel && !b->oneCell && !b->expectations && m->kind != SA_EMIT_HDP && getenv("SA_NO_LATENCY_CLASS") == nullptr) {
+        const double ideal = (double) b->bandCells * (double) chunkCount / 30e9;
+        std::vector<int32_t> keep;
+        for (int32_t i : b->fOrder[2]) {
+            const double solo = (double) (items[i].lX + items[i].lY) * 2.3e-6;
+            if ((int64_t) b->latOrder.size() < 2 * (int64_t) nSM && solo > 0.5 * ideal) {
+                b->latOrder.push_back(i);
+                b->latRows = std::max(b->latRows, geo[i].maxRows);
+            } else keep.push_back(i);
+        }
+        b->fOrder[2].swap(keep);
+        if (!b->latOrder.empty()) {
+            if ((rc = b->dLatOrder.upload(b->latOrder, st, &b->h2dBytes))) return rc;
+            b->latBlocks = (int) b->latOrder.size();
+            if ((rc = b->dLatScratch.alloc((size_t) b->latBlocks * b->latRows * (3 * 128 + 2), st))) return rc;
+        }
+    }
     {
         int64_t need = 1;
         for (int c = 0; c < 4; c++) {
-            std::stable_sort(b->fOrder[c].begin(), b->fOrder[c].end(), byWork);
             if ((rc = b->dFOrder[c].upload(b->fOrder[c], st, &b->h2dBytes))) return rc;
             if (b->fOrder[c].empty()) continue;
             int bps = 1;
@@ -822,7 +859,7 @@ static int prepareBatch(const sa_model_t *m, const sa_read_t *reads, int64_t nRe
 
 extern "C" int sa_batch_prepare(const sa_model_t *m, const sa_read_t *reads, int64_t nReads, const sa_params_t *p,
                                 const sa_ambig_t *ambig, int expectations, sa_batch_t **out) {
-    return prepareBatch(m, reads, nReads, p, ambig, expectations, 0, out);
+    return prepareBatch(m, reads, nReads, p, ambig, expectations, 0, 1, out);
 }
 
 // queue the batch's kernels on its stream; returns without waiting for them
@@ -832,8 +869,23 @@ static int launchBatch(sa_batch_t *b) {
     b->lastLaunches = 0;
     CK(cudaMemsetAsync(b->dCounters.p, 0, 8 * sizeof(int32_t), st));
     CK(cudaEventRecord(b->ev[0], st));
+    if (!b->latOrder.empty()) {                // first, so that its CTAs are resident before the persistent grid fills the SMs
+        CK(cudaEventRecord(b->evFork, st));
+        CK(cudaStreamWaitEvent(b->lat, b->evFork, 0));
+        FParams f = b->fp;
+        f.order = b->dLatOrder.p; f.nOrder = (int32_t) b->latOrder.size(); f.counter = b->dCounters.p + 5;
+        f.rowsCap = b->latRows;
+        f.scratch = b->dLatScratch.p;
+        sa_cta_kernel<4, 1, false, false><<<b->latBlocks, 128, 0, b->lat>>>(f);
+        b->lastLaunches++;
+        CK(cudaGetLastError());
+        CK(cudaEventRecord(b->evJoin, b->lat));
+    }
     for (int c = 3; c >= 0; c--) {             // widest class first; [ev0, ev1) = W >= 4, [ev1, ev2) = W <= 2
-        if (c == 1) CK(cudaEventRecord(b->ev[1], st));
+        if (c == 1) {
+            if (!b->latOrder.empty()) CK(cudaStreamWaitEvent(st, b->evJoin, 0));   // counted with the 128-slot class
+            CK(cudaEventRecord(b->ev[1], st));
+        }
         if (b->fOrder[c].empty()) continue;
         FParams f = b->fp;
         f.order = b->dFOrder[c].p; f.nOrder = (int32_t) b->fOrder[c].size(); f.counter = b->dCounters.p + c;
@@ -1100,7 +1152,7 @@ extern "C" int64_t sa_batch_band_cells(const sa_batch_t *b) { return b->bandCell
 extern "C" void sa_batch_kernel_items(const sa_batch_t *b, int64_t *o) {
     o[0] = (int64_t) b->gOrder.size();
     o[1] = (int64_t) (b->fOrder[0].size() + b->fOrder[1].size());
-    o[2] = (int64_t) (b->fOrder[2].size() + b->fOrder[3].size());
+    o[2] = (int64_t) (b->fOrder[2].size() + b->fOrder[3].size() + b->latOrder.size());
 }
 extern "C" int64_t sa_batch_h2d_bytes(const sa_batch_t *b) { return b->h2dBytes; }
 extern "C" int64_t sa_batch_d2h_bytes(const sa_batch_t *b) { return b->d2hBytes; }
@@ -1165,7 +1217,7 @@ static int alignPipelined(const sa_model_t *m, const sa_read_t *reads, int64_t n
     int rc = SA_OK;
     for (int64_t k = 0; k < nch; k++) {
         sa_batch_t *b = nullptr;
-        if ((rc = prepareBatch(m, reads + lo[k], lo[k + 1] - lo[k], p, ambig, 0, lo[k], &b))) break;
+        if ((rc = prepareBatch(m, reads + lo[k], lo[k + 1] - lo[k], p, ambig, 0, lo[k], nch, &b))) break;
         bs.emplace_back(b);
         if ((rc = launchBatch(b))) break;
     }
@@ -1179,10 +1231,10 @@ static int alignPipelined(const sa_model_t *m, const sa_read_t *reads, int64_t n
     r->pairOffsets = (int64_t *) calloc(nReads + 1, sizeof(int64_t));
     PairSink sink;
     int64_t capAll = 1;
-    for (auto &b : bs)
-        for (auto &it : b->items) capAll += it.pairCap;
+    for (auto &b : bs) capAll += b->events + b->events / 2 + 64 * (int64_t) b->items.size();
     g_lastH2d = g_lastD2h = g_lastLaunches = 0;
-    // the upper bound (3 pairs per event) only costs address space of the cached pinned slab; typical use is < 1/3
+    // first guess 1.5 pairs per event (nanopore reads give 1.0 - 1.3 at threshold 0.01); the sink grows when a chunk
+    // needs more (every D2H into it has completed by then)
     rc = sinkReserve(sink, capAll);
     for (int64_t k = 0; k < nch && !rc; k++) {
         sa_batch *b = bs[k].get();

@@ -28,12 +28,16 @@ def gapped_batch():
     return reads, table
 
 
-def _run_and_compare(reads, table, p, max_dp=10, force_general=False, expect_fast=None):
+def _run_and_compare(reads, table, p, max_dp=10, force_general=False, expect_fast=None, no_latency=False):
+    """no_latency: keep small batches on the throughput mapping (two cells per thread); by default the scheduler sends
+    reads that dominate their batch to the one-cell mapping, which is every read of a six-read test batch."""
     trans = synth.nanopore_transitions()
     model = sa.Model.from_tables("ACGT", 6, trans, table)
     pm = port_model_from("ACGT", 6, trans, table)
     if force_general:
         os.environ["SA_FORCE_GENERAL"] = "1"
+    if no_latency:
+        os.environ["SA_NO_LATENCY_CLASS"] = "1"
     try:
         b = sa.Batch(model, [sa_read(r) for r in reads], p)
         kernels = b.kernel_items
@@ -42,6 +46,7 @@ def _run_and_compare(reads, table, p, max_dp=10, force_general=False, expect_fas
         b.close()
     finally:
         os.environ.pop("SA_FORCE_GENERAL", None)
+        os.environ.pop("SA_NO_LATENCY_CLASS", None)
     if force_general:
         assert kernels[1] == 0 and kernels[2] == 0
     elif expect_fast is not None:
@@ -64,6 +69,8 @@ def test_gaussian_meanonly_small(small_batch, expansion, trace_back, min_diags, 
     p = sa.default_params(threshold=0.01, expansion=expansion, trace_back=trace_back, min_diags=min_diags)
     expect = {50: 1, 100: 2, 20: 1, 6: 1}[expansion]
     _run_and_compare(reads, table, p, force_general=force_general, expect_fast=expect)
+    if not force_general and expansion == 100:      # 128-slot class: both mappings
+        _run_and_compare(reads, table, p, expect_fast=expect, no_latency=True)
 
 
 @pytest.mark.parametrize("expansion", [20, 50, 100])
@@ -85,6 +92,7 @@ def test_medium_reads_many_blocks():
     reads, table = synth.make_batch(3, seed=5, mean_len=2500, min_len=2000, max_len=3000, trim=0)
     p = sa.default_params(threshold=0.01, expansion=100, trace_back=50, min_diags=1000)
     _run_and_compare(reads, table, p, expect_fast=2)
+    _run_and_compare(reads, table, p, expect_fast=2, no_latency=True)
 
 
 @pytest.mark.parametrize("expansion,trace_back,min_diags", [(50, 50, 200), (100, 50, 300), (20, 40, 1000), (6, 2, 10)])
@@ -281,7 +289,13 @@ def test_config3_size_reads_band_kernel_equals_general_kernel():
     p = sa.default_params(threshold=bench.THRESHOLD, expansion=bench.EXPANSION, trace_back=bench.TRACE_BACK,
                           min_diags=bench.MIN_DIAGS)
     rs = [sa_read(r) for r in reads]
-    fast = sa.align_batch(model, rs, p)
+    lat = sa.align_batch(model, rs, p)              # 48 reads: every read is in the latency class (one cell per thread)
+    os.environ["SA_NO_LATENCY_CLASS"] = "1"
+    try:
+        fast = sa.align_batch(model, rs, p)         # two cells per thread
+    finally:
+        os.environ.pop("SA_NO_LATENCY_CLASS", None)
+    assert np.array_equal(lat.pair_offsets, fast.pair_offsets) and np.array_equal(lat.pairs, fast.pairs)
     fe = sa.expectations_batch(model, rs, p)
     os.environ["SA_FORCE_GENERAL"] = "1"
     try:
