@@ -136,21 +136,29 @@ static std::mutex g_pinMu;
 static std::vector<PinnedSlot> g_pins;
 static void *pinAcquire(size_t bytes) {
     std::lock_guard<std::mutex> lk(g_pinMu);
-    int best = -1, idle = -1;
+    int best = -1;
+    size_t total = 0;
     for (int i = 0; i < (int) g_pins.size(); i++) {
-        if (g_pins[i].busy) continue;
-        idle = i;
+        total += g_pins[i].cap;
+        if (g_pins[i].busy || !g_pins[i].p) continue;
         if (g_pins[i].cap >= bytes && (best < 0 || g_pins[i].cap < g_pins[best].cap)) best = i;
     }
     if (best < 0) {
-        if (idle < 0) { g_pins.push_back(PinnedSlot()); idle = (int) g_pins.size() - 1; }
-        PinnedSlot &sl = g_pins[idle];
-        if (sl.p) cudaFreeHost(sl.p);
-        sl.p = nullptr; sl.cap = 0;
+        // nothing idle fits: add a slab (never re-size an idle one — it is somebody's steady-state size and replacing it
+        // makes every call pay cudaHostAlloc again); idle slabs are only given back once the pool passes 32 GB
         size_t cap = bytes + bytes / 4 + 4096;
-        if (cudaHostAlloc(&sl.p, cap, cudaHostAllocDefault) != cudaSuccess) { sl.p = nullptr; return nullptr; }
+        if (total + cap > ((size_t) 32 << 30))
+            for (auto &sl : g_pins)
+                if (!sl.busy && sl.p) { cudaFreeHost(sl.p); sl.p = nullptr; sl.cap = 0; }
+        int slot = -1;
+        for (int i = 0; i < (int) g_pins.size(); i++)
+            if (!g_pins[i].p) { slot = i; break; }
+        if (slot < 0) { g_pins.push_back(PinnedSlot()); slot = (int) g_pins.size() - 1; }
+        PinnedSlot &sl = g_pins[slot];
+        if (cudaHostAlloc(&sl.p, cap, cudaHostAllocDefault) != cudaSuccess) { sl.p = nullptr; sl.cap = 0; return nullptr; }
         sl.cap = cap;
-        best = idle;
+        sl.busy = false;
+        best = slot;
     }
     g_pins[best].busy = true;
     return g_pins[best].p;
