@@ -11,7 +11,10 @@ import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 REF_DIR = os.path.join(HERE, "_ref")
-LIB_PATH = os.path.join(REF_DIR, "libsaref.so")
+# SA_REF_LIB: load another build of the same harness instead — tests/test_gpu_shim.py points it at libsaref_gpu.so (the
+# reference with its two entry points bound to libsagpu) in a process of its own
+LIB_PATH = os.environ.get("SA_REF_LIB") or os.path.join(REF_DIR, "libsaref.so")
+GPU_LIB_PATH = os.path.join(REF_DIR, "libsaref_gpu.so")
 
 _lib = None
 

@@ -1,0 +1,162 @@
+/*
+ * signalalign_shim.c — the reference-side binding of libsagpu: the two entry points signalMachine calls,
+ *
+ *     getAlignedPairsUsingAnchors   (reference inc/pairwiseAligner.h:406-414, call site impl/signalMachine.c:436-437)
+ *     getExpectationsUsingAnchors   (reference inc/pairwiseAligner.h:417-429, call site impl/signalMachine.c:479-480)
+ *
+ * with the reference's own prototypes, implemented on the C-ABI of include/signalalign_b200.h.  This file is compiled
+ * INSIDE the reference tree (it needs inc/stateMachine.h, inc/pairwiseAligner.h and sonLib) next to pairwiseAligner.c,
+ * whose own two definitions are renamed at compile time (-DgetAlignedPairsUsingAnchors=cpu_getAlignedPairsUsingAnchors
+ * -DgetExpectationsUsingAnchors=cpu_getExpectationsUsingAnchors on that one translation unit), so every caller —
+ * signalMachine.c, the C test suites — links against the GPU path unchanged.  See INTEGRATION.md.
+ *
+ * Behaviour kept from the reference: inputs are borrowed; the returned stList owns stIntTuple4(floor(p*1e7), x, y,
+ * (int64_t) char *kmer) with destructor stIntTuple_destruct and kmer strings that are never freed
+ * (impl/pairwiseAligner.c:665-668, 2064); expectations are added into the caller's Hmm through its own function
+ * pointers; any failure aborts the process through st_errAbort (no return codes, no CPU fallback).
+ * Not covered here: StateMachine3_HDP (hdp.c keeps its structs private: load the same .nhdp with sa_model_load),
+ * and per-Sequence ambiguity tables other than the built-in one (create_ambig_bases2(NULL)).
+ */
+#include <stdlib.h>
+#include <string.h>
+
+#include "signalalign_b200.h"
+
+#include "pairwiseAligner.h"
+#include "stateMachine.h"
+#include "continuousHmm.h"
+
+/* one device model per StateMachine (keyed by the struct's address and its table pointers) */
+#define SHIM_CACHE 8
+static struct {
+    const StateMachine *sM;
+    const double *match;
+    sa_model_t *model;
+} g_cache[SHIM_CACHE];
+static int g_cacheNext = 0, g_inited = 0;
+
+static sa_model_t *shimModel(StateMachine *sM) {
+    if (!g_inited) {
+        const char *dev = getenv("SA_SHIM_DEVICE");
+        if (sa_gpu_init(dev ? atoi(dev) : 0) != SA_OK) st_errAbort("libsagpu: %s\n", sa_last_error());
+        g_inited = 1;
+    }
+    for (int i = 0; i < SHIM_CACHE; i++)
+        if (g_cache[i].model && g_cache[i].sM == sM && g_cache[i].match == sM->EMISSION_MATCH_MATRIX) return g_cache[i].model;
+    if (sM->type != threeState)
+        st_errAbort("signalalign_shim: only the 3-state Gaussian machine is bound through the StateMachine struct; "
+                    "for StateMachine3_HDP load the .model/.nhdp pair with sa_model_load\n");
+    StateMachine3 *s3 = (StateMachine3 *) sM;
+    double t[9] = {s3->TRANSITION_MATCH_CONTINUE, s3->TRANSITION_MATCH_FROM_GAP_X, s3->TRANSITION_MATCH_FROM_GAP_Y,
+                   s3->TRANSITION_GAP_OPEN_X, s3->TRANSITION_GAP_OPEN_Y, s3->TRANSITION_GAP_EXTEND_X,
+                   s3->TRANSITION_GAP_EXTEND_Y, s3->TRANSITION_GAP_SWITCH_TO_X, s3->TRANSITION_GAP_SWITCH_TO_Y};
+    int kind;
+    if (s3->getMatchProbFcn == emissions_signal_strawManGetKmerEventMatchProbWithDescaling_MeanOnly)
+        kind = SA_EMIT_GAUSS_MEANONLY_DESCALE;
+    else if (s3->getMatchProbFcn == emissions_signal_strawManGetKmerEventMatchProbWithDescaling)
+        kind = SA_EMIT_GAUSS_NOISE_DESCALE;
+    else if (s3->getMatchProbFcn == emissions_signal_strawManGetKmerEventMatchProb)
+        kind = SA_EMIT_GAUSS_NOISE_SCALED;
+    else {
+        st_errAbort("signalalign_shim: unknown emission function in StateMachine3\n");
+        return NULL;
+    }
+    sa_model_t *m = sa_model_from_tables(sM->alphabet, (int32_t) sM->kmerLength, t, sM->EMISSION_MATCH_MATRIX,
+                                         sM->EMISSION_GAP_Y_MATRIX, sM->EMISSION_GAP_X_PROBS, kind);
+    if (!m) st_errAbort("libsagpu: %s\n", sa_last_error());
+    int slot = g_cacheNext++ % SHIM_CACHE;
+    if (g_cache[slot].model) sa_model_free(g_cache[slot].model);
+    g_cache[slot].sM = sM;
+    g_cache[slot].match = sM->EMISSION_MATCH_MATRIX;
+    g_cache[slot].model = m;
+    return m;
+}
+
+/* the flat view of one call's inputs; *anchorsOut is malloc'ed */
+static void shimRead(StateMachine *sM, Sequence *sX, Sequence *sY, stList *anchorPairs, bool raggedL, bool raggedR,
+                     sa_read_t *r, int64_t **anchorsOut) {
+    int64_t nA = stList_length(anchorPairs);
+    int64_t *an = st_malloc(sizeof(int64_t) * 2 * (nA + 1));
+    for (int64_t i = 0; i < nA; i++) {
+        stIntTuple *a = stList_get(anchorPairs, i);
+        an[2 * i] = stIntTuple_get(a, 0);
+        an[2 * i + 1] = stIntTuple_get(a, 1);
+    }
+    memset(r, 0, sizeof(*r));
+    r->target = (const char *) sX->elements;
+    r->targetLength = sX->length > 0 ? sX->length + sM->kmerLength - 1 : 0;   /* sX->length counts kmers */
+    r->events = (const double *) sY->elements;
+    r->nEvents = sY->length;
+    r->anchors = an;
+    r->nAnchors = nA;
+    r->scale = sM->scale; r->shift = sM->shift; r->var = sM->var;
+    r->raggedLeft = raggedL; r->raggedRight = raggedR;
+    *anchorsOut = an;
+}
+
+static void shimParams(const PairwiseAlignmentParameters *p, sa_params_t *sp) {
+    sa_params_default(sp);
+    sp->threshold = p->threshold;
+    sp->minDiagsBetweenTraceBack = p->minDiagsBetweenTraceBack;
+    sp->traceBackDiagonals = p->traceBackDiagonals;
+    sp->diagonalExpansion = p->diagonalExpansion;
+    sp->splitMatrixBiggerThanThis = p->splitMatrixBiggerThanThis;
+}
+
+stList *getAlignedPairsUsingAnchors(StateMachine *sM, Sequence *SsX, Sequence *SsY, stList *anchorPairs,
+                                    PairwiseAlignmentParameters *p,
+                                    void (*diagonalPosteriorProbFn)(StateMachine *sM, int64_t xay, DpMatrix *forwardDpMatrix,
+                                                                    DpMatrix *backwardDpMatrix, Sequence *sX, Sequence *sY,
+                                                                    double totalProbability,
+                                                                    PairwiseAlignmentParameters *p, void *extraArgs),
+                                    bool alignmentHasRaggedLeftEnd, bool alignmentHasRaggedRightEnd) {
+    if (diagonalPosteriorProbFn != diagonalCalculationPosteriorMatchProbs)
+        st_errAbort("signalalign_shim: getAlignedPairsUsingAnchors is bound for diagonalCalculationPosteriorMatchProbs only\n");
+    sa_model_t *m = shimModel(sM);
+    sa_read_t r;
+    int64_t *an;
+    shimRead(sM, SsX, SsY, anchorPairs, alignmentHasRaggedLeftEnd, alignmentHasRaggedRightEnd, &r, &an);
+    sa_params_t sp;
+    shimParams(p, &sp);
+    sa_result_t *res = NULL;
+    if (sa_gpu_align_batch(m, &r, 1, &sp, NULL, &res) != SA_OK) st_errAbort("libsagpu: %s\n", sa_last_error());
+    stList *out = stList_construct3(0, (void (*)(void *)) stIntTuple_destruct);
+    const int64_t n = res->pairOffsets[1], k = sM->kmerLength;
+    /* one arena for the call's kmer strings; like the reference's, they outlive the list and are never freed */
+    char *arena = n > 0 ? st_malloc((size_t) n * (k + 1)) : NULL;
+    for (int64_t i = 0; i < n; i++) {
+        char *km = arena + i * (k + 1);
+        sa_kmer_string(m, res->pairs[i].kmerIdx, km);
+        stList_append(out, stIntTuple_construct4(res->pairs[i].p, res->pairs[i].x, res->pairs[i].y, (int64_t) km));
+    }
+    sa_result_free(res);
+    free(an);
+    return out;
+}
+
+void getExpectationsUsingAnchors(StateMachine *sM, Hmm *hmmExpectations, Sequence *SsX, Sequence *SsY, stList *anchorPairs,
+                                 PairwiseAlignmentParameters *p,
+                                 void (*diagonalCalcExpectationFcn)(StateMachine *sM, int64_t xay, DpMatrix *forwardDpMatrix,
+                                                                    DpMatrix *backwardDpMatrix, Sequence *sX, Sequence *sY,
+                                                                    double totalProbability,
+                                                                    PairwiseAlignmentParameters *p, void *extraArgs),
+                                 bool alignmentHasRaggedLeftEnd, bool alignmentHasRaggedRightEnd) {
+    if (diagonalCalcExpectationFcn != diagonalCalculation_Expectations)
+        st_errAbort("signalalign_shim: getExpectationsUsingAnchors is bound for diagonalCalculation_Expectations only\n");
+    sa_model_t *m = shimModel(sM);
+    sa_read_t r;
+    int64_t *an;
+    shimRead(sM, SsX, SsY, anchorPairs, alignmentHasRaggedLeftEnd, alignmentHasRaggedRightEnd, &r, &an);
+    sa_params_t sp;
+    shimParams(p, &sp);
+    sa_result_t *res = NULL;
+    if (sa_gpu_expectations_batch(m, &r, 1, &sp, NULL, &res) != SA_OK) st_errAbort("libsagpu: %s\n", sa_last_error());
+    /* cell_signal_updateExpectations adds every term through the Hmm's own function (continuousHmm.c:147-149);
+     * the likelihood is a plain field (pairwiseAligner.c:1432) */
+    for (int64_t from = 0; from < 3; from++)
+        for (int64_t to = 0; to < 3; to++)
+            hmmExpectations->addToTransitionExpectationFcn(hmmExpectations, from, to, res->transitions[from * 3 + to]);
+    hmmExpectations->likelihood += res->likelihood[0];
+    sa_result_free(res);
+    free(an);
+}

@@ -1,0 +1,90 @@
+"""-m gpu: the reference's OWN entry points on the GPU.
+
+oracle/_ref/libsaref_gpu.so is the unmodified reference (compiled by oracle/Makefile) with getAlignedPairsUsingAnchors /
+getExpectationsUsingAnchors bound to libsagpu.so by signalalign_b200/shim/signalalign_shim.c — the link-time
+substitution INTEGRATION.md describes.  The reference's loaders build the StateMachine from a .model file, the harness
+calls the entry points exactly as signalMachine.c does, and the results are compared with the golden outputs of the
+unmodified reference (tests/golden/).  Runs in a process of its own: two builds of the same C library must not share a
+symbol namespace.
+"""
+import json
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+from helpers import ROOT_DIR, compare_expectations, compare_pairs, golden, params_from, write_model_file
+
+pytestmark = pytest.mark.gpu
+
+GPU_LIB = os.path.join(ROOT_DIR, "oracle", "_ref", "libsaref_gpu.so")
+
+CHILD = r"""
+import ctypes, json, os, sys
+import numpy as np
+sys.path.insert(0, sys.argv[1])
+from oracle import ref
+job = json.load(open(sys.argv[2]))
+z = np.load(job["inputs"])
+sm = ref.RefStateMachine(job["model"], kind=0)
+sm.set_scaling(*job["scaling"])
+out = {}
+for tag, par in job["params"].items():
+    pairs, kmers, sec = sm.align(str(z["target"]), z["events"], z["anchors"], **par)
+    out["pairs_" + tag] = pairs
+    out["kmers_" + tag] = np.array(kmers)
+    tr, lik, _, _, _ = sm.expectations(str(z["target"]), z["events"], z["anchors"], **par)
+    out["tr_" + tag] = tr
+    out["lik_" + tag] = np.array(lik)
+sagpu = ctypes.CDLL(os.path.join(sys.argv[1], "signalalign_b200", "libsagpu.so"))
+a, b, c = ctypes.c_int64(0), ctypes.c_int64(0), ctypes.c_int64(0)
+sagpu.sa_last_call_stats(ctypes.byref(a), ctypes.byref(b), ctypes.byref(c))
+out["gpu_launches_last_align"] = np.array(c.value)
+out["has_cpu_symbol"] = np.array(hasattr(ref.lib(), "cpu_getAlignedPairsUsingAnchors"))
+np.savez(job["out"], **out)
+"""
+
+
+def _run_child(tmp_path, model_file, scaling, inputs, params):
+    job = dict(model=model_file, scaling=[float(v) for v in scaling], inputs=os.path.join(str(tmp_path), "in.npz"),
+               params=params, out=os.path.join(str(tmp_path), "out.npz"))
+    np.savez(job["inputs"], **inputs)
+    with open(os.path.join(str(tmp_path), "job.json"), "w") as f:
+        json.dump(job, f)
+    env = dict(os.environ, SA_REF_LIB=GPU_LIB)
+    r = subprocess.run([sys.executable, "-c", CHILD, ROOT_DIR, os.path.join(str(tmp_path), "job.json")], env=env,
+                       capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-2000:]
+    with np.load(job["out"]) as z:
+        return {k: z[k] for k in z.files}
+
+
+def _kw(par):
+    return dict(threshold=par["threshold"], min_diags=par["min_diags"], trace_back=par["trace_back"],
+                expansion=par["expansion"], split_bigger=par["split_bigger"])
+
+
+@pytest.mark.skipif(not os.path.exists(GPU_LIB), reason="oracle/_ref/libsaref_gpu.so not built (needs /root/reference at build time)")
+def test_reference_entry_points_run_on_the_gpu(tmp_path):
+    g = golden("zymo_meanonly")
+    t = golden("model_r73_acegot")
+    model_file = os.path.join(str(tmp_path), "acegot.model")
+    write_model_file(model_file, str(t["alphabet"]), int(t["k"]), t["trans"], t["match"])
+    tags = ("cli", "lib", "tight", "split")
+    params = {tag: _kw(params_from(g["params_" + tag])) for tag in tags}
+    out = _run_child(tmp_path, model_file, g["tparams"][:3], dict(target=g["target"], events=g["events"], anchors=g["anchors"]),
+                     params)
+    assert bool(out["has_cpu_symbol"]) and int(out["gpu_launches_last_align"]) > 0      # the shim build, on the device
+    alphabet, k = str(t["alphabet"]), int(t["k"])
+    for tag in tags:
+        want = g["pairs_" + tag]                      # (p, x, y, kmer index) from the unmodified reference
+        got = out["pairs_" + tag]
+        idx = np.array([sum(alphabet.index(c) * len(alphabet) ** (k - 1 - i) for i, c in enumerate(s)) for s in out["kmers_" + tag]],
+                       np.int64)
+        got4 = np.concatenate([got, idx[:, None]], axis=1)
+        # the reference returns its list unordered per block; compare as the other GPU tests do (same order expected)
+        assert compare_pairs(got4.astype(np.int32), want, params[tag]["threshold"]) <= 20, tag
+        compare_expectations(out["tr_" + tag], float(out["lik_" + tag]), g["exp_transitions_" + tag],
+                             float(g["exp_likelihood_" + tag]))

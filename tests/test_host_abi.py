@@ -245,3 +245,21 @@ def test_real_nhdp_loads_identically():
     assert pp.shape == (352, 100)   # 352 observed DPs, grid 0..100 x 100
     assert np.array_equal(grid, h["grid"]) and np.array_equal(k2r, h["kmer_to_row"]) and np.array_equal(own, h["own_row"])
     assert np.array_equal(pp, h["post_pred"]) and np.array_equal(sl, h["slopes"])
+
+
+def test_drop_in_build_exports_the_reference_entry_points():
+    """oracle/_ref/libsaref_gpu.so (built where /root/reference exists): the reference's two entry points are provided by
+    signalalign_b200/shim/signalalign_shim.c on top of libsagpu, the reference's own definitions are kept under cpu_*."""
+    import shutil
+    import subprocess
+    path = os.path.join(ROOT_DIR, "oracle", "_ref", "libsaref_gpu.so")
+    if not os.path.exists(path) or shutil.which("nm") is None:
+        pytest.skip("drop-in build not present")
+    out = subprocess.run(["nm", "-D", path], capture_output=True, text=True, check=True).stdout
+    defined = {l.split()[-1] for l in out.splitlines() if " T " in l}
+    undefined = {l.split()[-1] for l in out.splitlines() if " U " in l}
+    for s in ("getAlignedPairsUsingAnchors", "getExpectationsUsingAnchors", "cpu_getAlignedPairsUsingAnchors",
+              "cpu_getExpectationsUsingAnchors"):
+        assert s in defined, s
+    for s in ("sa_gpu_align_batch", "sa_gpu_expectations_batch", "sa_model_from_tables", "sa_kmer_string"):
+        assert s in undefined, s
