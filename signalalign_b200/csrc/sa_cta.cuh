@@ -189,13 +189,15 @@ struct CtaK {
         if (q <= x0) v = yv[0] - sv[0] * (x0 - q);
         else if (q >= xn) v = yv[n - 1] + sv[n - 1] * (q - xn);
         else {
-            const double dx = P.gridDx;
-            int32_t il = (int32_t) ((q - x0) / dx);
+            // (reciprocal multiplies instead of the reference's three divisions: the knot index can only differ for q
+            // within an ulp of a knot, where both intervals give the knot's value; results move by ~1e-16 relative)
+            const double dx = P.gridDx, rdx = P.gridInvDx;
+            int32_t il = (int32_t) ((q - x0) * rdx);
             il = il > n - 2 ? n - 2 : il;
             const int32_t ir = il + 1;
             const double yl = yv[il], yr = yv[ir], dy = yr - yl;
             const double a = sv[il] * dx - dy, b = dy - sv[ir] * dx;
-            const double tl = (q - P.grid[il]) / dx, tr = 1.0 - tl;
+            const double tl = (q - P.grid[il]) * rdx, tr = 1.0 - tl;
             v = (tr * yl + tl * yr) + (tl * tr) * (a * tr + b * tl);
         }
         const double dens = v > 0.0 ? v : 0.0;
@@ -208,7 +210,7 @@ struct CtaK {
         if (HD) {
             const long long row = __double_as_longlong(S.cst[2][cs]);
             // de-scaled event mean (stateMachine.c:344-348): (mean + var mu - scale mu - shift) / var
-            const double q = (((S.evs[y & (RN - 1)] + S.cst[0][cs]) - S.cst[1][cs]) - I.shift) / I.var;
+            const double q = (((S.evs[y & (RN - 1)] + S.cst[0][cs]) - S.cst[1][cs]) - I.shift) * I.invVar;
             double e = SA_NEG_INF;
             if (row >= 0) e = hdpLogDensity(P, I, row, q);
             eM = e; eY = e;

@@ -69,7 +69,7 @@ struct FParams {
     const double *grid, *pp, *slopes;
     const int32_t *kmerToRow;
     int32_t G;
-    double gridDx;           // grid[1] - grid[0]
+    double gridDx, gridInvDx; // grid[1] - grid[0] and its reciprocal
 };
 
 // ---------------------------------------------------------------------------------------------- band iterator

@@ -693,6 +693,7 @@ static int prepareBatch(const sa_model_t *m, const sa_read_t *reads, int64_t nRe
             f.grid = m->dev->grid; f.pp = m->dev->pp; f.slopes = m->dev->slopes; f.kmerToRow = m->dev->kmerToRow;
             f.G = (int32_t) m->G;
             f.gridDx = m->grid[1] - m->grid[0];
+            f.gridInvDx = 1.0 / f.gridDx;
             f.eX = -2.3025850929940455;     // stateMachine3HDP_cellCalculate's literal X-gap emission
         }
         sa_geometry_kernel<<<(unsigned) n, 32, 0, st>>>(f);
