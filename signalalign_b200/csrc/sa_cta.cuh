@@ -57,6 +57,7 @@ struct CtaK {
     static constexpr int NH = W * C;         // hit-mask words per diagonal: [warp][cell]
     static constexpr int ROW = 3 * NS + 2;   // doubles per stored forward row
     static constexpr int RN = 2 * NS;        // entries of the column / event rings
+    static constexpr double kExpZero = -746.0;   // exp() of anything below is exactly +0.0 (denormal minimum: e^-745.13)
 
     struct Smem {
         double cst[5][RN];       // km, iM, cM, iY, cY per column (index = column & (RN - 1))
@@ -422,6 +423,15 @@ struct CtaK {
             const int32_t rowP = rowI == 0 ? cap - 1 : rowI - 1;   // ... of d2 - 1
             const double *row = ring + (int64_t) rowI * ROW;
             const bool post = d2 <= tracedBackFrom;
+            if (EX && d2 - 3 >= tracedBackTo) {
+                // the expectations read f(d2 - 1) and f(d2 - 2) of every cell; f(d2 - 2) is first touched on this step
+                // and comes from HBM (a traceback block's rows exceed L2): start the next step's row now
+                int32_t r3 = rowI - 3;
+                r3 = r3 < 0 ? r3 + cap : r3;
+                const double *q = ring + (int64_t) r3 * ROW + 2 + t * C;
+#pragma unroll
+                for (int pl = 0; pl < 3; pl++) asm volatile("prefetch.global.L1 [%0];" ::"l"(q + pl * NS));
+            }
             double fM[C];
 #pragma unroll
             for (int j = 0; j < C; j++) fM[j] = 0.0;
@@ -527,8 +537,9 @@ struct CtaK {
                     if (__any_sync(0xffffffffu, lower)) {
                         const double f0 = r1[sp], f1 = r1[NS + sp];
                         const double a0 = ((f0 + qX[j]) + cOX) - total, a1 = ((f1 + qX[j]) + cEX) - total;
-                        acc[1] += lower ? exp(a0) : 0.0;
-                        acc[3] += lower ? exp(a1) : 0.0;
+                        // exp(a) is exactly 0.0 below -745.2: such terms (and -inf) are skipped, NaN is not
+                        if (__any_sync(0xffffffffu, lower && !(a0 < kExpZero))) acc[1] += lower ? exp(a0) : 0.0;
+                        if (__any_sync(0xffffffffu, lower && !(a1 < kExpZero))) acc[3] += lower ? exp(a1) : 0.0;
                         yxNaN |= lower && !(total > SA_NEG_INF);   // exp(-inf - total): NaN exactly when total is -inf
                     }
                     if (__any_sync(0xffffffffu, middle)) {
@@ -536,16 +547,16 @@ struct CtaK {
                         const double a0 = ((f0 + curM[j]) + (curE[j] + T[T_MATCH_CONTINUE])) - total;
                         const double a1 = ((f1 + curM[j]) + (curE[j] + T[T_MATCH_FROM_GAP_X])) - total;
                         const double a2 = ((f2 + curM[j]) + (curE[j] + T[T_MATCH_FROM_GAP_Y])) - total;
-                        acc[0] += middle ? exp(a0) : 0.0;
-                        acc[2] += middle ? exp(a1) : 0.0;
-                        acc[4] += middle ? exp(a2) : 0.0;
+                        if (__any_sync(0xffffffffu, middle && !(a0 < kExpZero))) acc[0] += middle ? exp(a0) : 0.0;
+                        if (__any_sync(0xffffffffu, middle && !(a1 < kExpZero))) acc[2] += middle ? exp(a1) : 0.0;
+                        if (__any_sync(0xffffffffu, middle && !(a2 < kExpZero))) acc[4] += middle ? exp(a2) : 0.0;
                     }
                     if (__any_sync(0xffffffffu, upper)) {
                         const double f0 = r1[sl], f2 = r1[2 * NS + sl];
                         const double a0 = ((f0 + qY[j]) + (qE[j] + T[T_GAP_OPEN_Y])) - total;
                         const double a2 = ((f2 + qY[j]) + (qE[j] + T[T_GAP_EXTEND_Y])) - total;
-                        acc[5] += upper ? exp(a0) : 0.0;
-                        acc[6] += upper ? exp(a2) : 0.0;
+                        if (__any_sync(0xffffffffu, upper && !(a0 < kExpZero))) acc[5] += upper ? exp(a0) : 0.0;
+                        if (__any_sync(0xffffffffu, upper && !(a2 < kExpZero))) acc[6] += upper ? exp(a2) : 0.0;
                     }
                 }
                 sa_mbArrive(&S.mbar);

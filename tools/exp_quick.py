@@ -16,3 +16,8 @@ for i in range(3):
     cells = r.band_cells
     print("expectations: %d reads, %.3e cells, %.1f ms, %.2f GCUPS, %.3e events/s; likelihood sum %.6f" %
           (n, cells, 1e3 * (t1 - t0), cells / (t1 - t0) / 1e9, r.events / (t1 - t0), float(r.likelihood.sum())))
+b = sa.Batch(model, reads, p, expectations=True)
+for i in range(2):
+    b.run()
+    ms, _ = b.timing()
+    print("expectations resident: kernel %.1f ms, %.2f GCUPS" % (sum(ms), b.band_cells / sum(ms) / 1e6))
