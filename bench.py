@@ -314,6 +314,12 @@ def main():
         # planes on 2 of 10 rows (6.4 B), inputs / outputs 0.4 B
         alg_bytes_per_cell = 22.8
         achieved_gbs = cells * alg_bytes_per_cell / (float(np.mean(kern_ms)) * 1e-3) / 1e9
+        # measured DRAM traffic of the kernel (one ncu --set full capture, profiles/): bytes per band cell x this launch's cells
+        traffic = None
+        try:
+            traffic = json.load(open(os.path.join(ROOT, "profiles", "r1_dram_per_cell.json")))["bytes_per_cell"] * cells
+        except Exception:
+            pass
         sm_mhz = (clocks or {}).get("sm_mhz") or 1965.0
         # FP64 pipe: ~150 algorithmic FP64 lane-instructions per band cell; peak = measured DFMA/DADD/DMUL
         # issue rate of this pool's B200 (tools/peak_fp.cu -> profiles/r1_peak_fp.jsonl), else 64 lanes/SM/clk nominal
@@ -349,7 +355,8 @@ def main():
                     "d2h_bytes_per_step": int(d2h), "gcups": cells_all / e2e_max / 1e9,
                     "ms_each_call_rank0": [round(1e3 * t, 1) for t in e2e_t]},
             "roofline": {"bound": "hbm", "achieved": achieved_gbs, "peak": hbm_peak, "unit": "GB/s",
-                         "frac": achieved_gbs / hbm_peak, "traffic": None, "peak_source": peak_src,
+                         "frac": achieved_gbs / hbm_peak, "traffic": traffic, "algorithmic_bytes": alg_bytes_per_cell * cells,
+                         "peak_source": peak_src,
                          "note": "kernel is FP64-issue bound, not HBM bound: see roofline_compute"},
             "roofline_compute": {"bound": "fp64_pipe", "achieved": cells * fp64_per_cell / (float(np.mean(kern_ms)) * 1e-3),
                                  "peak": fp64_peak, "peak_source": fp64_src, "unit": "FP64 lane-instr/s",
