@@ -349,9 +349,8 @@ struct CtaK {
                                                      int32_t bw, int32_t &cLo, int32_t &eLo, int32_t tracedBackTo,
                                                      int32_t tracedBackFrom, bool atEnd, double cOX, double cEX,
                                                      unsigned &phase, int64_t &nPairs, double (&acc)[7], double &lik,
-                                                     bool &yxNaN) {
+                                                     bool &yxNaN, int32_t cap) {
         const double *T = P.trans;
-        const int32_t cap = P.rowsCap;
         // end / ragged-end state on diagonal d (reference stateMachine.c:1147-1173)
         const bool rag = atEnd && (I.flags & 2);
         const double e0 = rag ? (T[T_GAP_OPEN_X] + T[T_GAP_OPEN_Y]) / 2.0 : T[T_MATCH_CONTINUE];
@@ -584,6 +583,9 @@ struct CtaK {
         if (pendValid) flush();
     }
 
+    // FWD = true: the forward sweep only, every row kept (ring of lX + lY + 1 rows = no wrap); the traceback blocks of
+    // the item are then independent work items of sa_cta_block_kernel (split mode for reads that dominate a batch)
+    template <bool FWD>
     static __device__ void run(const FParams &P, const FItem &I, int it, double *ring, Smem &S, unsigned &phase) {
         const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
         const double *T = P.trans;
@@ -634,7 +636,7 @@ struct CtaK {
         int32_t nextT = nTb > 0 ? tbList[0] : nDiag;
         int32_t curFrom = nextT - (nextT == nDiag ? 0 : P.traceBack + 1);
         const double cOX = P.eX + T[T_GAP_OPEN_X], cEX = P.eX + T[T_GAP_EXTEND_X];
-        const int32_t cap = P.rowsCap;
+        const int32_t cap = FWD ? nDiag + 1 : P.rowsCap;
         int32_t rowI = 0;                       // ring row of diagonal d (= d mod cap, kept incrementally)
         int32_t backMod = (curFrom - 1) % 10;   // (curFrom - d) mod 10 while it is >= 0
         for (int32_t d = 1; d <= nDiag; d++) {
@@ -695,14 +697,16 @@ struct CtaK {
             // ------------------------------------------------------------------ traceback from diagonal d
             const bool atEnd = d == nDiag;
             const int32_t tracedBackFrom = curFrom;
-            traceback(P, I, S, ring, t, lane, warp, d, rowI, xlo, xhi, wlo, cLo, eLo, tracedBackTo, tracedBackFrom, atEnd,
-                      cOX, cEX, phase, nPairs, acc, lik, yxNaN);
+            if (!FWD)
+                traceback(P, I, S, ring, t, lane, warp, d, rowI, xlo, xhi, wlo, cLo, eLo, tracedBackTo, tracedBackFrom,
+                          atEnd, cOX, cEX, phase, nPairs, acc, lik, yxNaN, cap);
             tracedBackTo = tracedBackFrom;
             tbI++;
             nextT = tbI < nTb ? tbList[tbI] : nDiag;
             curFrom = nextT - (nextT == nDiag ? 0 : P.traceBack + 1);
             backMod = (curFrom - (d + 1)) % 10;
             if (atEnd) break;
+            if (FWD) continue;                 // nothing disturbed the sweep
             // restore the forward sweep: f(d), f(d-1) from the ring (all three planes were kept above tracedBackFrom)
             __syncthreads();
             {
@@ -762,7 +766,35 @@ struct CtaK {
                 o[9] = lik;
             }
         }
-        if (t == 0) P.pairCount[it] = nPairs;
+        if (FWD) sa_mbWait(&S.mbar, phase);    // consume the last step's arrival: the next item starts with a clean phase
+        if (t == 0 && !FWD) P.pairCount[it] = nPairs;
+    }
+
+    // One traceback block of an item whose forward rows are all in `ring` (row index = diagonal): the body of the
+    // reference's traceback point (impl/pairwiseAligner.c:1500-1570) as an independent work item.
+    static __device__ void runBlock(const FParams &P, const FBlock &B, int blk, Smem &S, unsigned &phase) {
+        const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+        const double *T = P.trans;
+        FItem I = P.items[B.item];
+        I.pairOff = B.pairOff; I.pairCap = B.pairCap;
+        const int32_t nDiag = I.lX + I.lY, d = B.d;
+        double *ring = P.scratch + I.fullOff;
+        const int2 hdr = *reinterpret_cast<const int2 *>(ring + (int64_t) d * ROW);
+        const int32_t xlo = hdr.x, xhi = hdr.y;
+        __syncthreads();                       // previous work item finished with shared memory
+        // any window [bw, bw + NS) over the band of d works: slots are columns mod NS, order is by column
+        int32_t bw = xlo, cLo = bw - NS / 2, eLo = (d - (bw + NS - 1)) - NS / 2;
+        fillConsts(P, I, S, t, cLo);
+        fillEvents(P, I, S, t, eLo);
+        __syncthreads();
+        sa_mbArrive(&S.mbar);                  // stands for the forward step the traceback waits for
+        int64_t nPairs = 0;
+        double acc[7] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0}, lik = 0.0;
+        bool yxNaN = false;
+        const double cOX = P.eX + T[T_GAP_OPEN_X], cEX = P.eX + T[T_GAP_EXTEND_X];
+        traceback(P, I, S, ring, t, lane, warp, d, d, xlo, xhi, bw, cLo, eLo, B.tracedBackTo, B.tracedBackFrom,
+                  d == nDiag, cOX, cEX, phase, nPairs, acc, lik, yxNaN, nDiag + 1);
+        if (t == 0) P.blockPairCount[blk] = nPairs;
     }
 };
 
@@ -787,6 +819,41 @@ __global__ void __launch_bounds__(32 * W, CtaOcc<W, C, EX, HD>::kMinBlocks) sa_c
         const int n = S.sItem;
         if (n >= P.nOrder) break;
         const int it = P.order[n];
-        CtaK<W, C, EX, HD>::run(P, P.items[it], it, ring, S, phase);
+        CtaK<W, C, EX, HD>::template run<false>(P, P.items[it], it, ring, S, phase);
+    }
+}
+
+// Split mode, phase 1: forward sweeps of the listed items into their full-length row buffers (P.scratch + fullOff).
+template <int W, int C>
+__global__ void __launch_bounds__(32 * W, CtaOcc<W, C, false, false>::kMinBlocks) sa_cta_forward_kernel(const FParams P) {
+    __shared__ typename CtaK<W, C, false, false>::Smem S;
+    if (threadIdx.x == 0) sa_mbInit(&S.mbar, 32 * W);
+    sa_logAdd_init();
+    unsigned phase = 0;
+    for (;;) {
+        __syncthreads();
+        if (threadIdx.x == 0) S.sItem = atomicAdd(P.counter, 1);
+        __syncthreads();
+        const int n = S.sItem;
+        if (n >= P.nOrder) break;
+        const int it = P.order[n];
+        CtaK<W, C, false, false>::template run<true>(P, P.items[it], it, P.scratch + P.items[it].fullOff, S, phase);
+    }
+}
+
+// Split mode, phase 2: the traceback blocks of those items, each an independent work item (P.blocks, heaviest first).
+template <int W, int C>
+__global__ void __launch_bounds__(32 * W, CtaOcc<W, C, false, false>::kMinBlocks) sa_cta_block_kernel(const FParams P) {
+    __shared__ typename CtaK<W, C, false, false>::Smem S;
+    if (threadIdx.x == 0) sa_mbInit(&S.mbar, 32 * W);
+    sa_logAdd_init();
+    unsigned phase = 0;
+    for (;;) {
+        __syncthreads();
+        if (threadIdx.x == 0) S.sItem = atomicAdd(P.counter, 1);
+        __syncthreads();
+        const int n = S.sItem;
+        if (n >= P.nBlocks) break;
+        CtaK<W, C, false, false>::runBlock(P, P.blocks[n], n, S, phase);
     }
 }

@@ -33,6 +33,14 @@ struct FItem {
     int32_t pad;
     double scale, shift, invVar, logInvVar;
     double var;
+    int64_t fullOff;    // split mode: offset (doubles) of the item's full-length row buffer in FParams.scratch
+};
+
+struct FBlock {          // split mode: one traceback block of an item
+    int32_t item;
+    int32_t d;           // the traceback starts on this diagonal
+    int32_t tracedBackTo, tracedBackFrom;
+    int64_t pairOff, pairCap;
 };
 
 struct FGeo {            // per item, written by sa_geometry_kernel
@@ -69,6 +77,10 @@ struct FParams {
     const double *grid, *pp, *slopes;
     const int32_t *kmerToRow;
     int32_t G;
+    // split mode
+    const FBlock *blocks;
+    int32_t nBlocks;
+    int64_t *blockPairCount;
     double gridDx, gridInvDx; // grid[1] - grid[0] and its reciprocal
 };
 

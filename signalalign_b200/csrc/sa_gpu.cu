@@ -279,10 +279,16 @@ struct sa_batch {
     // latency class: the few reads whose own sweep is long against the whole batch run on the one-cell-per-thread
     // mapping (<4, 1>: half the instructions per thread and diagonal) next to the throughput kernel, on their own stream
     cudaStream_t lat = nullptr;
-    cudaEvent_t evFork = nullptr, evJoin = nullptr;
+    cudaEvent_t evFork = nullptr, evJoin = nullptr, evJoinSplit = nullptr;
     std::vector<int32_t> latOrder;
     int latBlocks = 0;
     int32_t latRows = 1;
+    // split mode (the longest of those, while their full-length row buffers fit a memory budget): the forward sweep
+    // runs alone on the one-cell mapping keeping every row; the traceback blocks then are independent work items
+    std::vector<int32_t> splitOrder;
+    std::vector<FBlock> blocks;          // block b of the list; blockItemFirst[i] .. : blocks of split item i in order
+    std::vector<int64_t> blockCountHost;
+    int blockGrid = 0;
     cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     std::vector<ItemRec> items;  // global item id = index
     // shared inputs
@@ -308,8 +314,11 @@ struct sa_batch {
     DevBuf<FItem> dFItems;
     DevBuf<int32_t> dFOrder[4], dTb;
     DevBuf<FGeo> dGeo;
-    DevBuf<double> dFScratch, dLatScratch;
-    DevBuf<int32_t> dLatOrder;
+    DevBuf<double> dFScratch, dLatScratch, dSplitRows;
+    DevBuf<int32_t> dLatOrder, dSplitOrder;
+    DevBuf<FBlock> dBlocks;
+    DevBuf<int64_t> dBlockCount;
+    DevBuf<sa_pair_t> dSplitPairs;
     FParams fp;
     int fBlocks[4] = {0, 0, 0, 0};
     int32_t fRows[4] = {1, 1, 1, 1};
@@ -327,6 +336,7 @@ struct sa_batch {
         if (evPrepared) cudaEventDestroy(evPrepared);
         if (evFork) cudaEventDestroy(evFork);
         if (evJoin) cudaEventDestroy(evJoin);
+        if (evJoinSplit) cudaEventDestroy(evJoinSplit);
     }
 };
 
@@ -425,6 +435,7 @@ static int prepareBatch(const sa_model_t *m, const sa_read_t *reads, int64_t nRe
     b->lat = b->latOwner.s;
     CK(cudaEventCreateWithFlags(&b->evFork, cudaEventDisableTiming));
     CK(cudaEventCreateWithFlags(&b->evJoin, cudaEventDisableTiming));
+    CK(cudaEventCreateWithFlags(&b->evJoinSplit, cudaEventDisableTiming));
     for (auto &e : b->ev) CK(cudaEventCreate(&e));
     CK(cudaEventCreateWithFlags(&b->evPrepared, cudaEventDisableTiming));
     cudaStream_t st = b->aux;
@@ -744,6 +755,55 @@ static int prepareBatch(const sa_model_t *m, const sa_read_t *reads, int64_t nRe
             } else keep.push_back(i);
         }
         b->fOrder[2].swap(keep);
+        // split mode for the longest of them while the row buffers fit (3088 B per diagonal; SA_SPLIT_GB, default 24)
+        if (!b->latOrder.empty() && getenv("SA_NO_SPLIT") == nullptr) {
+            const char *eg = getenv("SA_SPLIT_GB");
+            const int64_t budget = (int64_t) ((eg ? atof(eg) : 24.0) * 1073741824.0 / 8.0);   // doubles
+            std::vector<int32_t> tbHost((size_t) std::max<int64_t>(1, b->dTb.n));
+            CK(cudaMemcpyAsync(tbHost.data(), b->dTb.p, sizeof(int32_t) * b->dTb.n, cudaMemcpyDeviceToHost, st));
+            CK(cudaStreamSynchronize(st));
+            int64_t fullTotal = 0, pairTotal = 0;
+            std::vector<int32_t> ring;
+            b->latRows = 1;
+            for (int32_t i : b->latOrder) {
+                const int64_t nDiag = items[i].lX + items[i].lY, need = (nDiag + 1) * (3 * 128 + 2);
+                if (fullTotal + need > budget) {
+                    ring.push_back(i);
+                    b->latRows = std::max(b->latRows, geo[i].maxRows);
+                    continue;
+                }
+                b->splitOrder.push_back(i);
+                b->fItems[i].fullOff = fullTotal;
+                fullTotal += need;
+                int32_t to = 0;
+                for (int32_t k = 0; k < geo[i].nTb; k++) {
+                    FBlock B;
+                    B.item = i;
+                    B.d = tbHost[b->fItems[i].tbOff + k];
+                    B.tracedBackTo = to;
+                    B.tracedBackFrom = B.d - (B.d == nDiag ? 0 : (int32_t) p->traceBackDiagonals + 1);
+                    B.pairOff = pairTotal;
+                    B.pairCap = 4 * (int64_t) (B.tracedBackFrom - to) + 256;
+                    if (const char *ec = getenv("SA_SPLIT_PAIRCAP")) B.pairCap = atoll(ec);   // tests: force the re-run path
+                    pairTotal += B.pairCap;
+                    to = B.tracedBackFrom;
+                    b->blocks.push_back(B);
+                }
+            }
+            b->latOrder.swap(ring);
+            if (!b->splitOrder.empty()) {
+                if ((rc = b->dFItems.upload(b->fItems, st, &b->h2dBytes))) return rc;   // (fullOff)
+                f.items = b->dFItems.p;
+                if ((rc = b->dSplitOrder.upload(b->splitOrder, st, &b->h2dBytes))) return rc;
+                if ((rc = b->dBlocks.upload(b->blocks, st, &b->h2dBytes))) return rc;
+                if ((rc = b->dBlockCount.alloc(b->blocks.size(), st))) return rc;
+                if ((rc = b->dSplitRows.alloc((size_t) fullTotal, st))) return rc;
+                if ((rc = b->dSplitPairs.alloc((size_t) std::max<int64_t>(1, pairTotal), st))) return rc;
+                int bps = 1;
+                CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, sa_cta_block_kernel<2, 2>, 64, 0));
+                b->blockGrid = (int) std::min<int64_t>((int64_t) nSM * std::max(1, bps), (int64_t) b->blocks.size());
+            }
+        }
         if (!b->latOrder.empty()) {
             if ((rc = b->dLatOrder.upload(b->latOrder, st, &b->h2dBytes))) return rc;
             b->latBlocks = (int) b->latOrder.size();
@@ -878,9 +938,27 @@ static int launchBatch(sa_batch_t *b) {
     b->lastLaunches = 0;
     CK(cudaMemsetAsync(b->dCounters.p, 0, 8 * sizeof(int32_t), st));
     CK(cudaEventRecord(b->ev[0], st));
-    if (!b->latOrder.empty()) {                // first, so that its CTAs are resident before the persistent grid fills the SMs
+    const bool latStream = !b->latOrder.empty() || !b->splitOrder.empty();
+    if (latStream) {                           // first, so that its CTAs are resident before the persistent grid fills the SMs
         CK(cudaEventRecord(b->evFork, st));
         CK(cudaStreamWaitEvent(b->lat, b->evFork, 0));
+        CK(cudaStreamWaitEvent(b->aux, b->evFork, 0));
+    }
+    if (!b->splitOrder.empty()) {              // on the aux stream (idle during a run): beside the ring-mode latency kernel
+        FParams f = b->fp;
+        f.order = b->dSplitOrder.p; f.nOrder = (int32_t) b->splitOrder.size(); f.counter = b->dCounters.p + 6;
+        f.scratch = b->dSplitRows.p;
+        sa_cta_forward_kernel<4, 1><<<(unsigned) b->splitOrder.size(), 128, 0, b->aux>>>(f);
+        CK(cudaGetLastError());
+        f.counter = b->dCounters.p + 7;
+        f.blocks = b->dBlocks.p; f.nBlocks = (int32_t) b->blocks.size(); f.blockPairCount = b->dBlockCount.p;
+        f.pairs = b->dSplitPairs.p;
+        sa_cta_block_kernel<2, 2><<<b->blockGrid, 64, 0, b->aux>>>(f);
+        CK(cudaGetLastError());
+        b->lastLaunches += 2;
+        CK(cudaEventRecord(b->evJoinSplit, b->aux));
+    }
+    if (!b->latOrder.empty()) {
         FParams f = b->fp;
         f.order = b->dLatOrder.p; f.nOrder = (int32_t) b->latOrder.size(); f.counter = b->dCounters.p + 5;
         f.rowsCap = b->latRows;
@@ -888,11 +966,12 @@ static int launchBatch(sa_batch_t *b) {
         sa_cta_kernel<4, 1, false, false><<<b->latBlocks, 128, 0, b->lat>>>(f);
         b->lastLaunches++;
         CK(cudaGetLastError());
-        CK(cudaEventRecord(b->evJoin, b->lat));
     }
+    if (latStream) CK(cudaEventRecord(b->evJoin, b->lat));
     for (int c = 3; c >= 0; c--) {             // widest class first; [ev0, ev1) = W >= 4, [ev1, ev2) = W <= 2
         if (c == 1) {
-            if (!b->latOrder.empty()) CK(cudaStreamWaitEvent(st, b->evJoin, 0));   // counted with the 128-slot class
+            if (latStream) CK(cudaStreamWaitEvent(st, b->evJoin, 0));   // counted with the 128-slot class
+            if (!b->splitOrder.empty()) CK(cudaStreamWaitEvent(st, b->evJoinSplit, 0));
             CK(cudaEventRecord(b->ev[1], st));
         }
         if (b->fOrder[c].empty()) continue;
@@ -928,16 +1007,17 @@ extern "C" int sa_batch_run(sa_batch_t *b) {
     return SA_OK;
 }
 
-// meta per item: source offset, destination offset, count, (x1 << 32 | y1)
-__global__ void __launch_bounds__(128) sa_compact_pairs_kernel(const sa_pair_t *src, sa_pair_t *dst, const int64_t *meta, int64_t nItems) {
-    for (int64_t it = blockIdx.x; it < nItems; it += gridDim.x) {
-        const int64_t so = meta[4 * it], dO = meta[4 * it + 1], cnt = meta[4 * it + 2], sh = meta[4 * it + 3];
+// meta per segment (an item, or one traceback block of a split item): source offset, END of its destination range, count,
+// (x1 << 32 | y1).  The j-th pair written goes to dstEnd - 1 - j: a region's list is popped from its end.
+__global__ void __launch_bounds__(128) sa_compact_pairs_kernel(const sa_pair_t *src, sa_pair_t *dst, const int64_t *meta, int64_t nSeg) {
+    for (int64_t it = blockIdx.x; it < nSeg; it += gridDim.x) {
+        const int64_t so = meta[4 * it], dE = meta[4 * it + 1], cnt = meta[4 * it + 2], sh = meta[4 * it + 3];
         const int32_t x1 = (int32_t) (sh >> 32), y1 = (int32_t) (sh & 0xffffffffLL);
-        for (int64_t q = threadIdx.x; q < cnt; q += blockDim.x) {
-            sa_pair_t pr = src[so + cnt - 1 - q];
+        for (int64_t j = threadIdx.x; j < cnt; j += blockDim.x) {
+            sa_pair_t pr = src[so + j];
             pr.x += x1;
             pr.y += y1;
-            dst[dO + q] = pr;
+            dst[dE - 1 - j] = pr;
         }
     }
 }
@@ -1007,6 +1087,48 @@ static int sinkReserve(PairSink &k, int64_t need) {
     return SA_OK;
 }
 
+// split items: per-block pair counts (blocks that out-grew their slot get the exact size and the block kernel runs again
+// over the rows still in HBM); the item's count is the sum of its blocks'
+static int fetchBlockCounts(sa_batch_t *b) {
+    cudaStream_t st = b->stream;
+    const int64_t nb = (int64_t) b->blocks.size();
+    for (int attempt = 0; attempt < 3; attempt++) {
+        b->blockCountHost.assign((size_t) nb, 0);
+        CK(cudaMemcpyAsync(b->blockCountHost.data(), b->dBlockCount.p, sizeof(int64_t) * nb, cudaMemcpyDeviceToHost, st));
+        CK(cudaStreamSynchronize(st));
+        b->d2hBytes += sizeof(int64_t) * nb;
+        bool overflow = false;
+        for (int64_t k = 0; k < nb; k++) overflow |= b->blockCountHost[k] > b->blocks[k].pairCap;
+        if (!overflow) break;
+        if (attempt == 2) {
+            sa_set_error("sa_batch_fetch: traceback-block slots still overflow after re-run");
+            return SA_ERR_CUDA;
+        }
+        int64_t total = 0;
+        for (int64_t k = 0; k < nb; k++) {
+            b->blocks[k].pairCap = std::max(b->blocks[k].pairCap, b->blockCountHost[k]);
+            b->blocks[k].pairOff = total;
+            total += b->blocks[k].pairCap;
+        }
+        int rc;
+        if ((rc = b->dBlocks.upload(b->blocks, st, &b->h2dBytes))) return rc;
+        if ((rc = b->dSplitPairs.alloc((size_t) std::max<int64_t>(1, total), st))) return rc;
+        CK(cudaMemsetAsync(b->dCounters.p + 7, 0, sizeof(int32_t), st));
+        FParams f = b->fp;
+        f.scratch = b->dSplitRows.p;
+        f.counter = b->dCounters.p + 7;
+        f.blocks = b->dBlocks.p; f.nBlocks = (int32_t) nb; f.blockPairCount = b->dBlockCount.p;
+        f.pairs = b->dSplitPairs.p;
+        sa_cta_block_kernel<2, 2><<<b->blockGrid, 64, 0, st>>>(f);
+        CK(cudaGetLastError());
+        b->lastLaunches++;
+    }
+    for (int32_t i : b->splitOrder) b->pairCountHost[i] = 0;     // (the forward-only sweep writes no item count)
+    for (int64_t k = 0; k < nb; k++) b->pairCountHost[b->blocks[k].item] += b->blockCountHost[k];
+    for (int32_t i : b->splitOrder) b->items[i].pairCap = std::max(b->items[i].pairCap, b->pairCountHost[i]);
+    return SA_OK;
+}
+
 // wait for the batch's kernels, read the per-item counts, re-run with larger slots if any overflowed
 static int fetchCounts(sa_batch_t *b) {
     int64_t n = (int64_t) b->items.size();
@@ -1019,6 +1141,10 @@ static int fetchCounts(sa_batch_t *b) {
                                cudaMemcpyDeviceToHost, st));
             CK(cudaStreamSynchronize(st));
             b->d2hBytes += sizeof(int64_t) * n;
+            if (!b->splitOrder.empty()) {
+                int rc = fetchBlockCounts(b);
+                if (rc) return rc;
+            }
             for (int64_t i = 0; i < n; i++) overflow |= b->pairCountHost[i] > b->items[i].pairCap;
         } else if (b->model->kind == SA_EMIT_HDP) {
             b->assignCountHost.assign(std::max<int64_t>(1, n), 0);
@@ -1047,16 +1173,34 @@ static int fetchPairs(sa_batch_t *b, PairSink &sink, int64_t *pairOffsets) {
     int64_t n = (int64_t) b->items.size();
     cudaStream_t st = b->aux;   // (fetchCounts has waited for the band kernels)
     int64_t total = 0;
-    std::vector<int64_t> meta((size_t) std::max<int64_t>(1, n) * 4);
+    std::vector<int64_t> meta((size_t) std::max<int64_t>(1, n) * 4), metaSplit;
+    std::vector<int64_t> itemBase;           // split items: start of the item's destination range
+    if (!b->splitOrder.empty()) itemBase.assign((size_t) n, -1);
+    for (int32_t s : b->splitOrder) itemBase[s] = 0;
     int64_t i = 0;
     for (int64_t rd = 0; rd < b->nReads; rd++) {
         pairOffsets[rd] = sink.used + total;
         for (; i < n && b->items[i].read == rd; i++) {
+            const bool split = !itemBase.empty() && itemBase[i] >= 0;
+            if (split) itemBase[i] = total;
             meta[4 * i] = b->items[i].pairOff;
-            meta[4 * i + 1] = total;
-            meta[4 * i + 2] = b->pairCountHost[i];
+            meta[4 * i + 1] = total + b->pairCountHost[i];
+            meta[4 * i + 2] = split ? 0 : b->pairCountHost[i];   // (split items are gathered block by block below)
             meta[4 * i + 3] = (b->items[i].x1 << 32) | (b->items[i].y1 & 0xffffffffLL);
             total += b->pairCountHost[i];
+        }
+    }
+    if (!b->splitOrder.empty()) {
+        // the item's list is its blocks' lists in block order; the whole list is popped from its end
+        std::vector<int64_t> done((size_t) n, 0);
+        for (size_t k = 0; k < b->blocks.size(); k++) {
+            const FBlock &B = b->blocks[k];
+            const int64_t it = B.item;
+            metaSplit.push_back(B.pairOff);
+            metaSplit.push_back(itemBase[it] + b->pairCountHost[it] - done[it]);
+            metaSplit.push_back(b->blockCountHost[k]);
+            metaSplit.push_back((b->items[it].x1 << 32) | (b->items[it].y1 & 0xffffffffLL));
+            done[it] += b->blockCountHost[k];
         }
     }
     pairOffsets[b->nReads] = sink.used + total;
@@ -1069,6 +1213,15 @@ static int fetchPairs(sa_batch_t *b, PairSink &sink, int64_t *pairOffsets) {
         if ((rc = dDense.alloc(total, st))) return rc;
         sa_compact_pairs_kernel<<<(unsigned) std::min<int64_t>(n, 148 * 16), 128, 0, st>>>(b->dPairs.p, dDense.p, dMeta.p, n);
         CK(cudaGetLastError());
+        DevBuf<int64_t> dMetaSplit;
+        if (!metaSplit.empty()) {
+            const int64_t ns = (int64_t) metaSplit.size() / 4;
+            if ((rc = dMetaSplit.upload(metaSplit, st, &b->h2dBytes))) return rc;
+            sa_compact_pairs_kernel<<<(unsigned) std::min<int64_t>(ns, 148 * 16), 128, 0, st>>>(b->dSplitPairs.p, dDense.p,
+                                                                                          dMetaSplit.p, ns);
+            CK(cudaGetLastError());
+            b->lastLaunches++;
+        }
         CK(cudaMemcpyAsync(sink.p + sink.used, dDense.p, sizeof(sa_pair_t) * total, cudaMemcpyDeviceToHost, st));
         CK(cudaStreamSynchronize(st));
         b->d2hBytes += sizeof(sa_pair_t) * total;
@@ -1161,7 +1314,7 @@ extern "C" int64_t sa_batch_band_cells(const sa_batch_t *b) { return b->bandCell
 extern "C" void sa_batch_kernel_items(const sa_batch_t *b, int64_t *o) {
     o[0] = (int64_t) b->gOrder.size();
     o[1] = (int64_t) (b->fOrder[0].size() + b->fOrder[1].size());
-    o[2] = (int64_t) (b->fOrder[2].size() + b->fOrder[3].size() + b->latOrder.size());
+    o[2] = (int64_t) (b->fOrder[2].size() + b->fOrder[3].size() + b->latOrder.size() + b->splitOrder.size());
 }
 extern "C" int64_t sa_batch_h2d_bytes(const sa_batch_t *b) { return b->h2dBytes; }
 extern "C" int64_t sa_batch_d2h_bytes(const sa_batch_t *b) { return b->d2hBytes; }

@@ -289,13 +289,21 @@ def test_config3_size_reads_band_kernel_equals_general_kernel():
     p = sa.default_params(threshold=bench.THRESHOLD, expansion=bench.EXPANSION, trace_back=bench.TRACE_BACK,
                           min_diags=bench.MIN_DIAGS)
     rs = [sa_read(r) for r in reads]
-    lat = sa.align_batch(model, rs, p)              # 48 reads: every read is in the latency class (one cell per thread)
-    os.environ["SA_NO_LATENCY_CLASS"] = "1"
-    try:
-        fast = sa.align_batch(model, rs, p)         # two cells per thread
-    finally:
-        os.environ.pop("SA_NO_LATENCY_CLASS", None)
-    assert np.array_equal(lat.pair_offsets, fast.pair_offsets) and np.array_equal(lat.pairs, fast.pairs)
+    # 48 reads: every read dominates the batch -> split mode (forward sweep on the one-cell mapping keeping every row,
+    # traceback blocks as independent work items); the same through the ring-mode latency class, through the block
+    # kernel's re-run path (slots of 8 pairs), and on the throughput mapping (two cells per thread): all bit-identical
+    lat = sa.align_batch(model, rs, p)
+    outs = []
+    for env in ({"SA_NO_SPLIT": "1"}, {"SA_SPLIT_PAIRCAP": "8"}, {"SA_NO_LATENCY_CLASS": "1"}):
+        os.environ.update(env)
+        try:
+            outs.append(sa.align_batch(model, rs, p))
+        finally:
+            for k in env:
+                os.environ.pop(k, None)
+    fast = outs[2]
+    for o in outs:
+        assert np.array_equal(lat.pair_offsets, o.pair_offsets) and np.array_equal(lat.pairs, o.pairs)
     fe = sa.expectations_batch(model, rs, p)
     os.environ["SA_FORCE_GENERAL"] = "1"
     try:
