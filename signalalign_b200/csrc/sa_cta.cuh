@@ -824,9 +824,9 @@ __global__ void __launch_bounds__(32 * W, CtaOcc<W, C, EX, HD>::kMinBlocks) sa_c
 }
 
 // Split mode, phase 1: forward sweeps of the listed items into their full-length row buffers (P.scratch + fullOff).
-template <int W, int C>
-__global__ void __launch_bounds__(32 * W, CtaOcc<W, C, false, false>::kMinBlocks) sa_cta_forward_kernel(const FParams P) {
-    __shared__ typename CtaK<W, C, false, false>::Smem S;
+template <int W, int C, bool HD>
+__global__ void __launch_bounds__(32 * W, CtaOcc<W, C, false, HD>::kMinBlocks) sa_cta_forward_kernel(const FParams P) {
+    __shared__ typename CtaK<W, C, false, HD>::Smem S;
     if (threadIdx.x == 0) sa_mbInit(&S.mbar, 32 * W);
     sa_logAdd_init();
     unsigned phase = 0;
@@ -837,14 +837,14 @@ __global__ void __launch_bounds__(32 * W, CtaOcc<W, C, false, false>::kMinBlocks
         const int n = S.sItem;
         if (n >= P.nOrder) break;
         const int it = P.order[n];
-        CtaK<W, C, false, false>::template run<true>(P, P.items[it], it, P.scratch + P.items[it].fullOff, S, phase);
+        CtaK<W, C, false, HD>::template run<true>(P, P.items[it], it, P.scratch + P.items[it].fullOff, S, phase);
     }
 }
 
 // Split mode, phase 2: the traceback blocks of those items, each an independent work item (P.blocks, heaviest first).
-template <int W, int C>
-__global__ void __launch_bounds__(32 * W, CtaOcc<W, C, false, false>::kMinBlocks) sa_cta_block_kernel(const FParams P) {
-    __shared__ typename CtaK<W, C, false, false>::Smem S;
+template <int W, int C, bool HD>
+__global__ void __launch_bounds__(32 * W, CtaOcc<W, C, false, HD>::kMinBlocks) sa_cta_block_kernel(const FParams P) {
+    __shared__ typename CtaK<W, C, false, HD>::Smem S;
     if (threadIdx.x == 0) sa_mbInit(&S.mbar, 32 * W);
     sa_logAdd_init();
     unsigned phase = 0;
@@ -854,6 +854,6 @@ __global__ void __launch_bounds__(32 * W, CtaOcc<W, C, false, false>::kMinBlocks
         __syncthreads();
         const int n = S.sItem;
         if (n >= P.nBlocks) break;
-        CtaK<W, C, false, false>::runBlock(P, P.blocks[n], n, S, phase);
+        CtaK<W, C, false, HD>::runBlock(P, P.blocks[n], n, S, phase);
     }
 }

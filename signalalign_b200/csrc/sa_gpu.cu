@@ -744,7 +744,7 @@ static int prepareBatch(const sa_model_t *m, const sa_read_t *reads, int64_t nRe
     // when that alone exceeds half of what the whole batch needs at full throughput (~30 GCUPS), the read decides the
     // makespan (heavy-tailed lengths, BASELINE config 5; batches smaller than the resident grid).  Those reads, at most
     // two per SM and longest first, go to the one-cell mapping, whose step is about half as long.
-    if (!useWarpKernel && !b->oneCell && !b->expectations && m->kind != SA_EMIT_HDP && getenv("SA_NO_LATENCY_CLASS") == nullptr) {
+    if (!useWarpKernel && !b->oneCell && !b->expectations && getenv("SA_NO_LATENCY_CLASS") == nullptr) {
         const double ideal = (double) b->bandCells * (double) chunkCount / 30e9;
         std::vector<int32_t> keep;
         for (int32_t i : b->fOrder[2]) {
@@ -800,7 +800,8 @@ static int prepareBatch(const sa_model_t *m, const sa_read_t *reads, int64_t nRe
                 if ((rc = b->dSplitRows.alloc((size_t) fullTotal, st))) return rc;
                 if ((rc = b->dSplitPairs.alloc((size_t) std::max<int64_t>(1, pairTotal), st))) return rc;
                 int bps = 1;
-                CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, sa_cta_block_kernel<2, 2>, 64, 0));
+                if (m->kind == SA_EMIT_HDP) CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, sa_cta_block_kernel<2, 2, true>, 64, 0));
+                else CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, sa_cta_block_kernel<2, 2, false>, 64, 0));
                 b->blockGrid = (int) std::min<int64_t>((int64_t) nSM * std::max(1, bps), (int64_t) b->blocks.size());
             }
         }
@@ -948,12 +949,15 @@ static int launchBatch(sa_batch_t *b) {
         FParams f = b->fp;
         f.order = b->dSplitOrder.p; f.nOrder = (int32_t) b->splitOrder.size(); f.counter = b->dCounters.p + 6;
         f.scratch = b->dSplitRows.p;
-        sa_cta_forward_kernel<4, 1><<<(unsigned) b->splitOrder.size(), 128, 0, b->aux>>>(f);
+        const bool hdp = b->model->kind == SA_EMIT_HDP;
+        if (hdp) sa_cta_forward_kernel<4, 1, true><<<(unsigned) b->splitOrder.size(), 128, 0, b->aux>>>(f);
+        else sa_cta_forward_kernel<4, 1, false><<<(unsigned) b->splitOrder.size(), 128, 0, b->aux>>>(f);
         CK(cudaGetLastError());
         f.counter = b->dCounters.p + 7;
         f.blocks = b->dBlocks.p; f.nBlocks = (int32_t) b->blocks.size(); f.blockPairCount = b->dBlockCount.p;
         f.pairs = b->dSplitPairs.p;
-        sa_cta_block_kernel<2, 2><<<b->blockGrid, 64, 0, b->aux>>>(f);
+        if (hdp) sa_cta_block_kernel<2, 2, true><<<b->blockGrid, 64, 0, b->aux>>>(f);
+        else sa_cta_block_kernel<2, 2, false><<<b->blockGrid, 64, 0, b->aux>>>(f);
         CK(cudaGetLastError());
         b->lastLaunches += 2;
         CK(cudaEventRecord(b->evJoinSplit, b->aux));
@@ -963,7 +967,8 @@ static int launchBatch(sa_batch_t *b) {
         f.order = b->dLatOrder.p; f.nOrder = (int32_t) b->latOrder.size(); f.counter = b->dCounters.p + 5;
         f.rowsCap = b->latRows;
         f.scratch = b->dLatScratch.p;
-        sa_cta_kernel<4, 1, false, false><<<b->latBlocks, 128, 0, b->lat>>>(f);
+        if (b->model->kind == SA_EMIT_HDP) sa_cta_kernel<4, 1, false, true><<<b->latBlocks, 128, 0, b->lat>>>(f);
+        else sa_cta_kernel<4, 1, false, false><<<b->latBlocks, 128, 0, b->lat>>>(f);
         b->lastLaunches++;
         CK(cudaGetLastError());
     }
@@ -1119,7 +1124,8 @@ static int fetchBlockCounts(sa_batch_t *b) {
         f.counter = b->dCounters.p + 7;
         f.blocks = b->dBlocks.p; f.nBlocks = (int32_t) nb; f.blockPairCount = b->dBlockCount.p;
         f.pairs = b->dSplitPairs.p;
-        sa_cta_block_kernel<2, 2><<<b->blockGrid, 64, 0, st>>>(f);
+        if (b->model->kind == SA_EMIT_HDP) sa_cta_block_kernel<2, 2, true><<<b->blockGrid, 64, 0, st>>>(f);
+        else sa_cta_block_kernel<2, 2, false><<<b->blockGrid, 64, 0, st>>>(f);
         CK(cudaGetLastError());
         b->lastLaunches++;
     }
