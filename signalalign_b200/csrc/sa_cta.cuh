@@ -55,7 +55,7 @@ struct CtaK {
     static constexpr int NS = NT * C;        // slots
     static constexpr int NL = NS / 32;       // slots per lane when ONE warp walks all of them (the ordered fold)
     static constexpr int NH = W * C;         // hit-mask words per diagonal: [warp][cell]
-    static constexpr int ROW = 3 * NS + 2;   // doubles per stored forward row
+    static constexpr int ROW = (HD ? 4 : 3) * NS + 2;   // doubles per stored forward row (HDP: + the emission plane)
     static constexpr int RN = 2 * NS;        // entries of the column / event rings
     static constexpr double kExpZero = -746.0;   // exp() of anything below is exactly +0.0 (denormal minimum: e^-745.13)
 
@@ -302,8 +302,13 @@ struct CtaK {
     }
 
     static __device__ __forceinline__ void storeRow(double *row, int t, int32_t xlo, int32_t xhi, bool full,
-                                                    const double (&f)[C][3]) {
+                                                    const double (&f)[C][3], const double (&e)[C]) {
         if (t == 0) *reinterpret_cast<int2 *>(row) = make_int2(xlo, xhi);
+        if (HD) {                              // the cell's log density: the traceback reads it back instead of
+            double *q = row + 2 + 3 * NS + t * C;   // evaluating the spline and the log a second time
+            if (C == 2) *reinterpret_cast<double2 *>(q) = make_double2(e[0], e[C - 1]);
+            else q[0] = e[0];
+        }
 #pragma unroll
         for (int pl = 0; pl < 3; pl++) {
             if (pl > 0 && !full) break;
@@ -365,7 +370,11 @@ struct CtaK {
             myx[j] = slotX(t * C + j, bw);
             const bool act = myx[j] >= xlo && myx[j] <= xhi;
             double eM, eY;
-            emissions(P, I, S, myx[j], d - myx[j], eM, eY);
+            if (HD) {
+                double ev[C];
+                loadRow(ring + (int64_t) rowI * ROW, 3, t, ev);
+                eM = eY = ev[j];
+            } else emissions(P, I, S, myx[j], d - myx[j], eM, eY);
             curM[j] = act ? e0 : SA_NEG_INF; curE[j] = eM;
             qX[j] = act ? e1 : SA_NEG_INF; qY[j] = act ? e2 : SA_NEG_INF; qE[j] = eY;
             nxtM[j] = SA_NEG_INF; nxtE[j] = 0.0;
@@ -454,8 +463,14 @@ struct CtaK {
                     }
                 }
                 double eM[C], eY[C];
+                if (HD) {
+                    loadRow(row, 3, t, eM);
 #pragma unroll
-                for (int j = 0; j < C; j++) emissions(P, I, S, myx[j], d2 - myx[j], eM[j], eY[j]);
+                    for (int j = 0; j < C; j++) eY[j] = eM[j];
+                } else {
+#pragma unroll
+                    for (int j = 0; j < C; j++) emissions(P, I, S, myx[j], d2 - myx[j], eM[j], eY[j]);
+                }
                 sa_mbWait(&S.mbar, phase);     // mailbox and hit masks of diagonal d2 + 1 are visible
                 if (pendValid) flush();
                 double nb[3];
@@ -628,7 +643,10 @@ struct CtaK {
             nbA[0] = nbA[1] = nbA[2] = SA_NEG_INF;
             nbB[0] = nbB[1] = nbB[2] = SA_NEG_INF;
         }
-        storeRow(ring, t, 0, 0, true, fa);
+        {
+            const double e0[C] = {};
+            storeRow(ring, t, 0, 0, true, fa, e0);
+        }
         publish(S, 0, t, fa[C - 1]);           // the right neighbour thread reads the LAST cell
         sa_mbArrive(&S.mbar);
         int32_t tracedBackTo = 0;
@@ -681,7 +699,7 @@ struct CtaK {
                 }
                 publish(S, d & 1, t, fb[C - 1]);
                 sa_mbArrive(&S.mbar);
-                storeRow(row, t, xlo, xhi, full, fb);
+                storeRow(row, t, xlo, xhi, full, fb, eM);
             } else {
                 fetchUp(S, (d - 1) & 1, t, nbB);
 #pragma unroll
@@ -691,7 +709,7 @@ struct CtaK {
                 }
                 publish(S, d & 1, t, fa[C - 1]);
                 sa_mbArrive(&S.mbar);
-                storeRow(row, t, xlo, xhi, full, fa);
+                storeRow(row, t, xlo, xhi, full, fa, eM);
             }
             if (d != nextT) continue;
             // ------------------------------------------------------------------ traceback from diagonal d

@@ -714,6 +714,7 @@ static int prepareBatch(const sa_model_t *m, const sa_read_t *reads, int64_t nRe
         timer.lap("geometry kernel + D2H");
     }
     static const int kW[4] = {1, 2, 4, 8};
+    const int64_t planes = m->kind == SA_EMIT_HDP ? 4 : 3;   // forward row = header + M, X, Y (+ the HDP log density)
     const bool useWarpKernel = getenv("SA_WARP_KERNEL") != nullptr && !b->expectations;   // the superseded warp-per-read kernel (A/B runs only)
     for (int64_t i = 0; i < n; i++) {
         ItemRec &it = items[i];
@@ -746,10 +747,12 @@ static int prepareBatch(const sa_model_t *m, const sa_read_t *reads, int64_t nRe
     // two per SM and longest first, go to the one-cell mapping, whose step is about half as long.
     if (!useWarpKernel && !b->oneCell && !b->expectations && getenv("SA_NO_LATENCY_CLASS") == nullptr) {
         const double ideal = (double) b->bandCells * (double) chunkCount / 30e9;
+        const char *ef = getenv("SA_LAT_FACTOR");
+        const double latFactor = ef ? atof(ef) : 0.5;
         std::vector<int32_t> keep;
         for (int32_t i : b->fOrder[2]) {
             const double solo = (double) (items[i].lX + items[i].lY) * 2.3e-6;
-            if ((int64_t) b->latOrder.size() < 2 * (int64_t) nSM && solo > 0.5 * ideal) {
+            if ((int64_t) b->latOrder.size() < 2 * (int64_t) nSM && solo > latFactor * ideal) {
                 b->latOrder.push_back(i);
                 b->latRows = std::max(b->latRows, geo[i].maxRows);
             } else keep.push_back(i);
@@ -766,7 +769,7 @@ static int prepareBatch(const sa_model_t *m, const sa_read_t *reads, int64_t nRe
             std::vector<int32_t> ring;
             b->latRows = 1;
             for (int32_t i : b->latOrder) {
-                const int64_t nDiag = items[i].lX + items[i].lY, need = (nDiag + 1) * (3 * 128 + 2);
+                const int64_t nDiag = items[i].lX + items[i].lY, need = (nDiag + 1) * (planes * 128 + 2);
                 if (fullTotal + need > budget) {
                     ring.push_back(i);
                     b->latRows = std::max(b->latRows, geo[i].maxRows);
@@ -808,7 +811,7 @@ static int prepareBatch(const sa_model_t *m, const sa_read_t *reads, int64_t nRe
         if (!b->latOrder.empty()) {
             if ((rc = b->dLatOrder.upload(b->latOrder, st, &b->h2dBytes))) return rc;
             b->latBlocks = (int) b->latOrder.size();
-            if ((rc = b->dLatScratch.alloc((size_t) b->latBlocks * b->latRows * (3 * 128 + 2), st))) return rc;
+            if ((rc = b->dLatScratch.alloc((size_t) b->latBlocks * b->latRows * (planes * 128 + 2), st))) return rc;
         }
     }
     {
@@ -825,7 +828,7 @@ static int prepareBatch(const sa_model_t *m, const sa_read_t *reads, int64_t nRe
             } else {
                 if ((rc = ctaOccupancy(c, b->oneCell, b->expectations, m->kind == SA_EMIT_HDP, &bps))) return rc;
                 b->fBlocks[c] = (int) std::min<int64_t>((int64_t) nSM * std::max(1, bps), nIt);
-                rowD = (int64_t) b->fBlocks[c] * b->fRows[c] * (3 * 32 * kW[c] + 2);
+                rowD = (int64_t) b->fBlocks[c] * b->fRows[c] * (planes * 32 * kW[c] + 2);
             }
             need = std::max(need, rowD);
         }
