@@ -818,7 +818,11 @@ struct CtaK {
 
 // resident CTAs per SM the register allocation is held to
 template <int W, int C, bool EX, bool HD> struct CtaOcc {
-    static constexpr int kMinBlocks = (EX || HD) ? (W == 1 ? 12 : W == 2 ? 6 : 3)
+#ifndef SA_HD_OCC
+#define SA_HD_OCC 7
+#endif
+    static constexpr int kMinBlocks = (HD && !EX) ? (W == 1 ? 2 * SA_HD_OCC : W == 2 ? SA_HD_OCC : SA_HD_OCC / 2)
+                                    : EX ? (W == 1 ? 12 : W == 2 ? 6 : 3)
                                          : C == 1 ? (W == 1 ? 16 : W == 2 ? 10 : W == 4 ? 5 : 2)
                                                   : (W == 1 ? 16 : W == 2 ? 8 : 4);
 };
