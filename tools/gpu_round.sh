@@ -16,7 +16,7 @@ python bench.py --steps 2 --warmup 1 --no-cpu --no-expectations > gpurun_out/${T
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/${TAG}_launches.csv \
     python bench.py --steps 2 --warmup 1 --no-cpu --no-expectations > gpurun_out/${TAG}_ncu_launches.log 2>&1
 python bench.py --steps 1 --warmup 1 --reads ${NCU_READS} --no-cpu --no-expectations > gpurun_out/${TAG}_bench_ncu_cfg.json 2>> gpurun_out/${TAG}_bench.err && \
-ncu --set full --clock-control none --import-source on -k "regex:sa_cta_kernel<2, 2" -c 1 -f -o gpurun_out/${TAG}_cta_full \
+ncu --set full --clock-control none --import-source on --kernel-name-base demangled -k "regex:sa_cta_kernel<\(int\)2, \(int\)2, \(bool\)0, \(bool\)0>" -c 1 -f -o gpurun_out/${TAG}_cta_full \
     python bench.py --steps 1 --warmup 0 --reads ${NCU_READS} --no-cpu --no-expectations > gpurun_out/${TAG}_ncu_full.log 2>&1
 tail -3 gpurun_out/${TAG}_pytest.txt; cat gpurun_out/${TAG}_smoke.txt | tail -2; cat gpurun_out/${TAG}_peak_fp.jsonl
 cut -c1-600 gpurun_out/${TAG}_bench_reference.json; cut -c1-2500 gpurun_out/${TAG}_bench.json
