@@ -68,6 +68,7 @@ struct CtaK {
         int2 bandTab[NT];        // [xlo, xhi] of forward diagonals bd0 .. bd0 + NT - 1
         int32_t aX[NT + 1], aY[NT + 1], aD[NT + 1];   // staged anchors (+1 coordinates) and their diagonals
         alignas(16) unsigned hitM[2][NH < 4 ? 4 : NH];   // posterior hits per warp and cell (ballot), double buffered
+        unsigned hitA[2][3][(EX && HD) ? NH : 1];        // HDP expectations: match terms >= threshold, per from-state
         int32_t sItem, sAi;
         unsigned long long mbar; // split barrier of the diagonal steps
     };
@@ -423,6 +424,46 @@ struct CtaK {
             nPairs += tot;
             pendValid = false;
         };
+        // HDP expectations: the assignments of the previous diagonal (cell order, then from-state M, X, Y), written after
+        // the next barrier like the pairs; nPairs counts them
+        unsigned pendA[C];
+#pragma unroll
+        for (int j = 0; j < C; j++) pendA[j] = 0u;
+        auto flushA = [&]() {
+            unsigned m[3][NH];
+            int tot[3], all = 0;
+#pragma unroll
+            for (int s3 = 0; s3 < 3; s3++) {
+                tot[s3] = 0;
+#pragma unroll
+                for (int w = 0; w < NH; w++) { m[s3][w] = S.hitA[pendD & 1][s3][w]; tot[s3] += __popc(m[s3][w]); }
+                all += tot[s3];
+            }
+#pragma unroll
+            for (int j = 0; j < C; j++) {
+                if (!pendA[j]) continue;
+                const int sl = t * C + j;
+                int before = 0;
+#pragma unroll
+                for (int s3 = 0; s3 < 3; s3++) {
+                    const int a = hitsBelow(m[s3], pendS0), b = hitsBelow(m[s3], sl);
+                    before += pendS0 <= sl ? b - a : tot[s3] - a + b;
+                }
+                int64_t w = nPairs + before;
+#pragma unroll
+                for (int s3 = 0; s3 < 3; s3++) {
+                    if (!((pendA[j] >> s3) & 1u)) continue;
+                    if (w < I.assignCap) {
+                        // kmer position x - 1 (clamped at 0 like the reference's index), event y - 1
+                        P.assignK[I.assignOff + w] = pendX[j] - 1 >= 0 ? pendX[j] - 1 : 0;
+                        P.assignE[I.assignOff + w] = pendD - pendX[j] - 1;
+                    }
+                    w++;
+                }
+            }
+            nPairs += all;
+            pendValid = false;
+        };
         int2 hdrNext = make_int2(0, 0);   // band of d2 - 1 (the expectations also need it on the block's lowest diagonal)
         if (EX || d - 1 > tracedBackTo) hdrNext = *reinterpret_cast<const int2 *>(ring + (int64_t) (rowI == 0 ? cap - 1 : rowI - 1) * ROW);
         rowI = rowI + 1 == cap ? 0 : rowI + 1;
@@ -472,7 +513,9 @@ struct CtaK {
                     for (int j = 0; j < C; j++) emissions(P, I, S, myx[j], d2 - myx[j], eM[j], eY[j]);
                 }
                 sa_mbWait(&S.mbar, phase);     // mailbox and hit masks of diagonal d2 + 1 are visible
-                if (pendValid) flush();
+                if (pendValid) {
+                    if (EX && HD) flushA(); else flush();
+                }
                 double nb[3];
                 fetchDown(S, (d2 + 1) & 1, t, nb);
                 // ascending j: cell j reads the values cell j + 1 held BEFORE this step
@@ -556,14 +599,25 @@ struct CtaK {
                         if (__any_sync(0xffffffffu, lower && !(a1 < kExpZero))) acc[3] += lower ? exp(a1) : 0.0;
                         yxNaN |= lower && !(total > SA_NEG_INF);   // exp(-inf - total): NaN exactly when total is -inf
                     }
+                    double pr[3] = {0.0, 0.0, 0.0};   // the three match terms (HDP: also the assignment test)
                     if (__any_sync(0xffffffffu, middle)) {
                         const double f0 = r2[sp], f1 = r2[NS + sp], f2 = r2[2 * NS + sp];
                         const double a0 = ((f0 + curM[j]) + (curE[j] + T[T_MATCH_CONTINUE])) - total;
                         const double a1 = ((f1 + curM[j]) + (curE[j] + T[T_MATCH_FROM_GAP_X])) - total;
                         const double a2 = ((f2 + curM[j]) + (curE[j] + T[T_MATCH_FROM_GAP_Y])) - total;
-                        if (__any_sync(0xffffffffu, middle && !(a0 < kExpZero))) acc[0] += middle ? exp(a0) : 0.0;
-                        if (__any_sync(0xffffffffu, middle && !(a1 < kExpZero))) acc[2] += middle ? exp(a1) : 0.0;
-                        if (__any_sync(0xffffffffu, middle && !(a2 < kExpZero))) acc[4] += middle ? exp(a2) : 0.0;
+                        if (__any_sync(0xffffffffu, middle && !(a0 < kExpZero))) { pr[0] = middle ? exp(a0) : 0.0; acc[0] += pr[0]; }
+                        if (__any_sync(0xffffffffu, middle && !(a1 < kExpZero))) { pr[1] = middle ? exp(a1) : 0.0; acc[2] += pr[1]; }
+                        if (__any_sync(0xffffffffu, middle && !(a2 < kExpZero))) { pr[2] = middle ? exp(a2) : 0.0; acc[4] += pr[2]; }
+                    }
+                    if (HD) {
+                        pendA[j] = 0u;
+#pragma unroll
+                        for (int s3 = 0; s3 < 3; s3++) {
+                            const bool hs = middle && pr[s3] >= P.threshold;
+                            S.hitA[d2 & 1][s3][warp * C + j] = __ballot_sync(0xffffffffu, hs);
+                            pendA[j] |= hs ? (1u << s3) : 0u;
+                        }
+                        pendX[j] = x;
                     }
                     if (__any_sync(0xffffffffu, upper)) {
                         const double f0 = r1[sl], f2 = r1[2 * NS + sl];
@@ -573,6 +627,7 @@ struct CtaK {
                         if (__any_sync(0xffffffffu, upper && !(a2 < kExpZero))) acc[6] += upper ? exp(a2) : 0.0;
                     }
                 }
+                if (HD) { pendValid = true; pendD = d2; pendS0 = bw & (NS - 1); }
                 sa_mbArrive(&S.mbar);
                 continue;
             }
@@ -595,7 +650,9 @@ struct CtaK {
             sa_mbArrive(&S.mbar);
         }
         sa_mbWait(&S.mbar, phase);             // the last diagonal's hit masks
-        if (pendValid) flush();
+        if (pendValid) {
+            if (EX && HD) flushA(); else flush();
+        }
     }
 
     // FWD = true: the forward sweep only, every row kept (ring of lX + lY + 1 rows = no wrap); the traceback blocks of
@@ -612,6 +669,7 @@ struct CtaK {
         if (nDiag == 0) {
             if (t == 0) {
                 P.pairCount[it] = 0;
+                if (EX && HD) P.assignCount[it] = 0;
                 if (EX)
                     for (int i = 0; i < 10; i++) P.expOut[(int64_t) it * 10 + i] = 0.0;
             }
@@ -785,7 +843,10 @@ struct CtaK {
             }
         }
         if (FWD) sa_mbWait(&S.mbar, phase);    // consume the last step's arrival: the next item starts with a clean phase
-        if (t == 0 && !FWD) P.pairCount[it] = nPairs;
+        if (t == 0 && !FWD) {
+            if (EX && HD) { P.pairCount[it] = 0; P.assignCount[it] = nPairs; }
+            else P.pairCount[it] = nPairs;
+        }
     }
 
     // One traceback block of an item whose forward rows are all in `ring` (row index = diagonal): the body of the

@@ -34,6 +34,7 @@ struct FItem {
     double scale, shift, invVar, logInvVar;
     double var;
     int64_t fullOff;    // split mode: offset (doubles) of the item's full-length row buffer in FParams.scratch
+    int64_t assignOff, assignCap;   // HDP expectations: the item's slot in FParams.assignK / assignE
 };
 
 struct FBlock {          // split mode: one traceback block of an item
@@ -81,6 +82,10 @@ struct FParams {
     const FBlock *blocks;
     int32_t nBlocks;
     int64_t *blockPairCount;
+    // HDP expectations: (kmer position, event) of every match term >= threshold (reference continuousHmm.c, the
+    // assignments of cell_signal_updateExpectationsAndAssignments), in the reference's order
+    int32_t *assignK, *assignE;
+    int64_t *assignCount;
     double gridDx, gridInvDx; // grid[1] - grid[0] and its reciprocal
 };
 

@@ -350,7 +350,7 @@ static int64_t nextPow2(int64_t v) {
 static bool modelFastEligible(const sa_model *m, bool expectations) {
     const bool hdp = m->kind == SA_EMIT_HDP;
     if (m->kind != SA_EMIT_GAUSS_MEANONLY_DESCALE && !hdp) return false;
-    if (hdp && (expectations || m->G < 2)) return false;
+    if (hdp && m->G < 2) return false;
     if (!(m->trans[T_GAP_SWITCH_TO_X] == -INFINITY)) return false;
     // the HDP machine's X-gap emission is the literal log(0.1) (stateMachine.c:1394), whatever the table says
     for (int64_t i = 0; i < m->K; i++) {
@@ -382,11 +382,13 @@ static void ctaLaunchT(int c, bool oneCell, int blocks, cudaStream_t st, const F
 // ex: the expectations variant of the kernels (getExpectationsUsingAnchors) instead of the aligned-pairs one;
 // hdp: the HDP emission instead of the Gaussian tables (alignment only: HDP expectations collect assignments)
 static int ctaOccupancy(int c, bool oneCell, bool ex, bool hdp, int *bps) {
+    if (hdp && ex) return ctaOccupancyT<true, true>(c, false, bps);
     if (hdp) return ctaOccupancyT<false, true>(c, false, bps);
     return ex ? ctaOccupancyT<true, false>(c, false, bps) : ctaOccupancyT<false, false>(c, oneCell, bps);
 }
 static void ctaLaunch(int c, bool oneCell, bool ex, bool hdp, int blocks, cudaStream_t st, const FParams &f) {
-    if (hdp) ctaLaunchT<false, true>(c, false, blocks, st, f);
+    if (hdp && ex) ctaLaunchT<true, true>(c, false, blocks, st, f);
+    else if (hdp) ctaLaunchT<false, true>(c, false, blocks, st, f);
     else if (ex) ctaLaunchT<true, false>(c, false, blocks, st, f);
     else ctaLaunchT<false, false>(c, oneCell, blocks, st, f);
 }
@@ -679,6 +681,7 @@ static int prepareBatch(const sa_model_t *m, const sa_read_t *reads, int64_t nRe
             fi.nTbCap = (int32_t) ((it.lX + it.lY) / (p->minDiagsBetweenTraceBack - p->traceBackDiagonals - 1) + 2);
             tbTotal += fi.nTbCap;
             fi.pairOff = it.pairOff; fi.pairCap = it.pairCap;
+            fi.assignOff = it.assignOff; fi.assignCap = it.assignCap;
             fi.lX = (int32_t) it.lX; fi.lY = (int32_t) it.lY;
             fi.flags = it.flags;
             fi.scale = it.scale; fi.shift = it.shift;
@@ -700,6 +703,7 @@ static int prepareBatch(const sa_model_t *m, const sa_read_t *reads, int64_t nRe
         f.expansion = (int32_t) p->diagonalExpansion;
         f.pairs = b->dPairs.p; f.pairCount = b->dPairCount.p;
         f.expOut = b->expectations ? b->dExpOut.p : nullptr;
+        if (b->expectations) { f.assignK = b->dAssignK.p; f.assignE = b->dAssignE.p; f.assignCount = b->dAssignCount.p; }
         if (m->kind == SA_EMIT_HDP) {
             f.grid = m->dev->grid; f.pp = m->dev->pp; f.slopes = m->dev->slopes; f.kmerToRow = m->dev->kmerToRow;
             f.G = (int32_t) m->G;
@@ -1047,6 +1051,7 @@ static int growAndRerun(sa_batch_t *b) {
         }
         if (it.kernel) {
             b->fItems[i].pairOff = it.pairOff; b->fItems[i].pairCap = it.pairCap;
+            b->fItems[i].assignOff = it.assignOff; b->fItems[i].assignCap = it.assignCap;
         } else {
             b->gItems[i].pairOff = it.pairOff; b->gItems[i].pairCap = it.pairCap;
             b->gItems[i].assignOff = it.assignOff; b->gItems[i].assignCap = it.assignCap;
@@ -1070,6 +1075,8 @@ static int growAndRerun(sa_batch_t *b) {
         if ((rc = b->dAssignE.alloc(std::max<int64_t>(1, at), b->stream))) return rc;
         b->gp.assignK = b->dAssignK.p;
         b->gp.assignE = b->dAssignE.p;
+        b->fp.assignK = b->dAssignK.p;
+        b->fp.assignE = b->dAssignE.p;
     }
     return sa_batch_run(b);
 }

@@ -221,6 +221,33 @@ def test_hdp_emission_on_the_band_kernel(small_batch, expansion, trace_back, min
         ora, _ = oracle_align(pm, r, port_params(p))
         assert compare_pairs(fast.read_pairs(i), ora, p.threshold) <= 20
         assert compare_pairs(fast.read_pairs(i), gen.read_pairs(i), p.threshold) <= 20
+    # expectations + assignments of the HDP machine on the band kernel (<W, C, EX = true, HD = true>): transitions and
+    # likelihood against the oracle, the assignment list (order included) bit-exact against oracle and general kernel
+    fe = sa.expectations_batch(model, [sa_read(r) for r in rs], p)
+    os.environ["SA_FORCE_GENERAL"] = "1"
+    try:
+        ge = sa.expectations_batch(model, [sa_read(r) for r in rs], p)
+    finally:
+        os.environ.pop("SA_FORCE_GENERAL", None)
+    assert np.array_equal(fe.assign_offsets, ge.assign_offsets)
+    assert np.array_equal(fe.assign_kmer_pos, ge.assign_kmer_pos) and np.array_equal(fe.assign_event, ge.assign_event)
+    assert fe.assign_offsets[-1] > 0
+    for i, r in enumerate(rs):
+        tr, lik, ak, ae = oracle_expectations(pm, r, port_params(p))
+        compare_expectations(fe.transitions[i], fe.likelihood[i], tr, lik)
+        compare_expectations(fe.transitions[i], fe.likelihood[i], ge.transitions[i], ge.likelihood[i])
+        a0, a1 = fe.assign_offsets[i], fe.assign_offsets[i + 1]
+        assert np.array_equal(fe.assign_kmer_pos[a0:a1], ak) and np.array_equal(fe.assign_event[a0:a1], ae)
+    # a batch this small is all latency class -> split mode (forward sweep keeping every row and its log-density plane,
+    # traceback blocks as work items); ring mode, the block re-run path and the throughput mapping must give the same bytes
+    for env in ({"SA_NO_SPLIT": "1"}, {"SA_SPLIT_PAIRCAP": "8"}, {"SA_NO_LATENCY_CLASS": "1"}):
+        os.environ.update(env)
+        try:
+            o = sa.align_batch(model, [sa_read(r) for r in rs], p)
+        finally:
+            for k in env:
+                os.environ.pop(k, None)
+        assert np.array_equal(fast.pair_offsets, o.pair_offsets) and np.array_equal(fast.pairs, o.pairs), env
 
 
 def test_ambiguous_reference_iupac(gapped_batch):

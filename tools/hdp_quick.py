@@ -29,3 +29,7 @@ for i in range(3):
     print("HDP G=%d K=%d rows: %d reads, %.3e cells, kernel %.1f ms, %.2f GCUPS" % (G, K, n, b.band_cells, sum(ms), b.band_cells / sum(ms) / 1e6))
 r = b.fetch()
 print("pairs", int(r.pair_offsets[-1]))
+if os.environ.get("HDP_EXPECT"):
+    for i in range(3):
+        t0 = time.time(); e = sa.expectations_batch(model, reads, p); dt = time.time() - t0
+        print("HDP expectations end to end: %.1f ms, %.2f GCUPS, %d assignments" % (1e3 * dt, b.band_cells / dt / 1e9, int(e.assign_offsets[-1])))
