@@ -51,6 +51,10 @@ sa_model_t *sa_model_from_tables(const char *alphabet, int32_t kmerLength, const
  * kmers stateMachine3_setModelToHdpExpectedValues replaces); NULL = every kmer's own DP is observed */
 int sa_model_set_hdp(sa_model_t *m, int64_t gridLength, const double *grid, const int32_t *kmerToRow,
                      const int32_t *ownRow, int64_t nRows, const double *postPred, const double *slopes);
+/* attach the HDP of an .nhdp file (what deserialize_nhdp reads, impl/nanopore_hdp.c:1088-1115) to a model built with
+ * sa_model_from_tables; the emission kind becomes SA_EMIT_HDP.  The drop-in shim uses it with the file the reference's
+ * own serialize_nhdp (impl/nanopore_hdp.c:1076-1086) writes from a live StateMachine3_HDP (%.17lg: exact round trip) */
+int sa_model_attach_nhdp(sa_model_t *m, const char *nhdpFile);
 int sa_model_set_hdp_expected_values(sa_model_t *m);
 /* emissions_signal_scaleNoise (impl/stateMachine.c:721-741) / emissions_signal_scaleModel (:743-779) */
 int sa_model_scale_noise(sa_model_t *m, double scale_sd, double var_sd);

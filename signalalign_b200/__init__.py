@@ -47,7 +47,8 @@ class SaResult(C.Structure):
 
 
 EXPORTS = [
-    "sa_model_load", "sa_model_from_tables", "sa_model_set_hdp", "sa_model_set_hdp_expected_values",
+    "sa_model_load", "sa_model_from_tables", "sa_model_set_hdp", "sa_model_attach_nhdp",
+    "sa_model_set_hdp_expected_values",
     "sa_model_scale_noise", "sa_model_scale_model", "sa_model_free", "sa_model_num_kmers", "sa_model_kmer_length",
     "sa_model_alphabet", "sa_model_get_tables", "sa_model_hdp_density", "sa_params_default", "sa_ambig_load",
     "sa_ambig_free", "sa_result_free", "sa_kmer_string", "sa_gpu_init", "sa_last_error", "sa_gpu_device_count",
@@ -84,6 +85,7 @@ def lib():
     L.sa_model_from_tables.argtypes = [C.c_char_p, C.c_int32, c_f64p, c_f64p, c_f64p, c_f64p, C.c_int]
     L.sa_model_set_hdp.argtypes = [C.c_void_p, C.c_int64, c_f64p, c_i32p, c_i32p, C.c_int64, c_f64p, c_f64p]
     L.sa_model_set_hdp_expected_values.argtypes = [C.c_void_p]
+    L.sa_model_attach_nhdp.argtypes = [C.c_void_p, C.c_char_p]
     L.sa_model_scale_noise.argtypes = [C.c_void_p, C.c_double, C.c_double]
     L.sa_model_scale_model.argtypes = [C.c_void_p] + [C.c_double] * 5
     L.sa_model_free.argtypes = [C.c_void_p]
@@ -192,6 +194,9 @@ class Model:
 
     def set_hdp_expected_values(self):
         _check(lib().sa_model_set_hdp_expected_values(self.h))
+
+    def attach_nhdp(self, nhdp_file):
+        _check(lib().sa_model_attach_nhdp(self.h, nhdp_file.encode()))
 
     def scale_noise(self, scale_sd, var_sd):
         _check(lib().sa_model_scale_noise(self.h, scale_sd, var_sd))

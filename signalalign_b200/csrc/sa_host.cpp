@@ -422,6 +422,17 @@ static bool loadNhdp(sa_model *m, const char *path) {
     return true;
 }
 
+extern "C" int sa_model_attach_nhdp(sa_model_t *m, const char *nhdpFile) {
+    if (!m || !nhdpFile || !nhdpFile[0]) {
+        sa_set_error("sa_model_attach_nhdp: no model or no file");
+        return SA_ERR_INPUT;
+    }
+    if (!loadNhdp(m, nhdpFile)) return SA_ERR_INPUT;
+    m->kind = SA_EMIT_HDP;
+    sa_model_drop_device(m);
+    return SA_OK;
+}
+
 extern "C" int sa_model_set_hdp(sa_model_t *m, int64_t G, const double *grid, const int32_t *kmerToRow,
                                 const int32_t *ownRow, int64_t nRows, const double *postPred, const double *slopes) {
     m->kind = SA_EMIT_HDP;

@@ -14,11 +14,16 @@
  * (int64_t) char *kmer) with destructor stIntTuple_destruct and kmer strings that are never freed
  * (impl/pairwiseAligner.c:665-668, 2064); expectations are added into the caller's Hmm through its own function
  * pointers; any failure aborts the process through st_errAbort (no return codes, no CPU fallback).
- * Not covered here: StateMachine3_HDP (hdp.c keeps its structs private: load the same .nhdp with sa_model_load),
- * and per-Sequence ambiguity tables other than the built-in one (create_ambig_bases2(NULL)).
+ * StateMachine3_HDP: hdp.c keeps its structs private, so the machine's NanoporeHDP travels through the reference's own
+ * serialize_nhdp (impl/nanopore_hdp.c:1076-1086, %.17lg: exact round trip) into a temporary file that
+ * sa_model_attach_nhdp parses; HDP expectations append their (kmer, event) assignments through HdpHmm::addToAssignments
+ * with pointers into sX->elements / sY->elements, as cell_signal_updateExpectationsAndAssignments does
+ * (impl/pairwiseAligner.c:946-968).
+ * Not covered here: per-Sequence ambiguity tables other than the built-in one (create_ambig_bases2(NULL)).
  */
 #include <stdlib.h>
 #include <string.h>
+#include <unistd.h>
 
 #include "signalalign_b200.h"
 
@@ -31,6 +36,7 @@
 static struct {
     const StateMachine *sM;
     const double *match;
+    const void *hdp;
     sa_model_t *model;
 } g_cache[SHIM_CACHE];
 static int g_cacheNext = 0, g_inited = 0;
@@ -41,33 +47,61 @@ static sa_model_t *shimModel(StateMachine *sM) {
         if (sa_gpu_init(dev ? atoi(dev) : 0) != SA_OK) st_errAbort("libsagpu: %s\n", sa_last_error());
         g_inited = 1;
     }
+    const void *hdp = sM->type == threeStateHdp ? (const void *) ((StateMachine3_HDP *) sM)->hdpModel : NULL;
     for (int i = 0; i < SHIM_CACHE; i++)
-        if (g_cache[i].model && g_cache[i].sM == sM && g_cache[i].match == sM->EMISSION_MATCH_MATRIX) return g_cache[i].model;
-    if (sM->type != threeState)
-        st_errAbort("signalalign_shim: only the 3-state Gaussian machine is bound through the StateMachine struct; "
-                    "for StateMachine3_HDP load the .model/.nhdp pair with sa_model_load\n");
-    StateMachine3 *s3 = (StateMachine3 *) sM;
-    double t[9] = {s3->TRANSITION_MATCH_CONTINUE, s3->TRANSITION_MATCH_FROM_GAP_X, s3->TRANSITION_MATCH_FROM_GAP_Y,
-                   s3->TRANSITION_GAP_OPEN_X, s3->TRANSITION_GAP_OPEN_Y, s3->TRANSITION_GAP_EXTEND_X,
-                   s3->TRANSITION_GAP_EXTEND_Y, s3->TRANSITION_GAP_SWITCH_TO_X, s3->TRANSITION_GAP_SWITCH_TO_Y};
-    int kind;
-    if (s3->getMatchProbFcn == emissions_signal_strawManGetKmerEventMatchProbWithDescaling_MeanOnly)
-        kind = SA_EMIT_GAUSS_MEANONLY_DESCALE;
-    else if (s3->getMatchProbFcn == emissions_signal_strawManGetKmerEventMatchProbWithDescaling)
-        kind = SA_EMIT_GAUSS_NOISE_DESCALE;
-    else if (s3->getMatchProbFcn == emissions_signal_strawManGetKmerEventMatchProb)
-        kind = SA_EMIT_GAUSS_NOISE_SCALED;
-    else {
-        st_errAbort("signalalign_shim: unknown emission function in StateMachine3\n");
-        return NULL;
+        if (g_cache[i].model && g_cache[i].sM == sM && g_cache[i].match == sM->EMISSION_MATCH_MATRIX && g_cache[i].hdp == hdp)
+            return g_cache[i].model;
+    sa_model_t *m = NULL;
+    if (sM->type == threeStateHdp) {
+        /* StateMachine3_HDP keeps the transition block at the same place as StateMachine3 (inc/stateMachine.h:150-191);
+         * the tables are taken as they are (stateMachine3_setModelToHdpExpectedValues has or has not been applied by
+         * the caller, impl/stateMachine.c:1275-1304) */
+        StateMachine3_HDP *sh = (StateMachine3_HDP *) sM;
+        if (sh->getMatchProbFcn != emissions_signal_getHdpKmerDensity || sh->hdpModel == NULL)
+            st_errAbort("signalalign_shim: unknown emission function in StateMachine3_HDP\n");
+        double t[9] = {sh->TRANSITION_MATCH_CONTINUE, sh->TRANSITION_MATCH_FROM_GAP_X, sh->TRANSITION_MATCH_FROM_GAP_Y,
+                       sh->TRANSITION_GAP_OPEN_X, sh->TRANSITION_GAP_OPEN_Y, sh->TRANSITION_GAP_EXTEND_X,
+                       sh->TRANSITION_GAP_EXTEND_Y, sh->TRANSITION_GAP_SWITCH_TO_X, sh->TRANSITION_GAP_SWITCH_TO_Y};
+        m = sa_model_from_tables(sM->alphabet, (int32_t) sM->kmerLength, t, sM->EMISSION_MATCH_MATRIX,
+                                 sM->EMISSION_GAP_Y_MATRIX, sM->EMISSION_GAP_X_PROBS, SA_EMIT_HDP);
+        if (!m) st_errAbort("libsagpu: %s\n", sa_last_error());
+        const char *dir = getenv("TMPDIR");
+        char path[4096];
+        snprintf(path, sizeof(path), "%s/sagpu_nhdp_XXXXXX", dir && dir[0] ? dir : "/tmp");
+        int fd = mkstemp(path);
+        if (fd < 0) st_errAbort("signalalign_shim: cannot create %s\n", path);
+        close(fd);
+        serialize_nhdp(sh->hdpModel, path);
+        int rc = sa_model_attach_nhdp(m, path);
+        unlink(path);
+        if (rc != SA_OK) st_errAbort("libsagpu: %s\n", sa_last_error());
+    } else if (sM->type == threeState) {
+        StateMachine3 *s3 = (StateMachine3 *) sM;
+        double t[9] = {s3->TRANSITION_MATCH_CONTINUE, s3->TRANSITION_MATCH_FROM_GAP_X, s3->TRANSITION_MATCH_FROM_GAP_Y,
+                       s3->TRANSITION_GAP_OPEN_X, s3->TRANSITION_GAP_OPEN_Y, s3->TRANSITION_GAP_EXTEND_X,
+                       s3->TRANSITION_GAP_EXTEND_Y, s3->TRANSITION_GAP_SWITCH_TO_X, s3->TRANSITION_GAP_SWITCH_TO_Y};
+        int kind;
+        if (s3->getMatchProbFcn == emissions_signal_strawManGetKmerEventMatchProbWithDescaling_MeanOnly)
+            kind = SA_EMIT_GAUSS_MEANONLY_DESCALE;
+        else if (s3->getMatchProbFcn == emissions_signal_strawManGetKmerEventMatchProbWithDescaling)
+            kind = SA_EMIT_GAUSS_NOISE_DESCALE;
+        else if (s3->getMatchProbFcn == emissions_signal_strawManGetKmerEventMatchProb)
+            kind = SA_EMIT_GAUSS_NOISE_SCALED;
+        else {
+            st_errAbort("signalalign_shim: unknown emission function in StateMachine3\n");
+            return NULL;
+        }
+        m = sa_model_from_tables(sM->alphabet, (int32_t) sM->kmerLength, t, sM->EMISSION_MATCH_MATRIX,
+                                 sM->EMISSION_GAP_Y_MATRIX, sM->EMISSION_GAP_X_PROBS, kind);
+        if (!m) st_errAbort("libsagpu: %s\n", sa_last_error());
+    } else {
+        st_errAbort("signalalign_shim: only threeState and threeStateHdp machines are bound (signalMachine builds no other)\n");
     }
-    sa_model_t *m = sa_model_from_tables(sM->alphabet, (int32_t) sM->kmerLength, t, sM->EMISSION_MATCH_MATRIX,
-                                         sM->EMISSION_GAP_Y_MATRIX, sM->EMISSION_GAP_X_PROBS, kind);
-    if (!m) st_errAbort("libsagpu: %s\n", sa_last_error());
     int slot = g_cacheNext++ % SHIM_CACHE;
     if (g_cache[slot].model) sa_model_free(g_cache[slot].model);
     g_cache[slot].sM = sM;
     g_cache[slot].match = sM->EMISSION_MATCH_MATRIX;
+    g_cache[slot].hdp = hdp;
     g_cache[slot].model = m;
     return m;
 }
@@ -149,6 +183,8 @@ void getExpectationsUsingAnchors(StateMachine *sM, Hmm *hmmExpectations, Sequenc
     shimRead(sM, SsX, SsY, anchorPairs, alignmentHasRaggedLeftEnd, alignmentHasRaggedRightEnd, &r, &an);
     sa_params_t sp;
     shimParams(p, &sp);
+    /* the assignment gate is the HdpHmm's own threshold (impl/pairwiseAligner.c:963), not the alignment parameter's */
+    if (sM->type == threeStateHdp) sp.threshold = ((HdpHmm *) hmmExpectations)->threshold;
     sa_result_t *res = NULL;
     if (sa_gpu_expectations_batch(m, &r, 1, &sp, NULL, &res) != SA_OK) st_errAbort("libsagpu: %s\n", sa_last_error());
     /* cell_signal_updateExpectations adds every term through the Hmm's own function (continuousHmm.c:147-149);
@@ -157,6 +193,14 @@ void getExpectationsUsingAnchors(StateMachine *sM, Hmm *hmmExpectations, Sequenc
         for (int64_t to = 0; to < 3; to++)
             hmmExpectations->addToTransitionExpectationFcn(hmmExpectations, from, to, res->transitions[from * 3 + to]);
     hmmExpectations->likelihood += res->likelihood[0];
+    if (sM->type == threeStateHdp && res->assignOffsets != NULL) {
+        /* the list holds POINTERS into the caller's sequences (continuousHmm.c:510-514), in the reference's order */
+        HdpHmm *hh = (HdpHmm *) hmmExpectations;
+        char *target = (char *) SsX->elements;
+        double *events = (double *) SsY->elements;
+        for (int64_t i = res->assignOffsets[0]; i < res->assignOffsets[1]; i++)
+            hh->addToAssignments(hh, target + res->assignKmerPos[i], events + (int64_t) res->assignEvent[i] * NB_EVENT_PARAMS);
+    }
     sa_result_free(res);
     free(an);
 }

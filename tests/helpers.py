@@ -182,4 +182,25 @@ def write_nhdp_file(path, alphabet, k, grid, post_pred_by_dp, slopes_by_dp, pare
         for table in (post_pred_by_dp, slopes_by_dp):
             for i in range(n):
                 f.write((fmt(table[i]) if i in table else "") + "\n")
-        f.write("\n")
+        # no factor lines: the density query never reads the factor tree, and deserialize_hdp (impl/hdp.c:3262-3318)
+        # takes every further line, blank ones included, for a factor
+
+
+def write_golden_hdp_files(dirname):
+    """The ACEGOT 6-mer .model / .nhdp pair of BASELINE config 2 rebuilt from the golden tables (model_r73_acegot,
+    hdp_single_level_fixed) in the reference's own text formats, for tests that run the REFERENCE's loaders where
+    /root/reference does not exist.  Single level: every kmer DP hangs off the root, DP id K."""
+    h = golden("hdp_single_level_fixed")
+    t = golden("model_r73_acegot")
+    own = h["own_row"]
+    K = len(own)
+    seen = np.nonzero(own >= 0)[0]
+    root_row = int(h["kmer_to_row"][own < 0][0])
+    pp = {int(k): h["post_pred"][own[k]] for k in seen}
+    sl = {int(k): h["slopes"][own[k]] for k in seen}
+    pp[K], sl[K] = h["post_pred"][root_row], h["slopes"][root_row]
+    model_file = os.path.join(dirname, "acegot.model")
+    nhdp_file = os.path.join(dirname, "single_level_fixed.nhdp")
+    write_model_file(model_file, str(t["alphabet"]), int(t["k"]), t["trans"], t["match"])
+    write_nhdp_file(nhdp_file, str(t["alphabet"]), int(t["k"]), h["grid"], pp, sl, [K] * K + [-1], seen)
+    return model_file, nhdp_file

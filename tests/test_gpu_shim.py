@@ -15,7 +15,8 @@ import sys
 import numpy as np
 import pytest
 
-from helpers import ROOT_DIR, compare_expectations, compare_pairs, golden, params_from, write_model_file
+from helpers import (ROOT_DIR, compare_expectations, compare_pairs, golden, params_from, write_golden_hdp_files,
+                     write_model_file)
 
 pytestmark = pytest.mark.gpu
 
@@ -28,16 +29,19 @@ sys.path.insert(0, sys.argv[1])
 from oracle import ref
 job = json.load(open(sys.argv[2]))
 z = np.load(job["inputs"])
-sm = ref.RefStateMachine(job["model"], kind=0)
+sm = ref.RefStateMachine(job["model"], kind=0, nhdp_file=job.get("nhdp"))
 sm.set_scaling(*job["scaling"])
-out = {}
+out = {"sm_type": np.array(sm.type)}
 for tag, par in job["params"].items():
     pairs, kmers, sec = sm.align(str(z["target"]), z["events"], z["anchors"], **par)
     out["pairs_" + tag] = pairs
     out["kmers_" + tag] = np.array(kmers)
-    tr, lik, _, _, _ = sm.expectations(str(z["target"]), z["events"], z["anchors"], **par)
+    epar = dict(par, **job.get("exp_params", {}).get(tag, {}))
+    tr, lik, ak, ae, _ = sm.expectations(str(z["target"]), z["events"], z["anchors"], **epar)
     out["tr_" + tag] = tr
     out["lik_" + tag] = np.array(lik)
+    out["ak_" + tag] = ak
+    out["ae_" + tag] = ae
 sagpu = ctypes.CDLL(os.path.join(sys.argv[1], "signalalign_b200", "libsagpu.so"))
 a, b, c = ctypes.c_int64(0), ctypes.c_int64(0), ctypes.c_int64(0)
 sagpu.sa_last_call_stats(ctypes.byref(a), ctypes.byref(b), ctypes.byref(c))
@@ -47,9 +51,9 @@ np.savez(job["out"], **out)
 """
 
 
-def _run_child(tmp_path, model_file, scaling, inputs, params):
+def _run_child(tmp_path, model_file, scaling, inputs, params, nhdp_file=None, exp_params=None):
     job = dict(model=model_file, scaling=[float(v) for v in scaling], inputs=os.path.join(str(tmp_path), "in.npz"),
-               params=params, out=os.path.join(str(tmp_path), "out.npz"))
+               params=params, out=os.path.join(str(tmp_path), "out.npz"), nhdp=nhdp_file, exp_params=exp_params or {})
     np.savez(job["inputs"], **inputs)
     with open(os.path.join(str(tmp_path), "job.json"), "w") as f:
         json.dump(job, f)
@@ -88,3 +92,26 @@ def test_reference_entry_points_run_on_the_gpu(tmp_path):
         assert compare_pairs(got4.astype(np.int32), want, params[tag]["threshold"]) <= 20, tag
         compare_expectations(out["tr_" + tag], float(out["lik_" + tag]), g["exp_transitions_" + tag],
                              float(g["exp_likelihood_" + tag]))
+
+
+@pytest.mark.skipif(not os.path.exists(GPU_LIB), reason="oracle/_ref/libsaref_gpu.so not built (needs /root/reference at build time)")
+def test_reference_hdp_machine_runs_on_the_gpu(tmp_path):
+    """StateMachine3_HDP through the struct: the reference's deserialize_nhdp builds the machine, the shim hands its
+    NanoporeHDP to libsagpu through serialize_nhdp, and pairs, transition sums and the (kmer, event) assignment list
+    match the unmodified reference (1217 pairs at 0.1: tests/stateMachineTests.c:902-918)."""
+    g = golden("zymo_hdp")
+    model_file, nhdp_file = write_golden_hdp_files(str(tmp_path))
+    par = _kw(params_from(g["params"]))
+    exp_thr = 0.01                                     # the golden expectations ran with the library defaults
+    out = _run_child(tmp_path, model_file, g["tparams"][:3], dict(target=g["target"], events=g["events"], anchors=g["anchors"]),
+                     dict(hdp=par), nhdp_file=nhdp_file, exp_params=dict(hdp=dict(threshold=exp_thr)))
+    assert bool(out["has_cpu_symbol"]) and int(out["gpu_launches_last_align"]) > 0
+    assert int(out["sm_type"]) == 7                    # threeStateHdp (inc/stateMachine.h:37-46)
+    t = golden("model_r73_acegot")
+    alphabet, k = str(t["alphabet"]), int(t["k"])
+    idx = np.array([sum(alphabet.index(c) * len(alphabet) ** (k - 1 - i) for i, c in enumerate(s)) for s in out["kmers_hdp"]], np.int64)
+    got4 = np.concatenate([out["pairs_hdp"], idx[:, None]], axis=1)
+    assert len(got4) == 1217
+    assert compare_pairs(got4.astype(np.int32), g["pairs"], par["threshold"]) <= 20
+    compare_expectations(out["tr_hdp"], float(out["lik_hdp"]), g["exp_transitions"], float(g["exp_likelihood"]))
+    assert np.array_equal(out["ak_hdp"], g["exp_assign_kmer"]) and np.array_equal(out["ae_hdp"], g["exp_assign_event"])

@@ -177,6 +177,13 @@ def test_nhdp_loader_and_density(tmp_path):
     model = sa.Model.load(mp, hp)
     g2, k2r, lpp, lsl, _ = model.hdp_tables()
     assert np.array_equal(g2, grid)   # linspace restated exactly (impl/hdp_math_utils.c:497-510)
+    # the shim's route: tables from the StateMachine struct, then the .nhdp attached (sa_model_attach_nhdp)
+    attached = sa.Model.from_tables("ACGT", 2, trans, table)
+    attached.attach_nhdp(hp)
+    for a, b in zip(attached.hdp_tables(), model.hdp_tables()):
+        assert np.array_equal(a, b)
+    with pytest.raises(RuntimeError):
+        attached.attach_nhdp(str(tmp_path / "absent.nhdp"))
     assert lpp.shape == (6, G)        # observed DPs: 0, 5, 7, 16, 17, 20
     resolve = {0: 0, 5: 5, 7: 7, 1: 16, 4: 17, 6: 17, 9: 20, 15: 20}
     pm = port.PortModel("ACGT", 2, trans, table, kind=port.EMIT_HDP, grid=g2, kmer_to_row=k2r, post_pred=lpp, slopes=lsl)
