@@ -57,7 +57,10 @@ struct CtaK {
     static constexpr int NH = W * C;         // hit-mask words per diagonal: [warp][cell]
     static constexpr int ROW = (HD ? 4 : 3) * NS + 2;   // doubles per stored forward row (HDP: + the emission plane)
     static constexpr int RN = 2 * NS;        // entries of the column / event rings
-    static constexpr double kExpZero = -746.0;   // exp() of anything below is exactly +0.0 (denormal minimum: e^-745.13)
+    // Expectation terms below e^-50 = 2e-22 are not evaluated: a read adds ~1e7 terms to sums of order 1..1e4 that are
+    // compared at 1e-6 relative (structural zeros: 1e-9 absolute).  The test is per WARP (__any_sync): on most diagonals
+    // the alignment path crosses only one of the CTA's warps, and the other skips all fourteen exp() of its two cells.
+    static constexpr double kExpZero = -50.0;
 
     struct Smem {
         double cst[5][RN];       // km, iM, cM, iY, cY per column (index = column & (RN - 1))
@@ -594,9 +597,9 @@ struct CtaK {
                     if (__any_sync(0xffffffffu, lower)) {
                         const double f0 = r1[sp], f1 = r1[NS + sp];
                         const double a0 = ((f0 + qX[j]) + cOX) - total, a1 = ((f1 + qX[j]) + cEX) - total;
-                        // exp(a) is exactly 0.0 below -745.2: such terms (and -inf) are skipped, NaN is not
-                        if (__any_sync(0xffffffffu, lower && !(a0 < kExpZero))) acc[1] += lower ? exp(a0) : 0.0;
-                        if (__any_sync(0xffffffffu, lower && !(a1 < kExpZero))) acc[3] += lower ? exp(a1) : 0.0;
+                        // terms below kExpZero (and -inf) are skipped, NaN is not
+                        if (__any_sync(0xffffffffu, lower && !(a0 < kExpZero))) acc[1] += lower ? sa_expSum(a0) : 0.0;
+                        if (__any_sync(0xffffffffu, lower && !(a1 < kExpZero))) acc[3] += lower ? sa_expSum(a1) : 0.0;
                         yxNaN |= lower && !(total > SA_NEG_INF);   // exp(-inf - total): NaN exactly when total is -inf
                     }
                     double pr[3] = {0.0, 0.0, 0.0};   // the three match terms (HDP: also the assignment test)
@@ -605,9 +608,9 @@ struct CtaK {
                         const double a0 = ((f0 + curM[j]) + (curE[j] + T[T_MATCH_CONTINUE])) - total;
                         const double a1 = ((f1 + curM[j]) + (curE[j] + T[T_MATCH_FROM_GAP_X])) - total;
                         const double a2 = ((f2 + curM[j]) + (curE[j] + T[T_MATCH_FROM_GAP_Y])) - total;
-                        if (__any_sync(0xffffffffu, middle && !(a0 < kExpZero))) { pr[0] = middle ? exp(a0) : 0.0; acc[0] += pr[0]; }
-                        if (__any_sync(0xffffffffu, middle && !(a1 < kExpZero))) { pr[1] = middle ? exp(a1) : 0.0; acc[2] += pr[1]; }
-                        if (__any_sync(0xffffffffu, middle && !(a2 < kExpZero))) { pr[2] = middle ? exp(a2) : 0.0; acc[4] += pr[2]; }
+                        if (__any_sync(0xffffffffu, middle && !(a0 < kExpZero))) { pr[0] = middle ? sa_expSum(a0) : 0.0; acc[0] += pr[0]; }
+                        if (__any_sync(0xffffffffu, middle && !(a1 < kExpZero))) { pr[1] = middle ? sa_expSum(a1) : 0.0; acc[2] += pr[1]; }
+                        if (__any_sync(0xffffffffu, middle && !(a2 < kExpZero))) { pr[2] = middle ? sa_expSum(a2) : 0.0; acc[4] += pr[2]; }
                     }
                     if (HD) {
                         pendA[j] = 0u;
@@ -623,8 +626,8 @@ struct CtaK {
                         const double f0 = r1[sl], f2 = r1[2 * NS + sl];
                         const double a0 = ((f0 + qY[j]) + (qE[j] + T[T_GAP_OPEN_Y])) - total;
                         const double a2 = ((f2 + qY[j]) + (qE[j] + T[T_GAP_EXTEND_Y])) - total;
-                        if (__any_sync(0xffffffffu, upper && !(a0 < kExpZero))) acc[5] += upper ? exp(a0) : 0.0;
-                        if (__any_sync(0xffffffffu, upper && !(a2 < kExpZero))) acc[6] += upper ? exp(a2) : 0.0;
+                        if (__any_sync(0xffffffffu, upper && !(a0 < kExpZero))) acc[5] += upper ? sa_expSum(a0) : 0.0;
+                        if (__any_sync(0xffffffffu, upper && !(a2 < kExpZero))) acc[6] += upper ? sa_expSum(a2) : 0.0;
                     }
                 }
                 if (HD) { pendValid = true; pendD = d2; pendS0 = bw & (NS - 1); }

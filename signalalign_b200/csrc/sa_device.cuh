@@ -56,3 +56,32 @@ __device__ __forceinline__ double sa_logAdd(double x, double y) {
     r = __dadd_rn(__dadd_rn(r, cb.y), lo);
     return far ? hi : r;
 }
+
+// exp() for the expectation sums (cell_signal_updateExpectations, impl/pairwiseAligner.c:914-944): every band cell adds
+// seven exp(f + b + eP + tP - total) terms, so the library exp() (about 35 instructions with its special-case branches)
+// was 45 % of the expectations kernel.  Here: n = rint(a log2 e) by the 1.5 * 2^52 shift, Cody-Waite reduction with a
+// two-word ln 2, degree-10 Taylor polynomial on |r| <= 0.347 (truncation 2.2e-13 relative), 2^n added into the exponent
+// field.  Results below the normal range (a < -708) are flushed to zero: each is < 1e-307 against sums >= 1e-3
+// (the parity bar on the sums is 1e-6 relative).  NaN, +inf and a > 700 take the library exp().
+__device__ __noinline__ double sa_expSlow(double a) { return exp(a); }
+__device__ __forceinline__ double sa_expSum(double a) {
+    if (!(a <= 700.0)) return sa_expSlow(a);
+    const double t = fma(a, 1.4426950408889634, 6755399441055744.0);
+    const int n = __double2loint(t);
+    const double nf = __dsub_rn(t, 6755399441055744.0);
+    double r = fma(nf, -6.93147180369123816490e-01, a);
+    r = fma(nf, -1.90821492927058770002e-10, r);
+    double p = 2.7557319223985893e-07;            // 1/10!
+    p = fma(p, r, 2.7557319223985888e-06);        // 1/9!
+    p = fma(p, r, 2.4801587301587302e-05);        // 1/8!
+    p = fma(p, r, 1.9841269841269841e-04);        // 1/7!
+    p = fma(p, r, 1.3888888888888889e-03);        // 1/6!
+    p = fma(p, r, 8.3333333333333332e-03);        // 1/5!
+    p = fma(p, r, 4.1666666666666664e-02);        // 1/4!
+    p = fma(p, r, 1.6666666666666666e-01);        // 1/3!
+    p = fma(p, r, 0.5);
+    p = fma(p, r, 1.0);
+    p = fma(p, r, 1.0);
+    const double v = __hiloint2double(__double2hiint(p) + (n << 20), __double2loint(p));
+    return a < -708.0 ? 0.0 : v;
+}

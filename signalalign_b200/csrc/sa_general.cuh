@@ -51,6 +51,7 @@ struct GParams {
     const int32_t *kmerToRow;
     // alignment parameters
     double threshold;
+    double logThrGate;    // log(threshold) - 1e-6: a cell whose f + b - total is below it cannot reach the threshold (no exp)
     int64_t minDiags, traceBack, expansion;
     // per-CTA scratch slab: [ring*3][3*maxDiagPC*3][2*maxWidth]
     double *scratch;
@@ -337,13 +338,27 @@ __device__ void g_totalProbability(const GCtx &c, int64_t d, int64_t top, double
     }
     __syncthreads();
     if (threadIdx.x == 0) {
-        double tot = SA_NEG_INF;
-        for (int32_t ci = 0; ci < g.W; ci++) tot = sa_logAdd(tot, c.vals[ci]);
-        if (hasMatch) {
-            double t2 = SA_NEG_INF;
-            for (int32_t ci = 0; ci < gb.W; ci++) t2 = sa_logAdd(t2, c.vals[c.P->maxWidth + ci]);
-            tot = sa_logAdd(tot, t2);
+        // The reference's sequential folds, both chains in flight.  In a band of at most 256 cells a value 7.6 or more
+        // below the running maximum is an exact no-op (the accumulator stays within 0.1 of that maximum: each logAdd
+        // returns at least max - 5e-4, and |x - y| >= 7.5 returns the larger operand unchanged), so it is skipped
+        // without touching the dependent chain — as the band kernel's fold does (sa_cta.cuh, orderedFold2).
+        const bool skipOk = g.W <= 256 && (!hasMatch || gb.W <= 256);
+        const int32_t nB = hasMatch ? gb.W : 0, nMax = g.W > nB ? g.W : nB;
+        const double *vb = c.vals + c.P->maxWidth;
+        double tot = SA_NEG_INF, t2 = SA_NEG_INF, mx = SA_NEG_INF, mx2 = SA_NEG_INF;
+        for (int32_t ci = 0; ci < nMax; ci++) {
+            if (ci < g.W) {
+                const double v = c.vals[ci];
+                if (!(skipOk && v <= mx - 7.6)) tot = sa_logAdd(tot, v);
+                mx = v > mx ? v : mx;
+            }
+            if (ci < nB) {
+                const double v = vb[ci];
+                if (!(skipOk && v <= mx2 - 7.6)) t2 = sa_logAdd(t2, v);
+                mx2 = v > mx2 ? v : mx2;
+            }
         }
+        if (hasMatch) tot = sa_logAdd(tot, t2);
         *sTotal = tot;
     }
     __syncthreads();
@@ -386,8 +401,8 @@ __device__ void g_posteriorDiag(const GCtx &c, int64_t d, double total, int64_t 
                 for (int32_t fp = 0; fp < nP; fp++)
                     for (int32_t bp = 0; bp < nP; bp++)
                         if (kC[fp] == kC[bp]) {
-                            double pp = exp(__dsub_rn(__dadd_rn(g_F(c, g, pc + fp)[0], g_B(c, d, pc + bp)[0]), total));
-                            if (pp >= c.P->threshold) cnt++;
+                            double v = __dsub_rn(__dadd_rn(g_F(c, g, pc + fp)[0], g_B(c, d, pc + bp)[0]), total);
+                            if (v >= c.P->logThrGate && exp(v) >= c.P->threshold) cnt++;
                         }
             }
         }
@@ -399,8 +414,9 @@ __device__ void g_posteriorDiag(const GCtx &c, int64_t d, double total, int64_t 
             for (int32_t fp = 0; fp < nP; fp++)
                 for (int32_t bp = 0; bp < nP; bp++)
                     if (kC[fp] == kC[bp]) {
-                        double pp = exp(__dsub_rn(__dadd_rn(g_F(c, g, pc + fp)[0], g_B(c, d, pc + bp)[0]), total));
-                        if (pp >= c.P->threshold) {
+                        double v = __dsub_rn(__dadd_rn(g_F(c, g, pc + fp)[0], g_B(c, d, pc + bp)[0]), total);
+                        double pp = v >= c.P->logThrGate ? exp(v) : 0.0;
+                        if (v >= c.P->logThrGate && pp >= c.P->threshold) {
                             if (pp > 1.0) pp = 1.0;
                             if (w < c.I->pairCap) {
                                 sa_pair_t o;
@@ -564,15 +580,18 @@ __global__ void __launch_bounds__(128) sa_general_kernel(const GParams P) {
                 int64_t tracedBackFrom = d - (atEnd ? 0 : P.traceBack + 1);
                 double total = SA_NEG_INF;
                 int64_t nPost = 0;
+                // One barrier interval per diagonal: b[d2] is complete at the top; the callback of d2 (reads f and
+                // b[d2], b[d2+1]) and the backward step INTO d2-1 (reads b[d2], b[d2+1]; writes the third slot of the
+                // 3-row backward ring) do not depend on each other.
                 for (int64_t d2 = d; d2 > tracedBackTo; d2--) {
                     __syncthreads();
-                    if (d2 < d) g_backwardDiag(c, d2, d);
-                    __syncthreads();
-                    if (d2 <= tracedBackFrom) {
-                        if (nPost++ % 10 == 0) {
-                            g_totalProbability(c, d2, d, &sTotal);
-                            total = sTotal;
-                        }
+                    const bool post = d2 <= tracedBackFrom;
+                    if (post && nPost++ % 10 == 0) {
+                        g_totalProbability(c, d2, d, &sTotal);
+                        total = sTotal;
+                    }
+                    if (d2 - 1 > tracedBackTo) g_backwardDiag(c, d2 - 1, d);
+                    if (post) {
                         if (EXPECT) {
                             likelihood += total;
                             g_expectationsDiag(c, d2, total, tracedBackTo, acc9, &nAssign, sWarp);

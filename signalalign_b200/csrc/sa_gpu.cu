@@ -921,7 +921,9 @@ static int prepareBatch(const sa_model_t *m, const sa_read_t *reads, int64_t nRe
         memcpy(g.trans, m->trans, sizeof(g.trans));
         g.kind = m->kind; g.A = m->A; g.suffixMod = m->K / m->A;
         g.G = m->G; g.grid = m->dev->grid; g.pp = m->dev->pp; g.slopes = m->dev->slopes; g.kmerToRow = m->dev->kmerToRow;
-        g.threshold = p->threshold; g.minDiags = p->minDiagsBetweenTraceBack; g.traceBack = p->traceBackDiagonals;
+        g.threshold = p->threshold;
+        g.logThrGate = p->threshold > 0 ? log(p->threshold) - 1e-6 : -INFINITY;
+        g.minDiags = p->minDiagsBetweenTraceBack; g.traceBack = p->traceBackDiagonals;
         g.expansion = p->diagonalExpansion;
         g.scratch = b->dGScratch.p; g.slabDoubles = slab; g.ringSize = ring; g.maxDiagPC = maxDiagPC; g.maxWidth = maxWidth;
         g.pairs = b->dPairs.p; g.pairCount = b->dPairCount.p; g.expOut = b->dExpOut.p;
@@ -1434,6 +1436,13 @@ static int alignPipelined(const sa_model_t *m, const sa_read_t *reads, int64_t n
     }
     r->pairs = sink.p;
     timer.lap("results fetched");
+    if (timer.on)   // device timeline of the chunks' kernels, relative to the first chunk's start
+        for (int64_t k = 0; k < nch; k++) {
+            float t0 = 0, t1 = 0;
+            cudaEventElapsedTime(&t0, bs[0]->ev[0], bs[k]->ev[0]);
+            cudaEventElapsedTime(&t1, bs[0]->ev[0], bs[k]->ev[3]);
+            fprintf(stderr, "[sa timing] align / chunk %lld kernels: start +%.1f ms, end +%.1f ms\n", (long long) k, t0, t1);
+        }
     *out = r;
     return SA_OK;
 }
