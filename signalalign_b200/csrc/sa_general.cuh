@@ -46,6 +46,10 @@ struct GParams {
     double trans[9];
     int32_t kind, A;
     int64_t suffixMod;    // A^(k-1)
+    // floor(n / A) and floor(n / suffixMod) for kmer indices n < 2^31 as a multiply and a shift (round-up magic numbers:
+    // M = ceil(2^sh / D), sh = 31 + ceil(log2 D)); path_checkLegal runs for every (path, neighbour path) pair of every cell
+    uint32_t divA_M, divS_M;
+    int32_t divA_sh, divS_sh;
     int64_t G;
     const double *grid, *pp, *slopes;
     const int32_t *kmerToRow;
@@ -132,7 +136,9 @@ __device__ __forceinline__ double g_gapX(const GCtx &c, int32_t ki) {
 }
 __device__ __forceinline__ bool g_legal(const GCtx &c, int32_t kq, int32_t kp) {  // path_checkLegal (:595-621)
     if (kq < 0 || kp < 0) return true;
-    return (kq % c.P->suffixMod) == (kp / c.P->A);
+    const uint32_t pre = (uint32_t) (((uint64_t) (uint32_t) kp * c.P->divA_M) >> c.P->divA_sh);   // kp / A
+    const uint32_t hi = (uint32_t) (((uint64_t) (uint32_t) kq * c.P->divS_M) >> c.P->divS_sh);    // kq / suffixMod
+    return (uint32_t) kq - hi * (uint32_t) c.P->suffixMod == pre;                                  // kq % suffixMod
 }
 
 // geometry of diagonal d of the current item

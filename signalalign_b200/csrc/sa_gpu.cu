@@ -920,6 +920,16 @@ static int prepareBatch(const sa_model_t *m, const sa_read_t *reads, int64_t nRe
         g.kt = m->dev->kt; g.gapX = m->dev->gapX;
         memcpy(g.trans, m->trans, sizeof(g.trans));
         g.kind = m->kind; g.A = m->A; g.suffixMod = m->K / m->A;
+        {
+            auto magic = [](uint64_t D, uint32_t *M, int32_t *sh) {
+                int l = 0;
+                while ((1ull << l) < D) l++;
+                *sh = 31 + l;
+                *M = (uint32_t) (((1ull << (31 + l)) + D - 1) / D);
+            };
+            magic((uint64_t) g.A, &g.divA_M, &g.divA_sh);
+            magic((uint64_t) g.suffixMod, &g.divS_M, &g.divS_sh);
+        }
         g.G = m->G; g.grid = m->dev->grid; g.pp = m->dev->pp; g.slopes = m->dev->slopes; g.kmerToRow = m->dev->kmerToRow;
         g.threshold = p->threshold;
         g.logThrGate = p->threshold > 0 ? log(p->threshold) - 1e-6 : -INFINITY;
@@ -1394,6 +1404,28 @@ static int alignPipelined(const sa_model_t *m, const sa_read_t *reads, int64_t n
     std::vector<std::unique_ptr<sa_batch>> bs;
     std::vector<int64_t> lo((size_t) nch + 1);
     for (int64_t k = 0; k <= nch; k++) lo[k] = nReads * k / nch;
+    if (const char *e = getenv("SA_CHUNK_FRACS")) {   // experiments: relative chunk sizes, e.g. "1,3,3,2"
+        std::vector<double> w;
+        for (const char *q = e; *q;) {
+            char *end = nullptr;
+            double v = strtod(q, &end);
+            if (end == q) break;
+            if (v > 0) w.push_back(v);
+            q = *end ? end + 1 : end;
+        }
+        if (!w.empty() && (int64_t) w.size() <= std::max<int64_t>(1, nReads)) {
+            nch = (int64_t) w.size();
+            lo.assign((size_t) nch + 1, 0);
+            double tot = 0, acc = 0;
+            for (double v : w) tot += v;
+            for (int64_t k = 0; k < nch; k++) {
+                acc += w[(size_t) k];
+                lo[(size_t) k + 1] = std::max<int64_t>(lo[(size_t) k] + 1, (int64_t) llround((double) nReads * acc / tot));
+            }
+            lo[(size_t) nch] = nReads;
+            for (int64_t k = nch - 1; k > 0; k--) lo[(size_t) k] = std::min(lo[(size_t) k], lo[(size_t) k + 1] - 1);
+        }
+    }
     int rc = SA_OK;
     for (int64_t k = 0; k < nch; k++) {
         sa_batch_t *b = nullptr;
