@@ -8,6 +8,7 @@ nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,power.limit --format=csv > g
 nproc > gpurun_out/${TAG}_nproc.txt
 python -m pytest tests -m gpu -x -q 2>&1 | tail -15 > gpurun_out/${TAG}_pytest.txt
 python -c "import __graft_entry__ as g; g.smoke(); print('smoke ok')" > gpurun_out/${TAG}_smoke.txt 2>&1
+[ -x tools/peak_fp ] || nvcc -O3 -gencode arch=compute_100a,code=sm_100a -o tools/peak_fp tools/peak_fp.cu
 tools/peak_fp > gpurun_out/${TAG}_peak_fp.jsonl 2>&1
 python bench.py --impl reference --steps 1 --warmup 0 > gpurun_out/${TAG}_bench_reference.json 2> gpurun_out/${TAG}_bench_reference.err
 python bench.py > gpurun_out/${TAG}_bench.json 2> gpurun_out/${TAG}_bench.err
