@@ -135,6 +135,7 @@ void sa_kmer_string(const sa_model_t *m, int64_t kmerIdx, char *out /* k+1 bytes
 
 /* ---------------------------------------------------------------------------------------------- device */
 int sa_gpu_init(int device);                 /* select device for this process/thread; SA_ERR_CUDA if none */
+int sa_gpu_shutdown(void);                   /* wait for the device; give cached pinned / pool memory back */
 const char *sa_last_error(void);
 /* host threads the packing passes of this process may use (default: OpenMP's, i.e. OMP_NUM_THREADS or all cores) */
 void sa_set_host_threads(int n);

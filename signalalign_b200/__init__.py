@@ -47,7 +47,7 @@ class SaResult(C.Structure):
 
 
 EXPORTS = [
-    "sa_model_load", "sa_model_from_tables", "sa_model_set_hdp", "sa_model_attach_nhdp",
+    "sa_gpu_shutdown", "sa_model_load", "sa_model_from_tables", "sa_model_set_hdp", "sa_model_attach_nhdp",
     "sa_model_set_hdp_expected_values",
     "sa_model_scale_noise", "sa_model_scale_model", "sa_model_free", "sa_model_num_kmers", "sa_model_kmer_length",
     "sa_model_alphabet", "sa_model_get_tables", "sa_model_hdp_density", "sa_params_default", "sa_ambig_load",
@@ -145,6 +145,10 @@ def _check(rc):
 
 def gpu_init(device=0):
     _check(lib().sa_gpu_init(device))
+
+
+def gpu_shutdown():
+    _check(lib().sa_gpu_shutdown())
 
 
 def default_params(**kw):

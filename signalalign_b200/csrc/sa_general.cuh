@@ -168,20 +168,40 @@ __device__ __forceinline__ double *g_B(const GCtx &c, int64_t d, int64_t pc) {
     return c.B + ((d % 3) * c.P->maxDiagPC + pc) * 3;
 }
 
+// Work is dealt out per PATH-CELL, not per cell: thread j of a diagonal takes the j-th (cell, path) pair, so a warp that
+// holds a multi-path column does not serialise that column's paths while its other lanes wait (the forward and backward
+// values of a path depend only on the neighbour cells, never on the sibling paths of the same cell).  The cell of
+// path-cell j is found by bisection over the column prefix; with `extra` paths beyond one per column in the diagonal the
+// bracket is extra + 1 columns wide (0 steps where the window holds no ambiguity code).
+__device__ __forceinline__ int32_t g_locate(const GCtx &c, const GDiag &g, int32_t base, int32_t nPC, int32_t j) {
+    const int32_t extra = nPC - g.W;
+    int32_t lo = j - extra > 0 ? j - extra : 0, hi = j < g.W - 1 ? j : g.W - 1;
+    while (lo < hi) {   // largest ci whose first path-cell is <= j
+        const int32_t mid = (lo + hi + 1) >> 1;
+        if (c.pathOff[g.x0 + mid] - base <= j) lo = mid;
+        else hi = mid - 1;
+    }
+    return lo;
+}
+
 __device__ void g_forwardDiag(const GCtx &c, int64_t d) {
     const double *T = c.P->trans;
+    const bool swX = T[T_GAP_SWITCH_TO_X] > SA_NEG_INF || T[T_GAP_SWITCH_TO_X] != T[T_GAP_SWITCH_TO_X];
     GDiag g = g_diag(c, d), g1 = g_diag(c, d - 1), g2 = g1;
     bool has2 = d >= 2;
     if (has2) g2 = g_diag(c, d - 2);
-    for (int32_t ci = threadIdx.x; ci < g.W; ci += blockDim.x) {
+    const int32_t pcBase = c.pathOff[g.x0], nPC = c.pathOff[g.x0 + g.W] - pcBase;
+    for (int32_t j = threadIdx.x; j < nPC; j += blockDim.x) {
+        const int32_t ci = g_locate(c, g, pcBase, nPC, j);
         int64_t xmy = (int64_t) g.L + 2 * ci;
         int32_t x = g.x0 + ci, y = g.y0 - ci, xl = 0, xm = 0, xu = 0;
-        int64_t pc = c.pathOff[x] - c.pathOff[g.x0];
+        int64_t pc = c.pathOff[x] - pcBase;
         int32_t nP = c.pathOff[x + 1] - c.pathOff[x];
         int64_t pl = g_cellPC(c, g1, xmy - 1, &xl), pu = g_cellPC(c, g1, xmy + 1, &xu);
         int64_t pm = has2 ? g_cellPC(c, g2, xmy, &xm) : -1;
         const int32_t *kC = c.pathKmer + c.pathOff[x];
-        for (int32_t p = 0; p < nP; p++) {
+        {
+            const int32_t p = j - (int32_t) pc;
             int32_t kp = kC[p];
             double M = SA_NEG_INF, X = SA_NEG_INF, Y = SA_NEG_INF;
             if (pl >= 0) {
@@ -193,7 +213,8 @@ __device__ void g_forwardDiag(const GCtx &c, int64_t d) {
                         const double *f = g_F(c, g1, pl + q);
                         X = sa_logAdd(X, __dadd_rn(f[0], __dadd_rn(eP, T[T_GAP_OPEN_X])));
                         X = sa_logAdd(X, __dadd_rn(f[1], __dadd_rn(eP, T[T_GAP_EXTEND_X])));
-                        X = sa_logAdd(X, __dadd_rn(f[2], __dadd_rn(eP, T[T_GAP_SWITCH_TO_X])));
+                        // GAP_SWITCH_TO_X is -inf in every model loaded from a .model file: logAdd(X, -inf) == X exactly
+                        if (swX) X = sa_logAdd(X, __dadd_rn(f[2], __dadd_rn(eP, T[T_GAP_SWITCH_TO_X])));
                     }
             }
             if (pm >= 0) {
@@ -226,20 +247,24 @@ __device__ void g_forwardDiag(const GCtx &c, int64_t d) {
 // b[d] for every cell by gathering from b[d+1] / b[d+2] (which exist up to the traceback start diagonal `top`)
 __device__ void g_backwardDiag(const GCtx &c, int64_t d, int64_t top) {
     const double *T = c.P->trans;
+    const bool swX = T[T_GAP_SWITCH_TO_X] > SA_NEG_INF || T[T_GAP_SWITCH_TO_X] != T[T_GAP_SWITCH_TO_X];
     GDiag g = g_diag(c, d), g1 = g, g2 = g;
     bool has1 = d + 1 <= top, has2 = d + 2 <= top;
     if (has1) g1 = g_diag(c, d + 1);
     if (has2) g2 = g_diag(c, d + 2);
-    for (int32_t ci = threadIdx.x; ci < g.W; ci += blockDim.x) {
+    const int32_t pcBase = c.pathOff[g.x0], nPC = c.pathOff[g.x0 + g.W] - pcBase;
+    for (int32_t j = threadIdx.x; j < nPC; j += blockDim.x) {   // one path-cell per thread (see g_locate)
+        const int32_t ci = g_locate(c, g, pcBase, nPC, j);
         int64_t xmy = (int64_t) g.L + 2 * ci;
         int32_t x = g.x0 + ci, y = g.y0 - ci, xa = 0, xu = 0, xl = 0;
-        int64_t pc = c.pathOff[x] - c.pathOff[g.x0];
+        int64_t pc = c.pathOff[x] - pcBase;
         int32_t nQ = c.pathOff[x + 1] - c.pathOff[x];
         int64_t pa = has2 ? g_cellPC(c, g2, xmy, &xa) : -1;       // (x+1, y+1): this cell is its "middle"
         int64_t pu = has1 ? g_cellPC(c, g1, xmy - 1, &xu) : -1;   // (x,   y+1): this cell is its "upper"
         int64_t pl = has1 ? g_cellPC(c, g1, xmy + 1, &xl) : -1;   // (x+1, y  ): this cell is its "lower"
         const int32_t *kZ = c.pathKmer + c.pathOff[x];
-        for (int32_t q = 0; q < nQ; q++) {
+        {
+            const int32_t q = j - (int32_t) pc;
             int32_t kq = kZ[q];
             double M = SA_NEG_INF, X = SA_NEG_INF, Y = SA_NEG_INF;
             if (pa >= 0) {
@@ -272,7 +297,7 @@ __device__ void g_backwardDiag(const GCtx &c, int64_t d, int64_t top) {
                         double a = g_B(c, d + 1, pl + p)[1];
                         M = sa_logAdd(M, __dadd_rn(a, __dadd_rn(eP, T[T_GAP_OPEN_X])));
                         X = sa_logAdd(X, __dadd_rn(a, __dadd_rn(eP, T[T_GAP_EXTEND_X])));
-                        Y = sa_logAdd(Y, __dadd_rn(a, __dadd_rn(eP, T[T_GAP_SWITCH_TO_X])));
+                        if (swX) Y = sa_logAdd(Y, __dadd_rn(a, __dadd_rn(eP, T[T_GAP_SWITCH_TO_X])));
                     }
             }
             double *o = g_B(c, d, pc + q);

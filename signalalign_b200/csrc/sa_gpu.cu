@@ -172,6 +172,25 @@ static bool pinRelease(void *p) {
 }
 // sa_result_free (sa_host.cpp): the pairs array of a result is a slab of this pool, D2H'ed into directly
 bool sa_pinned_release(void *p) { return pinRelease(p); }
+
+// Teardown for a long-lived host process (signalMachine itself just exits): waits for the device, gives the idle
+// page-locked slabs and the cached device pool memory back.  Results still held by the caller keep their slabs; models
+// and batches are freed by their own calls.  The library stays usable afterwards (caches refill on the next call).
+extern "C" int sa_gpu_shutdown(void) {
+    if (cudaDeviceSynchronize() != cudaSuccess) {
+        sa_set_error("sa_gpu_shutdown: %s", cudaGetErrorString(cudaGetLastError()));
+        return SA_ERR_CUDA;
+    }
+    {
+        std::lock_guard<std::mutex> lk(g_pinMu);
+        for (auto &sl : g_pins)
+            if (!sl.busy && sl.p) { cudaFreeHost(sl.p); sl.p = nullptr; sl.cap = 0; }
+    }
+    int dev = 0;
+    cudaMemPool_t pool;
+    if (cudaGetDevice(&dev) == cudaSuccess && cudaDeviceGetDefaultMemPool(&pool, dev) == cudaSuccess) cudaMemPoolTrimTo(pool, 0);
+    return SA_OK;
+}
 template <class T>
 struct PinVec {  // the few vector operations the packer needs, over pinned memory
     T *p = nullptr;

@@ -369,3 +369,27 @@ def test_pipelined_call_equals_single_batch():
     for o in outs[1:]:
         assert np.array_equal(o[0], outs[0][0]) and np.array_equal(o[1], outs[0][1]) and o[2:] == outs[0][2:]
     assert outs[0][0][12] == outs[0][0][11]     # the empty read has no pairs
+
+
+def test_uneven_chunks_and_shutdown_keep_results():
+    """Relative chunk sizes (SA_CHUNK_FRACS, the experiment knob of the pipelined call) do not change the result, and
+    sa_gpu_shutdown gives the cached pinned / pool memory back without breaking a result the caller still holds or the
+    next call."""
+    reads, table = synth.make_batch(17, seed=77, mean_len=600, min_len=200, max_len=1200, trim=0)
+    model = sa.Model.from_tables("ACGT", 6, synth.nanopore_transitions(), table)
+    p = sa.default_params(threshold=0.01, expansion=50, trace_back=50, min_diags=200)
+    rs = [sa_read(r) for r in reads]
+    base = sa.align_batch(model, rs, p)
+    want = (base.pair_offsets.copy(), base.pairs.copy())
+    for fr in ("5,1", "1,2,3", "1,1,1,1,1,1,1,1,1,1,1,1,1,1,1,1,1,1,1,1"):
+        os.environ["SA_CHUNK_FRACS"] = fr
+        try:
+            r = sa.align_batch(model, rs, p)
+        finally:
+            os.environ.pop("SA_CHUNK_FRACS", None)
+        assert np.array_equal(r.pair_offsets, want[0]) and np.array_equal(r.pairs, want[1]), fr
+        del r
+    sa.gpu_shutdown()
+    assert np.array_equal(base.pairs, want[1])          # the held result's slab survives the shutdown
+    again = sa.align_batch(model, rs, p)
+    assert np.array_equal(again.pair_offsets, want[0]) and np.array_equal(again.pairs, want[1])
