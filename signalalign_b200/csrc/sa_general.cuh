@@ -79,13 +79,10 @@ struct GCtx {
     int64_t ringMask;
 };
 
-// One copy of the emission code (four Gaussian kinds + the HDP spline, ~400 instructions with their FP64 divisions) instead
-// of one per call site: inlined eight times it pushed the kernel past 100 KB of SASS and the sweeps out of the 32 KB
-// instruction cache (ncu: no_instruction was the top stall reason, profiles/r1y_general.txt).
-struct GEmitCtx { const GParams *P; const GItem *I; };
-__device__ __noinline__ double g_emitImpl(const GParams *Pp, const GItem *Ip, int32_t ki, int64_t y, bool match) {
-    const GParams &P = *Pp;
-    GEmitCtx c{Pp, Ip};
+// (A non-inlined single copy of this function was tried against the instruction-cache stalls ncu shows: 5208 instead of
+// 6776 SASS instructions, but 122 registers instead of 96 and no gain — 2.44 against 2.53 GCUPS on the config-2 shape.)
+__device__ __forceinline__ double g_emit(const GCtx &c, int32_t ki, int64_t y, bool match) {
+    const GParams &P = *c.P;
     if (ki < 0) return SA_NEG_INF;  // NULL kmer of matrix column 0
     double mean = y > 0 ? P.evMean[c.I->evOff + y - 1] : SA_NEG_INF;  // NULLEVENT, pairwiseAligner.c:325
     const double *t = P.kt + (int64_t) ki * SA_KT_STRIDE + ((match || P.kind == SA_EMIT_HDP) ? 0 : 6);
@@ -133,10 +130,6 @@ __device__ __noinline__ double g_emitImpl(const GParams *Pp, const GItem *Ip, in
     double ln = __ddiv_rn(__dsub_rn(__dsub_rn(__dsub_rn(lnl, 1.8378770664093453), __dmul_rn(3.0, lnoise)),
                                     __ddiv_rn(__dmul_rn(__dmul_rn(nl, a2), a2), noise)), 2.0);
     return __dadd_rn(lp, ln);
-}
-
-__device__ __forceinline__ double g_emit(const GCtx &c, int32_t ki, int64_t y, bool match) {
-    return g_emitImpl(c.P, c.I, ki, y, match);
 }
 
 __device__ __forceinline__ double g_gapX(const GCtx &c, int32_t ki) {
@@ -555,11 +548,13 @@ __device__ void g_expectationsDiag(const GCtx &c, int64_t d, double total, int64
     }
 }
 
-#ifndef SA_GEN_MINB
-#define SA_GEN_MINB 1   // resident CTAs per SM the register allocation is held to (A/B knob)
+#ifdef SA_GEN_MINB   // A/B knob: resident CTAs per SM the register allocation is held to (default: ptxas' own choice, 96)
+#define SA_GEN_BOUNDS __launch_bounds__(128, SA_GEN_MINB)
+#else
+#define SA_GEN_BOUNDS __launch_bounds__(128)
 #endif
 template <bool EXPECT>
-__global__ void __launch_bounds__(128, SA_GEN_MINB) sa_general_kernel(const __grid_constant__ GParams P) {
+__global__ void SA_GEN_BOUNDS sa_general_kernel(const GParams P) {
     __shared__ int sItem;
     __shared__ double sTotal;
     __shared__ int sWarp[8];
