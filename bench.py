@@ -27,10 +27,13 @@ import numpy as np
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-WORKLOAD = "config3-synthetic: ~10k-event reads vs synthetic reference, ACGT 6-mer Gaussian table, -x 100, threshold 0.01"
+WORKLOAD = ("config3-synthetic: ~10k-event reads vs synthetic reference, ACGT 6-mer Gaussian table, -x 100, threshold 0.01, "
+            "guide anchors = match runs of geometric length 1/0.12 trimmed by 14 (SURVEY 8d)")
 EXPANSION, TRACE_BACK, MIN_DIAGS, THRESHOLD = 100, 50, 1000, 0.01
-# guide anchors: every kmer that owns an event, in runs of ~80 kmers separated by 1-5 dropped kmers
-GEN = dict(trim=0, block_mean=80)
+# guide anchors: SURVEY.md 8(d)'s generator (signalalign_b200/synth.py ANCHOR_PATTERNS); --anchors picks another pattern
+ANCHOR_PATTERN = "contract"
+from signalalign_b200.synth import ANCHOR_PATTERNS  # noqa: E402  (numpy only)
+GEN = dict(ANCHOR_PATTERNS[ANCHOR_PATTERN])
 
 
 def parse():

@@ -164,12 +164,16 @@ int sa_batch_prepare(const sa_model_t *m, const sa_read_t *reads, int64_t nReads
 int sa_batch_run(sa_batch_t *b);
 int sa_batch_fetch(sa_batch_t *b, sa_result_t **out);
 /* device time of the last sa_batch_run measured with CUDA events on the batch's stream (ms);
- * kernelMs[0] = CTA band kernel, 128- and 256-slot classes, [1] = CTA band kernel, 32- and 64-slot classes, [2] = general kernel;
+ * kernelMs[0] = wide band kernel + register-resident band kernel, 128- and 256-slot classes, [1] = register-resident band
+ * kernel, 32- and 64-slot classes, [2] = general kernel;
  * launches = #kernel launches of the run */
 int sa_batch_last_timing(const sa_batch_t *b, float *kernelMs3, int64_t *launches);
 int64_t sa_batch_band_cells(const sa_batch_t *b);
-/* how many work items each kernel handles: out[0] general kernel, out[1] CTA kernel 32/64 slots, out[2] CTA kernel 128/256 slots */
-void sa_batch_kernel_items(const sa_batch_t *b, int64_t *out3);
+/* how many work items each kernel handles: out[0] general kernel, out[1] register-resident band kernel 32/64 slots,
+ * out[2] the same, 128/256 slots (incl. latency class and split mode), out[3] wide band kernel (windows of 256 .. 4096 slots) */
+void sa_batch_kernel_items(const sa_batch_t *b, int64_t *out4);
+/* ... and the wide kernel's items by window class: out[0..4] = 256, 512, 1024, 2048, 4096 slots */
+void sa_batch_wide_items(const sa_batch_t *b, int64_t *out5);
 int64_t sa_batch_h2d_bytes(const sa_batch_t *b);
 int64_t sa_batch_d2h_bytes(const sa_batch_t *b);
 void sa_batch_free(sa_batch_t *b);

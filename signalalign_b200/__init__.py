@@ -53,7 +53,7 @@ EXPORTS = [
     "sa_model_alphabet", "sa_model_get_tables", "sa_model_hdp_density", "sa_params_default", "sa_ambig_load",
     "sa_ambig_free", "sa_result_free", "sa_kmer_string", "sa_gpu_init", "sa_last_error", "sa_gpu_device_count",
     "sa_gpu_align_batch", "sa_gpu_expectations_batch", "sa_batch_prepare", "sa_batch_run", "sa_batch_fetch",
-    "sa_batch_last_timing", "sa_batch_band_cells", "sa_batch_kernel_items", "sa_batch_h2d_bytes", "sa_batch_d2h_bytes", "sa_batch_free",
+    "sa_batch_last_timing", "sa_batch_band_cells", "sa_batch_kernel_items", "sa_batch_wide_items", "sa_batch_h2d_bytes", "sa_batch_d2h_bytes", "sa_batch_free",
     "sa_result_sum_expectations", "sa_debug_logadd", "sa_model_hdp_dims", "sa_model_get_hdp", "sa_debug_band",
     "sa_debug_split_points", "sa_debug_kmer_paths", "sa_last_call_stats", "sa_set_host_threads",
 ]
@@ -119,6 +119,7 @@ def lib():
         getattr(L, f).restype = C.c_int64
         getattr(L, f).argtypes = [C.c_void_p]
     L.sa_batch_kernel_items.argtypes = [C.c_void_p, c_i64p]
+    L.sa_batch_wide_items.argtypes = [C.c_void_p, c_i64p]
     L.sa_batch_free.argtypes = [C.c_void_p]
     L.sa_result_sum_expectations.argtypes = [C.POINTER(SaResult), c_f64p]
     L.sa_debug_logadd.argtypes = [c_f64p, c_f64p, c_f64p, C.c_int64]
@@ -436,9 +437,16 @@ class Batch:
 
     @property
     def kernel_items(self):
-        """(general, fast C=2, fast C=4) work-item counts"""
-        o = (C.c_int64 * 3)()
+        """work items by kernel: (general, band 32/64 slots, band 128/256 slots, wide)"""
+        o = (C.c_int64 * 4)()
         lib().sa_batch_kernel_items(self.h, o)
+        return tuple(o)
+
+    @property
+    def wide_items(self):
+        """work items of the wide band kernel by window class (256, 512, 1024, 2048, 4096 slots)"""
+        o = (C.c_int64 * 5)()
+        lib().sa_batch_wide_items(self.h, o)
         return tuple(o)
 
     @property

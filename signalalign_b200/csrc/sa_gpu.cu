@@ -16,6 +16,7 @@
 #include "sa_general.cuh"
 #include "sa_fast.cuh"
 #include "sa_cta.cuh"
+#include "sa_wide.cuh"
 
 #define CK(call)                                                                                   \
     do {                                                                                           \
@@ -267,6 +268,12 @@ struct DevBuf {
     ~DevBuf() { release(); }
 };
 
+// wide band kernel classes: window slots, threads per CTA (sa_wide.cuh)
+static const int kWideClasses = 5;
+static const int kWideNSW[kWideClasses] = {256, 512, 1024, 2048, 4096};
+static const int kWideNT[kWideClasses] = {128, 256, 512, 1024, 1024};
+static const size_t kSmemCap = 227 * 1024;
+
 // one work item = one sub-region of one read after getSplitPoints
 struct ItemRec {
     int64_t read, x1, y1, lX, lY;
@@ -277,7 +284,7 @@ struct ItemRec {
     int64_t pairOff = 0, pairCap = 0, assignOff = 0, assignCap = 0;
     int64_t cells = 0;        // band cells (integer band logic, same as the reference's)
     int64_t work = 0;         // path-cells
-    int kernel = 0;           // 0 general, 2 / 4 fast kernel with C cells per lane
+    int kernel = 0;           // 0 general; 1, 2, 4, 8 = warps of the register-resident band kernel; 100 + c = wide class c
     double scale, shift, var;
 };
 
@@ -341,7 +348,14 @@ struct sa_batch {
     FParams fp;
     int fBlocks[4] = {0, 0, 0, 0};
     int32_t fRows[4] = {1, 1, 1, 1};
-    bool warpKernel = false;
+    // wide kernel (sa_wide.cuh), classes by window size
+    std::vector<int32_t> wOrder[kWideClasses];
+    DevBuf<int32_t> dWOrder[kWideClasses];
+    DevBuf<double> dWRing[kWideClasses], dWFold[kWideClasses];
+    DevBuf<int4> dWHdr[kWideClasses];
+    int wBlocks[kWideClasses] = {0, 0, 0, 0, 0};
+    int32_t wRows[kWideClasses] = {1, 1, 1, 1, 1};
+    int64_t wRingDoubles[kWideClasses] = {0, 0, 0, 0, 0};
     bool oneCell = false;      // SA_CTA_C1: the 128-slot class with one cell per thread (A/B runs only)
     int64_t bandCells = 0, pathCells = 0, events = 0;
     int64_t h2dBytes = 0, d2hBytes = 0;
@@ -410,6 +424,29 @@ static void ctaLaunch(int c, bool oneCell, bool ex, bool hdp, int blocks, cudaSt
     else if (hdp) ctaLaunchT<false, true>(c, false, blocks, st, f);
     else if (ex) ctaLaunchT<true, false>(c, false, blocks, st, f);
     else ctaLaunchT<false, false>(c, oneCell, blocks, st, f);
+}
+
+// wide kernel: dynamic shared memory of a window class, occupancy and launch by (expectations, HDP) variant
+static size_t wideSmemBytes(bool hdp, bool ex, int NSW, bool foldInSmem) {
+    (void) hdp; (void) ex;
+    return WideK<false, false>::smemBytes(NSW, foldInSmem);
+}
+template <bool EX, bool HD>
+static int wideOccupancyT(int threads, size_t smem, int *bps) {
+    CK(cudaFuncSetAttribute(sa_wide_kernel<EX, HD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) kSmemCap));
+    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(bps, sa_wide_kernel<EX, HD>, threads, smem));
+    return SA_OK;
+}
+static int wideOccupancy(bool hdp, bool ex, int threads, size_t smem, int *bps) {
+    if (hdp && ex) return wideOccupancyT<true, true>(threads, smem, bps);
+    if (hdp) return wideOccupancyT<false, true>(threads, smem, bps);
+    return ex ? wideOccupancyT<true, false>(threads, smem, bps) : wideOccupancyT<false, false>(threads, smem, bps);
+}
+static void wideLaunch(bool hdp, bool ex, int blocks, int threads, size_t smem, cudaStream_t st, const FParams &f) {
+    if (hdp && ex) sa_wide_kernel<true, true><<<blocks, threads, smem, st>>>(f);
+    else if (hdp) sa_wide_kernel<false, true><<<blocks, threads, smem, st>>>(f);
+    else if (ex) sa_wide_kernel<true, false><<<blocks, threads, smem, st>>>(f);
+    else sa_wide_kernel<false, false><<<blocks, threads, smem, st>>>(f);
 }
 
 // readBase: index of reads[0] in the caller's array (error messages name the caller's read)
@@ -653,7 +690,7 @@ static int prepareBatch(const sa_model_t *m, const sa_read_t *reads, int64_t nRe
     if ((rc = b->dPathOff.upload(pathOff, st, &b->h2dBytes))) return rc;
     if ((rc = b->dPathKmer.upload(pathKmer, st, &b->h2dBytes))) return rc;
     if ((rc = b->dAnchors.upload(anchors32, st, &b->h2dBytes))) return rc;
-    if ((rc = b->dCounters.alloc(8, st))) return rc;
+    if ((rc = b->dCounters.alloc(16, st))) return rc;
 
     // output slots
     int64_t pairTotalCap = 0, assignTotalCap = 0;
@@ -730,6 +767,8 @@ static int prepareBatch(const sa_model_t *m, const sa_read_t *reads, int64_t nRe
             f.gridInvDx = 1.0 / f.gridDx;
             f.eX = -2.3025850929940455;     // stateMachine3HDP_cellCalculate's literal X-gap emission
         }
+        f.wPlanes = m->kind == SA_EMIT_HDP ? 4 : 3;
+        f.wAllFull = b->expectations ? 1 : 0;
         sa_geometry_kernel<<<(unsigned) n, 32, 0, st>>>(f);
         CK(cudaGetLastError());
         CK(cudaMemcpyAsync(geo.data(), b->dGeo.p, sizeof(FGeo) * n, cudaMemcpyDeviceToHost, st));
@@ -738,37 +777,49 @@ static int prepareBatch(const sa_model_t *m, const sa_read_t *reads, int64_t nRe
     }
     static const int kW[4] = {1, 2, 4, 8};
     const int64_t planes = m->kind == SA_EMIT_HDP ? 4 : 3;   // forward row = header + M, X, Y (+ the HDP log density)
-    const bool useWarpKernel = getenv("SA_WARP_KERNEL") != nullptr && !b->expectations;   // the superseded warp-per-read kernel (A/B runs only)
+    // Which band kernel: the register-resident one while three consecutive diagonals fit its widest window (254 columns)
+    // and the band never moves backwards; else the wide kernel, in the narrowest window class that holds them plus the
+    // slack of its emission rings (SA_WIDE_ONLY: every item, A/B runs); the general kernel only beyond 4096 slots.
+    const bool wideOnly = getenv("SA_WIDE_ONLY") != nullptr, noWide = getenv("SA_NO_WIDE") != nullptr;
+    int wideMax = kWideClasses;
+    while (wideMax > 0 && wideSmemBytes(m->kind == SA_EMIT_HDP, b->expectations, kWideNSW[wideMax - 1], false) > kSmemCap) wideMax--;
     for (int64_t i = 0; i < n; i++) {
         ItemRec &it = items[i];
         it.kernel = 0;
-        if (fastModel && it.maxP == 1 && geo[i].monotone) {
-            if (useWarpKernel) {
-                if (geo[i].maxSpan <= FastK<4>::NS - 4 - 1) it.kernel = 16;   // class 2 slot, warp kernel C = 4
-            } else {
+        if (fastModel && it.maxP == 1 && geo[i].nTb <= b->fItems[i].nTbCap) {
+            if (geo[i].monotone && !wideOnly)
                 for (int c = 0; c < 4 && !it.kernel; c++)
                     if (geo[i].maxSpan <= 32 * kW[c] - 2) it.kernel = kW[c];
-            }
+            if (!it.kernel && !noWide && (geo[i].maxSpan > 254 || wideOnly))
+                for (int c = 0; c < wideMax && !it.kernel; c++)
+                    if (geo[i].maxSpan + 24 <= kWideNSW[c]) it.kernel = 100 + c;
         }
         if (it.kernel) {
             it.cells = geo[i].cells;
             it.work = geo[i].cells;
             b->bandCells += it.cells;
             b->pathCells += it.cells;
-            int c = it.kernel == 16 ? 2 : (it.kernel == 1 ? 0 : it.kernel == 2 ? 1 : it.kernel == 4 ? 2 : 3);
+            if (it.kernel >= 100) {
+                const int c = it.kernel - 100;
+                b->wOrder[c].push_back((int32_t) i);
+                b->wRows[c] = std::max(b->wRows[c], geo[i].maxRows);
+                b->wRingDoubles[c] = std::max(b->wRingDoubles[c], geo[i].maxBlockDoubles + (int64_t) planes * geo[i].maxWidth);
+                continue;
+            }
+            int c = it.kernel == 1 ? 0 : it.kernel == 2 ? 1 : it.kernel == 4 ? 2 : 3;
             b->fOrder[c].push_back((int32_t) i);
             b->fRows[c] = std::max(b->fRows[c], geo[i].maxRows);
         }
     }
-    b->warpKernel = useWarpKernel;
     b->oneCell = getenv("SA_CTA_C1") != nullptr;
     auto byWork = [&](int32_t a, int32_t c) { return items[a].work > items[c].work; };
     for (int c = 0; c < 4; c++) std::stable_sort(b->fOrder[c].begin(), b->fOrder[c].end(), byWork);
+    for (int c = 0; c < kWideClasses; c++) std::stable_sort(b->wOrder[c].begin(), b->wOrder[c].end(), byWork);
     // Latency class.  A read is one CTA's sequential sweep (~2.3 us per diagonal on the two-cell mapping under load);
     // when that alone exceeds half of what the whole batch needs at full throughput (~30 GCUPS), the read decides the
     // makespan (heavy-tailed lengths, BASELINE config 5; batches smaller than the resident grid).  Those reads, at most
     // two per SM and longest first, go to the one-cell mapping, whose step is about half as long.
-    if (!useWarpKernel && !b->oneCell && !b->expectations && getenv("SA_NO_LATENCY_CLASS") == nullptr) {
+    if (!b->oneCell && !b->expectations && getenv("SA_NO_LATENCY_CLASS") == nullptr) {
         const double ideal = (double) b->bandCells * (double) chunkCount / 30e9;
         const char *ef = getenv("SA_LAT_FACTOR");
         const double latFactor = ef ? atof(ef) : 0.5;
@@ -844,19 +895,33 @@ static int prepareBatch(const sa_model_t *m, const sa_read_t *reads, int64_t nRe
             if (b->fOrder[c].empty()) continue;
             int bps = 1;
             int64_t rowD = 0, nIt = (int64_t) b->fOrder[c].size();
-            if (useWarpKernel) {
-                CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, sa_fast_kernel<4>, 128, 0));
-                b->fBlocks[c] = (int) std::min<int64_t>((int64_t) nSM * std::max(1, bps), (nIt + 3) / 4);
-                rowD = (int64_t) b->fBlocks[c] * 4 * b->fRows[c] * FastK<4>::ROW;
-            } else {
-                if ((rc = ctaOccupancy(c, b->oneCell, b->expectations, m->kind == SA_EMIT_HDP, &bps))) return rc;
-                b->fBlocks[c] = (int) std::min<int64_t>((int64_t) nSM * std::max(1, bps), nIt);
-                rowD = (int64_t) b->fBlocks[c] * b->fRows[c] * (planes * 32 * kW[c] + 2);
-            }
+            if ((rc = ctaOccupancy(c, b->oneCell, b->expectations, m->kind == SA_EMIT_HDP, &bps))) return rc;
+            b->fBlocks[c] = (int) std::min<int64_t>((int64_t) nSM * std::max(1, bps), nIt);
+            rowD = (int64_t) b->fBlocks[c] * b->fRows[c] * (planes * 32 * kW[c] + 2);
             need = std::max(need, rowD);
         }
         if ((rc = b->dFScratch.alloc((size_t) need, st))) return rc;
         f.scratch = b->dFScratch.p;
+    }
+    // wide kernel: per class a persistent grid, per CTA a ring of compact forward rows + a ring of row headers
+    for (int c = 0; c < kWideClasses; c++) {
+        if ((rc = b->dWOrder[c].upload(b->wOrder[c], st, &b->h2dBytes))) return rc;
+        if (b->wOrder[c].empty()) continue;
+        const bool hdp = m->kind == SA_EMIT_HDP;
+        const bool foldGlobal = wideSmemBytes(hdp, b->expectations, kWideNSW[c], true) > kSmemCap;
+        const size_t smem = wideSmemBytes(hdp, b->expectations, kWideNSW[c], !foldGlobal);
+        int bps = 1;
+        if ((rc = wideOccupancy(hdp, b->expectations, kWideNT[c], smem, &bps))) return rc;
+        b->wBlocks[c] = (int) std::min<int64_t>((int64_t) nSM * std::max(1, bps), (int64_t) b->wOrder[c].size());
+        b->wRows[c] += 4;
+        b->wRingDoubles[c] = (b->wRingDoubles[c] + 64 + 15) & ~(int64_t) 15;
+        if (b->wRingDoubles[c] > 0x7fffffffLL) {
+            sa_set_error("sa_batch_prepare: a traceback block needs %.1f GB of forward rows (band too wide)", b->wRingDoubles[c] * 8e-9);
+            return SA_ERR_INPUT;
+        }
+        if ((rc = b->dWRing[c].alloc((size_t) b->wBlocks[c] * b->wRingDoubles[c], st))) return rc;
+        if ((rc = b->dWHdr[c].alloc((size_t) b->wBlocks[c] * b->wRows[c], st))) return rc;
+        if (foldGlobal && (rc = b->dWFold[c].alloc((size_t) b->wBlocks[c] * 2 * kWideNSW[c], st))) return rc;
     }
 
     timer.lap("geometry pass + fast-kernel scratch");
@@ -975,7 +1040,7 @@ static int launchBatch(sa_batch_t *b) {
     cudaStream_t st = b->stream;
     CK(cudaStreamWaitEvent(st, b->evPrepared, 0));
     b->lastLaunches = 0;
-    CK(cudaMemsetAsync(b->dCounters.p, 0, 8 * sizeof(int32_t), st));
+    CK(cudaMemsetAsync(b->dCounters.p, 0, 16 * sizeof(int32_t), st));
     CK(cudaEventRecord(b->ev[0], st));
     const bool latStream = !b->latOrder.empty() || !b->splitOrder.empty();
     if (latStream) {                           // first, so that its CTAs are resident before the persistent grid fills the SMs
@@ -1011,7 +1076,19 @@ static int launchBatch(sa_batch_t *b) {
         CK(cudaGetLastError());
     }
     if (latStream) CK(cudaEventRecord(b->evJoin, b->lat));
-    for (int c = 3; c >= 0; c--) {             // widest class first; [ev0, ev1) = W >= 4, [ev1, ev2) = W <= 2
+    for (int c = kWideClasses - 1; c >= 0; c--) {   // wide kernel, widest window first (the heaviest items)
+        if (b->wOrder[c].empty()) continue;
+        const bool hdp = b->model->kind == SA_EMIT_HDP;
+        FParams f = b->fp;
+        f.order = b->dWOrder[c].p; f.nOrder = (int32_t) b->wOrder[c].size(); f.counter = b->dCounters.p + 8 + c;
+        f.wNSW = kWideNSW[c]; f.wRowsCap = b->wRows[c]; f.wRingDoubles = b->wRingDoubles[c];
+        f.scratch = b->dWRing[c].p; f.wHdr = b->dWHdr[c].p; f.wFold = b->dWFold[c].p;
+        wideLaunch(hdp, b->expectations, b->wBlocks[c], kWideNT[c],
+                   wideSmemBytes(hdp, b->expectations, kWideNSW[c], b->dWFold[c].p == nullptr), st, f);
+        b->lastLaunches++;
+        CK(cudaGetLastError());
+    }
+    for (int c = 3; c >= 0; c--) {             // widest class first; [ev0, ev1) = wide + W >= 4, [ev1, ev2) = W <= 2
         if (c == 1) {
             if (latStream) CK(cudaStreamWaitEvent(st, b->evJoin, 0));   // counted with the 128-slot class
             if (!b->splitOrder.empty()) CK(cudaStreamWaitEvent(st, b->evJoinSplit, 0));
@@ -1021,8 +1098,7 @@ static int launchBatch(sa_batch_t *b) {
         FParams f = b->fp;
         f.order = b->dFOrder[c].p; f.nOrder = (int32_t) b->fOrder[c].size(); f.counter = b->dCounters.p + c;
         f.rowsCap = b->fRows[c];
-        if (b->warpKernel) sa_fast_kernel<4><<<b->fBlocks[c], 128, 0, st>>>(f);
-        else ctaLaunch(c, b->oneCell, b->expectations, b->model->kind == SA_EMIT_HDP, b->fBlocks[c], st, f);
+        ctaLaunch(c, b->oneCell, b->expectations, b->model->kind == SA_EMIT_HDP, b->fBlocks[c], st, f);
         b->lastLaunches++;
         CK(cudaGetLastError());
     }
@@ -1089,7 +1165,10 @@ static int growAndRerun(sa_batch_t *b) {
         }
     }
     int rc;
-    if (!b->fOrder[0].empty() || !b->fOrder[1].empty() || !b->fOrder[2].empty() || !b->fOrder[3].empty()) {
+    bool anyBand = !b->latOrder.empty() || !b->splitOrder.empty();   // (latency-class / split items live in fItems too)
+    for (int c = 0; c < 4; c++) anyBand = anyBand || !b->fOrder[c].empty();
+    for (int c = 0; c < kWideClasses; c++) anyBand = anyBand || !b->wOrder[c].empty();
+    if (anyBand) {
         if ((rc = b->dFItems.upload(b->fItems, b->stream, &b->h2dBytes))) return rc;
         b->fp.items = b->dFItems.p;
     }
@@ -1362,6 +1441,11 @@ extern "C" void sa_batch_kernel_items(const sa_batch_t *b, int64_t *o) {
     o[0] = (int64_t) b->gOrder.size();
     o[1] = (int64_t) (b->fOrder[0].size() + b->fOrder[1].size());
     o[2] = (int64_t) (b->fOrder[2].size() + b->fOrder[3].size() + b->latOrder.size() + b->splitOrder.size());
+    o[3] = 0;
+    for (int c = 0; c < kWideClasses; c++) o[3] += (int64_t) b->wOrder[c].size();
+}
+extern "C" void sa_batch_wide_items(const sa_batch_t *b, int64_t *o) {
+    for (int c = 0; c < kWideClasses; c++) o[c] = (int64_t) b->wOrder[c].size();
 }
 extern "C" int64_t sa_batch_h2d_bytes(const sa_batch_t *b) { return b->h2dBytes; }
 extern "C" int64_t sa_batch_d2h_bytes(const sa_batch_t *b) { return b->d2hBytes; }

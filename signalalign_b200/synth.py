@@ -8,6 +8,17 @@ import numpy as np
 
 LOG_ZERO = -np.inf
 
+# Guide-anchor patterns (make_read's block_mean / trim).  "contract" is SURVEY.md §8(d)'s config-3 generator: 12 % of the
+# positions of the true diagonal start a 1-5 nt indel, i.e. match runs of geometric length 1 / 0.12, each trimmed by 14
+# on both sides (constraintDiagonalTrim, reference impl/pairwiseAligner.c:1624-1658, default :2029) — sparse anchors,
+# bands hundreds to thousands of cells wide.  "long_runs_trim14": match runs of ~80 (a guide alignment whose mismatches
+# stay inside M operations) with the same trim; "dense": round 1's pattern, every kmer that owns an event is an anchor.
+ANCHOR_PATTERNS = {
+    "contract": dict(trim=14, block_mean=1.0 / 0.12),
+    "long_runs_trim14": dict(trim=14, block_mean=80),
+    "dense": dict(trim=0, block_mean=80),
+}
+
 
 def nanopore_transitions():
     """3x3 transition probabilities in `.model` line-1 order -> the 9 log-transitions in StateMachine3 order.
