@@ -86,6 +86,8 @@ struct FParams {
     double *wFold;            // per-CTA 2 * wNSW doubles when the fold terms do not fit shared memory, else nullptr
     int32_t wPlanes;          // planes of a full stored row (3, HDP 4); geometry pass
     int32_t wAllFull;         // expectations: every row keeps all planes
+    int32_t wGeoAlways;       // size the wide kernel's row ring for every item, not only those wider than 254 columns
+    double *wRings;           // per-CTA 6 * wNSW doubles: emission rings of the window classes too large for shared memory
 };
 
 // ---------------------------------------------------------------------------------------------- band iterator
@@ -237,7 +239,7 @@ __global__ void __maxnreg__(40) sa_geometry_kernel(const FParams P) {
     g.nTb = __shfl_sync(0xffffffffu, g.nTb, 0);
     g.maxRows = __shfl_sync(0xffffffffu, g.maxRows, 0);
     g.monotone = __shfl_sync(0xffffffffu, g.monotone, 0);
-    if (g.maxSpan > 254 && g.nTb <= I.nTbCap) {
+    if ((g.maxSpan > 254 || P.wGeoAlways || !g.monotone) && g.nTb <= I.nTbCap) {
         __syncwarp();                          // lane 0's traceback list is visible to the warp
         int64_t need = 0;
         for (int32_t k = lane; k < g.nTb; k += 32) {

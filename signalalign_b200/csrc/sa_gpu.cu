@@ -272,7 +272,7 @@ struct DevBuf {
 static const int kWideClasses = 5;
 static const int kWideNSW[kWideClasses] = {256, 512, 1024, 2048, 4096};
 static const int kWideNT[kWideClasses] = {128, 256, 512, 1024, 1024};
-static const size_t kSmemCap = 227 * 1024;
+static const size_t kSmemCap = 227 * 1024 - 1024;   // opt-in shared memory per CTA minus the kernels' static part (logAdd table)
 
 // one work item = one sub-region of one read after getSplitPoints
 struct ItemRec {
@@ -351,7 +351,7 @@ struct sa_batch {
     // wide kernel (sa_wide.cuh), classes by window size
     std::vector<int32_t> wOrder[kWideClasses];
     DevBuf<int32_t> dWOrder[kWideClasses];
-    DevBuf<double> dWRing[kWideClasses], dWFold[kWideClasses];
+    DevBuf<double> dWRing[kWideClasses], dWFold[kWideClasses], dWRings[kWideClasses];
     DevBuf<int4> dWHdr[kWideClasses];
     int wBlocks[kWideClasses] = {0, 0, 0, 0, 0};
     int32_t wRows[kWideClasses] = {1, 1, 1, 1, 1};
@@ -427,27 +427,42 @@ static void ctaLaunch(int c, bool oneCell, bool ex, bool hdp, int blocks, cudaSt
 }
 
 // wide kernel: dynamic shared memory of a window class, occupancy and launch by (expectations, HDP) variant
-static size_t wideSmemBytes(bool hdp, bool ex, int NSW, bool foldInSmem) {
-    (void) hdp; (void) ex;
-    return WideK<false, false>::smemBytes(NSW, foldInSmem);
+// (gr: emission rings and fold terms in global memory — the 4096-slot class, whose DP state alone fills shared memory)
+static size_t wideSmemBytes(bool gr, int NSW, bool foldInSmem) {
+    return gr ? WideK<false, false, true>::smemBytes(NSW, false) : WideK<false, false, false>::smemBytes(NSW, foldInSmem);
 }
-template <bool EX, bool HD>
+template <bool EX, bool HD, bool GR>
 static int wideOccupancyT(int threads, size_t smem, int *bps) {
-    CK(cudaFuncSetAttribute(sa_wide_kernel<EX, HD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) kSmemCap));
-    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(bps, sa_wide_kernel<EX, HD>, threads, smem));
+    static size_t allowed = 0;   // (the attribute is per function and device; raised monotonically)
+    if (smem > 48 * 1024 && smem > allowed) {
+        CK(cudaFuncSetAttribute(sa_wide_kernel<EX, HD, GR>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) kSmemCap));
+        allowed = kSmemCap;
+    }
+    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(bps, sa_wide_kernel<EX, HD, GR>, threads, smem));
     return SA_OK;
 }
-static int wideOccupancy(bool hdp, bool ex, int threads, size_t smem, int *bps) {
-    if (hdp && ex) return wideOccupancyT<true, true>(threads, smem, bps);
-    if (hdp) return wideOccupancyT<false, true>(threads, smem, bps);
-    return ex ? wideOccupancyT<true, false>(threads, smem, bps) : wideOccupancyT<false, false>(threads, smem, bps);
+template <bool GR>
+static int wideOccupancyG(bool hdp, bool ex, int threads, size_t smem, int *bps) {
+    if (hdp && ex) return wideOccupancyT<true, true, GR>(threads, smem, bps);
+    if (hdp) return wideOccupancyT<false, true, GR>(threads, smem, bps);
+    return ex ? wideOccupancyT<true, false, GR>(threads, smem, bps) : wideOccupancyT<false, false, GR>(threads, smem, bps);
 }
-static void wideLaunch(bool hdp, bool ex, int blocks, int threads, size_t smem, cudaStream_t st, const FParams &f) {
-    if (hdp && ex) sa_wide_kernel<true, true><<<blocks, threads, smem, st>>>(f);
-    else if (hdp) sa_wide_kernel<false, true><<<blocks, threads, smem, st>>>(f);
-    else if (ex) sa_wide_kernel<true, false><<<blocks, threads, smem, st>>>(f);
-    else sa_wide_kernel<false, false><<<blocks, threads, smem, st>>>(f);
+static int wideOccupancy(bool gr, bool hdp, bool ex, int threads, size_t smem, int *bps) {
+    return gr ? wideOccupancyG<true>(hdp, ex, threads, smem, bps) : wideOccupancyG<false>(hdp, ex, threads, smem, bps);
 }
+template <bool GR>
+static void wideLaunchG(bool hdp, bool ex, int blocks, int threads, size_t smem, cudaStream_t st, const FParams &f) {
+    if (hdp && ex) sa_wide_kernel<true, true, GR><<<blocks, threads, smem, st>>>(f);
+    else if (hdp) sa_wide_kernel<false, true, GR><<<blocks, threads, smem, st>>>(f);
+    else if (ex) sa_wide_kernel<true, false, GR><<<blocks, threads, smem, st>>>(f);
+    else sa_wide_kernel<false, false, GR><<<blocks, threads, smem, st>>>(f);
+}
+static void wideLaunch(bool gr, bool hdp, bool ex, int blocks, int threads, size_t smem, cudaStream_t st, const FParams &f) {
+    if (gr) wideLaunchG<true>(hdp, ex, blocks, threads, smem, st, f);
+    else wideLaunchG<false>(hdp, ex, blocks, threads, smem, st, f);
+}
+// does the class keep its emission rings in global memory?
+static bool wideGlobalRings(int c) { return wideSmemBytes(false, kWideNSW[c], false) > kSmemCap; }
 
 // readBase: index of reads[0] in the caller's array (error messages name the caller's read)
 // chunkCount: how many sub-batches of this size the caller runs back to back (scales the latency-class decision)
@@ -769,6 +784,7 @@ static int prepareBatch(const sa_model_t *m, const sa_read_t *reads, int64_t nRe
         }
         f.wPlanes = m->kind == SA_EMIT_HDP ? 4 : 3;
         f.wAllFull = b->expectations ? 1 : 0;
+        f.wGeoAlways = getenv("SA_WIDE_ONLY") != nullptr ? 1 : 0;
         sa_geometry_kernel<<<(unsigned) n, 32, 0, st>>>(f);
         CK(cudaGetLastError());
         CK(cudaMemcpyAsync(geo.data(), b->dGeo.p, sizeof(FGeo) * n, cudaMemcpyDeviceToHost, st));
@@ -782,7 +798,7 @@ static int prepareBatch(const sa_model_t *m, const sa_read_t *reads, int64_t nRe
     // slack of its emission rings (SA_WIDE_ONLY: every item, A/B runs); the general kernel only beyond 4096 slots.
     const bool wideOnly = getenv("SA_WIDE_ONLY") != nullptr, noWide = getenv("SA_NO_WIDE") != nullptr;
     int wideMax = kWideClasses;
-    while (wideMax > 0 && wideSmemBytes(m->kind == SA_EMIT_HDP, b->expectations, kWideNSW[wideMax - 1], false) > kSmemCap) wideMax--;
+    while (wideMax > 0 && wideSmemBytes(true, kWideNSW[wideMax - 1], false) > kSmemCap) wideMax--;
     for (int64_t i = 0; i < n; i++) {
         ItemRec &it = items[i];
         it.kernel = 0;
@@ -908,10 +924,11 @@ static int prepareBatch(const sa_model_t *m, const sa_read_t *reads, int64_t nRe
         if ((rc = b->dWOrder[c].upload(b->wOrder[c], st, &b->h2dBytes))) return rc;
         if (b->wOrder[c].empty()) continue;
         const bool hdp = m->kind == SA_EMIT_HDP;
-        const bool foldGlobal = wideSmemBytes(hdp, b->expectations, kWideNSW[c], true) > kSmemCap;
-        const size_t smem = wideSmemBytes(hdp, b->expectations, kWideNSW[c], !foldGlobal);
+        const bool gr = wideGlobalRings(c);
+        const bool foldGlobal = gr || wideSmemBytes(false, kWideNSW[c], true) > kSmemCap;
+        const size_t smem = wideSmemBytes(gr, kWideNSW[c], !foldGlobal);
         int bps = 1;
-        if ((rc = wideOccupancy(hdp, b->expectations, kWideNT[c], smem, &bps))) return rc;
+        if ((rc = wideOccupancy(gr, hdp, b->expectations, kWideNT[c], smem, &bps))) return rc;
         b->wBlocks[c] = (int) std::min<int64_t>((int64_t) nSM * std::max(1, bps), (int64_t) b->wOrder[c].size());
         b->wRows[c] += 4;
         b->wRingDoubles[c] = (b->wRingDoubles[c] + 64 + 15) & ~(int64_t) 15;
@@ -922,6 +939,7 @@ static int prepareBatch(const sa_model_t *m, const sa_read_t *reads, int64_t nRe
         if ((rc = b->dWRing[c].alloc((size_t) b->wBlocks[c] * b->wRingDoubles[c], st))) return rc;
         if ((rc = b->dWHdr[c].alloc((size_t) b->wBlocks[c] * b->wRows[c], st))) return rc;
         if (foldGlobal && (rc = b->dWFold[c].alloc((size_t) b->wBlocks[c] * 2 * kWideNSW[c], st))) return rc;
+        if (gr && (rc = b->dWRings[c].alloc((size_t) b->wBlocks[c] * 6 * kWideNSW[c], st))) return rc;
     }
 
     timer.lap("geometry pass + fast-kernel scratch");
@@ -1082,9 +1100,10 @@ static int launchBatch(sa_batch_t *b) {
         FParams f = b->fp;
         f.order = b->dWOrder[c].p; f.nOrder = (int32_t) b->wOrder[c].size(); f.counter = b->dCounters.p + 8 + c;
         f.wNSW = kWideNSW[c]; f.wRowsCap = b->wRows[c]; f.wRingDoubles = b->wRingDoubles[c];
-        f.scratch = b->dWRing[c].p; f.wHdr = b->dWHdr[c].p; f.wFold = b->dWFold[c].p;
-        wideLaunch(hdp, b->expectations, b->wBlocks[c], kWideNT[c],
-                   wideSmemBytes(hdp, b->expectations, kWideNSW[c], b->dWFold[c].p == nullptr), st, f);
+        f.scratch = b->dWRing[c].p; f.wHdr = b->dWHdr[c].p; f.wFold = b->dWFold[c].p; f.wRings = b->dWRings[c].p;
+        const bool gr = wideGlobalRings(c);
+        wideLaunch(gr, hdp, b->expectations, b->wBlocks[c], kWideNT[c],
+                   wideSmemBytes(gr, kWideNSW[c], b->dWFold[c].p == nullptr), st, f);
         b->lastLaunches++;
         CK(cudaGetLastError());
     }

@@ -34,8 +34,10 @@
 #include "sa_fast.cuh"
 
 // EX: transition expectations + likelihood (diagonalCalculation_Expectations, reference impl/pairwiseAligner.c:1423-1443);
-// HD: HDP emission (stateMachine3HDP_cellCalculate: one kmer density for the match and the gap-Y state).
-template <bool EX, bool HD>
+// HD: HDP emission (stateMachine3HDP_cellCalculate: one kmer density for the match and the gap-Y state);
+// GR: the emission rings and the fold terms live in a per-CTA global-memory scratch (L1 / L2 resident) instead of shared
+//     memory — the 4096-slot window, whose DP state alone takes 192 KB.
+template <bool EX, bool HD, bool GR>
 struct WideK {
     static constexpr int BT = 256;             // band-table entries (diagonals per refill)
     static constexpr double kExpZero = -50.0;  // expectation terms below e^-50 are not evaluated (see sa_cta.cuh)
@@ -59,19 +61,22 @@ struct WideK {
     };
 
     static __host__ __device__ size_t smemBytes(int NSW, bool foldInSmem) {
-        size_t d = (size_t) 6 * NSW + 5 * NSW + NSW + (foldInSmem ? 2 * NSW : 0) + 2;   // doubles (+ sTotal, pad)
+        size_t d = (size_t) 6 * NSW + (GR ? 0 : 5 * NSW + NSW + (foldInSmem ? 2 * NSW : 0)) + 2;   // doubles (+ sTotal, pad)
         size_t b = d * 8;
         b += (size_t) (NSW / 32) * (2 * 8 + 2 * 4 + 2 * 4 + 6 * 4);   // cmax, candM, resetM, hitW
         b += (size_t) BT * 8 + 3 * (BT + 1) * 4 + 16;
         return b;
     }
-    static __device__ __forceinline__ void carve(Sm &S, double *base, int NSW, double *foldGlobal) {
+    static __device__ __forceinline__ void carve(Sm &S, double *base, int NSW, double *foldGlobal, double *ringsGlobal) {
         S.NSW = NSW; S.mask = NSW - 1; S.nCh = NSW / 32;
         double *p = base;
         S.st = p; p += 6 * NSW;
-        S.cst = p; p += 5 * NSW;
-        S.evs = p; p += NSW;
-        if (foldGlobal) S.foldv = foldGlobal; else { S.foldv = p; p += 2 * NSW; }
+        if (GR) { S.cst = ringsGlobal; S.evs = ringsGlobal + 5 * NSW; S.foldv = foldGlobal; }
+        else {
+            S.cst = p; p += 5 * NSW;
+            S.evs = p; p += NSW;
+            if (foldGlobal) S.foldv = foldGlobal; else { S.foldv = p; p += 2 * NSW; }
+        }
         S.sTotal = p; p += 2;
         S.cmax = reinterpret_cast<float2 *>(p); p += 2 * S.nCh;
         unsigned *u = reinterpret_cast<unsigned *>(p);
@@ -831,13 +836,14 @@ struct WideK {
 
 // Persistent grid, items pulled heaviest-first from an atomic queue.  Launch: blockDim = threads of the class, dynamic
 // shared memory = WideK::smemBytes(P.wNSW, P.wFold == nullptr).
-template <bool EX, bool HD>
+template <bool EX, bool HD, bool GR>
 __global__ void __launch_bounds__(1024, 1) sa_wide_kernel(const __grid_constant__ FParams P) {
     extern __shared__ __align__(16) double sa_wsm[];
-    typename WideK<EX, HD>::Sm S;
-    WideK<EX, HD>::carve(S, sa_wsm, P.wNSW, P.wFold ? P.wFold + (int64_t) blockIdx.x * 2 * P.wNSW : nullptr);
+    typename WideK<EX, HD, GR>::Sm S;
+    WideK<EX, HD, GR>::carve(S, sa_wsm, P.wNSW, P.wFold ? P.wFold + (int64_t) blockIdx.x * 2 * P.wNSW : nullptr,
+                             GR ? P.wRings + (int64_t) blockIdx.x * 6 * P.wNSW : nullptr);
     sa_logAdd_init();
-    typename WideK<EX, HD>::Rows RW;
+    typename WideK<EX, HD, GR>::Rows RW;
     RW.ring = P.scratch + (int64_t) blockIdx.x * P.wRingDoubles;
     RW.hdr = P.wHdr + (int64_t) blockIdx.x * P.wRowsCap;
     RW.cap = P.wRowsCap;
@@ -849,6 +855,6 @@ __global__ void __launch_bounds__(1024, 1) sa_wide_kernel(const __grid_constant_
         const int n = S.sInt[0];
         if (n >= P.nOrder) break;
         const int it = P.order[n];
-        WideK<EX, HD>::run(P, P.items[it], it, S, RW);
+        WideK<EX, HD, GR>::run(P, P.items[it], it, S, RW);
     }
 }

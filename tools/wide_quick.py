@@ -27,6 +27,7 @@ for i in range(3):
     b.run()
     m, _ = b.timing()
     ms.append(sum(m))
+    out.setdefault('ms_split', []).append([round(v, 1) for v in m])
 res = b.fetch()
 out["ms"] = ms
 out["gcups"] = cells / (min(ms) * 1e-3) / 1e9
