@@ -49,7 +49,13 @@ def parse():
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-expectations", action="store_true", help="skip the config-4 (expectations) figure")
     ap.add_argument("--seed", type=int, default=20261104)
-    return ap.parse_args()
+    ap.add_argument("--anchors", default=ANCHOR_PATTERN, choices=sorted(ANCHOR_PATTERNS),
+                    help="guide-anchor pattern of the synthetic reads (default: SURVEY 8d's)")
+    ap.add_argument("--no-dense", action="store_true", help="skip the secondary figure on round 1's dense anchor pattern")
+    a = ap.parse_args()
+    GEN.clear()
+    GEN.update(ANCHOR_PATTERNS[a.anchors])
+    return a
 
 
 # ------------------------------------------------------------------------------------------------ CPU arms
@@ -217,7 +223,8 @@ def main():
     # ---- resident arm: inputs in HBM before the timed region
     batch = sa.Batch(model, reads, p)
     cells = batch.band_cells
-    kernel_items = batch.kernel_items
+    kernel_items, wide_items = batch.kernel_items, batch.wide_items
+    n_diag = sum(len(r.target) - 5 + r.events.shape[0] + 1 for r in reads)
     for _ in range(a.warmup):
         batch.run()
     sampler = ClockSampler(local_rank)
@@ -243,6 +250,27 @@ def main():
     n_pairs = int(res.pair_offsets[-1])
     pairs_digest = [int(res.pairs[:, c].astype(np.int64).sum()) for c in range(4)]   # p, x, y, kmer column sums
     batch.close()
+
+    # ---- secondary, labelled: the same resident measurement on round 1's dense anchor pattern (every kmer an anchor)
+    dense = None
+    if not a.no_dense and a.anchors != "dense":
+        dn = max(148, a.reads // 4)
+        dreads_d, _ = synth.make_batch(dn, seed=a.seed + 1000 * rank + 7, table=table, **ANCHOR_PATTERNS["dense"])
+        dreads = [sa.Read(r["target"], r["events"], r["anchors"], r["scale"], r["shift"], r["var"]) for r in dreads_d]
+        db = sa.Batch(model, dreads, p)
+        db.run()
+        dms = []
+        for _ in range(2):
+            flush.fill_(1)
+            torch.cuda.synchronize()
+            db.run()
+            dms.append(sum(db.timing()[0]))
+        dense = {"anchor_pattern": "dense (trim 0, runs of ~80): round 1's workload", "reads": dn,
+                 "gcups": db.band_cells / (min(dms) * 1e-3) / 1e9,
+                 "events_per_s": sum(r.events.shape[0] for r in dreads) / (min(dms) * 1e-3),
+                 "work_items_by_kernel": dict(zip(("general", "band_32_64", "band_128_256", "wide"), db.kernel_items))}
+        db.close()
+        del dreads, dreads_d
 
     # ---- end-to-end arm: host buffers -> C-ABI call -> host result (pack + H2D + kernels + D2H timed)
     e2e_t = []
@@ -320,7 +348,7 @@ def main():
         # measured DRAM traffic of the kernel (one ncu --set full capture, profiles/): bytes per band cell x this launch's cells
         traffic = None
         try:
-            traffic = json.load(open(os.path.join(ROOT, "profiles", "r1_dram_per_cell.json")))["bytes_per_cell"] * cells
+            traffic = json.load(open(os.path.join(ROOT, "profiles", "r2_dram_per_cell.json")))[a.anchors]["bytes_per_cell"] * cells
         except Exception:
             pass
         sm_mhz = (clocks or {}).get("sm_mhz") or 1965.0
@@ -339,37 +367,42 @@ def main():
             "metric": "events_aligned_per_sec", "value": events_all / (step_ms_max * 1e-3), "unit": "events/s",
             "n_gpus": world, "steps": a.steps, "warmup": a.warmup, "ms_per_step": step_ms_max,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "reads_per_gpu_per_step": a.reads, "host_threads_per_rank": host_threads, "events_per_step": events_all,
+            "config": {"workload": WORKLOAD if a.anchors == ANCHOR_PATTERN else "config3-synthetic, anchor pattern " + a.anchors,
+                       "anchor_pattern": {"name": a.anchors, **ANCHOR_PATTERNS[a.anchors]},
+                       "mean_band_width_rank0": cells / n_diag, "dense_pattern_rank0": dense,
+                       "reads_per_gpu_per_step": a.reads, "host_threads_per_rank": host_threads, "events_per_step": events_all,
                        "band_cells_per_step": cells_all, "l2": "flushed between steps (256 MiB write) and inputs > L2",
                        "aligned_pairs_rank0": n_pairs, "pairs_column_sums_rank0": pairs_digest,
                        "expectations_e2e_rank0": None if exp_s is None else {
                            "call": "sa_gpu_expectations_batch (config 4 shape: same reads)", "events_per_s": events / exp_s,
                            "gcups": cells / exp_s / 1e9, "ms": 1e3 * exp_s,
                            "allreduce_ms": exp_ar_ms, "table_all_ranks": [float(v) for v in exp_table]},
-                       "kernel_ms_rank0": {"cta_128_256_slots": float(np.mean([m[0] for m in all_ms])),
-                                           "cta_32_64_slots": float(np.mean([m[1] for m in all_ms])),
+                       "kernel_ms_rank0": {"wide_and_band_128_256_slots": float(np.mean([m[0] for m in all_ms])),
+                                           "band_32_64_slots": float(np.mean([m[1] for m in all_ms])),
                                            "general": float(np.mean([m[2] for m in all_ms]))},
-                       "work_items_by_kernel_rank0": {"general": kernel_items[0], "cta_32_64_slots": kernel_items[1],
-                                                      "cta_128_256_slots": kernel_items[2]}},
+                       "work_items_by_kernel_rank0": {"general": kernel_items[0], "band_32_64_slots": kernel_items[1],
+                                                      "band_128_256_slots": kernel_items[2], "wide": kernel_items[3],
+                                                      "wide_by_window": dict(zip(("256", "512", "1024", "2048", "4096"), wide_items))}},
             "gcups": cells_all / (step_ms_max * 1e-3) / 1e9,
             "gpu_launches": launches,
             "clocks": clocks,
             "e2e": {"value": events_all / e2e_max, "unit": "events/s", "h2d_bytes_per_step": int(h2d),
                     "d2h_bytes_per_step": int(d2h), "gcups": cells_all / e2e_max / 1e9,
                     "ms_each_call_rank0": [round(1e3 * t, 1) for t in e2e_t]},
-            "roofline": {"bound": "hbm", "achieved": achieved_gbs, "peak": hbm_peak, "unit": "GB/s",
-                         "frac": achieved_gbs / hbm_peak, "traffic": traffic, "algorithmic_bytes": alg_bytes_per_cell * cells,
-                         "peak_source": peak_src,
-                         "note": "kernel is FP64-issue bound, not HBM bound: see roofline_compute"},
-            "roofline_compute": {"bound": "fp64_pipe", "achieved": cells * fp64_per_cell / (float(np.mean(kern_ms)) * 1e-3),
-                                 "peak": fp64_peak, "peak_source": fp64_src, "unit": "FP64 lane-instr/s",
-                                 "frac": cells * fp64_per_cell / (float(np.mean(kern_ms)) * 1e-3) / fp64_peak,
-                                 "per_cell": fp64_per_cell, "clock_mhz": sm_mhz},
+            # the binding roofline of the band kernels is the FP64 pipe; HBM is the secondary object
+            "roofline": {"bound": "fp64_pipe", "achieved": cells * fp64_per_cell / (float(np.mean(kern_ms)) * 1e-3),
+                         "peak": fp64_peak, "peak_source": fp64_src, "unit": "FP64 lane-instr/s",
+                         "frac": cells * fp64_per_cell / (float(np.mean(kern_ms)) * 1e-3) / fp64_peak,
+                         "per_cell": fp64_per_cell, "clock_mhz": sm_mhz, "traffic": traffic,
+                         "note": "not a contraction (no tensor cores) and not HBM bound: FP64 cubic logAdd, see roofline_hbm"},
+            "roofline_hbm": {"bound": "hbm", "achieved": achieved_gbs, "peak": hbm_peak, "unit": "GB/s",
+                             "frac": achieved_gbs / hbm_peak, "traffic": traffic, "algorithmic_bytes": alg_bytes_per_cell * cells,
+                             "peak_source": peak_src},
             "wall_s_resident_loop": wall_resident,
         }
         if world == 1 and not a.no_cpu:
             cores = os.cpu_count() or 1
-            n = a.cpu_reads or min(4 * cores, len(reads_d))
+            n = a.cpu_reads or min(cores, len(reads_d))
             kind, wall, ev, used = cpu_arm(reads_d[:n], table, cores)
             out["cpu_baseline"] = {"value": ev / wall, "unit": "events/s", "cores": used, "kind": kind,
                                    "sample": f"first {n} reads of the step's batch, one process per core, {wall:.1f} s"}
