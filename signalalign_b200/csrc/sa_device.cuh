@@ -12,49 +12,53 @@
 #define SA_NEG_INF (__longlong_as_double(0xfff0000000000000LL))
 
 // The reference's four cubics for log(1 + e^x) on [0,1], (1,2.5], (2.5,4.5], (4.5,7.5): FLOAT literals promoted
-// to double (impl/pairwiseAligner.c:305-311).  They live in a 512-byte shared-memory table with one row (c3 c2 c1 c0)
-// per value of n = ceil(2 |x - y|) = 0..15: the range tests d > 1, d > 2.5, d > 4.5 are exactly n >= 3, n >= 6, n >= 10
-// (2 d is exact and the thresholds are half-integers), so ONE F2I.F64.CEIL replaces three DSETP and the predicate
-// arithmetic, and a logAdd fetches its coefficients with two conflict-free LDS.128.  Every kernel calls
-// sa_logAdd_init() once per CTA.
-__shared__ __align__(16) double sa_lt[64];
+// to double (impl/pairwiseAligner.c:305-311).  They live in a shared-memory table with one row (c3 c2 c1 c0) per value of
+// n = ceil(2 |x - y|) = 0..15: the range tests d > 1, d > 2.5, d > 4.5 are exactly n >= 3, n >= 6, n >= 10 (2 d is exact
+// and the thresholds are half-integers), so one DFMA replaces three DSETP and the predicate arithmetic, and a logAdd
+// fetches its coefficients with two conflict-free LDS.128.  Row 16 is all zeros: the "far" case (|x - y| >= 7.5, or an
+// operand -inf) evaluates 0 + max(x, y) through the same instructions.  Every kernel calls sa_logAdd_init() once per CTA.
+__shared__ __align__(16) double sa_lt[68];
 
 __device__ __forceinline__ void sa_logAdd_init() {
     const float c[16] = {-0.009350833524763f, 0.130659527668286f, 0.498799810682272f, 0.693203116424741f,
                          -0.014532321752540f, 0.139942324101744f, 0.495635523139337f, 0.692140569840976f,
                          -0.004605031767994f, 0.063427417320019f, 0.695956496475118f, 0.514272634594009f,
                          -0.000458661602210f, 0.009695946122598f, 0.930734667215156f, 0.168037164329057f};
-    for (int i = threadIdx.x; i < 64; i += blockDim.x) {
+    for (int i = threadIdx.x; i < 68; i += blockDim.x) {
         const int n = i >> 2, range = (n >= 3) + (n >= 6) + (n >= 10), k = range * 4 + (i & 3);
         float v = c[0];
 #pragma unroll
         for (int q = 1; q < 16; q++) v = k == q ? c[q] : v;
-        sa_lt[i] = (double) v;
+        sa_lt[i] = n >= 16 ? 0.0 : (double) v;
     }
     __syncthreads();
 }
 
 // logAdd (impl/pairwiseAligner.c:314-318): max when either operand is -inf or |x-y| >= 7.5, else
-// min + lookup(|x-y|), Horner without contraction.  Branch-free.
+// min + lookup(|x-y|), Horner without contraction.  Branch-free, 19 instructions:
+//   * far = |diff| >= 7.5, +inf (one operand -inf) or NaN (both -inf), decided on the HIGH WORD of |diff| as an integer
+//     (7.5 = 0x401E0000 00000000: the low word cannot matter);
+//   * ONE two-word select picks the operand the polynomial is added to: the larger one when far (the zero row then adds
+//     +0, which is exact), the smaller one otherwise;
+//   * the polynomial's argument is |diff| with its high word clamped to that of 8.0, so that it stays finite in the far case
+//     (0 * inf would be NaN); for |diff| < 7.5 the clamp is the identity.
 __device__ __forceinline__ double sa_logAdd(double x, double y) {
     const double diff = __dsub_rn(x, y);
-    const bool xlt = __double2hiint(diff) < 0;     // x < y  (diff == +0 when equal; NaN only when both are -inf)
-    const double hi = xlt ? y : x;
-    const double lo = xlt ? x : y;
-    const double d = fabs(diff);                   // folded into the consumers as an operand modifier
-    // |diff| >= 7.5, |diff| == inf (one operand -inf) and NaN (both -inf): the cubic's result is discarded
-    const bool far = !(d < 7.5);
-    // n = ceil(2 d), clamped into the table: 2 d + 2^52 rounded UP leaves ceil(2 d) in the low mantissa word (one DFMA on
-    // the FP64 pipe instead of DADD + F2I on the XU pipe).  For d >= 2^31, inf and NaN the word is arbitrary, but those
-    // are `far` and the cubic is discarded; the unsigned clamp keeps the table index in range.
-    const unsigned n = umin((unsigned) __double2loint(__fma_ru(d, 2.0, 4503599627370496.0)), 15u);
+    const int dh = __double2hiint(diff);
+    const unsigned ah = (unsigned) dh & 0x7fffffffu;
+    const bool far = ah >= 0x401E0000u;
+    const bool xlt = dh < 0;                       // x < y  (diff == +0 when equal)
+    const double base = (far == xlt) ? y : x;      // far: max(x, y); else min(x, y)
+    const double d = __hiloint2double((int) umin(ah, 0x40200000u), __double2loint(diff));
+    // n = ceil(2 d): 2 d + 2^52 rounded UP leaves it in the low mantissa word (one DFMA on the FP64 pipe)
+    unsigned n = (unsigned) __double2loint(__fma_ru(d, 2.0, 4503599627370496.0));
+    n = far ? 16u : n;
     const double2 ca = *reinterpret_cast<const double2 *>(sa_lt + 4 * n);
     const double2 cb = *reinterpret_cast<const double2 *>(sa_lt + 4 * n + 2);
     double r = __dmul_rn(ca.x, d);
     r = __dmul_rn(__dadd_rn(r, ca.y), d);
     r = __dmul_rn(__dadd_rn(r, cb.x), d);
-    r = __dadd_rn(__dadd_rn(r, cb.y), lo);
-    return far ? hi : r;
+    return __dadd_rn(__dadd_rn(r, cb.y), base);
 }
 
 // exp() for the expectation sums (cell_signal_updateExpectations, impl/pairwiseAligner.c:914-944): every band cell adds

@@ -819,7 +819,7 @@ static int prepareBatch(const sa_model_t *m, const sa_read_t *reads, int64_t nRe
                 const int c = it.kernel - 100;
                 b->wOrder[c].push_back((int32_t) i);
                 b->wRows[c] = std::max(b->wRows[c], geo[i].maxRows);
-                b->wRingDoubles[c] = std::max(b->wRingDoubles[c], geo[i].maxBlockDoubles + (int64_t) planes * geo[i].maxWidth);
+                b->wRingDoubles[c] = std::max(b->wRingDoubles[c], geo[i].maxBlockDoubles + 2 * 256 * (int64_t) planes * geo[i].maxWidth);   // + the table being written, + the tail a wrap skips
                 continue;
             }
             int c = it.kernel == 1 ? 0 : it.kernel == 2 ? 1 : it.kernel == 4 ? 2 : 3;
@@ -930,7 +930,7 @@ static int prepareBatch(const sa_model_t *m, const sa_read_t *reads, int64_t nRe
         int bps = 1;
         if ((rc = wideOccupancy(gr, hdp, b->expectations, kWideNT[c], smem, &bps))) return rc;
         b->wBlocks[c] = (int) std::min<int64_t>((int64_t) nSM * std::max(1, bps), (int64_t) b->wOrder[c].size());
-        b->wRows[c] += 4;
+        b->wRows[c] += 4 + 256;      // + one descriptor table of headers written ahead
         b->wRingDoubles[c] = (b->wRingDoubles[c] + 64 + 15) & ~(int64_t) 15;
         if (b->wRingDoubles[c] > 0x7fffffffLL) {
             sa_set_error("sa_batch_prepare: a traceback block needs %.1f GB of forward rows (band too wide)", b->wRingDoubles[c] * 8e-9);

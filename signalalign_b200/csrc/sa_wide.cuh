@@ -39,24 +39,26 @@
 //     memory — the 4096-slot window, whose DP state alone takes 192 KB.
 template <bool EX, bool HD, bool GR>
 struct WideK {
-    static constexpr int BT = 256;             // band-table entries (diagonals per refill)
+    static constexpr int BT = 256;             // diagonals per descriptor table
     static constexpr double kExpZero = -50.0;  // expectation terms below e^-50 are not evaluated (see sa_cta.cuh)
     static constexpr int PL = HD ? 4 : 3;      // planes of a full stored row (HDP: + the cell's log density)
 
-    // CTA-uniform view of the dynamic shared memory (all derived from one __shared__ base: LDS / STS addressing)
+    // CTA-uniform view of the dynamic shared memory (all derived from one __shared__ base: LDS / STS addressing).
+    // The per-slot arrays are ARRAYS OF STRUCTS (3 doubles of state, 5 doubles of constants per slot): one address per
+    // slot, the planes at immediate offsets; strides of 24 B and 40 B keep 64-bit accesses of a warp conflict-free.
     struct Sm {
-        double *st;        // [2][3][NSW]   DP state by diagonal parity, plane, slot
-        double *cst;       // [5][NSW]      km, iM, cM, iY, cY per column (index = column & mask)
+        double *st;        // [2][NSW][3]   DP state by diagonal parity, slot, (M, X, Y)
+        double *cst;       // [NSW][5]      km, iM, cM, iY, cY per column (index = column & mask)
         double *evs;       // [NSW]         event mean per y (index = y & mask)
         double *foldv;     // [2][NSW]      total-probability terms by cell index (shared or global memory)
         float2 *cmax;      // [2][NSW/32]   per 32-cell chunk: max of the terms rounded down / up to float
         unsigned *candM;   // [2][NSW/32]   cells that can change the fold's accumulator
         unsigned *resetM;  // [2][NSW/32]   cells that replace it
         unsigned *hitW;    // [2][3][NSW/32] posterior hits per chunk, double buffered by diagonal parity (EX && HD: per from-state)
-        int2 *bandTab;     // [BT]
+        int4 *desc;        // [BT]          per diagonal of the table: xlo, xhi, row offset (doubles), planes stored
         int32_t *aX, *aY, *aD;   // [BT + 1] staged anchors
         double *sTotal;
-        int32_t *sInt;     // [0] work item, [1] anchor cursor
+        int32_t *sInt;     // [0] work item, [1] anchor cursor, [2] row-ring write offset after the table
         int32_t NSW, mask, nCh;  // nCh = NSW / 32
     };
 
@@ -64,7 +66,7 @@ struct WideK {
         size_t d = (size_t) 6 * NSW + (GR ? 0 : 5 * NSW + NSW + (foldInSmem ? 2 * NSW : 0)) + 2;   // doubles (+ sTotal, pad)
         size_t b = d * 8;
         b += (size_t) (NSW / 32) * (2 * 8 + 2 * 4 + 2 * 4 + 6 * 4);   // cmax, candM, resetM, hitW
-        b += (size_t) BT * 8 + 3 * (BT + 1) * 4 + 16;
+        b += (size_t) BT * 16 + 3 * (BT + 1) * 4 + 16 + 16;
         return b;
     }
     static __device__ __forceinline__ void carve(Sm &S, double *base, int NSW, double *foldGlobal, double *ringsGlobal) {
@@ -78,12 +80,12 @@ struct WideK {
             if (foldGlobal) S.foldv = foldGlobal; else { S.foldv = p; p += 2 * NSW; }
         }
         S.sTotal = p; p += 2;
+        S.desc = reinterpret_cast<int4 *>(p); p += 2 * BT;          // (16-byte aligned: every count above is even)
         S.cmax = reinterpret_cast<float2 *>(p); p += 2 * S.nCh;
         unsigned *u = reinterpret_cast<unsigned *>(p);
         S.candM = u; u += 2 * S.nCh;
         S.resetM = u; u += 2 * S.nCh;
         S.hitW = u; u += 6 * S.nCh;
-        S.bandTab = reinterpret_cast<int2 *>(u); u += 2 * BT;
         int32_t *q = reinterpret_cast<int32_t *>(u);
         S.aX = q; q += BT + 1;
         S.aY = q; q += BT + 1;
@@ -91,11 +93,18 @@ struct WideK {
         S.sInt = q;
     }
 
+    // per-CTA forward-row storage: a ring of doubles (rows never straddle its end) and a ring of row headers
+    struct Rows {
+        double *ring;
+        int4 *hdr;          // (xlo, xhi, offset in doubles, planes)
+        int32_t cap;        // header entries (> rows of a traceback block + BT)
+        int32_t ringDoubles;
+    };
+
     // ------------------------------------------------------------------------------------------ rings
     // emission constants of column x into its ring slot (column 0 is the NULL kmer; columns outside [1, lX] are never
     // active, their entries only have to be harmless numbers)
     static __device__ __forceinline__ void fillConst1(const FParams &P, const FItem &I, const Sm &S, int32_t x) {
-        const int s = x & S.mask;
         double km = 0.0, iM = 0.0, iY = 0.0, cM = SA_NEG_INF, cY = SA_NEG_INF;
         if (HD) {
             long long row = -1;
@@ -115,20 +124,21 @@ struct WideK {
             iY = ft[3] * I.invVar;
             cY = ft[4] + I.logInvVar;
         }
-        S.cst[s] = km; S.cst[S.NSW + s] = iM; S.cst[2 * S.NSW + s] = cM; S.cst[3 * S.NSW + s] = iY; S.cst[4 * S.NSW + s] = cY;
+        double *c = S.cst + (x & S.mask) * 5;
+        c[0] = km; c[1] = iM; c[2] = cM; c[3] = iY; c[4] = cY;
     }
-    // Make the rings hold columns [cl, ch] and events [el, eh] (both spans < NSW - 2 * kSlack).  cLo / eLo: first index the
-    // ring currently holds (it holds NSW consecutive ones).  fwd: the sweep moves towards larger indices, so a refill puts
-    // the slack ahead.  Uniform decisions; barriers only when refilling; only indices not yet present are loaded.
+    // Make the rings hold columns [cl, cl + span] and events [el, el + span] (span < NSW - 2 * kSlack).  cLo / eLo: first
+    // index the ring currently holds (it holds NSW consecutive ones).  fwd: the sweep moves towards larger indices, so a
+    // refill puts the slack ahead.  Uniform decisions; barriers only when refilling; only indices not yet present are loaded.
     static constexpr int kSlack = 8;
     static __device__ __forceinline__ void ensureRings(const FParams &P, const FItem &I, const Sm &S, int t, int NT,
-                                                       int32_t cl, int32_t ch, int32_t el, int32_t eh, bool fwd,
-                                                       int32_t &cLo, int32_t &eLo) {
-        const bool needC = cl < cLo || ch >= cLo + S.NSW, needE = el < eLo || eh >= eLo + S.NSW;
+                                                       int32_t cl, int32_t el, int32_t span, bool fwd, int32_t &cLo, int32_t &eLo) {
+        const unsigned room = (unsigned) (S.NSW - 1 - span);            // cl - cLo may be 0 .. room
+        const bool needC = (unsigned) (cl - cLo) > room, needE = (unsigned) (el - eLo) > room;
         if (!(needC || needE)) return;
         __syncthreads();                       // nobody still reads the entries that are replaced
         if (needC) {
-            const int32_t nLo = fwd ? cl - kSlack : ch + kSlack - (S.NSW - 1);
+            const int32_t nLo = fwd ? cl - kSlack : cl + span + kSlack - (S.NSW - 1);
             // new range [nLo, nLo + NSW); entries of the overlap with the old range stay
             for (int32_t k = t; k < S.NSW; k += NT) {
                 const int32_t x = nLo + k;
@@ -137,7 +147,7 @@ struct WideK {
             cLo = nLo;
         }
         if (needE) {
-            const int32_t nLo = fwd ? el - kSlack : eh + kSlack - (S.NSW - 1);
+            const int32_t nLo = fwd ? el - kSlack : el + span + kSlack - (S.NSW - 1);
             for (int32_t k = t; k < S.NSW; k += NT) {
                 const int32_t y = nLo + k;
                 if (y < eLo || y >= eLo + S.NSW)
@@ -148,8 +158,14 @@ struct WideK {
         __syncthreads();
     }
 
-    // band_construct in closed form for diagonals d0 .. d0 + BT - 1 (see CtaK::fillBand)
-    static __device__ __forceinline__ void fillBand(const FParams &P, const FItem &I, const Sm &S, int t, int NT, int32_t d0) {
+    // Descriptor table of diagonals d0 .. d0 + BT - 1: the band (band_construct in closed form from the staged anchors,
+    // see CtaK::fillBand), the planes the row keeps (all of them where the traceback reads the X / Y states: above
+    // tracedBackFrom of the diagonal's block, on every 10th posterior diagonal and its predecessor) and the row's offset
+    // in the CTA's row ring (prefix sum by warp 0; the table starts at the ring's origin when it would straddle its end).
+    // The headers go to the global header ring in one coalesced write.  wr: ring write offset, rowI0: header slot of d0.
+    static __device__ __forceinline__ void fillTable(const FParams &P, const FItem &I, const Sm &S, const Rows &RW, int t, int NT,
+                                                     int32_t d0, int32_t rowI0, int tbI, int32_t nTb, const int32_t *tbList,
+                                                     int32_t &wr) {
         __syncthreads();
         const int32_t base = S.sInt[1];        // anchors with diagonal < d0 - 1
         const int32_t *anch = P.anchors + 2 * I.anchorOff;
@@ -182,11 +198,52 @@ struct WideK {
             if ((z = (d - l) / 2 - yL) > 0) l += 2 * z;
             if ((z = (d + r) / 2 - xU) > 0) r -= 2 * z;
             if ((z = yU - (d - r) / 2) > 0) r -= 2 * z;
-            S.bandTab[q] = d <= nDiag ? make_int2((d + l) / 2, (d + r) / 2) : make_int2(0, 0);
+            int4 D4 = make_int4(0, -1, 0, 0);
+            if (d <= nDiag) {
+                int k = tbI;                   // the block of d ends at the first traceback diagonal >= d
+                while (k < nTb && tbList[k] < d) k++;
+                const int32_t T = k < nTb ? tbList[k] : nDiag;
+                const int32_t from = T - (T == nDiag ? 0 : P.traceBack + 1);
+                const bool full = EX || d > from || (from - d) % 10 <= 1;
+                D4 = make_int4((d + l) / 2, (d + r) / 2, 0, full ? PL : PL - 2);
+            }
+            S.desc[q] = D4;
             if (q == BT - 1) cLast = c;
         }
         if (((BT - 1) % NT) == t) S.sInt[1] = base + cLast;   // the thread that evaluated the table's last diagonal
         __syncthreads();
+        if (t < 32) {                          // row offsets: exclusive prefix of planes * width, 8 entries per lane
+            int32_t sz[BT / 32], sum = 0;
+#pragma unroll
+            for (int k = 0; k < BT / 32; k++) {
+                const int4 D4 = S.desc[t * (BT / 32) + k];
+                sz[k] = D4.w * (D4.y - D4.x + 1);
+                sum += sz[k];
+            }
+            int32_t inc = sum;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int32_t v = __shfl_up_sync(0xffffffffu, inc, o);
+                if (t >= o) inc += v;
+            }
+            const int32_t total = __shfl_sync(0xffffffffu, inc, 31);
+            const int32_t start = wr + total > RW.ringDoubles ? 0 : wr;
+            int32_t off = start + inc - sum;
+#pragma unroll
+            for (int k = 0; k < BT / 32; k++) {
+                S.desc[t * (BT / 32) + k].z = off;
+                off += sz[k];
+            }
+            if (t == 0) S.sInt[2] = start + total;
+        }
+        __syncthreads();
+        wr = S.sInt[2];
+        for (int q = t; q < BT; q += NT) {
+            if (d0 + q > nDiag) break;
+            int32_t r = rowI0 + q;
+            if (r >= RW.cap) r -= RW.cap;
+            RW.hdr[r] = S.desc[q];
+        }
     }
 
     // ------------------------------------------------------------------------------------------ emissions
@@ -213,37 +270,37 @@ struct WideK {
     // match and gap-Y emission of cell (x, y) from the rings
     static __device__ __forceinline__ void emissions(const FParams &P, const FItem &I, const Sm &S, int32_t x, int32_t y,
                                                      double &eM, double &eY) {
-        const int cs = x & S.mask;
+        const double *c = S.cst + (x & S.mask) * 5;
         const double ev = S.evs[y & S.mask];
         if (HD) {
-            const long long row = __double_as_longlong(S.cst[2 * S.NSW + cs]);
-            const double q = (((ev + S.cst[cs]) - S.cst[S.NSW + cs]) - I.shift) * I.invVar;
+            const long long row = __double_as_longlong(c[2]);
+            const double q = (((ev + c[0]) - c[1]) - I.shift) * I.invVar;
             double e = SA_NEG_INF;
             if (row >= 0) e = hdpLogDensity(P, I, row, q);
             eM = e; eY = e;
             return;
         }
-        const double d0 = ev - S.cst[cs];
-        const double aM = d0 * S.cst[S.NSW + cs], aY = d0 * S.cst[3 * S.NSW + cs];
-        eM = fma(-0.5 * aM, aM, S.cst[2 * S.NSW + cs]);
-        eY = fma(-0.5 * aY, aY, S.cst[4 * S.NSW + cs]);
+        const double d0 = ev - c[0];
+        const double aM = d0 * c[1], aY = d0 * c[3];
+        eM = fma(-0.5 * aM, aM, c[2]);
+        eY = fma(-0.5 * aY, aY, c[4]);
     }
     static __device__ __forceinline__ double emissionM(const FParams &P, const FItem &I, const Sm &S, int32_t x, int32_t y) {
-        const int cs = x & S.mask;
+        const double *c = S.cst + (x & S.mask) * 5;
         const double ev = S.evs[y & S.mask];
         if (HD) {
-            const long long row = __double_as_longlong(S.cst[2 * S.NSW + cs]);
-            const double q = (((ev + S.cst[cs]) - S.cst[S.NSW + cs]) - I.shift) * I.invVar;
+            const long long row = __double_as_longlong(c[2]);
+            const double q = (((ev + c[0]) - c[1]) - I.shift) * I.invVar;
             return row >= 0 ? hdpLogDensity(P, I, row, q) : SA_NEG_INF;
         }
-        const double aM = (ev - S.cst[cs]) * S.cst[S.NSW + cs];
-        return fma(-0.5 * aM, aM, S.cst[2 * S.NSW + cs]);
+        const double aM = (ev - c[0]) * c[1];
+        return fma(-0.5 * aM, aM, c[2]);
     }
     static __device__ __forceinline__ double emissionY(const FParams &P, const FItem &I, const Sm &S, int32_t x, int32_t y) {
         if (HD) return emissionM(P, I, S, x, y);
-        const int cs = x & S.mask;
-        const double aY = (S.evs[y & S.mask] - S.cst[cs]) * S.cst[3 * S.NSW + cs];
-        return fma(-0.5 * aY, aY, S.cst[4 * S.NSW + cs]);
+        const double *c = S.cst + (x & S.mask) * 5;
+        const double aY = (S.evs[y & S.mask] - c[0]) * c[3];
+        return fma(-0.5 * aY, aY, c[4]);
     }
 
     // ------------------------------------------------------------------------------------------ state helpers
@@ -266,13 +323,13 @@ struct WideK {
                     if (rowA) { v0 = rowA[i]; v1 = rowA[wA + i]; v2 = rowA[2 * wA + i]; }
                     else { v0 = cA[0]; v1 = cA[1]; v2 = cA[2]; }
                 }
-                bufA[s] = v0; bufA[S.NSW + s] = v1; bufA[2 * S.NSW + s] = v2;
+                bufA[3 * s] = v0; bufA[3 * s + 1] = v1; bufA[3 * s + 2] = v2;
             }
             {
                 const int32_t i = (s - jB - loB) & S.mask;
                 double v0 = SA_NEG_INF, v1 = SA_NEG_INF, v2 = SA_NEG_INF;
                 if (rowB && i < wB) { v0 = rowB[i]; v1 = rowB[wB + i]; v2 = rowB[2 * wB + i]; }
-                bufB[s] = v0; bufB[S.NSW + s] = v1; bufB[2 * S.NSW + s] = v2;
+                bufB[3 * s] = v0; bufB[3 * s + 1] = v1; bufB[3 * s + 2] = v2;
             }
         }
     }
@@ -359,14 +416,6 @@ struct WideK {
         return sa_logAdd(acc0, acc1);
     }
 
-    // per-CTA forward-row storage: a ring of doubles (rows never straddle its end) and a ring of row headers
-    struct Rows {
-        double *ring;
-        int4 *hdr;          // (xlo, xhi, offset in doubles, planes)
-        int32_t cap;        // header entries
-        int64_t ringDoubles;
-    };
-
     // ------------------------------------------------------------------------------------------ traceback
     // blocked traceback from diagonal d down to tracedBackTo + 1 (reference impl/pairwiseAligner.c:1500-1570)
     static __device__ void traceback(const FParams &P, const FItem &I, const Sm &S, const Rows &RW, int t, int NT, int32_t H,
@@ -392,7 +441,7 @@ struct WideK {
         // pending posterior hits of the previous diagonal (hit words in S.hitW[pendD & 1])
         bool pend = false;
         int32_t pendD = 0, pendXlo = 0, pendW = 0;
-        int64_t pendOff = 0;
+        int32_t pendOff = 0;
         double pendTotal = 0.0;
         auto flush = [&]() {
             // the CTA's last warp: hit words in chunk order; lane k owns the words k, k + 32, ...
@@ -400,7 +449,7 @@ struct WideK {
                 const int32_t nWords = (pendW + 31) >> 5;
                 const double *rowM = RW.ring + pendOff;
                 const int32_t jb = jbase(pendD, H);
-                const double *bM = S.st + (pendD & 1) * 3 * S.NSW;
+                const double *bM = S.st + (pendD & 1) * 3 * S.NSW;   // (array of structs: M at 3 * slot)
                 int64_t base = nPairs;
                 for (int32_t c0 = 0; c0 < nWords; c0 += 32) {
                     const int32_t c = c0 + lane;
@@ -417,7 +466,7 @@ struct WideK {
                         const int bit = __ffs(wv) - 1;
                         wv &= wv - 1;
                         const int32_t i = c * 32 + bit, x = pendXlo + i;
-                        const double pp = exp((rowM[i] + bM[(x + jb) & S.mask]) - pendTotal);
+                        const double pp = exp((rowM[i] + bM[3 * ((x + jb) & S.mask)]) - pendTotal);
                         if (w < I.pairCap) {
                             sa_pair_t o;
                             o.p = (int32_t) floor((pp > 1.0 ? 1.0 : pp) * 10000000.0);
@@ -483,7 +532,7 @@ struct WideK {
             const bool post = d2 <= tracedBackFrom;
             double *cur = S.st + par * 3 * S.NSW;                 // b(d2 + 2) -> b(d2)
             const double *prv = S.st + (par ^ 1) * 3 * S.NSW;     // b(d2 + 1)
-            const double *row = RW.ring + (int64_t) (unsigned) hCur.z;
+            const double *row = RW.ring + hCur.z;
             {
                 // what this step evaluates emissions for: cells (x + 1, y + 1), (x, y + 1), (x, y) of the band of d2 and the
                 // cells of d2 + 1 (total probability)
@@ -491,7 +540,7 @@ struct WideK {
                 const int32_t cl = up ? min(bxlo, hUp.x) : bxlo, ch = up ? max(bxhi + 1, hUp.y) : bxhi + 1;
                 const int32_t el = up ? min(d2 - bxhi, d2 + 1 - hUp.y) : d2 - bxhi;
                 const int32_t eh = up ? max(d2 - bxlo + 1, d2 + 1 - hUp.x) : d2 - bxlo + 1;
-                ensureRings(P, I, S, t, NT, cl, ch, el, eh, false, cLo, eLo);
+                ensureRings(P, I, S, t, NT, cl, el, max(ch - cl, eh - el), false, cLo, eLo);
             }
             if (d2 < d) {
                 const int32_t nChunks = (w + 31) >> 5;
@@ -501,14 +550,14 @@ struct WideK {
                         const int32_t x = bxlo + i, y = d2 - x;
                         const int32_t j = (x + jb) & S.mask, sq = (j - 1 + par) & S.mask, sl = (sq + 1) & S.mask;
                         // a = (x + 1, y + 1) on d2 + 2 (same slot), q = (x, y + 1) and l = (x + 1, y) on d2 + 1
-                        const double aM = cur[j], qY = prv[2 * S.NSW + sq], lX = prv[S.NSW + sl];
+                        const double aM = cur[3 * j], qY = prv[3 * sq + 2], lX = prv[3 * sl + 1];
                         double aE, qE;
                         if (HD) {               // the forward sweep kept every cell's log density
                             aE = qE = 0.0;
                             if (hUp2.y >= hUp2.x && x + 1 >= hUp2.x && x + 1 <= hUp2.y)
-                                aE = (RW.ring + (int64_t) (unsigned) hUp2.z)[(hUp2.w - 1) * (hUp2.y - hUp2.x + 1) + (x + 1 - hUp2.x)];
+                                aE = (RW.ring + hUp2.z)[(hUp2.w - 1) * (hUp2.y - hUp2.x + 1) + (x + 1 - hUp2.x)];
                             if (x >= hUp.x && x <= hUp.y)
-                                qE = (RW.ring + (int64_t) (unsigned) hUp.z)[(hUp.w - 1) * (hUp.y - hUp.x + 1) + (x - hUp.x)];
+                                qE = (RW.ring + hUp.z)[(hUp.w - 1) * (hUp.y - hUp.x + 1) + (x - hUp.x)];
                         } else {
                             aE = emissionM(P, I, S, x + 1, y + 1);
                             qE = emissionY(P, I, S, x, y + 1);
@@ -517,7 +566,7 @@ struct WideK {
                         const double M = sa_logAdd(sa_logAdd(aM + (aE + T[T_MATCH_CONTINUE]), qY + (qE + T[T_GAP_OPEN_Y])), lX + cOX);
                         const double X = sa_logAdd(aM + (aE + T[T_MATCH_FROM_GAP_X]), lX + cEX);
                         const double Y = sa_logAdd(aM + (aE + T[T_MATCH_FROM_GAP_Y]), qY + (qE + T[T_GAP_EXTEND_Y]));
-                        cur[j] = M; cur[S.NSW + j] = X; cur[2 * S.NSW + j] = Y;
+                        cur[3 * j] = M; cur[3 * j + 1] = X; cur[3 * j + 2] = Y;
                     }
                 }
                 // slots of d2 + 2 whose cell (x', .) has no successor (x' - 1, .) on d2: back to -inf
@@ -529,7 +578,7 @@ struct WideK {
                     for (int32_t k = NT - 1 - t; k < nLow + nHigh; k += NT) {
                         const int32_t xq = k < nLow ? hUp2.x + k : hiStart + (k - nLow);
                         const int32_t s = (xq + jb2) & S.mask;
-                        cur[s] = SA_NEG_INF; cur[S.NSW + s] = SA_NEG_INF; cur[2 * S.NSW + s] = SA_NEG_INF;
+                        cur[3 * s] = SA_NEG_INF; cur[3 * s + 1] = SA_NEG_INF; cur[3 * s + 2] = SA_NEG_INF;
                     }
                 }
             }
@@ -547,9 +596,9 @@ struct WideK {
                         double v = SA_NEG_INF;
                         if (i < w) {
                             const int32_t j = (bxlo + i + jb) & S.mask;
-                            v = row[i] + cur[j];
-                            v = sa_logAdd(v, row[w + i] + cur[S.NSW + j]);
-                            v = sa_logAdd(v, row[2 * w + i] + cur[2 * S.NSW + j]);
+                            v = row[i] + cur[3 * j];
+                            v = sa_logAdd(v, row[w + i] + cur[3 * j + 1]);
+                            v = sa_logAdd(v, row[2 * w + i] + cur[3 * j + 2]);
                             S.foldv[i] = v;
                         }
                         chunkMax(S, 0, c, lane, v);
@@ -558,7 +607,7 @@ struct WideK {
                     const int32_t w1 = hUp.y - hUp.x + 1, wD = hDn.y - hDn.x + 1;
                     const int32_t n1 = w1 > 0 ? w1 : 0;
                     {
-                        const double *rowD = RW.ring + (int64_t) (unsigned) hDn.z;
+                        const double *rowD = RW.ring + hDn.z;
                         const int32_t jb1 = jbase(d2 + 1, H);
                         const int32_t nChunks1 = (n1 + 31) >> 5;
                         for (int32_t c = warp; c < nChunks1; c += NW) {
@@ -569,11 +618,11 @@ struct WideK {
                                 double gM = SA_NEG_INF, gX = SA_NEG_INF, gY = SA_NEG_INF;
                                 if (iD >= 0 && iD < wD) { gM = rowD[iD]; gX = rowD[wD + iD]; gY = rowD[2 * wD + iD]; }
                                 double e;
-                                if (HD) e = (RW.ring + (int64_t) (unsigned) hUp.z)[(hUp.w - 1) * w1 + i];
+                                if (HD) e = (RW.ring + hUp.z)[(hUp.w - 1) * w1 + i];
                                 else e = emissionM(P, I, S, x, y);
                                 const double m = sa_logAdd(sa_logAdd(gM + (e + T[T_MATCH_CONTINUE]), gX + (e + T[T_MATCH_FROM_GAP_X])),
                                                            gY + (e + T[T_MATCH_FROM_GAP_Y]));
-                                v = m + prv[(x + jb1) & S.mask];
+                                v = m + prv[3 * ((x + jb1) & S.mask)];
                                 S.foldv[S.NSW + i] = v;
                             }
                             chunkMax(S, 1, c, lane, v);
@@ -599,7 +648,7 @@ struct WideK {
                     int4 h2 = make_int4(1, 0, 0, 0);
                     if (has2) h2 = hDn2;
                     const int32_t w1 = hDn.y - hDn.x + 1, w2 = h2.y - h2.x + 1;
-                    const double *r1 = RW.ring + (int64_t) (unsigned) hDn.z, *r2 = RW.ring + (int64_t) (unsigned) h2.z;
+                    const double *r1 = RW.ring + hDn.z, *r2 = RW.ring + h2.z;
                     const int32_t nChunks = (w + 31) >> 5;
                     for (int32_t c = warp; c < nChunks; c += NW) {
                         const int32_t i = c * 32 + lane;
@@ -610,7 +659,7 @@ struct WideK {
                         const bool middle = here && x - 1 >= h2.x && x - 1 <= h2.y;
                         double bM = 0.0, bX = 0.0, bY = 0.0, eM = 0.0, eY = 0.0;
                         if (here) {
-                            bM = cur[j]; bX = cur[S.NSW + j]; bY = cur[2 * S.NSW + j];
+                            bM = cur[3 * j]; bX = cur[3 * j + 1]; bY = cur[3 * j + 2];
                             if (HD) eM = eY = row[3 * w + i];
                             else emissions(P, I, S, x, y, eM, eY);
                         }
@@ -658,7 +707,7 @@ struct WideK {
                         bool cand = false;
                         double arg = 0.0;
                         if (i < w) {
-                            arg = (row[i] + cur[(x + jb) & S.mask]) - total;
+                            arg = (row[i] + cur[3 * ((x + jb) & S.mask)]) - total;
                             cand = x > 0 && d2 - x > 0 && arg >= P.logThrGate;
                         }
                         bool hit = false;
@@ -666,7 +715,7 @@ struct WideK {
                         const unsigned m = __ballot_sync(0xffffffffu, hit);
                         if (lane == 0) S.hitW[par * 3 * S.nCh + c] = m;
                     }
-                    pend = true; pendD = d2; pendXlo = bxlo; pendW = w; pendOff = (int64_t) (unsigned) hCur.z; pendTotal = total;
+                    pend = true; pendD = d2; pendXlo = bxlo; pendW = w; pendOff = hCur.z; pendTotal = total;
                 }
             }
             __syncthreads();                    // b(d2) and the hit words are complete
@@ -717,28 +766,28 @@ struct WideK {
                 RW.hdr[0] = make_int4(0, 0, 0, PL);
             }
         }
-        fillBand(P, I, S, t, NT, bd0);          // (barriers inside)
         int32_t tracedBackTo = 0;
         int tbI = 0;
         int32_t nextT = nTb > 0 ? tbList[0] : nDiag;
         int32_t curFrom = nextT - (nextT == nDiag ? 0 : P.traceBack + 1);
         const double cOX = P.eX + T[T_GAP_OPEN_X], cEX = P.eX + T[T_GAP_EXTEND_X];
         int32_t rowI = 0;                       // header-ring row of diagonal d
-        int64_t wr = PL;                        // next free double of the row ring
-        int32_t backMod = (curFrom - 1) % 10;   // (curFrom - d) mod 10 while it is >= 0
+        int32_t wr = PL;                        // next free double of the row ring
+        fillTable(P, I, S, RW, t, NT, bd0, 1, tbI, nTb, tbList, wr);
+        __syncthreads();
         int32_t xlo1 = 0, xhi1 = 0, xlo2 = 0, xhi2 = -1;   // bands of d - 1 and d - 2
         for (int32_t d = 1; d <= nDiag; d++) {
             rowI = rowI + 1 == RW.cap ? 0 : rowI + 1;
-            if (d >= bd0 + BT) { bd0 = d; fillBand(P, I, S, t, NT, bd0); }
-            const int2 bnd = S.bandTab[d - bd0];
-            const int32_t xlo = bnd.x, xhi = bnd.y, w = xhi - xlo + 1, par = d & 1, jb = jbase(d, H);
-            ensureRings(P, I, S, t, NT, xlo, xhi, d - xhi, d - xlo, true, cLo, eLo);
-            const bool full = EX || curFrom - d < 0 || backMod <= 1;
-            backMod = backMod == 0 ? 9 : backMod - 1;
-            const int32_t planes = full ? PL : (HD ? 2 : 1);
-            if (wr + (int64_t) planes * w > RW.ringDoubles) wr = 0;     // rows never straddle the end of the ring
-            double *row = RW.ring + wr;
-            if (t == 0) RW.hdr[rowI] = make_int4(xlo, xhi, (int32_t) wr, planes);
+            if (d >= bd0 + BT) {
+                bd0 = d;
+                fillTable(P, I, S, RW, t, NT, bd0, rowI, tbI, nTb, tbList, wr);
+                __syncthreads();
+            }
+            const int4 D4 = S.desc[d - bd0];
+            const int32_t xlo = D4.x, xhi = D4.y, w = xhi - xlo + 1, par = d & 1, jb = jbase(d, H);
+            ensureRings(P, I, S, t, NT, xlo, d - xhi, w - 1, true, cLo, eLo);
+            const bool full = D4.w == PL;
+            double *row = RW.ring + D4.z;
             double *cur = S.st + par * 3 * S.NSW;                       // f(d - 2) -> f(d)
             const double *prv = S.st + (par ^ 1) * 3 * S.NSW;           // f(d - 1)
             const int32_t nChunks = (w + 31) >> 5;
@@ -749,18 +798,20 @@ struct WideK {
                     const int32_t j = (x + jb) & S.mask, sl = (j - 1 + par) & S.mask, su = (sl + 1) & S.mask;
                     double eM, eY;
                     emissions(P, I, S, x, y, eM, eY);
-                    const double n1M = prv[sl], n1X = prv[S.NSW + sl];
-                    const double f1M = prv[su], f1Y = prv[2 * S.NSW + su];
-                    const double n2M = cur[j], n2X = cur[S.NSW + j], n2Y = cur[2 * S.NSW + j];
+                    double *pj = cur + 3 * j;
+                    const double *pl = prv + 3 * sl, *pu = prv + 3 * su;
+                    const double n1M = pl[0], n1X = pl[1];
+                    const double f1M = pu[0], f1Y = pu[2];
+                    const double n2M = pj[0], n2X = pj[1], n2Y = pj[2];
                     // stateMachine3_cellCalculate order; the first contribution lands on -inf (logAdd(-inf, v) == v exactly)
                     const double X = sa_logAdd(n1M + cOX, n1X + cEX);
                     const double M = sa_logAdd(sa_logAdd(n2M + (eM + T[T_MATCH_CONTINUE]), n2X + (eM + T[T_MATCH_FROM_GAP_X])),
                                                n2Y + (eM + T[T_MATCH_FROM_GAP_Y]));
                     const double Y = sa_logAdd(f1M + (eY + T[T_GAP_OPEN_Y]), f1Y + (eY + T[T_GAP_EXTEND_Y]));
-                    cur[j] = M; cur[S.NSW + j] = X; cur[2 * S.NSW + j] = Y;
+                    pj[0] = M; pj[1] = X; pj[2] = Y;
                     row[i] = M;
                     if (full) { row[w + i] = X; row[2 * w + i] = Y; }
-                    if (HD) row[(planes - 1) * w + i] = eM;
+                    if (HD) row[(D4.w - 1) * w + i] = eM;
                 }
             }
             // slots of d - 2 whose cell (x', .) has no successor (x' + 1, .) on d: back to -inf
@@ -771,13 +822,12 @@ struct WideK {
                 const int32_t nHigh = max(0, xhi2 - hiStart + 1);
                 for (int32_t k = NT - 1 - t; k < nLow + nHigh; k += NT) {
                     const int32_t xq = k < nLow ? xlo2 + k : hiStart + (k - nLow);
-                    const int32_t s = (xq + jb2) & S.mask;
-                    cur[s] = SA_NEG_INF; cur[S.NSW + s] = SA_NEG_INF; cur[2 * S.NSW + s] = SA_NEG_INF;
+                    double *ps = cur + 3 * ((xq + jb2) & S.mask);
+                    ps[0] = SA_NEG_INF; ps[1] = SA_NEG_INF; ps[2] = SA_NEG_INF;
                 }
             }
-            wr += (int64_t) planes * w;
             xlo2 = xlo1; xhi2 = xhi1; xlo1 = xlo; xhi1 = xhi;
-            __syncthreads();                    // f(d) is complete (and its header visible to the CTA)
+            __syncthreads();                    // f(d) is complete
             if (d != nextT) continue;
             // ------------------------------------------------------------------ traceback from diagonal d
             const bool atEnd = d == nDiag;
@@ -787,15 +837,13 @@ struct WideK {
             tbI++;
             nextT = tbI < nTb ? tbList[tbI] : nDiag;
             curFrom = nextT - (nextT == nDiag ? 0 : P.traceBack + 1);
-            backMod = (curFrom - (d + 1)) % 10;
             if (atEnd) break;
             // restore the forward sweep: f(d), f(d - 1) from the ring (all planes were kept above tracedBackFrom)
             __syncthreads();
             {
                 const int4 h0 = RW.hdr[rowI], h1 = RW.hdr[rowI == 0 ? RW.cap - 1 : rowI - 1];
                 const double none[3] = {SA_NEG_INF, SA_NEG_INF, SA_NEG_INF};
-                loadState(S, t, NT, H, d, h0.x, h0.y, RW.ring + (int64_t) (unsigned) h0.z, none, d - 1, h1.x, h1.y,
-                          RW.ring + (int64_t) (unsigned) h1.z);
+                loadState(S, t, NT, H, d, h0.x, h0.y, RW.ring + h0.z, none, d - 1, h1.x, h1.y, RW.ring + h1.z);
                 xlo1 = h0.x; xhi1 = h0.y; xlo2 = h1.x; xhi2 = h1.y;
             }
             __syncthreads();
@@ -847,7 +895,7 @@ __global__ void __launch_bounds__(1024, 1) sa_wide_kernel(const __grid_constant_
     RW.ring = P.scratch + (int64_t) blockIdx.x * P.wRingDoubles;
     RW.hdr = P.wHdr + (int64_t) blockIdx.x * P.wRowsCap;
     RW.cap = P.wRowsCap;
-    RW.ringDoubles = P.wRingDoubles;
+    RW.ringDoubles = (int32_t) P.wRingDoubles;
     for (;;) {
         __syncthreads();
         if (threadIdx.x == 0) S.sInt[0] = atomicAdd(P.counter, 1);
