@@ -271,7 +271,7 @@ struct DevBuf {
 // wide band kernel classes: window slots, threads per CTA (sa_wide.cuh)
 static const int kWideClasses = 5;
 static const int kWideNSW[kWideClasses] = {256, 512, 1024, 2048, 4096};
-static const int kWideNT[kWideClasses] = {128, 256, 512, 1024, 1024};
+static const int kWideNT[kWideClasses] = {128, 256, 512, 512, 1024};
 static const size_t kSmemCap = 227 * 1024 - 1024;   // opt-in shared memory per CTA minus the kernels' static part (logAdd table)
 
 // one work item = one sub-region of one read after getSplitPoints
@@ -461,8 +461,35 @@ static void wideLaunch(bool gr, bool hdp, bool ex, int blocks, int threads, size
     if (gr) wideLaunchG<true>(hdp, ex, blocks, threads, smem, st, f);
     else wideLaunchG<false>(hdp, ex, blocks, threads, smem, st, f);
 }
-// does the class keep its emission rings in global memory?
-static bool wideGlobalRings(int c) { return wideSmemBytes(false, kWideNSW[c], false) > kSmemCap; }
+// does the class keep its emission rings in global memory?  From the 2048-slot window on: with the rings in shared memory
+// one CTA of that class fills an SM (1024 threads, half of them idle on a typical diagonal); with only the DP state
+// there, two CTAs of 512 threads fit and overlap each other's barriers (+15 % on the contract pattern).
+// SA_WIDE_GR_FROM=<slots> moves the limit (experiments).
+static bool wideGlobalRings(int c) {
+    int from = 2048;
+    if (const char *e = getenv("SA_WIDE_GR_FROM")) from = atoi(e);
+    return kWideNSW[c] >= from || wideSmemBytes(false, kWideNSW[c], false) > kSmemCap;
+}
+// threads per CTA of a class (SA_WIDE_NT=a,b,c,d,e overrides the table; experiments)
+static int wideThreads(int c) {
+    if (const char *e = getenv("SA_WIDE_NT")) {
+        int v[kWideClasses], n = 0;
+        for (const char *q = e; *q && n < kWideClasses;) {
+            char *end = nullptr;
+            long x = strtol(q, &end, 10);
+            if (end == q) break;
+            v[n++] = (int) x;
+            q = *end ? end + 1 : end;
+        }
+        if (c < n && v[c] >= 32 && v[c] <= 1024 && v[c] % 32 == 0) return v[c];
+    }
+    return kWideNT[c];
+}
+static bool wideFoldGlobal(int c, bool gr) {
+    if (gr) return true;
+    if (const char *e = getenv("SA_WIDE_FOLDG_FROM")) if (kWideNSW[c] >= atoi(e)) return true;
+    return wideSmemBytes(false, kWideNSW[c], true) > kSmemCap;
+}
 
 // readBase: index of reads[0] in the caller's array (error messages name the caller's read)
 // chunkCount: how many sub-batches of this size the caller runs back to back (scales the latency-class decision)
@@ -925,10 +952,10 @@ static int prepareBatch(const sa_model_t *m, const sa_read_t *reads, int64_t nRe
         if (b->wOrder[c].empty()) continue;
         const bool hdp = m->kind == SA_EMIT_HDP;
         const bool gr = wideGlobalRings(c);
-        const bool foldGlobal = gr || wideSmemBytes(false, kWideNSW[c], true) > kSmemCap;
+        const bool foldGlobal = wideFoldGlobal(c, gr);
         const size_t smem = wideSmemBytes(gr, kWideNSW[c], !foldGlobal);
         int bps = 1;
-        if ((rc = wideOccupancy(gr, hdp, b->expectations, kWideNT[c], smem, &bps))) return rc;
+        if ((rc = wideOccupancy(gr, hdp, b->expectations, wideThreads(c), smem, &bps))) return rc;
         b->wBlocks[c] = (int) std::min<int64_t>((int64_t) nSM * std::max(1, bps), (int64_t) b->wOrder[c].size());
         b->wRows[c] += 4 + 256;      // + one descriptor table of headers written ahead
         b->wRingDoubles[c] = (b->wRingDoubles[c] + 64 + 15) & ~(int64_t) 15;
@@ -1102,7 +1129,7 @@ static int launchBatch(sa_batch_t *b) {
         f.wNSW = kWideNSW[c]; f.wRowsCap = b->wRows[c]; f.wRingDoubles = b->wRingDoubles[c];
         f.scratch = b->dWRing[c].p; f.wHdr = b->dWHdr[c].p; f.wFold = b->dWFold[c].p; f.wRings = b->dWRings[c].p;
         const bool gr = wideGlobalRings(c);
-        wideLaunch(gr, hdp, b->expectations, b->wBlocks[c], kWideNT[c],
+        wideLaunch(gr, hdp, b->expectations, b->wBlocks[c], wideThreads(c),
                    wideSmemBytes(gr, kWideNSW[c], b->dWFold[c].p == nullptr), st, f);
         b->lastLaunches++;
         CK(cudaGetLastError());

@@ -56,6 +56,7 @@ struct WideK {
         unsigned *resetM;  // [2][NSW/32]   cells that replace it
         unsigned *hitW;    // [2][3][NSW/32] posterior hits per chunk, double buffered by diagonal parity (EX && HD: per from-state)
         int4 *desc;        // [BT]          per diagonal of the table: xlo, xhi, row offset (doubles), planes stored
+        int4 *descB;       // [BT + 2]      the same for the traceback: entry q = header of diagonal (table top) - q
         int32_t *aX, *aY, *aD;   // [BT + 1] staged anchors
         double *sTotal;
         int32_t *sInt;     // [0] work item, [1] anchor cursor, [2] row-ring write offset after the table
@@ -66,7 +67,7 @@ struct WideK {
         size_t d = (size_t) 6 * NSW + (GR ? 0 : 5 * NSW + NSW + (foldInSmem ? 2 * NSW : 0)) + 2;   // doubles (+ sTotal, pad)
         size_t b = d * 8;
         b += (size_t) (NSW / 32) * (2 * 8 + 2 * 4 + 2 * 4 + 6 * 4);   // cmax, candM, resetM, hitW
-        b += (size_t) BT * 16 + 3 * (BT + 1) * 4 + 16 + 16;
+        b += (size_t) (2 * BT + 2) * 16 + 3 * (BT + 1) * 4 + 16 + 16;
         return b;
     }
     static __device__ __forceinline__ void carve(Sm &S, double *base, int NSW, double *foldGlobal, double *ringsGlobal) {
@@ -81,6 +82,7 @@ struct WideK {
         }
         S.sTotal = p; p += 2;
         S.desc = reinterpret_cast<int4 *>(p); p += 2 * BT;          // (16-byte aligned: every count above is even)
+        S.descB = reinterpret_cast<int4 *>(p); p += 2 * (BT + 2);
         S.cmax = reinterpret_cast<float2 *>(p); p += 2 * S.nCh;
         unsigned *u = reinterpret_cast<unsigned *>(p);
         S.candM = u; u += 2 * S.nCh;
@@ -429,15 +431,28 @@ struct WideK {
         const bool rag = atEnd && (I.flags & 2);
         const double endS[3] = {rag ? (T[T_GAP_OPEN_X] + T[T_GAP_OPEN_Y]) / 2.0 : T[T_MATCH_CONTINUE],
                                 rag ? T[T_GAP_EXTEND_X] : T[T_MATCH_FROM_GAP_X], rag ? T[T_GAP_EXTEND_Y] : T[T_MATCH_FROM_GAP_Y]};
-        int4 hCur = RW.hdr[rowI];               // header of d2
-        int4 hDn = RW.hdr[rowI == 0 ? cap - 1 : rowI - 1];   // ... of d2 - 1 (row tracedBackTo still exists)
-        __syncthreads();                        // the forward step's reads of the state are over
-        loadState(S, t, NT, H, d, hCur.x, hCur.y, nullptr, endS, d - 1, 0, -1, nullptr);
-        __syncthreads();
+        // row headers of the next BT steps from the global header ring into shared memory (entry q = diagonal top - q; two
+        // more for the total-probability / expectation reads of d2 - 1 and d2 - 2): one LDS.128 per step instead of global loads
+        auto fillBack = [&](int32_t rowTop) {
+            for (int32_t q = t; q < BT + 2; q += NT) {
+                int32_t r = rowTop - q;
+                if (r < 0) r += cap;
+                S.descB[q] = RW.hdr[r];
+            }
+        };
+        int32_t tTop = d;
+        {
+            const int4 hTop = RW.hdr[rowI];
+            __syncthreads();                    // the forward step's reads of the state are over
+            loadState(S, t, NT, H, d, hTop.x, hTop.y, nullptr, endS, d - 1, 0, -1, nullptr);
+            fillBack(rowI);
+            __syncthreads();
+        }
         double total = SA_NEG_INF;
         int32_t postMod = 0;                    // posterior diagonals since the last total, mod 10
         int4 hUp = make_int4(0, -1, 0, 0);      // header of d2 + 1
         int4 hUp2 = make_int4(0, -1, 0, 0);     // header of d2 + 2
+        int4 hCur = make_int4(0, -1, 0, 0);
         // pending posterior hits of the previous diagonal (hit words in S.hitW[pendD & 1])
         bool pend = false;
         int32_t pendD = 0, pendXlo = 0, pendW = 0;
@@ -447,6 +462,11 @@ struct WideK {
             // the CTA's last warp: hit words in chunk order; lane k owns the words k, k + 32, ...
             if (warp == NW - 1) {
                 const int32_t nWords = (pendW + 31) >> 5;
+                {                               // most diagonals have no hit at all
+                    unsigned any = 0u;
+                    for (int32_t c = lane; c < nWords; c += 32) any |= S.hitW[(pendD & 1) * 3 * S.nCh + c];
+                    if (!__any_sync(0xffffffffu, any != 0u)) { pend = false; return; }
+                }
                 const double *rowM = RW.ring + pendOff;
                 const int32_t jb = jbase(pendD, H);
                 const double *bM = S.st + (pendD & 1) * 3 * S.NSW;   // (array of structs: M at 3 * slot)
@@ -525,9 +545,13 @@ struct WideK {
             pend = false;
         };
         for (int32_t d2 = d; d2 > tracedBackTo; d2--) {
-            const int32_t rowP = rowI == 0 ? cap - 1 : rowI - 1;   // ring row of d2 - 1
-            const int32_t rowPP = rowP == 0 ? cap - 1 : rowP - 1;  // ... of d2 - 2
-            const int4 hDn2 = RW.hdr[rowPP];    // header of d2 - 2, one step ahead of its use (meaningless below tracedBackTo)
+            int32_t q = tTop - d2;
+            if (q == BT) {                      // (the previous step's barrier separates the table's last readers from the refill)
+                fillBack(rowI);
+                tTop = d2; q = 0;
+                __syncthreads();
+            }
+            hCur = S.descB[q];
             const int32_t bxlo = hCur.x, bxhi = hCur.y, w = bxhi - bxlo + 1, par = d2 & 1, jb = jbase(d2, H);
             const bool post = d2 <= tracedBackFrom;
             double *cur = S.st + par * 3 * S.NSW;                 // b(d2 + 2) -> b(d2)
@@ -542,10 +566,18 @@ struct WideK {
                 const int32_t eh = up ? max(d2 - bxlo + 1, d2 + 1 - hUp.x) : d2 - bxlo + 1;
                 ensureRings(P, I, S, t, NT, cl, el, max(ch - cl, eh - el), false, cLo, eLo);
             }
+            // posterior diagonals since the last total-probability refresh, mod 10 (reference :1538)
+            const bool newTotal = post && postMod == 0;
+            if (post) postMod = postMod == 9 ? 0 : postMod + 1;
+            // the posterior of a cell needs nothing but its own b(d2) and the running total: evaluated in the same pass
+            // unless this diagonal refreshes the total (or starts the traceback, where b(d2) is the end state)
+            const bool inlinePost = !EX && post && !newTotal;
             if (d2 < d) {
                 const int32_t nChunks = (w + 31) >> 5;
                 for (int32_t c = warp; c < nChunks; c += NW) {
                     const int32_t i = c * 32 + lane;
+                    bool cand = false;
+                    double arg = 0.0;
                     if (i < w) {
                         const int32_t x = bxlo + i, y = d2 - x;
                         const int32_t j = (x + jb) & S.mask, sq = (j - 1 + par) & S.mask, sl = (sq + 1) & S.mask;
@@ -567,6 +599,16 @@ struct WideK {
                         const double X = sa_logAdd(aM + (aE + T[T_MATCH_FROM_GAP_X]), lX + cEX);
                         const double Y = sa_logAdd(aM + (aE + T[T_MATCH_FROM_GAP_Y]), qY + (qE + T[T_GAP_EXTEND_Y]));
                         cur[3 * j] = M; cur[3 * j + 1] = X; cur[3 * j + 2] = Y;
+                        if (inlinePost) {
+                            arg = (row[i] + M) - total;
+                            cand = x > 0 && y > 0 && arg >= P.logThrGate;
+                        }
+                    }
+                    if (inlinePost) {
+                        bool hit = false;
+                        if (__any_sync(0xffffffffu, cand)) hit = cand && exp(arg) >= P.threshold;
+                        const unsigned m = __ballot_sync(0xffffffffu, hit);
+                        if (lane == 0) S.hitW[par * 3 * S.nCh + c] = m;
                     }
                 }
                 // slots of d2 + 2 whose cell (x', .) has no successor (x' - 1, .) on d2: back to -inf
@@ -586,8 +628,6 @@ struct WideK {
                 if (EX && HD) flushA(); else flush();
             }
             if (post) {
-                const bool newTotal = postMod == 0;
-                postMod = postMod == 9 ? 0 : postMod + 1;
                 if (newTotal) {
                     // diagonalCalculationTotalProbability (reference pairwiseAligner.c:1335-1353)
                     const int32_t nChunks = (w + 31) >> 5;
@@ -604,6 +644,7 @@ struct WideK {
                         chunkMax(S, 0, c, lane, v);
                     }
                     // matches jumping over d2: middle-only forward step from f(d2 - 1) into the cells of d2 + 1
+                    const int4 hDn = S.descB[q + 1];     // header of d2 - 1 (row tracedBackTo still exists)
                     const int32_t w1 = hUp.y - hUp.x + 1, wD = hDn.y - hDn.x + 1;
                     const int32_t n1 = w1 > 0 ? w1 : 0;
                     {
@@ -645,8 +686,9 @@ struct WideK {
                     // (d2 - 2 >= tracedBackTo).  Every term is exp(((f + b) + (eP + tP)) - total), as the reference adds it.
                     if (t == 0) lik += total;
                     const bool has2 = d2 - 2 >= tracedBackTo;
+                    const int4 hDn = S.descB[q + 1];
                     int4 h2 = make_int4(1, 0, 0, 0);
-                    if (has2) h2 = hDn2;
+                    if (has2) h2 = S.descB[q + 2];
                     const int32_t w1 = hDn.y - hDn.x + 1, w2 = h2.y - h2.x + 1;
                     const double *r1 = RW.ring + hDn.z, *r2 = RW.ring + h2.z;
                     const int32_t nChunks = (w + 31) >> 5;
@@ -701,7 +743,7 @@ struct WideK {
                     if (HD) { pend = true; pendD = d2; pendXlo = bxlo; pendW = w; }
                 } else {
                     // diagonalCalculationPosteriorMatchProbs (reference pairwiseAligner.c:1355-1421)
-                    const int32_t nChunks = (w + 31) >> 5;
+                    const int32_t nChunks = inlinePost && d2 < d ? 0 : (w + 31) >> 5;
                     for (int32_t c = warp; c < nChunks; c += NW) {
                         const int32_t i = c * 32 + lane, x = bxlo + i;
                         bool cand = false;
@@ -719,8 +761,8 @@ struct WideK {
                 }
             }
             __syncthreads();                    // b(d2) and the hit words are complete
-            hUp2 = hUp; hUp = hCur; hCur = hDn; hDn = hDn2;
-            rowI = rowP;
+            hUp2 = hUp; hUp = hCur;
+            rowI = rowI == 0 ? cap - 1 : rowI - 1;
         }
         if (pend) {
             if (EX && HD) flushA(); else flush();
