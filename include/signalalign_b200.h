@@ -104,6 +104,11 @@ void sa_params_default(sa_params_t *p);
 typedef struct sa_ambig sa_ambig_t;
 sa_ambig_t *sa_ambig_load(const char *file);
 void sa_ambig_free(sa_ambig_t *a);
+/* the same table built entry by entry from a caller's own code -> bases map (Sequence.ambigBases, the stHash that
+ * create_ambig_bases2 returns and hdCell_construct2 looks single characters up in, impl/pairwiseAligner.c:755):
+ * sa_ambig_create() is EMPTY (no code is ambiguous), sa_ambig_set adds / replaces one code (at most 15 bases) */
+sa_ambig_t *sa_ambig_create(void);
+int sa_ambig_set(sa_ambig_t *a, char code, const char *bases);
 
 /* ---------------------------------------------------------------------------------------------- outputs */
 /* one aligned pair = stIntTuple4(floor(p*1e7), x, y, kmer*) (impl/pairwiseAligner.c:1405-1408);

@@ -51,7 +51,7 @@ EXPORTS = [
     "sa_model_set_hdp_expected_values",
     "sa_model_scale_noise", "sa_model_scale_model", "sa_model_free", "sa_model_num_kmers", "sa_model_kmer_length",
     "sa_model_alphabet", "sa_model_get_tables", "sa_model_hdp_density", "sa_params_default", "sa_ambig_load",
-    "sa_ambig_free", "sa_result_free", "sa_kmer_string", "sa_gpu_init", "sa_last_error", "sa_gpu_device_count",
+    "sa_ambig_free", "sa_ambig_create", "sa_ambig_set", "sa_result_free", "sa_kmer_string", "sa_gpu_init", "sa_last_error", "sa_gpu_device_count",
     "sa_gpu_align_batch", "sa_gpu_expectations_batch", "sa_batch_prepare", "sa_batch_run", "sa_batch_fetch",
     "sa_batch_last_timing", "sa_batch_band_cells", "sa_batch_kernel_items", "sa_batch_wide_items", "sa_batch_h2d_bytes", "sa_batch_d2h_bytes", "sa_batch_free",
     "sa_result_sum_expectations", "sa_debug_logadd", "sa_model_hdp_dims", "sa_model_get_hdp", "sa_debug_band",
@@ -104,6 +104,8 @@ def lib():
     L.sa_ambig_load.restype = C.c_void_p
     L.sa_ambig_load.argtypes = [C.c_char_p]
     L.sa_ambig_free.argtypes = [C.c_void_p]
+    L.sa_ambig_create.restype = C.c_void_p
+    L.sa_ambig_set.argtypes = [C.c_void_p, C.c_char, C.c_char_p]
     L.sa_result_free.argtypes = [C.POINTER(SaResult)]
     L.sa_kmer_string.argtypes = [C.c_void_p, C.c_int64, C.c_char_p]
     L.sa_gpu_init.argtypes = [C.c_int]
@@ -294,8 +296,14 @@ def _read_array(reads):
 
 
 class Ambig:
-    def __init__(self, path=None):
-        self.h = lib().sa_ambig_load(path.encode() if path else None)
+    def __init__(self, path=None, table=None):
+        """path: a `code<TAB>bases` file (None = the built-in table); table: a dict code -> bases instead of a file"""
+        if table is not None:
+            self.h = lib().sa_ambig_create()
+            for code, bases in table.items():
+                _check(lib().sa_ambig_set(self.h, code.encode(), bases.encode()))
+        else:
+            self.h = lib().sa_ambig_load(path.encode() if path else None)
         if not self.h:
             raise SaError(lib().sa_last_error().decode(errors="replace"))
 

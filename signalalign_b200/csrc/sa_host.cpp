@@ -69,6 +69,23 @@ extern "C" sa_ambig_t *sa_ambig_load(const char *file) {  // create_ambig_bases2
 }
 extern "C" void sa_ambig_free(sa_ambig_t *a) { delete a; }
 
+// An EMPTY table, filled entry by entry: what a caller holding the reference's stHash of code -> bases
+// (Sequence.ambigBases, inc/pairwiseAligner.h:68) hands over; the drop-in shim converts the hash of every call this way.
+extern "C" sa_ambig_t *sa_ambig_create(void) {
+    sa_ambig *a = new sa_ambig;
+    memset(a, 0, sizeof(*a));
+    return a;
+}
+extern "C" int sa_ambig_set(sa_ambig_t *a, char code, const char *bases) {
+    if (!a || !bases || strlen(bases) > 15) {
+        sa_set_error("sa_ambig_set: a code stands for at most 15 bases");
+        return SA_ERR_INPUT;
+    }
+    memset(a->opts[(unsigned char) code], 0, 16);
+    snprintf(a->opts[(unsigned char) code], 16, "%s", bases);
+    return SA_OK;
+}
+
 // ------------------------------------------------------------------------------------------------ kmers
 static int64_t kmerId(const char *kmer, const sa_model &m) {  // kmer_id, impl/nanopore_hdp.c:377-410
     int64_t id = 0;

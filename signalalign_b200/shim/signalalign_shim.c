@@ -19,7 +19,12 @@
  * sa_model_attach_nhdp parses; HDP expectations append their (kmer, event) assignments through HdpHmm::addToAssignments
  * with pointers into sX->elements / sY->elements, as cell_signal_updateExpectationsAndAssignments does
  * (impl/pairwiseAligner.c:946-968).
- * Not covered here: per-Sequence ambiguity tables other than the built-in one (create_ambig_bases2(NULL)).
+ * The ambiguity table of the call is the one the caller put into the target Sequence (SsX->ambigBases: the stHash of
+ * create_ambig_bases2(ambig_path), impl/signalMachine.c:431, 474), converted entry by entry; a Sequence without one gets
+ * the built-in table.
+ * The device model of a StateMachine is cached by CONTENT (transitions, emission tables, scale-independent): a machine
+ * changed in place between two calls (hmmContinuous_loadIntoStateMachine, emissions_signal_scaleNoise, ...), or a new
+ * machine at a recycled address, is uploaded again.
  */
 #include <stdlib.h>
 #include <string.h>
@@ -31,15 +36,36 @@
 #include "stateMachine.h"
 #include "continuousHmm.h"
 
-/* one device model per StateMachine (keyed by the struct's address and its table pointers) */
+/* device models, keyed by the machine's CONTENT: type, emission function, kmer geometry, the nine transitions and a hash
+ * of the three emission tables (+ the address of the NanoporeHDP, whose private structs cannot be hashed from here) */
 #define SHIM_CACHE 8
 static struct {
-    const StateMachine *sM;
-    const double *match;
+    uint64_t key;
     const void *hdp;
     sa_model_t *model;
 } g_cache[SHIM_CACHE];
 static int g_cacheNext = 0, g_inited = 0;
+
+static uint64_t shimMix(uint64_t h, const void *data, size_t bytes) {
+    const uint64_t *w = (const uint64_t *) data;
+    for (size_t i = 0; i < bytes / 8; i++) {
+        h ^= w[i];
+        h *= 0x9E3779B97F4A7C15ULL;
+        h ^= h >> 29;
+    }
+    return h;
+}
+static uint64_t shimKey(const StateMachine *sM, const double *t9, const void *fn) {
+    uint64_t h = 0xcbf29ce484222325ULL;
+    uint64_t head[4] = {(uint64_t) sM->type, (uint64_t) sM->kmerLength, (uint64_t) sM->parameterSetSize, (uint64_t) (uintptr_t) fn};
+    h = shimMix(h, head, sizeof(head));
+    h = shimMix(h, t9, 9 * sizeof(double));
+    for (int64_t i = 0; i < sM->alphabetSize; i++) h = (h ^ (uint64_t) (unsigned char) sM->alphabet[i]) * 0x100000001b3ULL;
+    h = shimMix(h, sM->EMISSION_MATCH_MATRIX, (size_t) sM->parameterSetSize * MODEL_PARAMS * sizeof(double));
+    h = shimMix(h, sM->EMISSION_GAP_Y_MATRIX, (size_t) sM->parameterSetSize * MODEL_PARAMS * sizeof(double));
+    h = shimMix(h, sM->EMISSION_GAP_X_PROBS, (size_t) sM->parameterSetSize * sizeof(double));
+    return h;
+}
 
 static sa_model_t *shimModel(StateMachine *sM) {
     if (!g_inited) {
@@ -48,9 +74,16 @@ static sa_model_t *shimModel(StateMachine *sM) {
         g_inited = 1;
     }
     const void *hdp = sM->type == threeStateHdp ? (const void *) ((StateMachine3_HDP *) sM)->hdpModel : NULL;
+    uint64_t key = 0;
+    if (sM->type == threeStateHdp) {
+        StateMachine3_HDP *sh = (StateMachine3_HDP *) sM;
+        key = shimKey(sM, &sh->TRANSITION_MATCH_CONTINUE, (const void *) sh->getMatchProbFcn);
+    } else if (sM->type == threeState) {
+        StateMachine3 *s3 = (StateMachine3 *) sM;
+        key = shimKey(sM, &s3->TRANSITION_MATCH_CONTINUE, (const void *) s3->getMatchProbFcn);
+    }
     for (int i = 0; i < SHIM_CACHE; i++)
-        if (g_cache[i].model && g_cache[i].sM == sM && g_cache[i].match == sM->EMISSION_MATCH_MATRIX && g_cache[i].hdp == hdp)
-            return g_cache[i].model;
+        if (g_cache[i].model && g_cache[i].key == key && g_cache[i].hdp == hdp) return g_cache[i].model;
     sa_model_t *m = NULL;
     if (sM->type == threeStateHdp) {
         /* StateMachine3_HDP keeps the transition block at the same place as StateMachine3 (inc/stateMachine.h:150-191);
@@ -99,8 +132,7 @@ static sa_model_t *shimModel(StateMachine *sM) {
     }
     int slot = g_cacheNext++ % SHIM_CACHE;
     if (g_cache[slot].model) sa_model_free(g_cache[slot].model);
-    g_cache[slot].sM = sM;
-    g_cache[slot].match = sM->EMISSION_MATCH_MATRIX;
+    g_cache[slot].key = key;
     g_cache[slot].hdp = hdp;
     g_cache[slot].model = m;
     return m;
@@ -128,6 +160,22 @@ static void shimRead(StateMachine *sM, Sequence *sX, Sequence *sY, stList *ancho
     *anchorsOut = an;
 }
 
+/* SsX->ambigBases (stHash: code string -> bases string) as an sa_ambig_t; NULL = the built-in table.  hdCell_construct2
+ * looks up one character at a time (impl/pairwiseAligner.c:755), so only one-character codes can ever match. */
+static sa_ambig_t *shimAmbig(Sequence *sX) {
+    if (sX->ambigBases == NULL) return NULL;
+    sa_ambig_t *a = sa_ambig_create();
+    stHashIterator *it = stHash_getIterator((stHash *) sX->ambigBases);
+    char *code;
+    while ((code = stHash_getNext(it)) != NULL) {
+        const char *bases = stHash_search((stHash *) sX->ambigBases, code);
+        if (strlen(code) != 1 || bases == NULL) continue;
+        if (sa_ambig_set(a, code[0], bases) != SA_OK) st_errAbort("libsagpu: %s\n", sa_last_error());
+    }
+    stHash_destructIterator(it);
+    return a;
+}
+
 static void shimParams(const PairwiseAlignmentParameters *p, sa_params_t *sp) {
     sa_params_default(sp);
     sp->threshold = p->threshold;
@@ -153,7 +201,9 @@ stList *getAlignedPairsUsingAnchors(StateMachine *sM, Sequence *SsX, Sequence *S
     sa_params_t sp;
     shimParams(p, &sp);
     sa_result_t *res = NULL;
-    if (sa_gpu_align_batch(m, &r, 1, &sp, NULL, &res) != SA_OK) st_errAbort("libsagpu: %s\n", sa_last_error());
+    sa_ambig_t *amb = shimAmbig(SsX);
+    if (sa_gpu_align_batch(m, &r, 1, &sp, amb, &res) != SA_OK) st_errAbort("libsagpu: %s\n", sa_last_error());
+    sa_ambig_free(amb);
     stList *out = stList_construct3(0, (void (*)(void *)) stIntTuple_destruct);
     const int64_t n = res->pairOffsets[1], k = sM->kmerLength;
     /* one arena for the call's kmer strings; like the reference's, they outlive the list and are never freed */
@@ -186,7 +236,9 @@ void getExpectationsUsingAnchors(StateMachine *sM, Hmm *hmmExpectations, Sequenc
     /* the assignment gate is the HdpHmm's own threshold (impl/pairwiseAligner.c:963), not the alignment parameter's */
     if (sM->type == threeStateHdp) sp.threshold = ((HdpHmm *) hmmExpectations)->threshold;
     sa_result_t *res = NULL;
-    if (sa_gpu_expectations_batch(m, &r, 1, &sp, NULL, &res) != SA_OK) st_errAbort("libsagpu: %s\n", sa_last_error());
+    sa_ambig_t *amb = shimAmbig(SsX);
+    if (sa_gpu_expectations_batch(m, &r, 1, &sp, amb, &res) != SA_OK) st_errAbort("libsagpu: %s\n", sa_last_error());
+    sa_ambig_free(amb);
     /* cell_signal_updateExpectations adds every term through the Hmm's own function (continuousHmm.c:147-149);
      * the likelihood is a plain field (pairwiseAligner.c:1432) */
     for (int64_t from = 0; from < 3; from++)

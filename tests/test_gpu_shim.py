@@ -115,3 +115,45 @@ def test_reference_hdp_machine_runs_on_the_gpu(tmp_path):
     assert compare_pairs(got4.astype(np.int32), g["pairs"], par["threshold"]) <= 20
     compare_expectations(out["tr_hdp"], float(out["lik_hdp"]), g["exp_transitions"], float(g["exp_likelihood"]))
     assert np.array_equal(out["ak_hdp"], g["exp_assign_kmer"]) and np.array_equal(out["ae_hdp"], g["exp_assign_event"])
+
+
+MUTATE_CHILD = r"""
+import json, os, sys
+import numpy as np
+sys.path.insert(0, sys.argv[1])
+from oracle import ref
+job = json.load(open(sys.argv[2]))
+z = np.load(job["inputs"])
+sm = ref.RefStateMachine(job["model"], kind=2)
+sm.set_scaling(1.0, 0.0, 1.0)
+first, _, _ = sm.align(str(z["target"]), z["events"], z["anchors"], **job["params"])
+sm.scale_model(*job["tparams"])              # emissions_signal_scaleModel: rewrites the tables IN PLACE
+second, kmers, _ = sm.align(str(z["target"]), z["events"], z["anchors"], **job["params"])
+np.savez(job["out"], first=first, second=second, kmers=np.array(kmers))
+"""
+
+
+@pytest.mark.skipif(not os.path.exists(GPU_LIB), reason="oracle/_ref/libsaref_gpu.so not built (needs /root/reference at build time)")
+def test_machine_mutated_in_place_between_calls_is_uploaded_again(tmp_path):
+    """the shim caches device models by CONTENT: after emissions_signal_scaleModel rewrote the tables of the same
+    StateMachine in place, the next call must see the new tables (golden: loadScaledStateMachine3's 1076 pairs)"""
+    g = golden("zymo_scaled")
+    t = golden("model_r73_acegot")
+    model_file = os.path.join(str(tmp_path), "acegot.model")
+    write_model_file(model_file, str(t["alphabet"]), int(t["k"]), t["trans"], t["match"])
+    tp = [float(v) for v in g["tparams"]]
+    job = dict(model=model_file, inputs=os.path.join(str(tmp_path), "in.npz"), out=os.path.join(str(tmp_path), "out.npz"),
+               params=_kw(params_from(g["params"])), tparams=[tp[0], tp[1], tp[2], tp[4], tp[5]])
+    np.savez(job["inputs"], target=g["target"], events=g["events"], anchors=g["anchors"])
+    with open(os.path.join(str(tmp_path), "job.json"), "w") as f:
+        json.dump(job, f)
+    r = subprocess.run([sys.executable, "-c", MUTATE_CHILD, ROOT_DIR, os.path.join(str(tmp_path), "job.json")],
+                       env=dict(os.environ, SA_REF_LIB=GPU_LIB), capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-2000:]
+    with np.load(job["out"]) as z:
+        first, second, kmers = z["first"], z["second"], z["kmers"]
+    alphabet, k = str(t["alphabet"]), int(t["k"])
+    idx = np.array([sum(alphabet.index(c) * len(alphabet) ** (k - 1 - i) for i, c in enumerate(s)) for s in kmers], np.int64)
+    got4 = np.concatenate([second, idx[:, None]], axis=1)
+    assert len(got4) == 1076 and not np.array_equal(first, second)
+    assert compare_pairs(got4.astype(np.int32), g["pairs"], job["params"]["threshold"]) <= 20
