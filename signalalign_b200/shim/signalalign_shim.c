@@ -35,6 +35,7 @@
 #include "pairwiseAligner.h"
 #include "stateMachine.h"
 #include "continuousHmm.h"
+#include "signalalign_shim.h"
 
 /* device models, keyed by the machine's CONTENT: type, emission function, kmer geometry, the nine transitions and a hash
  * of the three emission tables (+ the address of the NanoporeHDP, whose private structs cannot be hashed from here) */
@@ -67,7 +68,7 @@ static uint64_t shimKey(const StateMachine *sM, const double *t9, const void *fn
     return h;
 }
 
-static sa_model_t *shimModel(StateMachine *sM) {
+sa_model_t *sa_shim_model(StateMachine *sM) {
     if (!g_inited) {
         const char *dev = getenv("SA_SHIM_DEVICE");
         if (sa_gpu_init(dev ? atoi(dev) : 0) != SA_OK) st_errAbort("libsagpu: %s\n", sa_last_error());
@@ -162,13 +163,13 @@ static void shimRead(StateMachine *sM, Sequence *sX, Sequence *sY, stList *ancho
 
 /* SsX->ambigBases (stHash: code string -> bases string) as an sa_ambig_t; NULL = the built-in table.  hdCell_construct2
  * looks up one character at a time (impl/pairwiseAligner.c:755), so only one-character codes can ever match. */
-static sa_ambig_t *shimAmbig(Sequence *sX) {
-    if (sX->ambigBases == NULL) return NULL;
+sa_ambig_t *sa_shim_ambig(stHash *ambigBases) {
+    if (ambigBases == NULL) return NULL;
     sa_ambig_t *a = sa_ambig_create();
-    stHashIterator *it = stHash_getIterator((stHash *) sX->ambigBases);
+    stHashIterator *it = stHash_getIterator(ambigBases);
     char *code;
     while ((code = stHash_getNext(it)) != NULL) {
-        const char *bases = stHash_search((stHash *) sX->ambigBases, code);
+        const char *bases = stHash_search(ambigBases, code);
         if (strlen(code) != 1 || bases == NULL) continue;
         if (sa_ambig_set(a, code[0], bases) != SA_OK) st_errAbort("libsagpu: %s\n", sa_last_error());
     }
@@ -194,14 +195,14 @@ stList *getAlignedPairsUsingAnchors(StateMachine *sM, Sequence *SsX, Sequence *S
                                     bool alignmentHasRaggedLeftEnd, bool alignmentHasRaggedRightEnd) {
     if (diagonalPosteriorProbFn != diagonalCalculationPosteriorMatchProbs)
         st_errAbort("signalalign_shim: getAlignedPairsUsingAnchors is bound for diagonalCalculationPosteriorMatchProbs only\n");
-    sa_model_t *m = shimModel(sM);
+    sa_model_t *m = sa_shim_model(sM);
     sa_read_t r;
     int64_t *an;
     shimRead(sM, SsX, SsY, anchorPairs, alignmentHasRaggedLeftEnd, alignmentHasRaggedRightEnd, &r, &an);
     sa_params_t sp;
     shimParams(p, &sp);
     sa_result_t *res = NULL;
-    sa_ambig_t *amb = shimAmbig(SsX);
+    sa_ambig_t *amb = sa_shim_ambig(SsX->ambigBases);
     if (sa_gpu_align_batch(m, &r, 1, &sp, amb, &res) != SA_OK) st_errAbort("libsagpu: %s\n", sa_last_error());
     sa_ambig_free(amb);
     stList *out = stList_construct3(0, (void (*)(void *)) stIntTuple_destruct);
@@ -227,7 +228,7 @@ void getExpectationsUsingAnchors(StateMachine *sM, Hmm *hmmExpectations, Sequenc
                                  bool alignmentHasRaggedLeftEnd, bool alignmentHasRaggedRightEnd) {
     if (diagonalCalcExpectationFcn != diagonalCalculation_Expectations)
         st_errAbort("signalalign_shim: getExpectationsUsingAnchors is bound for diagonalCalculation_Expectations only\n");
-    sa_model_t *m = shimModel(sM);
+    sa_model_t *m = sa_shim_model(sM);
     sa_read_t r;
     int64_t *an;
     shimRead(sM, SsX, SsY, anchorPairs, alignmentHasRaggedLeftEnd, alignmentHasRaggedRightEnd, &r, &an);
@@ -236,7 +237,7 @@ void getExpectationsUsingAnchors(StateMachine *sM, Hmm *hmmExpectations, Sequenc
     /* the assignment gate is the HdpHmm's own threshold (impl/pairwiseAligner.c:963), not the alignment parameter's */
     if (sM->type == threeStateHdp) sp.threshold = ((HdpHmm *) hmmExpectations)->threshold;
     sa_result_t *res = NULL;
-    sa_ambig_t *amb = shimAmbig(SsX);
+    sa_ambig_t *amb = sa_shim_ambig(SsX->ambigBases);
     if (sa_gpu_expectations_batch(m, &r, 1, &sp, amb, &res) != SA_OK) st_errAbort("libsagpu: %s\n", sa_last_error());
     sa_ambig_free(amb);
     /* cell_signal_updateExpectations adds every term through the Hmm's own function (continuousHmm.c:147-149);

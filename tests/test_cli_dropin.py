@@ -92,3 +92,44 @@ def test_signalmachine_linked_against_libsagpu_writes_the_same_files():
                 assert stdout.startswith("r9read 6514\t")        # "<label> <anchors>\t<pairs>(<score>)", signalMachine.c:917
         # a custom ambiguity table must change the calls (the shim once dropped it and used the built-in table)
         assert cc.read_golden("variantCaller_custom_table") != cc.read_golden("variantCaller_default_table")
+
+
+BATCH_BIN = os.path.join(cc.REF_BIN, "signalMachineBatch")
+
+
+@pytest.mark.gpu
+@pytest.mark.skipif(not os.path.exists(BATCH_BIN), reason="oracle/_ref/signalMachineBatch not built (needs /root/reference)")
+def test_signalmachinebatch_manifest_writes_the_same_files():
+    """one process, model parsed once, all reads of the manifest in one sa_gpu_align_batch call, every read's
+    file written by the reference's own writers — same bytes as the per-read CLI (golden from signalMachine_cpu)."""
+    with tempfile.TemporaryDirectory(prefix="sa_cli_") as work:
+        inp = cc.prepare_inputs(work)
+
+        def run(fmt, entries, extra=()):
+            man = os.path.join(work, "manifest_%s.tsv" % fmt)
+            outs = []
+            with open(man, "w") as f:
+                f.write("# npRead\tcigar\tfasta\tsequence\tlabel\toutput\n")
+                for i, fasta in enumerate(entries):
+                    out = os.path.join(work, "batch_%s_%d.tsv" % (fmt, i))
+                    if os.path.exists(out):
+                        os.remove(out)
+                    outs.append(out)
+                    f.write("\t".join([inp["npread"], inp["cigar"], fasta, "r9ref", "r9read", out]) + "\n")
+            cmd = [BATCH_BIN, "--manifest", man, "-T", inp["model"], "-s", str(fmt), "-x", "50", "-D", "0.01", "-m", "14", "--batch", "2"]
+            r = subprocess.run(cmd + list(extra), capture_output=True, text=True, timeout=900)
+            assert r.returncode == 0, r.stderr[-800:]
+            assert r.stderr.count("SUCCESS") == len(entries) and len(r.stdout.strip().splitlines()) == len(entries)
+            return [open(o).read() for o in outs], r.stdout
+
+        outs, stdout = run(0, [inp["fasta"], inp["fasta"], inp["fasta"]])      # two batches (2 + 1 reads)
+        for o in outs:
+            _compare_tsv("full", o, cc.read_golden("full"))
+        assert all(l.startswith("r9read 6514\t") for l in stdout.strip().splitlines())
+        outs, _ = run(2, [inp["fasta"]])
+        _compare_tsv("assignments", outs[0], cc.read_golden("assignments"))
+        outs, _ = run(1, [inp["fasta_variants"], inp["fasta"]])
+        _compare_tsv("variantCaller_default_table", outs[0], cc.read_golden("variantCaller_default_table"))
+        assert outs[1] == ""                                                      # no ambiguity code: nothing to report
+        outs, _ = run(1, [inp["fasta_variants"]], extra=["-a", inp["ambig"]])
+        _compare_tsv("variantCaller_custom_table", outs[0], cc.read_golden("variantCaller_custom_table"))
