@@ -299,19 +299,24 @@ def main():
             exp_table = shard.expectation_table(r3)
             del r3
         barrier()
-        # the one collective of the path: all-reduce of the per-GPU expectation tables (NCCL over NVLink at N > 1),
-        # checked against the all-gathered per-rank tables
+        # the one collective of the path: all-reduce of the per-GPU expectation tables through the C-ABI
+        # (sa_gpu_allreduce_expectations: libsagpu's own NCCL communicator over NVLink at N > 1; torch.distributed only
+        # carries the 128-byte id to the ranks), checked against the all-gathered per-rank tables
         if world > 1:
-            shard.allreduce_expectations(exp_table, device=torch.device("cuda", local_rank))     # warm-up (communicator)
+            ids = [sa.Comm.unique_id() if rank == 0 else None]
+            dist.broadcast_object_list(ids, src=0)
+            comm = sa.Comm(ids[0], world, rank)
+            comm.allreduce_expectations(exp_table.copy())                                        # warm-up (communicator)
             barrier()
             t1 = time.time()
-            reduced = shard.allreduce_expectations(exp_table, device=torch.device("cuda", local_rank))
+            reduced = comm.allreduce_expectations(exp_table.copy())
             exp_ar_ms = 1e3 * (time.time() - t1)
             parts = [torch.zeros(10, dtype=torch.float64, device="cuda") for _ in range(world)]
             dist.all_gather(parts, torch.from_numpy(exp_table).to("cuda"))
             want = torch.stack(parts).sum(0).cpu().numpy()
             assert np.allclose(reduced, want, rtol=1e-12, atol=0), (reduced, want)
             exp_table = reduced
+            comm.close()
 
     def reduce_max(x):
         if world == 1:

@@ -196,6 +196,29 @@ int64_t sa_debug_split_points(const int64_t *anchors, int64_t nAnchors, int64_t 
                               int raggedLeft, int raggedRight, int64_t *out, int64_t cap);
 int64_t sa_debug_kmer_paths(const sa_model_t *m, const sa_ambig_t *ambig, const char *kmer, int32_t *out, int64_t cap);
 
+/* ---------------------------------------------------------------------------------------------- multi-GPU
+ * The one collective of the path: the element-wise sum of the per-GPU expectation tables of an EM
+ * iteration — what the reference does by adding per-read expectation files in Python
+ * (src/signalalign/hiddenMarkovModel.py:424-486, HmmModel.add_expectations_file) — as ncclAllReduce(sum, double) over
+ * NVLink, and the concatenation of the HDP assignment lists (impl/continuousHmm.c:510-514, 571-628).  One process per GPU;
+ * rank 0 creates the 128-byte id, the launcher carries it to the other ranks (MPI, a file, any key-value store), every
+ * rank then calls sa_gpu_comm_init on the device it selected with sa_gpu_init.  libnccl.so.2 is loaded on first use. */
+#define SA_COMM_UNIQUE_ID_BYTES 128
+typedef struct sa_comm sa_comm_t;
+int sa_gpu_comm_unique_id(void *id128);                                    /* ncclGetUniqueId */
+int sa_gpu_comm_init(const void *id128, int nRanks, int rank, sa_comm_t **out);   /* ncclCommInitRank */
+/* adopt a communicator the caller already owns (an ncclComm_t); it is not destroyed by sa_gpu_comm_free */
+int sa_gpu_comm_from_nccl(void *ncclComm, int nRanks, int rank, sa_comm_t **out);
+void sa_gpu_comm_free(sa_comm_t *c);
+/* in place on a host table of n doubles (same n on every rank): 10 = what sa_result_sum_expectations returns (9
+ * transitions + likelihood, all the reference's C path accumulates: the emission slots of the expectations file keep
+ * their pseudocounts, impl/pairwiseAligner.c:924-943), or 10 + 3 K for the file's full layout (continuousHmm.c:353-407) */
+int sa_gpu_allreduce_expectations(sa_comm_t *c, double *table, int64_t n);
+/* every rank's (kmer position, event) assignment list, concatenated in rank order on every rank; *allKmerPos and
+ * *allEvent are malloc'ed (free them), countsPerRank has nRanks entries */
+int sa_gpu_allgather_assignments(sa_comm_t *c, const int32_t *kmerPos, const int32_t *event, int64_t n,
+                                 int32_t **allKmerPos, int32_t **allEvent, int64_t *countsPerRank);
+
 /* expectation-table reduction across reads of one GPU (the per-GPU table NCCL then all-reduces):
  * out[0..8] = sum of transitions, out[9] = sum of likelihood */
 void sa_result_sum_expectations(const sa_result_t *r, double *out10);

@@ -56,6 +56,8 @@ EXPORTS = [
     "sa_batch_last_timing", "sa_batch_band_cells", "sa_batch_kernel_items", "sa_batch_wide_items", "sa_batch_h2d_bytes", "sa_batch_d2h_bytes", "sa_batch_free",
     "sa_result_sum_expectations", "sa_debug_logadd", "sa_model_hdp_dims", "sa_model_get_hdp", "sa_debug_band",
     "sa_debug_split_points", "sa_debug_kmer_paths", "sa_last_call_stats", "sa_set_host_threads",
+    "sa_gpu_comm_unique_id", "sa_gpu_comm_init", "sa_gpu_comm_from_nccl", "sa_gpu_comm_free",
+    "sa_gpu_allreduce_expectations", "sa_gpu_allgather_assignments",
 ]
 
 _lib = None
@@ -123,6 +125,12 @@ def lib():
     L.sa_batch_kernel_items.argtypes = [C.c_void_p, c_i64p]
     L.sa_batch_wide_items.argtypes = [C.c_void_p, c_i64p]
     L.sa_batch_free.argtypes = [C.c_void_p]
+    L.sa_gpu_comm_unique_id.argtypes = [C.c_void_p]
+    L.sa_gpu_comm_init.argtypes = [C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_void_p)]
+    L.sa_gpu_comm_from_nccl.argtypes = [C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_void_p)]
+    L.sa_gpu_comm_free.argtypes = [C.c_void_p]
+    L.sa_gpu_allreduce_expectations.argtypes = [C.c_void_p, c_f64p, C.c_int64]
+    L.sa_gpu_allgather_assignments.argtypes = [C.c_void_p, c_i32p, c_i32p, C.c_int64, C.POINTER(c_i32p), C.POINTER(c_i32p), c_i64p]
     L.sa_result_sum_expectations.argtypes = [C.POINTER(SaResult), c_f64p]
     L.sa_debug_logadd.argtypes = [c_f64p, c_f64p, c_f64p, C.c_int64]
     L.sa_model_hdp_dims.argtypes = [C.c_void_p, c_i64p]
@@ -373,6 +381,55 @@ def expectations_batch(model, reads, params=None, ambig=None):
     _check(lib().sa_gpu_expectations_batch(model.h, arr, len(reads), C.byref(params), ambig.h if ambig else None,
                                            C.byref(out)))
     return Result(out)
+
+
+class Comm:
+    """NCCL communicator behind the C-ABI (sa_gpu_comm_*): the all-reduce of the expectation tables and the gather of the
+    HDP assignment lists.  `unique_id()` on rank 0, carry the 128 bytes to the other ranks, then Comm(id, n, rank)."""
+
+    @staticmethod
+    def unique_id():
+        buf = C.create_string_buffer(128)
+        _check(lib().sa_gpu_comm_unique_id(buf))
+        return buf.raw
+
+    def __init__(self, unique_id, n_ranks, rank):
+        self.h = C.c_void_p()
+        self.n_ranks, self.rank = n_ranks, rank
+        _check(lib().sa_gpu_comm_init(C.c_char_p(unique_id), n_ranks, rank, C.byref(self.h)))
+
+    def allreduce_expectations(self, table):
+        """in-place sum over ranks of a float64 table (same length on every rank); returns it"""
+        t = np.ascontiguousarray(table, np.float64)
+        _check(lib().sa_gpu_allreduce_expectations(self.h, t.ctypes.data_as(c_f64p), t.size))
+        return t
+
+    def allgather_assignments(self, kmer_pos, event):
+        k = np.ascontiguousarray(kmer_pos, np.int32)
+        e = np.ascontiguousarray(event, np.int32)
+        ak, ae = c_i32p(), c_i32p()
+        counts = np.zeros(self.n_ranks, np.int64)
+        _check(lib().sa_gpu_allgather_assignments(self.h, k.ctypes.data_as(c_i32p), e.ctypes.data_as(c_i32p), k.size,
+                                                  C.byref(ak), C.byref(ae), counts.ctypes.data_as(c_i64p)))
+        total = int(counts.sum())
+        outk = np.ctypeslib.as_array(ak, shape=(max(total, 1),))[:total].copy()
+        oute = np.ctypeslib.as_array(ae, shape=(max(total, 1),))[:total].copy()
+        libc = C.CDLL(None)
+        libc.free.argtypes = [C.c_void_p]
+        libc.free(ak)
+        libc.free(ae)
+        return outk, oute, counts
+
+    def close(self):
+        if self.h:
+            lib().sa_gpu_comm_free(self.h)
+            self.h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
 
 
 def set_host_threads(n):
