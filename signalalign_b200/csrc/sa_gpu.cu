@@ -413,7 +413,7 @@ static void ctaLaunchT(int c, bool oneCell, int blocks, cudaStream_t st, const F
     else sa_cta_kernel<4, 2, EX, HD><<<blocks, 128, 0, st>>>(f);
 }
 // ex: the expectations variant of the kernels (getExpectationsUsingAnchors) instead of the aligned-pairs one;
-// hdp: the HDP emission instead of the Gaussian tables (alignment only: HDP expectations collect assignments)
+// hdp: the HDP emission instead of the Gaussian tables (with ex: the kmer / event assignment lists as well)
 static int ctaOccupancy(int c, bool oneCell, bool ex, bool hdp, int *bps) {
     if (hdp && ex) return ctaOccupancyT<true, true>(c, false, bps);
     if (hdp) return ctaOccupancyT<false, true>(c, false, bps);
@@ -541,7 +541,6 @@ static int prepareBatch(const sa_model_t *m, const sa_read_t *reads, int64_t nRe
     cudaStream_t st = b->aux;
 
     const bool needNoise = m->kind == SA_EMIT_GAUSS_NOISE_SCALED || m->kind == SA_EMIT_GAUSS_NOISE_DESCALE;
-    // (expectations of the HDP machine also collect kmer/event assignments: general kernel)
     const bool fastModel = modelFastEligible(m, b->expectations) && getenv("SA_FORCE_GENERAL") == nullptr;
     PinVec<int32_t> pathOff, pathKmer, anchors32;
     PinVec<double> evMean, evNoise, evLogNoise;
@@ -1033,6 +1032,14 @@ static int prepareBatch(const sa_model_t *m, const sa_read_t *reads, int64_t nRe
         int64_t slab = ring * 3 + 9 * maxDiagPC + 2 * maxWidth;
         size_t freeB = 0, totalB = 0;
         CK(cudaMemGetInfo(&freeB, &totalB));
+        {   // memory the stream-ordered pool holds but does not use (the release threshold is lifted) is available too
+            cudaMemPool_t pool;
+            uint64_t reserved = 0, used = 0;
+            if (cudaDeviceGetDefaultMemPool(&pool, dev) == cudaSuccess &&
+                cudaMemPoolGetAttribute(pool, cudaMemPoolAttrReservedMemCurrent, &reserved) == cudaSuccess &&
+                cudaMemPoolGetAttribute(pool, cudaMemPoolAttrUsedMemCurrent, &used) == cudaSuccess && reserved > used)
+                freeB += (size_t) (reserved - used);
+        }
         int nCta = (int) std::min<int64_t>((int64_t) b->gOrder.size(), (int64_t) nSM * 8);
         while (nCta > 1 && (double) nCta * slab * 8.0 > 0.6 * (double) freeB) nCta = nCta / 2;
         if ((double) nCta * slab * 8.0 > 0.9 * (double) freeB) {

@@ -88,6 +88,16 @@ def test_ragged_flags_and_thresholds(small_batch):
         _run_and_compare(rs, table, p)
 
 
+def test_pair_slots_overflow_and_grow_in_every_mode(small_batch):
+    """threshold 1e-7: far more than 3 pairs per event, so the first slot size overflows and the batch is re-slotted and
+    re-run — in the latency class (every read of a six-read batch), on the throughput mapping and on the general kernel"""
+    reads, table = small_batch
+    p = sa.default_params(threshold=1e-7, expansion=100, trace_back=50, min_diags=300)
+    _run_and_compare(reads[:3], table, p)
+    _run_and_compare(reads[:3], table, p, no_latency=True)
+    _run_and_compare(reads[:3], table, p, force_general=True)
+
+
 def test_medium_reads_many_blocks():
     reads, table = synth.make_batch(3, seed=5, mean_len=2500, min_len=2000, max_len=3000, trim=0)
     p = sa.default_params(threshold=0.01, expansion=100, trace_back=50, min_diags=1000)
