@@ -158,6 +158,26 @@ void sa_last_call_stats(int64_t *h2dBytes, int64_t *d2hBytes, int64_t *launches)
 int sa_gpu_expectations_batch(const sa_model_t *m, const sa_read_t *reads, int64_t nReads, const sa_params_t *p,
                               const sa_ambig_t *ambig, sa_result_t **out);
 
+/* ONE read, NO device allocation.  This entry point has no counterpart in the reference: it was added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid it).  Same result as sa_gpu_align_batch on that read (the wide band kernel, 512-slot window):
+ * pairs in the reference's list order into the caller's HOST buffer pairsOut[pairCap]; *nPairs = how many the read
+ * produces (SA_ERR_INPUT when that exceeds pairCap: nothing is written).  All device memory of the call — staged inputs,
+ * work-item record, traceback list, row headers, pair slots and the kernel's scratch (the ring of forward rows) — is one
+ * static device array of SA_NOALLOC_SCRATCH_BYTES that every GPU loading the library holds until exit; the call makes no
+ * cudaMalloc / cudaFree / pool allocation.  Limits (SA_ERR_INPUT with a message beyond them): SA_NOALLOC_MAX_KMERS reference
+ * kmers and anchors, SA_NOALLOC_MAX_EVENTS events, three consecutive diagonals spanning at most 488 columns, the forward rows
+ * of one traceback block within the array (about 1.7 M doubles: any -x 100 read with dense or CLI-trimmed anchors), no
+ * ambiguity codes, no anchor gap that getSplitPoints would cut at, production Gaussian emission (SA_EMIT_GAUSS_MEANONLY_DESCALE)
+ * only.  The model's tables must already be on the device (any earlier regular call with the model — sa_batch_prepare with
+ * zero reads suffices — uploads them; that upload allocates, this call does not).  Every call shares the array: calls that
+ * overlap on the GPU (two host threads, two processes' streams on one context) race; one call at a time per device. */
+#define SA_NOALLOC_SCRATCH_BYTES (16u << 20)
+#define SA_NOALLOC_MAX_EVENTS 32768
+#define SA_NOALLOC_MAX_KMERS 32768
+int sa_gpu_align_noalloc(const sa_model_t *m, const sa_read_t *read, const sa_params_t *p, sa_pair_t *pairsOut,
+                         int64_t pairCap, int64_t *nPairs);
+
 /* Staged form of the same call, so that callers (and bench.py) can keep a batch resident in HBM:
  *   prepare  = host packing + H2D of inputs (+ device geometry pass + scratch allocation)
  *   run      = kernels only, inputs and outputs resident in HBM; may be called repeatedly

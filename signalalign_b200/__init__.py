@@ -57,7 +57,7 @@ EXPORTS = [
     "sa_result_sum_expectations", "sa_debug_logadd", "sa_model_hdp_dims", "sa_model_get_hdp", "sa_debug_band",
     "sa_debug_split_points", "sa_debug_kmer_paths", "sa_last_call_stats", "sa_set_host_threads",
     "sa_gpu_comm_unique_id", "sa_gpu_comm_init", "sa_gpu_comm_from_nccl", "sa_gpu_comm_free",
-    "sa_gpu_allreduce_expectations", "sa_gpu_allgather_assignments",
+    "sa_gpu_allreduce_expectations", "sa_gpu_allgather_assignments", "sa_gpu_align_noalloc",
 ]
 
 _lib = None
@@ -125,6 +125,7 @@ def lib():
     L.sa_batch_kernel_items.argtypes = [C.c_void_p, c_i64p]
     L.sa_batch_wide_items.argtypes = [C.c_void_p, c_i64p]
     L.sa_batch_free.argtypes = [C.c_void_p]
+    L.sa_gpu_align_noalloc.argtypes = [C.c_void_p, C.POINTER(SaRead), C.POINTER(SaParams), C.POINTER(SaPair), C.c_int64, c_i64p]
     L.sa_gpu_comm_unique_id.argtypes = [C.c_void_p]
     L.sa_gpu_comm_init.argtypes = [C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_void_p)]
     L.sa_gpu_comm_from_nccl.argtypes = [C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_void_p)]
@@ -371,6 +372,18 @@ def align_batch(model, reads, params=None, ambig=None):
     _check(lib().sa_gpu_align_batch(model.h, arr, len(reads), C.byref(params), ambig.h if ambig else None,
                                     C.byref(out)))
     return Result(out)
+
+
+def align_noalloc(model, read, params=None, pair_cap=None):
+    """sa_gpu_align_noalloc: one read, no device allocation (static device scratch); int32 [n, 4] pairs like read_pairs"""
+    params = params or default_params()
+    cap = int(pair_cap if pair_cap is not None else 3 * read.events.shape[0] + 64)
+    out = np.zeros((max(cap, 1), 4), np.int32)
+    n = C.c_int64(0)
+    rs = read.cstruct()
+    _check(lib().sa_gpu_align_noalloc(model.h, C.byref(rs), C.byref(params), C.cast(out.ctypes.data, C.POINTER(SaPair)), cap,
+                                      C.byref(n)))
+    return out[:n.value].copy()
 
 
 def expectations_batch(model, reads, params=None, ambig=None):

@@ -1643,3 +1643,212 @@ extern "C" int sa_gpu_expectations_batch(const sa_model_t *m, const sa_read_t *r
                                          const sa_params_t *p, const sa_ambig_t *ambig, sa_result_t **out) {
     return runBatch(m, reads, nReads, p, ambig, 1, out);
 }
+
+// ================================================================================================ allocation-free call
+// sa_gpu_align_noalloc — ONE read through the wide band kernel (sa_wide.cuh, 512-slot window) WITHOUT any device
+// allocation.  No counterpart in the reference: added for callers that cannot call
+// cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+//
+// Everything the regular path allocates per batch — the staged inputs, the work-item record, the traceback list, the
+// row-header ring, the pair slots and the kernel's SCRATCH (the ring of forward rows the blocked traceback reads back) —
+// lives in ONE file-scope device array of SA_NOALLOC_SCRATCH_BYTES (16 MiB), carved up below.  Every GPU that loads the
+// library holds that array until the process exits.  Every call shares it and finds the previous call's contents: the
+// work-queue counter is cleared on each call, everything else is overwritten before it is read.  Calls that overlap on the
+// GPU (two host threads, two streams) RACE on it: one call at a time per device.
+//
+// In host code the array's name is a host-side stand-in, not a device address: its device address is taken once per
+// device, with that device current, by cudaGetSymbolAddress, and only that pointer is handed to kernels.
+static __device__ __align__(256) unsigned char sa_noalloc_scratch[SA_NOALLOC_SCRATCH_BYTES];
+
+namespace noalloc {
+constexpr int64_t kMaxEvents = SA_NOALLOC_MAX_EVENTS, kMaxKmers = SA_NOALLOC_MAX_KMERS, kMaxAnchors = SA_NOALLOC_MAX_KMERS;
+constexpr int64_t kTbCap = 4096, kHdrCap = 8192, kPairCap = 131072;
+constexpr int kNSW = 512, kNT = 256;
+// byte offsets inside the scratch array (all multiples of 256)
+constexpr size_t oCounter = 0, oItem = 256, oOrder = 1024, oGeo = 1280, oPairCount = 1536;
+constexpr size_t oTb = 4096;                                   // int32[kTbCap]
+constexpr size_t oHdr = oTb + kTbCap * 4;                      // int4[kHdrCap]
+constexpr size_t oEv = oHdr + kHdrCap * 16;                    // double[kMaxEvents]
+constexpr size_t oKmer = oEv + kMaxEvents * 8;                 // int32[kMaxKmers]
+constexpr size_t oAnch = oKmer + kMaxKmers * 4;                // int32[2 * kMaxAnchors]
+constexpr size_t oPairs = oAnch + kMaxAnchors * 8;             // sa_pair_t[kPairCap]
+constexpr size_t oRing = oPairs + kPairCap * 16;               // double[...]: the forward-row ring
+constexpr int64_t kRingDoubles = (int64_t) ((SA_NOALLOC_SCRATCH_BYTES - oRing) / 8);
+static_assert(sizeof(FItem) <= oOrder - oItem && sizeof(FGeo) <= oPairCount - oGeo, "control block layout");
+static_assert(oRing % 256 == 0 && oRing < SA_NOALLOC_SCRATCH_BYTES / 2, "scratch layout");
+
+static unsigned char *g_base[64] = {nullptr};   // device address of the array, per device
+// host staging of the packed inputs (fixed size: no heap allocation per call either)
+static double g_hEv[kMaxEvents];
+static int32_t g_hKmer[kMaxKmers], g_hAnch[2 * kMaxAnchors];
+
+static int setup(int dev, unsigned char **base) {
+    if (dev < 0 || dev >= 64) { sa_set_error("sa_gpu_align_noalloc: device index %d not supported", dev); return SA_ERR_CUDA; }
+    if (!g_base[dev]) {
+        unsigned char *ptr = nullptr;
+        CK(cudaGetSymbolAddress((void **) &ptr, sa_noalloc_scratch));     // with device `dev` current
+        CK(cudaFuncSetAttribute(sa_wide_kernel<false, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) kSmemCap));
+        g_base[dev] = ptr;
+    }
+    *base = g_base[dev];
+    return SA_OK;
+}
+}  // namespace noalloc
+
+extern "C" int sa_gpu_align_noalloc(const sa_model_t *m, const sa_read_t *R, const sa_params_t *p, sa_pair_t *pairsOut,
+                                    int64_t pairCap, int64_t *nPairsOut) {
+    using namespace noalloc;
+    if (!m || !R || !p || !nPairsOut || (pairCap > 0 && !pairsOut)) { sa_set_error("sa_gpu_align_noalloc: null argument"); return SA_ERR_INPUT; }
+    *nPairsOut = 0;
+    if (sa_gpu_device_count() == 0) {
+        sa_set_error("sa_gpu_align_noalloc: no CUDA device available; libsagpu has no CPU fallback");
+        return SA_ERR_CUDA;
+    }
+    if (p->diagonalExpansion % 2 != 0 || p->diagonalExpansion < 0 || p->traceBackDiagonals < 1 ||
+        p->minDiagsBetweenTraceBack < 2 || p->traceBackDiagonals + 1 >= p->minDiagsBetweenTraceBack) {
+        sa_set_error("sa_gpu_align_noalloc: parameters violate the prerequisites of getPosteriorProbsWithBanding "
+                     "(pairwiseAligner.c:1460-1464)");
+        return SA_ERR_INPUT;
+    }
+    if (m->kind != SA_EMIT_GAUSS_MEANONLY_DESCALE || !modelFastEligible(m, false)) {
+        sa_set_error("sa_gpu_align_noalloc: only the production Gaussian emission (MeanOnly, de-scaled) is supported here");
+        return SA_ERR_INPUT;
+    }
+    int dev = 0;
+    CK(cudaGetDevice(&dev));
+    if (!m->dev || m->devDevice != dev) {
+        sa_set_error("sa_gpu_align_noalloc: the model's tables are not resident on device %d and this entry point allocates "
+                     "nothing: run any regular call with this model first (sa_batch_prepare, even with zero reads, uploads it)", dev);
+        return SA_ERR_INPUT;
+    }
+    const int64_t lX = R->targetLength > 0 ? std::max<int64_t>(0, R->targetLength - (m->k - 1)) : 0, lY = R->nEvents;
+    if (lX > kMaxKmers || lY > kMaxEvents || R->nAnchors > kMaxAnchors) {
+        sa_set_error("sa_gpu_align_noalloc: read too large for the static scratch (%lld kmers, %lld events, %lld anchors; limits "
+                     "%lld / %lld / %lld): use sa_gpu_align_batch", (long long) lX, (long long) lY, (long long) R->nAnchors,
+                     (long long) kMaxKmers, (long long) kMaxEvents, (long long) kMaxAnchors);
+        return SA_ERR_INPUT;
+    }
+    const int64_t nDiag = lX + lY;
+    const int64_t nTbCap = nDiag / (p->minDiagsBetweenTraceBack - p->traceBackDiagonals - 1) + 2;
+    if (nTbCap > kTbCap) {
+        sa_set_error("sa_gpu_align_noalloc: %lld traceback blocks exceed the limit %lld", (long long) nTbCap, (long long) kTbCap);
+        return SA_ERR_INPUT;
+    }
+    // anchors: in range, strictly increasing (band_construct asserts it), and no gap that getSplitPoints would cut at
+    // (pairwiseAligner.c:1886-1937): the regions of a split read are separate work items of the regular path
+    {
+        int64_t x2 = 0, y2 = 0;
+        for (int64_t i = 0; i <= R->nAnchors; i++) {
+            const int64_t x3 = i < R->nAnchors ? R->anchors[2 * i] : lX, y3 = i < R->nAnchors ? R->anchors[2 * i + 1] : lY;
+            if (i < R->nAnchors && (x3 < x2 || y3 < y2 || x3 >= lX || y3 >= lY)) {
+                sa_set_error("sa_gpu_align_noalloc: anchor %lld (%lld, %lld) out of range or not strictly increasing",
+                             (long long) i, (long long) x3, (long long) y3);
+                return SA_ERR_INPUT;
+            }
+            if ((x3 - x2) * (y3 - y2) > p->splitMatrixBiggerThanThis) {
+                sa_set_error("sa_gpu_align_noalloc: the read has an anchor gap that getSplitPoints cuts at; use sa_gpu_align_batch");
+                return SA_ERR_INPUT;
+            }
+            if (i < R->nAnchors) {
+                g_hAnch[2 * i] = (int32_t) x3; g_hAnch[2 * i + 1] = (int32_t) y3;
+                x2 = x3 + 1; y2 = y3 + 1;
+            }
+        }
+    }
+    // rolling kmer index; every character must be in the alphabet (ambiguity codes need the general kernel)
+    {
+        int code[256];
+        for (int c = 0; c < 256; c++) {
+            const size_t j = m->alphabet.find((char) c);
+            code[c] = (c != 0 && j != std::string::npos) ? (int) j : -1;
+        }
+        const int64_t suffixK = m->K / m->A;
+        int64_t roll = 0;
+        for (int64_t i = 0; i < (lX > 0 ? R->targetLength : 0); i++) {
+            const int cc = code[(unsigned char) R->target[i]];
+            if (cc < 0) {
+                sa_set_error("sa_gpu_align_noalloc: character '%c' at reference position %lld is outside the alphabet %s "
+                             "(ambiguity codes: use sa_gpu_align_batch)", R->target[i], (long long) i, m->alphabet.c_str());
+                return SA_ERR_INPUT;
+            }
+            roll = (roll % suffixK) * m->A + cc;
+            if (i >= m->k - 1) g_hKmer[i - (m->k - 1)] = (int32_t) roll;
+        }
+    }
+    for (int64_t y = 0; y < lY; y++) g_hEv[y] = R->events[4 * y];
+    unsigned char *base = nullptr;
+    int rc = setup(dev, &base);
+    if (rc) return rc;
+    cudaStream_t st = 0;
+    const int64_t slotCap = std::min<int64_t>(kPairCap, 3 * lY + 64);
+
+    FItem fi;
+    memset(&fi, 0, sizeof(fi));
+    fi.nAnchors = (int32_t) R->nAnchors; fi.nTbCap = (int32_t) nTbCap;
+    fi.pairCap = slotCap;
+    fi.lX = (int32_t) lX; fi.lY = (int32_t) lY;
+    fi.flags = (R->raggedLeft ? 1 : 0) | (R->raggedRight ? 2 : 0);
+    fi.scale = R->scale; fi.shift = R->shift; fi.var = R->var;
+    fi.invVar = 1 / R->var;
+    fi.logInvVar = log((1 / R->var));
+
+    FParams f;
+    memset(&f, 0, sizeof(f));
+    f.items = (const FItem *) (base + oItem); f.nItems = 1;
+    f.counter = (int32_t *) (base + oCounter);
+    f.order = (const int32_t *) (base + oOrder); f.nOrder = 1;
+    f.evMean = (const double *) (base + oEv); f.kmerIdx = (const int32_t *) (base + oKmer);
+    f.anchors = (const int32_t *) (base + oAnch);
+    f.tb = (int32_t *) (base + oTb); f.geo = (FGeo *) (base + oGeo);
+    f.ft = m->dev->ft;
+    memcpy(f.trans, m->trans, sizeof(f.trans));
+    f.eX = m->gapX[0];
+    f.threshold = p->threshold;
+    f.logThrGate = p->threshold > 0 ? log(p->threshold) - 1e-6 : -INFINITY;
+    f.minDiags = (int32_t) p->minDiagsBetweenTraceBack; f.traceBack = (int32_t) p->traceBackDiagonals;
+    f.expansion = (int32_t) p->diagonalExpansion;
+    f.pairs = (sa_pair_t *) (base + oPairs); f.pairCount = (int64_t *) (base + oPairCount);
+    f.wPlanes = 3; f.wAllFull = 0; f.wGeoAlways = 1;
+    f.wNSW = kNSW; f.wRowsCap = (int32_t) kHdrCap; f.wRingDoubles = kRingDoubles;
+    f.scratch = (double *) (base + oRing); f.wHdr = (int4 *) (base + oHdr);
+
+    // what must start at zero: the work-queue counter, the item order (item 0) and the pair count (control block)
+    CK(cudaMemsetAsync(base, 0, oTb, st));
+    CK(cudaMemcpyAsync(base + oItem, &fi, sizeof(fi), cudaMemcpyHostToDevice, st));
+    if (lY > 0) CK(cudaMemcpyAsync(base + oEv, g_hEv, sizeof(double) * lY, cudaMemcpyHostToDevice, st));
+    if (lX > 0) CK(cudaMemcpyAsync(base + oKmer, g_hKmer, sizeof(int32_t) * lX, cudaMemcpyHostToDevice, st));
+    if (R->nAnchors > 0) CK(cudaMemcpyAsync(base + oAnch, g_hAnch, sizeof(int32_t) * 2 * R->nAnchors, cudaMemcpyHostToDevice, st));
+    sa_geometry_kernel<<<1, 32, 0, st>>>(f);
+    CK(cudaGetLastError());
+    FGeo geo;
+    CK(cudaMemcpyAsync(&geo, base + oGeo, sizeof(geo), cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    if (nDiag > 0) {
+        const int64_t ringNeed = geo.maxBlockDoubles + 2 * 256 * (int64_t) 3 * geo.maxWidth + 64;
+        if (geo.maxSpan + 24 > kNSW || geo.nTb > nTbCap || ringNeed > kRingDoubles || geo.maxRows + 260 > kHdrCap) {
+            sa_set_error("sa_gpu_align_noalloc: the read's band does not fit the static scratch (3 diagonals span %d columns, limit "
+                         "%d; forward rows of a traceback block need %lld doubles, limit %lld; %d rows, limit %lld): use "
+                         "sa_gpu_align_batch", geo.maxSpan, kNSW - 24, (long long) ringNeed, (long long) kRingDoubles,
+                         geo.maxRows, (long long) (kHdrCap - 260));
+            return SA_ERR_INPUT;
+        }
+    }
+    sa_wide_kernel<false, false, false><<<1, kNT, WideK<false, false, false>::smemBytes(kNSW, true), st>>>(f);
+    CK(cudaGetLastError());
+    int64_t n = 0;
+    CK(cudaMemcpyAsync(&n, base + oPairCount, sizeof(n), cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    *nPairsOut = n;
+    if (n > slotCap || n > pairCap) {
+        sa_set_error("sa_gpu_align_noalloc: the read produces %lld pairs; the caller's buffer holds %lld, the static slot %lld",
+                     (long long) n, (long long) pairCap, (long long) slotCap);
+        return SA_ERR_INPUT;
+    }
+    if (n > 0) {
+        CK(cudaMemcpyAsync(pairsOut, base + oPairs, sizeof(sa_pair_t) * n, cudaMemcpyDeviceToHost, st));
+        CK(cudaStreamSynchronize(st));
+        // the reference pops a region's list from its END (alignedPairCoordinateCorrectionFn, pairwiseAligner.c:2043-2050)
+        std::reverse(pairsOut, pairsOut + n);
+    }
+    return SA_OK;
+}
