@@ -296,7 +296,8 @@ struct sa_batch {
     struct StreamOwner {         // declared before every DevBuf: destroyed after their stream-ordered frees were queued
         cudaStream_t s = nullptr;
         ~StreamOwner() { if (s) cudaStreamDestroy(s); }
-    } streamOwner, auxOwner, latOwner;
+    } streamOwner, auxOwner, latOwner, wideOwner[5];
+    cudaEvent_t evWideJoin[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
     cudaStream_t stream = nullptr;  // the band kernels
     // everything else (H2D, geometry pass, compaction, D2H) on a HIGH-priority stream: when several batches are in
     // flight, these small kernels must overtake the not yet resident CTAs of another batch's persistent band kernel
@@ -370,6 +371,8 @@ struct sa_batch {
         if (evFork) cudaEventDestroy(evFork);
         if (evJoin) cudaEventDestroy(evJoin);
         if (evJoinSplit) cudaEventDestroy(evJoinSplit);
+        for (auto &e : evWideJoin)
+            if (e) cudaEventDestroy(e);
     }
 };
 
@@ -965,6 +968,14 @@ static int prepareBatch(const sa_model_t *m, const sa_read_t *reads, int64_t nRe
         if ((rc = b->dWRing[c].alloc((size_t) b->wBlocks[c] * b->wRingDoubles[c], st))) return rc;
         if ((rc = b->dWHdr[c].alloc((size_t) b->wBlocks[c] * b->wRows[c], st))) return rc;
         if (foldGlobal && (rc = b->dWFold[c].alloc((size_t) b->wBlocks[c] * 2 * kWideNSW[c], st))) return rc;
+        // a stream of its own per window class: the classes are separate persistent grids, and on one stream each would
+        // wait for the previous one's LAST item (a tail of one long read per SM) before its first CTA starts
+        if (!b->wideOwner[c].s) {
+            int prLo = 0, prHi = 0;
+            CK(cudaDeviceGetStreamPriorityRange(&prLo, &prHi));
+            CK(cudaStreamCreateWithPriority(&b->wideOwner[c].s, cudaStreamNonBlocking, prLo));
+            CK(cudaEventCreateWithFlags(&b->evWideJoin[c], cudaEventDisableTiming));
+        }
         if (gr && (rc = b->dWRings[c].alloc((size_t) b->wBlocks[c] * 6 * kWideNSW[c], st))) return rc;
     }
 
@@ -1128,8 +1139,15 @@ static int launchBatch(sa_batch_t *b) {
         CK(cudaGetLastError());
     }
     if (latStream) CK(cudaEventRecord(b->evJoin, b->lat));
+    bool wideFork = false;
+    static const bool wideOneStream = getenv("SA_WIDE_ONE_STREAM") != nullptr;
     for (int c = kWideClasses - 1; c >= 0; c--) {   // wide kernel, widest window first (the heaviest items)
         if (b->wOrder[c].empty()) continue;
+        cudaStream_t st = wideOneStream ? b->stream : b->wideOwner[c].s;
+        if (!wideOneStream) {
+            if (!wideFork) { CK(cudaEventRecord(b->evFork, b->stream)); wideFork = true; }
+            CK(cudaStreamWaitEvent(st, b->evFork, 0));
+        }
         const bool hdp = b->model->kind == SA_EMIT_HDP;
         FParams f = b->fp;
         f.order = b->dWOrder[c].p; f.nOrder = (int32_t) b->wOrder[c].size(); f.counter = b->dCounters.p + 8 + c;
@@ -1140,9 +1158,13 @@ static int launchBatch(sa_batch_t *b) {
                    wideSmemBytes(gr, kWideNSW[c], b->dWFold[c].p == nullptr), st, f);
         b->lastLaunches++;
         CK(cudaGetLastError());
+        if (!wideOneStream) CK(cudaEventRecord(b->evWideJoin[c], st));
     }
     for (int c = 3; c >= 0; c--) {             // widest class first; [ev0, ev1) = wide + W >= 4, [ev1, ev2) = W <= 2
         if (c == 1) {
+            if (!wideOneStream)
+                for (int wc = 0; wc < kWideClasses; wc++)
+                    if (!b->wOrder[wc].empty()) CK(cudaStreamWaitEvent(st, b->evWideJoin[wc], 0));
             if (latStream) CK(cudaStreamWaitEvent(st, b->evJoin, 0));   // counted with the 128-slot class
             if (!b->splitOrder.empty()) CK(cudaStreamWaitEvent(st, b->evJoinSplit, 0));
             CK(cudaEventRecord(b->ev[1], st));
