@@ -158,6 +158,28 @@ void sa_last_call_stats(int64_t *h2dBytes, int64_t *d2hBytes, int64_t *launches)
 int sa_gpu_expectations_batch(const sa_model_t *m, const sa_read_t *reads, int64_t nReads, const sa_params_t *p,
                               const sa_ambig_t *ambig, sa_result_t **out);
 
+/* Per-read scaling parameters for a batch of strands.
+ * Replaces: signalUtils_estimateNanoporeParams (impl/signalMachineUtils.c:186-225; call sites impl/signalMachine.c:778, 855)
+ * with assignmentFunction = signalUtils_templateOneDAssignmentsFromRead / ...complement... and the drift adjustment
+ * nanopore_adjust{Template,Complement}EventsForDrift: kmer <-> event assignments from the strand's event map
+ * (impl/nanopore.c:601-631), weighted least squares for shift / scale / drift and var (:756-826), for shift_sd / scale_sd /
+ * var_sd (:878-946), and `mean -= start_time * drift` on every event (:633-638) when adjustEvents != 0 (the mean column of
+ * the caller's events array is updated in place).  Results are bit-identical to the reference's (its summation order is
+ * kept).  The model's match table is used as loaded (call it before emissions_signal_scaleNoise, like the reference). */
+typedef struct {
+    const char *read;              /* base-called strand: NanoporeRead.templateRead / complementRead */
+    int64_t readLength;
+    const int64_t *strandEventMap; /* readLength entries: NanoporeRead.templateStrandEventMap / complementStrandEventMap */
+    double *events;                /* nEvents * 4 doubles: mean, sd, duration, start (NanoporeRead.templateEvents) */
+    int64_t nEvents;
+} sa_strand_t;
+typedef struct {                   /* NanoporeReadAdjustmentParameters (inc/nanopore.h:13-21) + the number of assignments */
+    double scale, shift, var, shift_sd, scale_sd, var_sd, drift;
+    int64_t nAssignments;
+} sa_scaling_t;
+int sa_gpu_estimate_params_batch(const sa_model_t *m, sa_strand_t *strands, int64_t nStrands, int adjustEvents,
+                                 sa_scaling_t *out);
+
 /* ONE read, NO device allocation.  This entry point has no counterpart in the reference: it was added
  * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,
  * harnesses that forbid it).  Same result as sa_gpu_align_batch on that read (the wide band kernel, 512-slot window):

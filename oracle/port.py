@@ -271,3 +271,22 @@ def kmer_id(kmer, alphabet):
 def emission(model, kmer_idx, mean, noise=1.0, match=True):
     m = model.cstruct()
     return lib().sao_emission(C.byref(m), kmer_idx, mean, noise, 1 if match else 0)
+
+
+def estimate_params(match_table, alphabet, k, read, event_map, events, adjust_events=True):
+    """signalUtils_estimateNanoporeParams (reference impl/signalMachineUtils.c:186-225) on one strand.
+
+    Returns (params dict, events after the drift adjustment, number of assignments); alphabet must be sorted."""
+    t = np.ascontiguousarray(match_table, np.float64)
+    em = np.ascontiguousarray(event_map, np.int64)
+    ev = np.array(events, np.float64, order="C", copy=True).reshape(-1, 4)
+    out = np.zeros(7)
+    L = lib()
+    L.sao_estimate_params.restype = C.c_int64
+    L.sao_estimate_params.argtypes = [c_f64p, C.c_char_p, C.c_int64, C.c_int64, C.c_char_p, C.c_int64, c_i64p, c_f64p,
+                                      C.c_int64, C.c_int, c_f64p]
+    rd = read.encode() if isinstance(read, str) else bytes(read)
+    n = L.sao_estimate_params(_f64(t), alphabet.encode(), len(alphabet), k, rd, len(rd), _i64(em), _f64(ev), ev.shape[0],
+                              int(adjust_events), _f64(out))
+    names = ["scale", "shift", "var", "shift_sd", "scale_sd", "var_sd", "drift"]
+    return dict(zip(names, out)), ev, int(n)

@@ -747,3 +747,120 @@ int64_t sao_align_noband(const sao_model *m, const char *target, int64_t lX, con
     ctx_free(&c);
     return n;
 }
+
+/* ------------------------------------------------------------------------------------------- per-read scaling
+ * signalUtils_estimateNanoporeParams (impl/signalMachineUtils.c:186-225) as signalMachine runs it before every alignment:
+ *   assignments ......... nanopore_getOneDAssignmentsFromRead, impl/nanopore.c:601-631: kmer i of the base-called read is
+ *                         paired with event map[i] whenever that event index exceeds every one taken so far
+ *   mean parameters ..... nanopore_compute_mean_scale_params(drift_out, var_out), :756-826: weighted least squares of the
+ *                         event mean on (1, level_mean, time), weights 1 / level_sd^2 -> shift, scale, drift; var = root of
+ *                         the mean squared weighted residual
+ *   noise parameters .... nanopore_compute_noise_scale_params, :878-946: the same in two unknowns on the event sd
+ *   solver .............. nanopore_lineq_solve, :691-748 (Gaussian elimination; the pivot swap is kept as written,
+ *                         including `x_out[swap] = x_out[i]`)
+ *   drift adjustment .... nanopore_adjustEventsForDriftP, :633-638: mean -= time * drift for EVERY event of the strand
+ * model: K x 5 match table (level_mean, level_sd, noise_mean, noise_sd, noise_lambda); events: n x 4 (mean, sd, duration,
+ * start time); out7 = scale, shift, var, shift_sd, scale_sd, var_sd, drift (NanoporeReadAdjustmentParameters order).
+ * Returns the number of assignments, or -1 when there are none / a kmer is outside the alphabet (the reference aborts). */
+#define SAO_MACHEP 1.11022302462515654042E-16 /* impl/hdp_math_utils.c / nanopore.c MACHEP */
+static int lineq_solve(const double *A, const double *b, double *x, int64_t n) {
+    double aux[9];
+    for (int64_t i = 0; i < n; i++) {
+        x[i] = b[i];
+        for (int64_t j = 0; j < n; j++) aux[i * n + j] = A[i * n + j];
+    }
+    for (int64_t i = 0; i < n; i++) {
+        if (fabs(aux[i * n + i]) < SAO_MACHEP) {
+            int64_t swap = i + 1;
+            if (swap >= n) return -1;
+            while (aux[swap * n + i] < SAO_MACHEP) {
+                swap++;
+                if (swap >= n) return -1;
+            }
+            for (int64_t j = 0; j < n; j++) {
+                double t = aux[i * n + j];
+                aux[i * n + j] = aux[swap * n + j];
+                aux[swap * n + j] = t;
+            }
+            x[i] = x[swap];
+            x[swap] = x[i];
+        }
+        double factor = 1.0 / aux[i * n + i];
+        x[i] *= factor;
+        for (int64_t j = 0; j < n; j++) aux[i * n + j] *= factor;
+        for (int64_t sub = i + 1; sub < n; sub++) {
+            factor = aux[sub * n + i];
+            x[sub] -= factor * x[i];
+            for (int64_t j = 0; j < n; j++) aux[sub * n + j] -= factor * aux[i * n + j];
+        }
+    }
+    for (int64_t i = n - 1; i >= 0; i--)
+        for (int64_t sub = i - 1; sub >= 0; sub--) {
+            double factor = aux[sub * n + i];
+            x[sub] -= factor * x[i];
+            for (int64_t j = 0; j < n; j++) aux[sub * n + j] -= factor * aux[i * n + j];
+        }
+    return 0;
+}
+
+int64_t sao_estimate_params(const double *model, const char *alphabet, int64_t alphabetSize, int64_t k, const char *read,
+                            int64_t readLength, const int64_t *eventMap, double *events, int64_t nEvents, int adjustEvents,
+                            double *out7) {
+    int64_t rows = readLength - (k - 1), n = 0, prev = -1;
+    if (rows <= 0) return -1;
+    double *ev = malloc(sizeof(double) * rows), *sd = malloc(sizeof(double) * rows), *tm = malloc(sizeof(double) * rows);
+    int64_t *id = malloc(sizeof(int64_t) * rows);
+    for (int64_t i = 0; i < rows; i++) {
+        int64_t e = eventMap[i];
+        int64_t ki = sao_kmer_id(read + i, alphabet, alphabetSize, k);
+        if (ki < 0) { free(ev); free(sd); free(tm); free(id); return -1; }
+        if (e > prev) {
+            ev[n] = events[4 * e]; sd[n] = events[4 * e + 1]; tm[n] = events[4 * e + 3]; id[n] = ki;
+            n++;
+            prev = e;
+        }
+    }
+    if (n == 0) { free(ev); free(sd); free(tm); free(id); return -1; }
+    double XWX[9] = {0}, XWy[3] = {0}, beta[3];
+    for (int64_t i = 0; i < n; i++) {
+        double level_mean = model[id[i] * 5], level_sd = model[id[i] * 5 + 1];
+        double inv_var = 1.0 / (level_sd * level_sd);
+        double scaled_mean = level_mean * inv_var, scaled_time = tm[i] * inv_var;
+        XWX[0] += inv_var; XWX[1] += scaled_mean; XWX[2] += scaled_time;
+        XWX[4] += scaled_mean * level_mean; XWX[5] += scaled_mean * tm[i]; XWX[8] += scaled_time * tm[i];
+        XWy[0] += inv_var * ev[i]; XWy[1] += scaled_mean * ev[i]; XWy[2] += scaled_time * ev[i];
+    }
+    XWX[3] = XWX[1]; XWX[6] = XWX[2]; XWX[7] = XWX[5];
+    int bad = lineq_solve(XWX, XWy, beta, 3);
+    out7[1] = beta[0]; out7[0] = beta[1]; out7[6] = beta[2];
+    double disp = 0.0;
+    for (int64_t i = 0; i < n; i++) {
+        double level_mean = model[id[i] * 5], level_sd = model[id[i] * 5 + 1];
+        double predicted = beta[0] + beta[1] * level_mean + beta[2] * tm[i];
+        double residual = ev[i] - predicted;
+        disp += (residual * residual) / (level_sd * level_sd);
+    }
+    out7[2] = sqrt(disp / n);
+    double NWX[4] = {0}, NWy[2] = {0}, nb[2];
+    for (int64_t i = 0; i < n; i++) {
+        double noise_mean = model[id[i] * 5 + 2], noise_sd = model[id[i] * 5 + 3];
+        double inv_var = 1.0 / (noise_sd * noise_sd);
+        double scaled_mean = noise_mean * inv_var;
+        NWX[0] += inv_var; NWX[1] += scaled_mean; NWX[3] += scaled_mean * noise_mean;
+        NWy[0] += inv_var * sd[i]; NWy[1] += scaled_mean * sd[i];
+    }
+    NWX[2] = NWX[1];
+    bad |= lineq_solve(NWX, NWy, nb, 2);
+    out7[3] = nb[0]; out7[4] = nb[1];
+    disp = 0.0;
+    for (int64_t i = 0; i < n; i++) {
+        double noise_mean = model[id[i] * 5 + 2], noise_sd = model[id[i] * 5 + 3];
+        double residual = sd[i] - (nb[0] + nb[1] * noise_mean);
+        disp += (residual * residual) / (noise_sd * noise_sd);
+    }
+    out7[5] = sqrt(disp / n);
+    if (adjustEvents)
+        for (int64_t i = 0; i < nEvents; i++) events[4 * i] = events[4 * i] - events[4 * i + 3] * out7[6];
+    free(ev); free(sd); free(tm); free(id);
+    return bad ? -1 : n;
+}

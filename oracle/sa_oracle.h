@@ -99,4 +99,9 @@ int64_t sao_align_noband(const sao_model *m, const char *target, int64_t lX, con
 #ifdef __cplusplus
 }
 #endif
+/* signalUtils_estimateNanoporeParams (impl/signalMachineUtils.c:186-225): see sa_oracle.c */
+int64_t sao_estimate_params(const double *model, const char *alphabet, int64_t alphabetSize, int64_t k, const char *read,
+                            int64_t readLength, const int64_t *eventMap, double *events, int64_t nEvents, int adjustEvents,
+                            double *out7);
+
 #endif

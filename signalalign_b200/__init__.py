@@ -39,6 +39,16 @@ class SaPair(C.Structure):
     _fields_ = [("p", C.c_int32), ("x", C.c_int32), ("y", C.c_int32), ("kmerIdx", C.c_int32)]
 
 
+class SaStrand(C.Structure):
+    _fields_ = [("read", C.c_char_p), ("readLength", C.c_int64), ("strandEventMap", c_i64p), ("events", c_f64p),
+                ("nEvents", C.c_int64)]
+
+
+class SaScaling(C.Structure):
+    _fields_ = [("scale", C.c_double), ("shift", C.c_double), ("var", C.c_double), ("shift_sd", C.c_double),
+                ("scale_sd", C.c_double), ("var_sd", C.c_double), ("drift", C.c_double), ("nAssignments", C.c_int64)]
+
+
 class SaResult(C.Structure):
     _fields_ = [("nReads", C.c_int64), ("pairOffsets", c_i64p), ("pairs", C.POINTER(SaPair)),
                 ("transitions", c_f64p), ("likelihood", c_f64p), ("assignOffsets", c_i64p),
@@ -57,7 +67,7 @@ EXPORTS = [
     "sa_result_sum_expectations", "sa_debug_logadd", "sa_model_hdp_dims", "sa_model_get_hdp", "sa_debug_band",
     "sa_debug_split_points", "sa_debug_kmer_paths", "sa_last_call_stats", "sa_set_host_threads",
     "sa_gpu_comm_unique_id", "sa_gpu_comm_init", "sa_gpu_comm_from_nccl", "sa_gpu_comm_free",
-    "sa_gpu_allreduce_expectations", "sa_gpu_allgather_assignments", "sa_gpu_align_noalloc",
+    "sa_gpu_allreduce_expectations", "sa_gpu_allgather_assignments", "sa_gpu_align_noalloc", "sa_gpu_estimate_params_batch",
 ]
 
 _lib = None
@@ -126,6 +136,7 @@ def lib():
     L.sa_batch_wide_items.argtypes = [C.c_void_p, c_i64p]
     L.sa_batch_free.argtypes = [C.c_void_p]
     L.sa_gpu_align_noalloc.argtypes = [C.c_void_p, C.POINTER(SaRead), C.POINTER(SaParams), C.POINTER(SaPair), C.c_int64, c_i64p]
+    L.sa_gpu_estimate_params_batch.argtypes = [C.c_void_p, C.POINTER(SaStrand), C.c_int64, C.c_int, C.POINTER(SaScaling)]
     L.sa_gpu_comm_unique_id.argtypes = [C.c_void_p]
     L.sa_gpu_comm_init.argtypes = [C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_void_p)]
     L.sa_gpu_comm_from_nccl.argtypes = [C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_void_p)]
@@ -384,6 +395,25 @@ def align_noalloc(model, read, params=None, pair_cap=None):
     _check(lib().sa_gpu_align_noalloc(model.h, C.byref(rs), C.byref(params), C.cast(out.ctypes.data, C.POINTER(SaPair)), cap,
                                       C.byref(n)))
     return out[:n.value].copy()
+
+
+def estimate_params_batch(model, strands, adjust_events=True):
+    """signalUtils_estimateNanoporeParams for a batch: strands = [(read string, event map int64[len(read)], events [n, 4])].
+
+    Returns (list of dicts scale / shift / var / shift_sd / scale_sd / var_sd / drift / n_assignments, list of the events
+    arrays after the drift adjustment)."""
+    keep, arr = [], (SaStrand * max(1, len(strands)))()
+    for i, (read, emap, events) in enumerate(strands):
+        rd = read.encode() if isinstance(read, str) else bytes(read)
+        em = np.ascontiguousarray(emap, np.int64)
+        ev = np.array(events, np.float64, order="C", copy=True).reshape(-1, 4)
+        keep.append((rd, em, ev))
+        arr[i] = SaStrand(rd, len(rd), em.ctypes.data_as(c_i64p), ev.ctypes.data_as(c_f64p), ev.shape[0])
+    out = (SaScaling * max(1, len(strands)))()
+    _check(lib().sa_gpu_estimate_params_batch(model.h, arr, len(strands), int(adjust_events), out))
+    names = ["scale", "shift", "var", "shift_sd", "scale_sd", "var_sd", "drift"]
+    params = [dict({k: getattr(out[i], k) for k in names}, n_assignments=out[i].nAssignments) for i in range(len(strands))]
+    return params, [k[2] for k in keep]
 
 
 def expectations_batch(model, reads, params=None, ambig=None):

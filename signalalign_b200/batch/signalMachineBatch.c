@@ -15,7 +15,9 @@
  * -Dmain=signalMachine_cli_main so that its writers and helpers link here (`make -C oracle cli`).
  *
  *   signalMachineBatch --manifest reads.tsv -T template.model [-v template.nhdp] [-s 0|1|2] [-x 50] [-D 0.01] [-m 14]
- *                      [-g 50] [-a ambig.tsv] [--batch 2048] [--rna]
+ *                      [-g 50] [-a ambig.tsv] [--batch 2048] [--rna] [--host-estimate]
+ *   the per-read scale / shift / var / drift re-estimation (signalUtils_estimateNanoporeParams) runs on the device for the
+ *   whole batch at once (sa_gpu_estimate_params_batch, bit-identical); --host-estimate keeps the reference's function
  *   manifest line:  npRead <TAB> guide cigar file <TAB> forward reference FASTA <TAB> sequence name <TAB> read label <TAB> output file
  *
  * 1-D (template strand) reads; 2-D complement alignment and the expectations pass stay with `signalMachine`.
@@ -63,7 +65,7 @@ static char *field(char **cursor) {
 
 /* everything impl/signalMachine.c:main does for one read before performSignalAlignment (:650-760, :848-861) */
 static void prepareRead(BatchRead *b, StateMachine *sM, NanoporeHDP *nHdp, const double *pristineMatch,
-                        const double *pristineGapY, PairwiseAlignmentParameters *p, bool rna) {
+                        const double *pristineGapY, PairwiseAlignmentParameters *p, bool rna, bool hostEstimate) {
     if (!stFile_exists(b->cigarFile)) st_errAbort("[signalMachineBatch]ERROR: no guide alignment %s\n", b->cigarFile);
     FILE *fh = fopen(b->cigarFile, "r");
     struct PairwiseAlignment *pA = cigarRead(fh);
@@ -89,8 +91,9 @@ static void prepareRead(BatchRead *b, StateMachine *sM, NanoporeHDP *nHdp, const
     sM->scale = b->npRead->templateParams.scale;
     sM->shift = b->npRead->templateParams.shift;
     sM->var = b->npRead->templateParams.var;
-    signalUtils_estimateNanoporeParams(sM, b->npRead, &b->npRead->templateParams, ASSIGNMENT_THRESHOLD,
-                                       signalUtils_templateOneDAssignmentsFromRead, nanopore_adjustTemplateEventsForDrift);
+    if (hostEstimate)
+        signalUtils_estimateNanoporeParams(sM, b->npRead, &b->npRead->templateParams, ASSIGNMENT_THRESHOLD,
+                                           signalUtils_templateOneDAssignmentsFromRead, nanopore_adjustTemplateEventsForDrift);
     if (sM->type == threeStateHdp) stateMachine3_setModelToHdpExpectedValues(sM, nHdp);
     b->scale = sM->scale; b->shift = sM->shift; b->var = sM->var;
     b->anchors = signalUtils_getRemappedAnchorPairs(guide, b->npRead->templateStrandEventMap, pA->start2);
@@ -118,7 +121,7 @@ static void releaseRead(BatchRead *b) {
 int main(int argc, char *argv[]) {
     int64_t diagExpansion = 50, constraintTrim = 14, traceBackDiagonals = 50, outFmt = 0, batchSize = 2048;
     double threshold = 0.01;
-    bool rna = FALSE;
+    bool rna = FALSE, hostEstimate = FALSE;
     char *manifest = NULL, *modelFile = NULL, *hdpFile = NULL, *ambigFile = NULL;
     static struct option longOptions[] = {
         {"manifest", required_argument, 0, 'M'}, {"templateModel", required_argument, 0, 'T'},
@@ -126,9 +129,9 @@ int main(int argc, char *argv[]) {
         {"diagonalExpansion", required_argument, 0, 'x'}, {"threshold", required_argument, 0, 'D'},
         {"constraintTrim", required_argument, 0, 'm'}, {"traceBackDiagonals", required_argument, 0, 'g'},
         {"ambig_model", required_argument, 0, 'a'}, {"batch", required_argument, 0, 'B'}, {"rna", no_argument, 0, 'r'},
-        {0, 0, 0, 0}};
+        {"host-estimate", no_argument, 0, 'H'}, {0, 0, 0, 0}};
     int key;
-    while ((key = getopt_long(argc, argv, "M:T:v:s:x:D:m:g:a:B:r", longOptions, NULL)) != -1) {
+    while ((key = getopt_long(argc, argv, "M:T:v:s:x:D:m:g:a:B:rH", longOptions, NULL)) != -1) {
         switch (key) {
             case 'M': manifest = stString_copy(optarg); break;
             case 'T': modelFile = stString_copy(optarg); break;
@@ -141,6 +144,7 @@ int main(int argc, char *argv[]) {
             case 'g': traceBackDiagonals = atoll(optarg); break;
             case 'B': batchSize = atoll(optarg); break;
             case 'r': rna = TRUE; break;
+            case 'H': hostEstimate = TRUE; break;
             default:
                 fprintf(stderr, "usage: signalMachineBatch --manifest reads.tsv -T model [-v nhdp] [-s 0|1|2] [-x n] [-D thr] "
                                 "[-m trim] [-g traceBack] [-a ambig] [--batch n] [--rna]\n");
@@ -189,6 +193,10 @@ int main(int argc, char *argv[]) {
     BatchRead *reads = st_calloc(batchSize, sizeof(BatchRead));
     sa_read_t *flat = st_calloc(batchSize, sizeof(sa_read_t));
     sa_model_t *model = NULL;
+    /* the estimation reads the match table AS LOADED (before scaleNoise / the HDP's expected values touch it) */
+    sa_model_t *estModel = hostEstimate ? NULL : sa_shim_model(sM);
+    sa_strand_t *strands = st_calloc(batchSize, sizeof(sa_strand_t));
+    sa_scaling_t *scalings = st_calloc(batchSize, sizeof(sa_scaling_t));
     int64_t done = 0;
     while (done < nReads) {
         const int64_t n = nReads - done < batchSize ? nReads - done : batchSize;
@@ -199,10 +207,30 @@ int main(int argc, char *argv[]) {
             b->npReadFile = field(&cursor); b->cigarFile = field(&cursor); b->fasta = field(&cursor);
             b->seqName = field(&cursor); b->label = field(&cursor); b->out = field(&cursor);
             if (!b->out) st_errAbort("[signalMachineBatch]ERROR: manifest line %lld needs 6 tab-separated fields\n", (long long) (done + i + 1));
-            prepareRead(b, sM, nHdp, pristineMatch, pristineGapY, p, rna);
+            prepareRead(b, sM, nHdp, pristineMatch, pristineGapY, p, rna, hostEstimate);
+            strands[i].read = b->npRead->templateRead;
+            strands[i].readLength = b->npRead->templateReadLength;
+            strands[i].strandEventMap = b->npRead->templateStrandEventMap;
+            strands[i].events = b->npRead->templateEvents;
+            strands[i].nEvents = b->npRead->nbTemplateEvents;
             /* the device model: the emission the path reads is columns 0 / 1 of the tables (and the HDP), which the per-read
              * noise scaling never touches, so one upload serves every read */
             if (!model) model = sa_shim_model(sM);
+        }
+        if (!hostEstimate) {
+            /* signalUtils_estimateNanoporeParams for the whole batch: parameters into every read's templateParams, event
+             * means drift-adjusted in place (impl/signalMachineUtils.c:186-225) */
+            if (sa_gpu_estimate_params_batch(estModel, strands, n, 1, scalings) != SA_OK) st_errAbort("libsagpu: %s\n", sa_last_error());
+            for (int64_t i = 0; i < n; i++) {
+                NanoporeReadAdjustmentParameters *q = &reads[i].npRead->templateParams;
+                q->scale = scalings[i].scale; q->shift = scalings[i].shift; q->var = scalings[i].var;
+                q->shift_sd = scalings[i].shift_sd; q->scale_sd = scalings[i].scale_sd; q->var_sd = scalings[i].var_sd;
+                q->drift = scalings[i].drift;
+                reads[i].scale = q->scale; reads[i].shift = q->shift; reads[i].var = q->var;
+            }
+        }
+        for (int64_t i = 0; i < n; i++) {
+            BatchRead *b = &reads[i];
             char *target = b->R->getTemplateTargetSequence(b->R);
             memset(&flat[i], 0, sizeof(sa_read_t));
             flat[i].target = target;

@@ -17,6 +17,7 @@
 #include "sa_fast.cuh"
 #include "sa_cta.cuh"
 #include "sa_wide.cuh"
+#include "sa_estimate.cuh"
 
 #define CK(call)                                                                                   \
     do {                                                                                           \
@@ -31,12 +32,13 @@
 struct DeviceModel {
     double *kt = nullptr, *ft = nullptr, *gapX = nullptr, *grid = nullptr, *pp = nullptr, *slopes = nullptr;
     int32_t *kmerToRow = nullptr;
+    double *raw = nullptr;     // K x 5 match table as loaded (per-read parameter estimation, sa_estimate.cuh); uploaded on first use
 };
 
 void sa_model_drop_device(const sa_model *m) {
     if (!m->dev) return;
     cudaFree(m->dev->kt); cudaFree(m->dev->ft); cudaFree(m->dev->gapX); cudaFree(m->dev->grid); cudaFree(m->dev->pp);
-    cudaFree(m->dev->slopes); cudaFree(m->dev->kmerToRow);
+    cudaFree(m->dev->slopes); cudaFree(m->dev->kmerToRow); cudaFree(m->dev->raw);
     delete m->dev;
     m->dev = nullptr;
     m->devDevice = -1;
@@ -1664,6 +1666,119 @@ extern "C" int sa_gpu_align_batch(const sa_model_t *m, const sa_read_t *reads, i
 extern "C" int sa_gpu_expectations_batch(const sa_model_t *m, const sa_read_t *reads, int64_t nReads,
                                          const sa_params_t *p, const sa_ambig_t *ambig, sa_result_t **out) {
     return runBatch(m, reads, nReads, p, ambig, 1, out);
+}
+
+// ================================================================================================ per-read scaling (N2)
+// signalUtils_estimateNanoporeParams (reference impl/signalMachineUtils.c:186-225) for a batch of strands: see
+// sa_estimate.cuh.  Host side: pack the strands (three event columns as arrays, the event map as int32), one kernel, copy
+// the 8 doubles per strand and — when the events are to be drift-adjusted — the mean column back into the caller's events.
+extern "C" int sa_gpu_estimate_params_batch(const sa_model_t *m, sa_strand_t *strands, int64_t n, int adjustEvents,
+                                            sa_scaling_t *out) {
+    if (sa_gpu_device_count() == 0) {
+        sa_set_error("sa_gpu_estimate_params_batch: no CUDA device available; libsagpu has no CPU fallback");
+        return SA_ERR_CUDA;
+    }
+    if (n <= 0) return SA_OK;
+    int rc = uploadModel(m);
+    if (rc) return rc;
+    if (!m->dev->raw) {
+        CK(cudaMalloc(&m->dev->raw, sizeof(double) * m->match.size()));
+        CK(cudaMemcpy(m->dev->raw, m->match.data(), sizeof(double) * m->match.size(), cudaMemcpyHostToDevice));
+    }
+    if ((rc = poolInit())) return rc;
+    std::vector<EstStrand> es((size_t) n);
+    int64_t rt = 0, et = 0;
+    for (int64_t i = 0; i < n; i++) {
+        const sa_strand_t &S = strands[i];
+        if (S.readLength < 0 || S.nEvents < 0 || S.readLength > 0x3fffffff || S.nEvents > 0x3fffffff) {
+            sa_set_error("sa_gpu_estimate_params_batch: strand %lld: bad lengths", (long long) i);
+            return SA_ERR_INPUT;
+        }
+        es[(size_t) i].readOff = rt; es[(size_t) i].mapOff = rt; es[(size_t) i].evOff = et;
+        es[(size_t) i].readLength = (int32_t) S.readLength; es[(size_t) i].nEvents = (int32_t) S.nEvents;
+        rt += S.readLength; et += S.nEvents;
+    }
+    PinVec<char> hRead;
+    PinVec<int32_t> hMap;
+    PinVec<double> hMean, hSd, hTime, hOut;
+    if (!hRead.resize((size_t) std::max<int64_t>(1, rt)) || !hMap.resize((size_t) std::max<int64_t>(1, rt)) ||
+        !hMean.resize((size_t) std::max<int64_t>(1, et)) || !hSd.resize((size_t) std::max<int64_t>(1, et)) ||
+        !hTime.resize((size_t) std::max<int64_t>(1, et)) || !hOut.resize((size_t) n * 8)) {
+        sa_set_error("sa_gpu_estimate_params_batch: cannot allocate pinned staging memory");
+        return SA_ERR_CUDA;
+    }
+    bool mapBad = false;
+#pragma omp parallel for schedule(dynamic, 8) reduction(|| : mapBad)
+    for (int64_t i = 0; i < n; i++) {
+        const sa_strand_t &S = strands[i];
+        const EstStrand &E = es[(size_t) i];
+        memcpy(hRead.data() + E.readOff, S.read, (size_t) S.readLength);
+        for (int64_t q = 0; q < S.readLength; q++) {
+            const int64_t e = S.strandEventMap[q];
+            mapBad = mapBad || e < 0 || e > 0x7fffffff;
+            hMap[(size_t) (E.mapOff + q)] = (int32_t) e;
+        }
+        for (int64_t y = 0; y < S.nEvents; y++) {
+            hMean[(size_t) (E.evOff + y)] = S.events[4 * y];
+            hSd[(size_t) (E.evOff + y)] = S.events[4 * y + 1];
+            hTime[(size_t) (E.evOff + y)] = S.events[4 * y + 3];
+        }
+    }
+    if (mapBad) {
+        sa_set_error("sa_gpu_estimate_params_batch: negative entry in a strand event map");
+        return SA_ERR_INPUT;
+    }
+    cudaStream_t st;
+    CK(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
+    struct StreamGuard { cudaStream_t s; ~StreamGuard() { cudaStreamSynchronize(s); cudaStreamDestroy(s); } } guard{st};
+    DevBuf<EstStrand> dS;
+    DevBuf<char> dRead;
+    DevBuf<int32_t> dMap, dErr;
+    DevBuf<double> dMean, dSd, dTime, dOut;
+    int64_t bytes = 0;
+    if ((rc = dS.upload(es, st, &bytes)) || (rc = dRead.upload(hRead, st, &bytes)) || (rc = dMap.upload(hMap, st, &bytes)) ||
+        (rc = dMean.upload(hMean, st, &bytes)) || (rc = dSd.upload(hSd, st, &bytes)) || (rc = dTime.upload(hTime, st, &bytes)) ||
+        (rc = dOut.alloc((size_t) n * 8, st)) || (rc = dErr.alloc(1, st)))
+        return rc;
+    CK(cudaMemsetAsync(dErr.p, 0, sizeof(int32_t), st));
+    CK(cudaMemsetAsync(dOut.p, 0, sizeof(double) * n * 8, st));
+    EstParams P;
+    memset(&P, 0, sizeof(P));
+    P.strands = dS.p; P.reads = dRead.p; P.maps = dMap.p; P.mean = dMean.p; P.sd = dSd.p; P.time = dTime.p;
+    P.table = m->dev->raw;
+    for (int c = 0; c < 256; c++) {
+        const size_t j = m->alphabet.find((char) c);
+        P.code[c] = (c != 0 && j != std::string::npos) ? (int32_t) j : -1;
+    }
+    P.A = m->A; P.k = m->k; P.adjust = adjustEvents ? 1 : 0;
+    P.out = dOut.p; P.err = dErr.p;
+    sa_estimate_kernel<256><<<(unsigned) n, 256, 0, st>>>(P);
+    CK(cudaGetLastError());
+    int32_t err = 0;
+    CK(cudaMemcpyAsync(hOut.data(), dOut.p, sizeof(double) * n * 8, cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(&err, dErr.p, sizeof(err), cudaMemcpyDeviceToHost, st));
+    if (adjustEvents && et > 0) CK(cudaMemcpyAsync(hMean.data(), dMean.p, sizeof(double) * et, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    if (err) {
+        sa_set_error(err == 1 ? "sa_gpu_estimate_params_batch: a base-called strand contains a character outside the alphabet "
+                                "(the reference exits in kmer_to_word, nanopore_hdp.c:393-398)"
+                   : err == 3 ? "sa_gpu_estimate_params_batch: a strand event map points past the strand's events"
+                              : "sa_gpu_estimate_params_batch: a strand has no assignments or a singular system (the reference "
+                                "aborts: nanopore.c:762, :700)");
+        return SA_ERR_INPUT;
+    }
+    for (int64_t i = 0; i < n; i++) {
+        const double *o = hOut.data() + i * 8;
+        sa_scaling_t &q = out[i];
+        q.scale = o[0]; q.shift = o[1]; q.var = o[2]; q.shift_sd = o[3]; q.scale_sd = o[4]; q.var_sd = o[5]; q.drift = o[6];
+        q.nAssignments = (int64_t) o[7];
+    }
+    if (adjustEvents) {
+#pragma omp parallel for schedule(dynamic, 8)
+        for (int64_t i = 0; i < n; i++)
+            for (int64_t y = 0; y < strands[i].nEvents; y++) strands[i].events[4 * y] = hMean[(size_t) (es[(size_t) i].evOff + y)];
+    }
+    return SA_OK;
 }
 
 // ================================================================================================ allocation-free call

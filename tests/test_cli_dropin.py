@@ -128,6 +128,10 @@ def test_signalmachinebatch_manifest_writes_the_same_files():
         assert all(l.startswith("r9read 6514\t") for l in stdout.strip().splitlines())
         outs, _ = run(2, [inp["fasta"]])
         _compare_tsv("assignments", outs[0], cc.read_golden("assignments"))
+        # the scaling re-estimation runs on the device by default (bit-identical): the reference's host function gives the
+        # same bytes
+        host, _ = run(0, [inp["fasta"]], extra=["--host-estimate"])
+        assert host[0] == run(0, [inp["fasta"]])[0][0]
         outs, _ = run(1, [inp["fasta_variants"], inp["fasta"]])
         _compare_tsv("variantCaller_default_table", outs[0], cc.read_golden("variantCaller_default_table"))
         assert outs[1] == ""                                                      # no ambiguity code: nothing to report
