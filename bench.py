@@ -32,6 +32,7 @@ WORKLOAD = ("config3-synthetic: ~10k-event reads vs synthetic reference, ACGT 6-
 EXPANSION, TRACE_BACK, MIN_DIAGS, THRESHOLD = 100, 50, 1000, 0.01
 # guide anchors: SURVEY.md 8(d)'s generator (signalalign_b200/synth.py ANCHOR_PATTERNS); --anchors picks another pattern
 ANCHOR_PATTERN = "contract"
+CPU_EXPECTATIONS = False     # --workload config4: the CPU arm times getExpectationsUsingAnchors
 from signalalign_b200.synth import ANCHOR_PATTERNS  # noqa: E402  (numpy only)
 GEN = dict(ANCHOR_PATTERNS[ANCHOR_PATTERN])
 
@@ -52,7 +53,17 @@ def parse():
     ap.add_argument("--anchors", default=ANCHOR_PATTERN, choices=sorted(ANCHOR_PATTERNS),
                     help="guide-anchor pattern of the synthetic reads (default: SURVEY 8d's)")
     ap.add_argument("--no-dense", action="store_true", help="skip the secondary figure on round 1's dense anchor pattern")
+    ap.add_argument("--strong", action="store_true",
+                    help="strong scaling: ONE read set of --reads reads (same seed on every rank) split across the ranks by "
+                         "signalalign_b200.shard.partition_lpt (longest-processing-time-first on estimated band cells); the "
+                         "default is weak scaling (every rank its own --reads reads)")
+    ap.add_argument("--workload", default="config3", choices=["config3", "config4", "config5"],
+                    help="config3 (default, BASELINE's headline): alignment of ~10k-event reads, 6-mer Gaussian table; config4: "
+                         "the expectations pass (getExpectationsUsingAnchors) on the same reads; config5: 5-mer table, HDP "
+                         "emission (synthetic spline tables), log-normal read lengths (median ~20k events, tail to 400k)")
     a = ap.parse_args()
+    global CPU_EXPECTATIONS
+    CPU_EXPECTATIONS = a.workload == "config4"
     GEN.clear()
     GEN.update(ANCHOR_PATTERNS[a.anchors])
     return a
@@ -77,8 +88,9 @@ def _cpu_worker(args):
         sm = ref.RefStateMachine(model_path, kind=0)
         for r in reads:
             sm.set_scaling(r["scale"], r["shift"], r["var"])
-            sm.align(r["target"], r["events"], r["anchors"], threshold=THRESHOLD, min_diags=MIN_DIAGS,
-                     trace_back=TRACE_BACK, expansion=EXPANSION)
+            fn = sm.expectations if CPU_EXPECTATIONS else sm.align
+            fn(r["target"], r["events"], r["anchors"], threshold=THRESHOLD, min_diags=MIN_DIAGS,
+               trace_back=TRACE_BACK, expansion=EXPANSION)
     else:
         from oracle import port
         pm = port.load_model_file(model_path)
@@ -205,9 +217,37 @@ def main():
     host_threads = max(1, (os.cpu_count() or 1) // max(1, int(os.environ.get("LOCAL_WORLD_SIZE", world))))
     sa.set_host_threads(host_threads)
 
-    reads_d, table = synth.make_batch(a.reads, seed=a.seed + 1000 * rank, **GEN)
     trans = synth.nanopore_transitions()
-    model = sa.Model.from_tables("ACGT", 6, trans, table)
+    expect = a.workload == "config4"
+    if a.workload == "config5":
+        # RNA-like: ~1.3 events per nt, median 20 k events; the RNA .nhdp of BASELINE config 5 is absent from the reference
+        # snapshot: spline tables of the same shape (one row per kmer, 1200 grid points, two-component mixtures)
+        if a.reads == 4736:
+            a.reads = 768
+        reads_d, table = synth.make_batch(a.reads, seed=a.seed + 1 + 1000 * rank, alphabet="ACGT", k=5, ref_len=3_000_000,
+                                          mean_len=15400, sigma_len=1.35, min_len=770, max_len=300000,
+                                          n_probs=(0.05, 0.70, 0.18, 0.07), **GEN)
+        model = sa.Model.from_tables("ACGT", 5, trans, table, kind=sa.EMIT_HDP)
+        grid = np.linspace(50.0, 140.0, 1200)
+        mu = table[:, 0]
+        pp = 0.7 * np.exp(-0.5 * ((grid[None, :] - mu[:, None]) / 2.0) ** 2) / (2.0 * np.sqrt(2 * np.pi)) + \
+            0.3 * np.exp(-0.5 * ((grid[None, :] - mu[:, None] - 3.0) / 4.0) ** 2) / (4.0 * np.sqrt(2 * np.pi))
+        model.set_hdp(grid, np.arange(table.shape[0], dtype=np.int32), pp, np.gradient(pp, grid, axis=1))
+        a.no_cpu = a.no_dense = a.no_expectations = True
+    else:
+        reads_d, table = synth.make_batch(a.reads, seed=a.seed + (0 if a.strong else 1000 * rank), **GEN)
+        model = sa.Model.from_tables("ACGT", 6, trans, table)
+    shard_info = None
+    if a.strong and world > 1:
+        from signalalign_b200 import shard
+        work = [shard.estimate_band_cells(max(0, len(r["target"]) - 5), r["events"].shape[0], EXPANSION) for r in reads_d]
+        parts = shard.partition_lpt(work, world)
+        loads = [int(sum(work[i] for i in part)) for part in parts]
+        shard_info = {"reads_total": len(reads_d), "reads_per_rank": [len(q) for q in parts],
+                      "estimated_load_imbalance": max(loads) / (sum(loads) / world)}
+        reads_d = [reads_d[i] for i in parts[rank]]
+    if expect:
+        a.no_dense = a.no_expectations = True
     p = sa.default_params(threshold=THRESHOLD, expansion=EXPANSION, trace_back=TRACE_BACK, min_diags=MIN_DIAGS)
     reads = [sa.Read(r["target"], r["events"], r["anchors"], r["scale"], r["shift"], r["var"]) for r in reads_d]
     events = sum(r.events.shape[0] for r in reads)
@@ -221,8 +261,9 @@ def main():
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
 
     # ---- resident arm: inputs in HBM before the timed region
-    batch = sa.Batch(model, reads, p)
+    batch = sa.Batch(model, reads, p, expectations=expect)
     cells = batch.band_cells
+    batch_h2d = batch.h2d_bytes
     kernel_items, wide_items = batch.kernel_items, batch.wide_items
     n_diag = sum(len(r.target) - 5 + r.events.shape[0] + 1 for r in reads)
     for _ in range(a.warmup):
@@ -248,7 +289,10 @@ def main():
     step_ms = float(np.sum(dev_ms)) / a.steps
     res = batch.fetch()
     n_pairs = int(res.pair_offsets[-1])
-    pairs_digest = [int(res.pairs[:, c].astype(np.int64).sum()) for c in range(4)]   # p, x, y, kmer column sums
+    if expect:        # the expectations pass returns 9 transition sums + the likelihood per read
+        pairs_digest = [float(v) for v in res.transitions.sum(0)] + [float(res.likelihood.sum())]
+    else:
+        pairs_digest = [int(res.pairs[:, c].astype(np.int64).sum()) for c in range(4)]   # p, x, y, kmer column sums
     batch.close()
 
     # ---- secondary, labelled: the same resident measurement on round 1's dense anchor pattern (every kmer an anchor)
@@ -278,11 +322,16 @@ def main():
     barrier()
     for i in range(max(2, a.steps) + 1):           # one untimed call (pinned / device pools), then the timed ones
         t1 = time.time()
-        r2 = sa.align_batch(model, reads, p)       # sa_gpu_align_batch: host buffers in, host result out
+        # sa_gpu_align_batch / sa_gpu_expectations_batch: host buffers in, host result out
+        r2 = sa.expectations_batch(model, reads, p) if expect else sa.align_batch(model, reads, p)
         if i > 0:
             e2e_t.append(time.time() - t1)
         assert int(r2.pair_offsets[-1]) == n_pairs, "the one-shot call and the staged batch disagree"
-        h2d, d2h, _ = sa.last_call_stats()
+        if expect:
+            assert np.allclose(r2.transitions.sum(0), pairs_digest[:9], rtol=1e-9)
+            h2d, d2h = batch_h2d, 10 * 8 * len(reads)
+        else:
+            h2d, d2h, _ = sa.last_call_stats()
         del r2
     barrier()
     e2e_s = float(np.mean(e2e_t))
@@ -371,13 +420,21 @@ def main():
         out = {
             "metric": "events_aligned_per_sec", "value": events_all / (step_ms_max * 1e-3), "unit": "events/s",
             "n_gpus": world, "steps": a.steps, "warmup": a.warmup, "ms_per_step": step_ms_max,
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": WORKLOAD if a.anchors == ANCHOR_PATTERN else "config3-synthetic, anchor pattern " + a.anchors,
+            "higher_is_better": True, "scaling": "strong" if a.strong else "weak", "vs_baseline": None, "dtype": "f64",
+            "data": "synthetic",
+            "config": {"strong_scaling_shards": shard_info,
+                       "workload": {"config3": WORKLOAD if a.anchors == ANCHOR_PATTERN else "config3-synthetic, anchor pattern " + a.anchors,
+                                    "config4": "config4-synthetic: expectations pass (getExpectationsUsingAnchors) over config 3's reads",
+                                    "config5": "config5-synthetic: ACGT 5-mer table, HDP emission (1024 rows x 1200 grid points), "
+                                               "log-normal read lengths (median ~20k events, clipped at 400k), -x 100"}[a.workload],
                        "anchor_pattern": {"name": a.anchors, **ANCHOR_PATTERNS[a.anchors]},
                        "mean_band_width_rank0": cells / n_diag, "dense_pattern_rank0": dense,
                        "reads_per_gpu_per_step": a.reads, "host_threads_per_rank": host_threads, "events_per_step": events_all,
                        "band_cells_per_step": cells_all, "l2": "flushed between steps (256 MiB write) and inputs > L2",
-                       "aligned_pairs_rank0": n_pairs, "pairs_column_sums_rank0": pairs_digest,
+                       "aligned_pairs_rank0": n_pairs,
+                       ("expectation_sums_rank0" if expect else "pairs_column_sums_rank0"): pairs_digest,
+                       "events_per_read_rank0": {"median": float(np.median([r.events.shape[0] for r in reads])),
+                                                 "max": int(max(r.events.shape[0] for r in reads))},
                        "expectations_e2e_rank0": None if exp_s is None else {
                            "call": "sa_gpu_expectations_batch (config 4 shape: same reads)", "events_per_s": events / exp_s,
                            "gcups": cells / exp_s / 1e9, "ms": 1e3 * exp_s,
