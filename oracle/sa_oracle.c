@@ -53,6 +53,35 @@ double sao_logAdd(double x, double y) { /* pairwiseAligner.c:314-318 */
 }
 #define logAdd sao_logAdd
 
+#ifdef SAO_FP32_STUDY
+/* ---- FP32 STUDY (never part of the pinned oracle: built as libsa_oracle_fp32.so by `make fp32study`).
+ * What an FP32 band kernel with per-diagonal renormalisation would compute: every DP value is a FLOAT relative to an
+ * integer offset of its diagonal (forward: round(max f(d-1)), backward: round(max b(d+1)); kept in double, exact), every
+ * logAdd, dot product and posterior runs in float arithmetic on the relative values.  The cubic logAdd only sees
+ * differences, so the offsets never change which of its branches is taken. */
+#ifndef SAO_FP32_EVERY
+#define SAO_FP32_EVERY 16
+#endif
+static double *g_offF = NULL, *g_offB = NULL;
+static int64_t g_d = 0;      /* diagonal of the cell being computed */
+static int g_nbr = 1;        /* its neighbour in the running transition: diagonal g_d - 1 or g_d - 2 */
+static inline float lookupF(float x) {
+    if (x <= 1.00f) return ((-0.009350833524763f * x + 0.130659527668286f) * x + 0.498799810682272f) * x + 0.693203116424741f;
+    if (x <= 2.50f) return ((-0.014532321752540f * x + 0.139942324101744f) * x + 0.495635523139337f) * x + 0.692140569840976f;
+    if (x <= 4.50f) return ((-0.004605031767994f * x + 0.063427417320019f) * x + 0.695956496475118f) * x + 0.514272634594009f;
+    return ((-0.000458661602210f * x + 0.009695946122598f) * x + 0.930734667215156f) * x + 0.168037164329057f;
+}
+static inline float logAddF(float x, float y) {
+    if (x < y) return (x == -INFINITY || y - x >= 7.5f) ? y : lookupF(y - x) + x;
+    return (y == -INFINITY || x - y >= 7.5f) ? x : lookupF(x - y) + y;
+}
+static double roundedMax(const double *v, int64_t n) {
+    double m = -INFINITY;
+    for (int64_t i = 0; i < n; i++) if (v[i] > m) m = v[i];
+    return (m == -INFINITY || m != m) ? 0.0 : rint(m);
+}
+#endif
+
 /* ------------------------------------------------------------------------------------------- ambiguity */
 
 void sao_ambig_default(sao_ambig *a) { /* pairwiseAligner.c:32-65 */
@@ -376,8 +405,23 @@ typedef struct {
 
 static inline void doTransition(const Op *op, double *from, double *to, int f, int t, double eP, double tP) {
     switch (op->mode) {
+#ifdef SAO_FP32_STUDY
+    case 0: {   /* `to` on diagonal g_d, `from` on g_d - g_nbr, both relative to their forward offsets */
+        const double oC = g_offF[g_d], oN = g_offF[g_d - g_nbr];
+        const float c = ((float) eP + (float) tP) + (float) (oN - oC);
+        to[t] = oC + (double) logAddF((float) (to[t] - oC), (float) (from[f] - oN) + c);
+        break;
+    }
+    case 1: {   /* `to` on the source diagonal g_d, `from` is the target on g_d - g_nbr: backward offsets */
+        const double oC = g_offB[g_d], oN = g_offB[g_d - g_nbr];
+        const float c = ((float) eP + (float) tP) + (float) (oC - oN);
+        from[f] = oN + (double) logAddF((float) (from[f] - oN), (float) (to[t] - oC) + c);
+        break;
+    }
+#else
     case 0: to[t] = logAdd(to[t], from[f] + (eP + tP)); break;       /* :852-858 */
     case 1: from[f] = logAdd(from[f], to[t] + (eP + tP)); break;     /* :866-871 */
+#endif
     default: {                                                       /* :914-968 */
         double p = exp(from[f] + to[t] + (eP + tP) - op->total);
         op->trans9[f * 3 + t] += p;
@@ -400,6 +444,9 @@ static void cellCalculate(const Ctx *c, const Op *op, int64_t x, int64_t y, doub
     /* event pointer: index y-1, or NULLEVENT {-inf, 0} when y == 0 (pairwiseAligner.c:325, 509-512) */
     double eMean = y > 0 ? c->events[(y - 1) * 4] : LOG_ZERO;
     double eNoise = y > 0 ? c->events[(y - 1) * 4 + 1] : 0.0;
+#ifdef SAO_FP32_STUDY
+    g_nbr = 1;
+#endif
     if (lower != NULL) {
         const int32_t *kL = c->pathKmer + c->pathOff[x - 1];
         for (int64_t p = 0; p < nCur; p++)
@@ -411,6 +458,9 @@ static void cellCalculate(const Ctx *c, const Op *op, int64_t x, int64_t y, doub
                     doTransition(op, lower + 3 * q, cur + 3 * p, ST_Y, ST_X, eP, t[SAO_T_GAP_SWITCH_TO_X]);
                 }
     }
+#ifdef SAO_FP32_STUDY
+    g_nbr = 2;
+#endif
     if (middle != NULL) {
         const int32_t *kM = c->pathKmer + c->pathOff[x - 1];
         for (int64_t p = 0; p < nCur; p++)
@@ -422,6 +472,9 @@ static void cellCalculate(const Ctx *c, const Op *op, int64_t x, int64_t y, doub
                     doTransition(op, middle + 3 * q, cur + 3 * p, ST_Y, ST_M, eP, t[SAO_T_MATCH_FROM_GAP_Y]);
                 }
     }
+#ifdef SAO_FP32_STUDY
+    g_nbr = 1;
+#endif
     if (upper != NULL) {
         for (int64_t p = 0; p < nCur; p++)
             for (int64_t q = 0; q < nUpper; q++)
@@ -436,6 +489,9 @@ static void cellCalculate(const Ctx *c, const Op *op, int64_t x, int64_t y, doub
 /* diagonalCalculation (:1280-1311): cells in ascending xmy */
 static void diagonalCalculation(const Ctx *c, Op *op, DpDiag *cur, DpDiag *m1, DpDiag *m2) {
     Diag d = cur->d;
+#ifdef SAO_FP32_STUDY
+    g_d = d.xay;
+#endif
     for (int64_t xmy = d.xmyL; xmy <= d.xmyR; xmy += 2) {
         int64_t x = diagX(d.xay, xmy), y = diagY(d.xay, xmy);
         int64_t nC = 0, nL = 0, nM = 0, nU = 0;
@@ -462,14 +518,28 @@ static double dotProduct(const Ctx *c, DpDiag *a, DpDiag *b) {
         for (int64_t p = 0; p < n1; p++)
             for (int64_t q = 0; q < n2; q++)
                 if (sameKmer(km[p], km[q])) {
+#ifdef SAO_FP32_STUDY
+                    const double oF = g_offF[d.xay], oB = g_offB[d.xay];
+                    float t = (float) (c1[3 * p] - oF) + (float) (c2[3 * q] - oB);
+                    t = logAddF(t, (float) (c1[3 * p + 1] - oF) + (float) (c2[3 * q + 1] - oB));
+                    t = logAddF(t, (float) (c1[3 * p + 2] - oF) + (float) (c2[3 * q + 2] - oB));
+                    cellTotal = (double) logAddF((float) cellTotal, t);
+#else
                     double t = c1[3 * p] + c2[3 * q];
                     t = logAdd(t, c1[3 * p + 1] + c2[3 * q + 1]);
                     t = logAdd(t, c1[3 * p + 2] + c2[3 * q + 2]);
                     cellTotal = logAdd(cellTotal, t);
+#endif
                 }
+#ifdef SAO_FP32_STUDY
+        total = (double) logAddF((float) total, (float) cellTotal);
+    }
+    return total + (g_offF[d.xay] + g_offB[d.xay]);      /* (relative inside the loop, absolute outside) */
+#else
         total = logAdd(total, cellTotal);
     }
     return total;
+#endif
 }
 
 /* diagonalCalculationTotalProbability (:1335-1353) */
@@ -482,7 +552,14 @@ static double totalProbability(const Ctx *c, int64_t xay, DpDiag **f, DpDiag **b
         dd_fill(md, ZERO3);
         Op op = {0};
         diagonalCalculation(c, &op, md, NULL, fm1);
+#ifdef SAO_FP32_STUDY
+        {   /* both totals relative to the first one's offset, combined in float */
+            const double O1 = g_offF[xay] + g_offB[xay], t2 = dotProduct(c, md, bp1);
+            total = O1 + (double) logAddF((float) (total - O1), (float) (t2 - O1));
+        }
+#else
         total = logAdd(total, dotProduct(c, md, bp1));
+#endif
         dd_free(md);
     }
     return total;
@@ -510,7 +587,12 @@ static void posteriorMatchProbs(const Ctx *c, int64_t xay, DpDiag **f, DpDiag **
             for (int64_t fp = 0; fp < nf; fp++)
                 for (int64_t bp = 0; bp < nb; bp++)
                     if (sameKmer(km[fp], km[bp])) {
+#ifdef SAO_FP32_STUDY
+                        const double oF = g_offF[d.xay], oB = g_offB[d.xay];
+                        double pp = exp((double) (((float) (cf[3 * fp] - oF) + (float) (cb[3 * bp] - oB)) - (float) (total - (oF + oB))));
+#else
                         double pp = exp((cf[3 * fp] + cb[3 * bp]) - total);
+#endif
                         if (pp >= s->threshold) {
                             if (pp > 1.0) pp = 1.0;
                             pp = floor(pp * 10000000.0); /* PAIR_ALIGNMENT_PROB_1 */
@@ -538,6 +620,10 @@ static void bandedDriver(const Ctx *c, const int64_t *anchors, int64_t nA, const
     if (nDiag == 0) return;
     Diag *band = band_build(anchors, nA, c->lX, c->lY, p->diagonalExpansion);
     DpDiag **f = calloc(nDiag + 1, sizeof(DpDiag *)), **b = calloc(nDiag + 1, sizeof(DpDiag *));
+#ifdef SAO_FP32_STUDY
+    free(g_offF); free(g_offB);
+    g_offF = calloc(nDiag + 2, sizeof(double)); g_offB = calloc(nDiag + 2, sizeof(double));
+#endif
     double sv[3];
     f[0] = dd_new(c, band[0]);
     stateValues(c->m, raggedL ? 1 : 0, sv);
@@ -552,6 +638,12 @@ static void bandedDriver(const Ctx *c, const int64_t *anchors, int64_t nA, const
         Diag d = band[xay];
         f[xay] = dd_new(c, d);
         dd_fill(f[xay], ZERO3);
+#ifdef SAO_FP32_STUDY
+        /* SAO_FP32_EVERY: the offset is refreshed only on every n-th diagonal (what a kernel would do to avoid a block-wide
+         * maximum per step); default 16 (what sa_wide32.cuh does) */
+        g_offF[xay] = (xay % SAO_FP32_EVERY == 0) ? roundedMax(f[xay - 1]->v, 3 * f[xay - 1]->off[diagWidth(f[xay - 1]->d)])
+                                                  : g_offF[xay - 1];
+#endif
         s->stats[0] += diagWidth(d);
         s->stats[1] += f[xay]->off[diagWidth(d)];
         diagonalCalculation(c, &fwd, f[xay], f[xay - 1], xay - 2 >= 0 ? f[xay - 2] : NULL);
@@ -562,6 +654,10 @@ static void bandedDriver(const Ctx *c, const int64_t *anchors, int64_t nA, const
             b[xay] = dd_new(c, d);
             stateValues(c->m, (atEnd && raggedR) ? 3 : 2, sv);
             dd_fill(b[xay], sv);
+#ifdef SAO_FP32_STUDY
+            g_offB[xay] = 0.0;
+            if (xay >= 1) g_offB[xay - 1] = 0.0;
+#endif
             if (xay > tracedBackTo + 1) {
                 b[xay - 1] = dd_new(c, band[xay - 1]);
                 dd_fill(b[xay - 1], ZERO3);
@@ -574,6 +670,11 @@ static void bandedDriver(const Ctx *c, const int64_t *anchors, int64_t nA, const
                     b[d2 - 2] = dd_new(c, band[d2 - 2]);
                     dd_fill(b[d2 - 2], ZERO3);
                 }
+#ifdef SAO_FP32_STUDY
+                /* offset of the diagonal about to be completed two steps from now: the level of the newest complete one */
+                if (d2 >= 2) g_offB[d2 - 2] = ((d2 - 2) % SAO_FP32_EVERY == 0) ? roundedMax(b[d2]->v, 3 * b[d2]->off[diagWidth(b[d2]->d)])
+                                                                                : g_offB[d2 - 1];
+#endif
                 if (d2 > tracedBackTo + 1)
                     diagonalCalculation(c, &bwd, b[d2], b[d2 - 1], d2 - 2 >= 0 ? b[d2 - 2] : NULL);
                 if (d2 <= tracedBackFrom) {
