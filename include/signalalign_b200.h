@@ -146,6 +146,18 @@ const char *sa_last_error(void);
 void sa_set_host_threads(int n);
 int sa_gpu_device_count(void);
 
+/* Arithmetic of the wide band kernel (bands wider than 254 columns) on alignment runs with the production Gaussian
+ * emission.  SA_PRECISION_FP64 (default): the reference's double-precision arithmetic, operation for operation (posteriors
+ * within 2e-6 of the reference).  SA_PRECISION_FP32: DP state, stored rows and every logAdd in single precision, each value
+ * relative to a per-diagonal integer offset kept in double (sa_wide32.cuh): coordinates and kmers still bit-exact,
+ * posteriors within the contract's 1e-4 (measured: 3e-5), about twice the throughput.  The reference has one precision
+ * (double, impl/pairwiseAligner.c:298-318); BASELINE's north_star asks for the FP32 variant.  Process-wide; the environment
+ * variable SA_PRECISION=fp32 sets the default.  Expectations, the HDP emission and narrow bands always run in FP64. */
+#define SA_PRECISION_FP64 0
+#define SA_PRECISION_FP32 1
+int sa_gpu_set_precision(int precision);
+int sa_gpu_get_precision(void);
+
 /* One-shot drop-in for a batch of getAlignedPairsUsingAnchors calls (host buffers in, host result out).
  * Large batches run as a pipeline of chunks: host packing, H2D, the band kernels and compaction + D2H of consecutive
  * chunks overlap.  result->pairs is page-locked memory of libsagpu's pool: release it with sa_result_free only. */

@@ -67,7 +67,7 @@ EXPORTS = [
     "sa_result_sum_expectations", "sa_debug_logadd", "sa_model_hdp_dims", "sa_model_get_hdp", "sa_debug_band",
     "sa_debug_split_points", "sa_debug_kmer_paths", "sa_last_call_stats", "sa_set_host_threads",
     "sa_gpu_comm_unique_id", "sa_gpu_comm_init", "sa_gpu_comm_from_nccl", "sa_gpu_comm_free",
-    "sa_gpu_allreduce_expectations", "sa_gpu_allgather_assignments", "sa_gpu_align_noalloc", "sa_gpu_estimate_params_batch",
+    "sa_gpu_allreduce_expectations", "sa_gpu_allgather_assignments", "sa_gpu_align_noalloc", "sa_gpu_estimate_params_batch", "sa_gpu_set_precision", "sa_gpu_get_precision",
 ]
 
 _lib = None
@@ -473,6 +473,16 @@ class Comm:
             self.close()
         except Exception:
             pass
+
+
+def set_precision(name):
+    """'fp64' (default: the reference's double arithmetic) or 'fp32' (wide band kernel with float state relative to
+    per-diagonal offsets, Gaussian alignment runs; posteriors within 1e-4)"""
+    _check(lib().sa_gpu_set_precision({"fp64": 0, "fp32": 1}[name]))
+
+
+def get_precision():
+    return ["fp64", "fp32"][lib().sa_gpu_get_precision()]
 
 
 def set_host_threads(n):

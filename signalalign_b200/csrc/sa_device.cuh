@@ -18,6 +18,7 @@
 // fetches its coefficients with two conflict-free LDS.128.  Row 16 is all zeros: the "far" case (|x - y| >= 7.5, or an
 // operand -inf) evaluates 0 + max(x, y) through the same instructions.  Every kernel calls sa_logAdd_init() once per CTA.
 __shared__ __align__(16) double sa_lt[68];
+__shared__ __align__(16) float sa_ltf[68];      // the same table in single precision (sa_logAddF, the FP32 band kernel)
 
 __device__ __forceinline__ void sa_logAdd_init() {
     const float c[16] = {-0.009350833524763f, 0.130659527668286f, 0.498799810682272f, 0.693203116424741f,
@@ -30,6 +31,7 @@ __device__ __forceinline__ void sa_logAdd_init() {
 #pragma unroll
         for (int q = 1; q < 16; q++) v = k == q ? c[q] : v;
         sa_lt[i] = n >= 16 ? 0.0 : (double) v;
+        sa_ltf[i] = n >= 16 ? 0.0f : v;
     }
     __syncthreads();
 }
@@ -59,6 +61,24 @@ __device__ __forceinline__ double sa_logAdd(double x, double y) {
     r = __dmul_rn(__dadd_rn(r, ca.y), d);
     r = __dmul_rn(__dadd_rn(r, cb.x), d);
     return __dadd_rn(__dadd_rn(r, cb.y), base);
+}
+
+// The same logAdd in single precision for the FP32 band kernel (sa_wide32.cuh): the reference's coefficients ARE float
+// literals, the range index ceil(2 d) comes from one FADD.RU (2 d + 2^23 rounded up leaves it in the low mantissa bits), the
+// four coefficients of a row arrive in one LDS.128, the cubic is three FFMA.  Thresholds and branches are those of the
+// reference; only the rounding differs (operands are values relative to a per-diagonal offset: see sa_wide32.cuh).
+__device__ __forceinline__ float sa_logAddF(float x, float y) {
+    const float diff = __fsub_rn(x, y);
+    const unsigned bits = __float_as_uint(diff), ah = bits & 0x7fffffffu;
+    const bool far = ah >= 0x40F00000u;                 // |diff| >= 7.5f, inf or NaN
+    const bool xlt = (int) bits < 0;
+    const float base = (far == xlt) ? y : x;            // far: max(x, y); else min(x, y)
+    const float d = __uint_as_float(umin(ah, 0x41000000u));
+    unsigned n = __float_as_uint(__fadd_ru(__fmul_rn(d, 2.0f), 8388608.0f)) & 0x7fffffu;
+    n = far ? 16u : n;
+    const float4 c = *reinterpret_cast<const float4 *>(sa_ltf + 4 * n);
+    const float r = fmaf(fmaf(fmaf(c.x, d, c.y), d, c.z), d, c.w);
+    return __fadd_rn(r, base);
 }
 
 // exp() for the expectation sums (cell_signal_updateExpectations, impl/pairwiseAligner.c:914-944): every band cell adds

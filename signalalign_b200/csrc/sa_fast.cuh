@@ -88,6 +88,8 @@ struct FParams {
     int32_t wAllFull;         // expectations: every row keeps all planes
     int32_t wGeoAlways;       // size the wide kernel's row ring for every item, not only those wider than 254 columns
     double *wRings;           // per-CTA 6 * wNSW doubles: emission rings of the window classes too large for shared memory
+    double *wOff;             // FP32 wide kernel: per-CTA forward offsets, one per 16 diagonals
+    int32_t wOffCap;
 };
 
 // ---------------------------------------------------------------------------------------------- band iterator

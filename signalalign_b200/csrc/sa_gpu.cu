@@ -17,6 +17,7 @@
 #include "sa_fast.cuh"
 #include "sa_cta.cuh"
 #include "sa_wide.cuh"
+#include "sa_wide32.cuh"
 #include "sa_estimate.cuh"
 
 #define CK(call)                                                                                   \
@@ -354,7 +355,9 @@ struct sa_batch {
     // wide kernel (sa_wide.cuh), classes by window size
     std::vector<int32_t> wOrder[kWideClasses];
     DevBuf<int32_t> dWOrder[kWideClasses];
-    DevBuf<double> dWRing[kWideClasses], dWFold[kWideClasses], dWRings[kWideClasses];
+    DevBuf<double> dWRing[kWideClasses], dWFold[kWideClasses], dWRings[kWideClasses], dWOff[kWideClasses];
+    bool fp32 = false;                  // the wide classes run on sa_wide32_kernel (Gaussian alignment, SA_PRECISION_FP32)
+    int32_t wOffCap[kWideClasses] = {0, 0, 0, 0, 0};
     DevBuf<int4> dWHdr[kWideClasses];
     int wBlocks[kWideClasses] = {0, 0, 0, 0, 0};
     int32_t wRows[kWideClasses] = {1, 1, 1, 1, 1};
@@ -466,6 +469,53 @@ static void wideLaunch(bool gr, bool hdp, bool ex, int blocks, int threads, size
     if (gr) wideLaunchG<true>(hdp, ex, blocks, threads, smem, st, f);
     else wideLaunchG<false>(hdp, ex, blocks, threads, smem, st, f);
 }
+// ---- precision of the wide band kernel for Gaussian alignment runs: FP64 (default, bit-faithful) or FP32 state relative to
+// per-diagonal offsets (sa_wide32.cuh; within the contract's 1e-4).  SA_PRECISION=fp32 in the environment sets the default.
+static int g_precision = -1;
+static int currentPrecision() {
+    if (g_precision < 0) {
+        const char *e = getenv("SA_PRECISION");
+        g_precision = (e && (!strcmp(e, "fp32") || !strcmp(e, "FP32") || !strcmp(e, "f32"))) ? SA_PRECISION_FP32 : SA_PRECISION_FP64;
+    }
+    return g_precision;
+}
+extern "C" int sa_gpu_set_precision(int precision) {
+    if (precision != SA_PRECISION_FP64 && precision != SA_PRECISION_FP32) {
+        sa_set_error("sa_gpu_set_precision: unknown precision %d", precision);
+        return SA_ERR_INPUT;
+    }
+    g_precision = precision;
+    return SA_OK;
+}
+extern "C" int sa_gpu_get_precision(void) { return currentPrecision(); }
+
+// FP32 wide kernel: rings in global memory from this window size on (SA_WIDE32_GR_FROM), shared-memory bytes, occupancy, launch
+static bool wide32GlobalRings(int c) {
+    int from = 2048;
+    if (const char *e = getenv("SA_WIDE32_GR_FROM")) from = atoi(e);
+    return kWideNSW[c] >= from || WideF<false>::smemBytes(kWideNSW[c], false) > kSmemCap;
+}
+static size_t wide32SmemBytes(bool gr, int NSW, bool foldInSmem) {
+    return gr ? WideF<true>::smemBytes(NSW, false) : WideF<false>::smemBytes(NSW, foldInSmem);
+}
+template <bool GR>
+static int wide32OccupancyT(int threads, size_t smem, int *bps) {
+    static bool raised = false;
+    if (smem > 48 * 1024 && !raised) {
+        CK(cudaFuncSetAttribute(sa_wide32_kernel<GR>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) kSmemCap));
+        raised = true;
+    }
+    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(bps, sa_wide32_kernel<GR>, threads, smem));
+    return SA_OK;
+}
+static int wide32Occupancy(bool gr, int threads, size_t smem, int *bps) {
+    return gr ? wide32OccupancyT<true>(threads, smem, bps) : wide32OccupancyT<false>(threads, smem, bps);
+}
+static void wide32Launch(bool gr, int blocks, int threads, size_t smem, cudaStream_t st, const FParams &f) {
+    if (gr) sa_wide32_kernel<true><<<blocks, threads, smem, st>>>(f);
+    else sa_wide32_kernel<false><<<blocks, threads, smem, st>>>(f);
+}
+
 // does the class keep its emission rings in global memory?  From the 2048-slot window on: with the rings in shared memory
 // one CTA of that class fills an SM (1024 threads, half of them idle on a typical diagonal); with only the DP state
 // there, two CTAs of 512 threads fit and overlap each other's barriers (+15 % on the contract pattern).
@@ -850,6 +900,7 @@ static int prepareBatch(const sa_model_t *m, const sa_read_t *reads, int64_t nRe
                 const int c = it.kernel - 100;
                 b->wOrder[c].push_back((int32_t) i);
                 b->wRows[c] = std::max(b->wRows[c], geo[i].maxRows);
+                b->wOffCap[c] = std::max<int32_t>(b->wOffCap[c], (int32_t) ((it.lX + it.lY) / 16 + 2));
                 b->wRingDoubles[c] = std::max(b->wRingDoubles[c], geo[i].maxBlockDoubles + 2 * 256 * (int64_t) planes * geo[i].maxWidth);   // + the table being written, + the tail a wrap skips
                 continue;
             }
@@ -955,11 +1006,14 @@ static int prepareBatch(const sa_model_t *m, const sa_read_t *reads, int64_t nRe
         if ((rc = b->dWOrder[c].upload(b->wOrder[c], st, &b->h2dBytes))) return rc;
         if (b->wOrder[c].empty()) continue;
         const bool hdp = m->kind == SA_EMIT_HDP;
-        const bool gr = wideGlobalRings(c);
-        const bool foldGlobal = wideFoldGlobal(c, gr);
-        const size_t smem = wideSmemBytes(gr, kWideNSW[c], !foldGlobal);
+        b->fp32 = currentPrecision() == SA_PRECISION_FP32 && !b->expectations && m->kind == SA_EMIT_GAUSS_MEANONLY_DESCALE;
+        const bool gr = b->fp32 ? wide32GlobalRings(c) : wideGlobalRings(c);
+        const bool foldGlobal = b->fp32 ? (gr || wide32SmemBytes(false, kWideNSW[c], true) > kSmemCap) : wideFoldGlobal(c, gr);
+        const size_t smem = b->fp32 ? wide32SmemBytes(gr, kWideNSW[c], !foldGlobal) : wideSmemBytes(gr, kWideNSW[c], !foldGlobal);
         int bps = 1;
-        if ((rc = wideOccupancy(gr, hdp, b->expectations, wideThreads(c), smem, &bps))) return rc;
+        if (b->fp32) {
+            if ((rc = wide32Occupancy(gr, wideThreads(c), smem, &bps))) return rc;
+        } else if ((rc = wideOccupancy(gr, hdp, b->expectations, wideThreads(c), smem, &bps))) return rc;
         b->wBlocks[c] = (int) std::min<int64_t>((int64_t) nSM * std::max(1, bps), (int64_t) b->wOrder[c].size());
         b->wRows[c] += 4 + 256;      // + one descriptor table of headers written ahead
         b->wRingDoubles[c] = (b->wRingDoubles[c] + 64 + 15) & ~(int64_t) 15;
@@ -979,6 +1033,7 @@ static int prepareBatch(const sa_model_t *m, const sa_read_t *reads, int64_t nRe
             CK(cudaEventCreateWithFlags(&b->evWideJoin[c], cudaEventDisableTiming));
         }
         if (gr && (rc = b->dWRings[c].alloc((size_t) b->wBlocks[c] * 6 * kWideNSW[c], st))) return rc;
+        if (b->fp32 && (rc = b->dWOff[c].alloc((size_t) b->wBlocks[c] * b->wOffCap[c], st))) return rc;
     }
 
     timer.lap("geometry pass + fast-kernel scratch");
@@ -1155,9 +1210,15 @@ static int launchBatch(sa_batch_t *b) {
         f.order = b->dWOrder[c].p; f.nOrder = (int32_t) b->wOrder[c].size(); f.counter = b->dCounters.p + 8 + c;
         f.wNSW = kWideNSW[c]; f.wRowsCap = b->wRows[c]; f.wRingDoubles = b->wRingDoubles[c];
         f.scratch = b->dWRing[c].p; f.wHdr = b->dWHdr[c].p; f.wFold = b->dWFold[c].p; f.wRings = b->dWRings[c].p;
-        const bool gr = wideGlobalRings(c);
-        wideLaunch(gr, hdp, b->expectations, b->wBlocks[c], wideThreads(c),
-                   wideSmemBytes(gr, kWideNSW[c], b->dWFold[c].p == nullptr), st, f);
+        if (b->fp32) {
+            const bool gr = b->dWRings[c].p != nullptr;
+            f.wOff = b->dWOff[c].p; f.wOffCap = b->wOffCap[c];
+            wide32Launch(gr, b->wBlocks[c], wideThreads(c), wide32SmemBytes(gr, kWideNSW[c], b->dWFold[c].p == nullptr), st, f);
+        } else {
+            const bool gr = wideGlobalRings(c);
+            wideLaunch(gr, hdp, b->expectations, b->wBlocks[c], wideThreads(c),
+                       wideSmemBytes(gr, kWideNSW[c], b->dWFold[c].p == nullptr), st, f);
+        }
         b->lastLaunches++;
         CK(cudaGetLastError());
         if (!wideOneStream) CK(cudaEventRecord(b->evWideJoin[c], st));

@@ -1,0 +1,571 @@
+// sa_wide32.cuh — the FP32 wide band kernel: sa_wide.cuh's mapping (one CTA per work item, DP state in shared memory
+// addressed by anti-diagonal offset, cells of a diagonal dealt out round-robin, compact forward rows in an HBM ring) with
+// the DP state, the stored rows and every logAdd in SINGLE precision.
+//
+// Why it is allowed.  The reference computes in double, and BASELINE's contract is: coordinates and kmers bit-exact, every
+// posterior within 1e-4, the pair set identical except within that tolerance of the threshold.  Plain FP32 fails it
+// (forward values reach -2.5e4 after 10 k events: one ulp is 2e-3).  But the cubic logAdd only ever sees DIFFERENCES of
+// its operands, so a constant may be subtracted from a whole diagonal without changing which branch is taken.  Here every
+// stored value is a float RELATIVE to an integer offset of its diagonal; the offsets (kept in double, exact) follow the
+// diagonal's maximum and are refreshed on every 16th diagonal, so the values that matter stay within a few tens of nats of
+// zero, where a float resolves 2e-6 .. 4e-6.  Measured on the CPU with the oracle restatement built the same way
+// (oracle -DSAO_FP32_STUDY, tools/fp32_study.py, profiles/r2_fp32_study.txt): identical pair sets, max |dp| 2.9e-5, nothing
+// above 1e-4 on the golden reads and six config-3 reads.  The FP64 kernels stay the default (bit-faithful, |dp| <= 2e-6);
+// this one is selected with sa_gpu_set_precision(SA_PRECISION_FP32) and is tested at the contract's tolerance.
+//
+// What stays double: the offsets, the event-minus-level difference of the emission (two numbers near 100 whose difference
+// is divided by a standard deviation near 1.5), the total probability (offset + float-derived fold, folded by the same
+// ordered chain as the FP64 kernel), and the final exp() of the few cells that can reach the threshold.
+//
+// Alignment with the Gaussian emission only (the headline path); expectations and the HDP emission run on sa_wide.cuh.
+#pragma once
+#include "sa_wide.cuh"
+
+template <bool GR>
+struct WideF {
+    using K = WideK<false, false, GR>;
+    using Sm = typename K::Sm;            // same struct; st / cst hold the layouts below behind the double pointers
+    using Rows = typename K::Rows;        // ring = floats behind the double pointer; offsets count floats
+    static constexpr int BT = K::BT;
+    static constexpr int kEvery = 16;     // offsets are refreshed on diagonals that are multiples of this
+
+    // shared memory: state float[2][NSW][3]; per column {double km; float iM, cM, iY, cY} (24 B); events double[NSW];
+    // fold terms double[2][NSW]; then the tables of WideK
+    static __host__ __device__ size_t smemBytes(int NSW, bool foldInSmem) {
+        size_t b = (size_t) 24 * NSW + (GR ? 0 : (size_t) (24 + 8 + (foldInSmem ? 16 : 0)) * NSW) + 16;
+        b += (size_t) (NSW / 32) * (2 * 8 + 2 * 4 + 2 * 4 + 6 * 4);
+        b += (size_t) (2 * BT + 2) * 16 + 3 * (BT + 1) * 4 + 16 + 16 + 64 * 4;
+        return b;
+    }
+    struct Extra {          // what the float variant adds to the shared tables
+        float *red;         // [64] per-warp maxima for the offset refresh
+    };
+    static __device__ __forceinline__ void carve(Sm &S, Extra &E, double *base, int NSW, double *foldGlobal, double *ringsGlobal) {
+        S.NSW = NSW; S.mask = NSW - 1; S.nCh = NSW / 32;
+        double *p = base;
+        S.st = p; p += 3 * NSW;                              // 24 B per slot
+        if (GR) { S.cst = ringsGlobal; S.evs = ringsGlobal + 3 * NSW; S.foldv = foldGlobal; }
+        else {
+            S.cst = p; p += 3 * NSW;
+            S.evs = p; p += NSW;
+            if (foldGlobal) S.foldv = foldGlobal; else { S.foldv = p; p += 2 * NSW; }
+        }
+        S.sTotal = p; p += 2;
+        S.desc = reinterpret_cast<int4 *>(p); p += 2 * BT;
+        S.descB = reinterpret_cast<int4 *>(p); p += 2 * (BT + 2);
+        S.cmax = reinterpret_cast<float2 *>(p); p += 2 * S.nCh;
+        unsigned *u = reinterpret_cast<unsigned *>(p);
+        S.candM = u; u += 2 * S.nCh;
+        S.resetM = u; u += 2 * S.nCh;
+        S.hitW = u; u += 6 * S.nCh;
+        int32_t *q = reinterpret_cast<int32_t *>(u);
+        S.aX = q; q += BT + 1;
+        S.aY = q; q += BT + 1;
+        S.aD = q; q += BT + 1;
+        S.sInt = q; q += 4;
+        E.red = reinterpret_cast<float *>(q);
+    }
+    static __device__ __forceinline__ float *stateF(const Sm &S, int parity) { return reinterpret_cast<float *>(S.st) + parity * 3 * S.NSW; }
+
+    // ------------------------------------------------------------------------------------------ rings
+    static __device__ __forceinline__ void fillConst1(const FParams &P, const FItem &I, const Sm &S, int32_t x) {
+        double km = 0.0;
+        float iM = 0.f, iY = 0.f, cM = -INFINITY, cY = -INFINITY;
+        if (x >= 1 && x <= I.lX) {
+            const double *ft = P.ft + (int64_t) P.kmerIdx[I.kmerOff + x - 1] * 5;
+            km = fma(I.scale, ft[0], I.shift);
+            iM = (float) (ft[1] * I.invVar);
+            cM = (float) (ft[2] + I.logInvVar);
+            iY = (float) (ft[3] * I.invVar);
+            cY = (float) (ft[4] + I.logInvVar);
+        }
+        double *c = S.cst + (x & S.mask) * 3;
+        c[0] = km;
+        *reinterpret_cast<float2 *>(c + 1) = make_float2(iM, cM);      // (8-byte aligned: 24 B per column)
+        *reinterpret_cast<float2 *>(c + 2) = make_float2(iY, cY);
+    }
+    static constexpr int kSlack = K::kSlack;
+    static __device__ __forceinline__ void ensureRings(const FParams &P, const FItem &I, const Sm &S, int t, int NT,
+                                                       int32_t cl, int32_t el, int32_t span, bool fwd, int32_t &cLo, int32_t &eLo) {
+        const unsigned room = (unsigned) (S.NSW - 1 - span);
+        const bool needC = (unsigned) (cl - cLo) > room, needE = (unsigned) (el - eLo) > room;
+        if (!(needC || needE)) return;
+        __syncthreads();
+        if (needC) {
+            const int32_t nLo = fwd ? cl - kSlack : cl + span + kSlack - (S.NSW - 1);
+            for (int32_t k = t; k < S.NSW; k += NT) {
+                const int32_t x = nLo + k;
+                if (x < cLo || x >= cLo + S.NSW) fillConst1(P, I, S, x);
+            }
+            cLo = nLo;
+        }
+        if (needE) {
+            const int32_t nLo = fwd ? el - kSlack : el + span + kSlack - (S.NSW - 1);
+            for (int32_t k = t; k < S.NSW; k += NT) {
+                const int32_t y = nLo + k;
+                if (y < eLo || y >= eLo + S.NSW)
+                    S.evs[y & S.mask] = (y >= 1 && y <= I.lY) ? P.evMean[I.evOff + y - 1] : 0.0;
+            }
+            eLo = nLo;
+        }
+        __syncthreads();
+    }
+
+    // match and gap-Y emission of cell (x, y): the difference in double, the rest in float
+    static __device__ __forceinline__ void emissions(const Sm &S, int32_t x, int32_t y, float &eM, float &eY) {
+        const double *c = S.cst + (x & S.mask) * 3;
+        const float2 qm = *reinterpret_cast<const float2 *>(c + 1), qy = *reinterpret_cast<const float2 *>(c + 2);   // (iM, cM), (iY, cY)
+        const float d0 = (float) (S.evs[y & S.mask] - c[0]);
+        const float aM = d0 * qm.x, aY = d0 * qy.x;
+        eM = fmaf(-0.5f * aM, aM, qm.y);
+        eY = fmaf(-0.5f * aY, aY, qy.y);
+    }
+    static __device__ __forceinline__ float emissionM(const Sm &S, int32_t x, int32_t y) {
+        const double *c = S.cst + (x & S.mask) * 3;
+        const float2 q = *reinterpret_cast<const float2 *>(c + 1);
+        const float aM = (float) (S.evs[y & S.mask] - c[0]) * q.x;
+        return fmaf(-0.5f * aM, aM, q.y);
+    }
+    static __device__ __forceinline__ float emissionY(const Sm &S, int32_t x, int32_t y) {
+        const double *c = S.cst + (x & S.mask) * 3;
+        const float2 q = *reinterpret_cast<const float2 *>(c + 2);
+        const float aY = (float) (S.evs[y & S.mask] - c[0]) * q.x;
+        return fmaf(-0.5f * aY, aY, q.y);
+    }
+
+    // both state buffers in one pass (see WideK::loadState); values are RELATIVE floats as stored
+    static __device__ __forceinline__ void loadState(const Sm &S, int t, int NT, int32_t H, int32_t dA, int32_t loA, int32_t hiA,
+                                                     const float *rowA, const float (&cA)[3], int32_t dB, int32_t loB,
+                                                     int32_t hiB, const float *rowB) {
+        const int32_t jA = K::jbase(dA, H), jB = K::jbase(dB, H);
+        float *bufA = stateF(S, dA & 1), *bufB = stateF(S, dB & 1);
+        const int32_t wA = hiA - loA + 1, wB = hiB - loB + 1;
+        for (int32_t s = t; s < S.NSW; s += NT) {
+            {
+                const int32_t i = (s - jA - loA) & S.mask;
+                float v0 = -INFINITY, v1 = -INFINITY, v2 = -INFINITY;
+                if (i < wA) {
+                    if (rowA) { v0 = rowA[i]; v1 = rowA[wA + i]; v2 = rowA[2 * wA + i]; }
+                    else { v0 = cA[0]; v1 = cA[1]; v2 = cA[2]; }
+                }
+                bufA[3 * s] = v0; bufA[3 * s + 1] = v1; bufA[3 * s + 2] = v2;
+            }
+            {
+                const int32_t i = (s - jB - loB) & S.mask;
+                float v0 = -INFINITY, v1 = -INFINITY, v2 = -INFINITY;
+                if (rowB && i < wB) { v0 = rowB[i]; v1 = rowB[wB + i]; v2 = rowB[2 * wB + i]; }
+                bufB[3 * s] = v0; bufB[3 * s + 1] = v1; bufB[3 * s + 2] = v2;
+            }
+        }
+    }
+
+    // block maximum of the values the threads wrote on a diagonal, left in E.red by the warps BEFORE the step's closing
+    // barrier and read by everybody after it: the next diagonal's offset moves by its rounded value
+    static __device__ __forceinline__ void postMax(const Extra &E, float tmax, int lane, int warp) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) tmax = fmaxf(tmax, __shfl_xor_sync(0xffffffffu, tmax, o));
+        if (lane == 0) E.red[warp] = tmax;
+    }
+    static __device__ __forceinline__ double readMax(const Extra &E, int NW) {
+        float m = -INFINITY;
+        for (int w = 0; w < NW; w++) m = fmaxf(m, E.red[w]);
+        return m > -INFINITY ? (double) rintf(m) : 0.0;
+    }
+
+    // ------------------------------------------------------------------------------------------ traceback
+    // blocked traceback from diagonal d down to tracedBackTo + 1 (reference impl/pairwiseAligner.c:1500-1570); see
+    // WideK::traceback for the structure.  b(d2) is relative to a backward offset oB(d2) (0 on the block's first diagonal,
+    // moved by the rounded maximum of the previous diagonal whenever d2 enters a new group of 16); f(d2) is relative to
+    // offF[d2 >> 4], written by the forward sweep.
+    static __device__ void traceback(const FParams &P, const FItem &I, const Sm &S, const Extra &E, const Rows &RW, const double *offF,
+                                     int t, int NT, int32_t H, int32_t d, int32_t rowI, int32_t &cLo, int32_t &eLo,
+                                     int32_t tracedBackTo, int32_t tracedBackFrom, bool atEnd, float cOX, float cEX,
+                                     int64_t &nPairs) {
+        const int lane = t & 31, warp = t >> 5, NW = NT >> 5;
+        const double *T = P.trans;
+        const float tMM = (float) T[T_MATCH_CONTINUE], tXM = (float) T[T_MATCH_FROM_GAP_X], tYM = (float) T[T_MATCH_FROM_GAP_Y];
+        const float tMY = (float) T[T_GAP_OPEN_Y], tYY = (float) T[T_GAP_EXTEND_Y];
+        const float gate = (float) P.logThrGate;
+        const int32_t cap = RW.cap;
+        const float *ringF = reinterpret_cast<const float *>(RW.ring);
+        const bool rag = atEnd && (I.flags & 2);
+        const float endS[3] = {(float) (rag ? (T[T_GAP_OPEN_X] + T[T_GAP_OPEN_Y]) / 2.0 : T[T_MATCH_CONTINUE]),
+                               (float) (rag ? T[T_GAP_EXTEND_X] : T[T_MATCH_FROM_GAP_X]),
+                               (float) (rag ? T[T_GAP_EXTEND_Y] : T[T_MATCH_FROM_GAP_Y])};
+        auto fillBack = [&](int32_t rowTop) {
+            for (int32_t q = t; q < BT + 2; q += NT) {
+                int32_t r = rowTop - q;
+                if (r < 0) r += cap;
+                S.descB[q] = RW.hdr[r];
+            }
+        };
+        int32_t tTop = d;
+        {
+            const int4 hTop = RW.hdr[rowI];
+            __syncthreads();
+            loadState(S, t, NT, H, d, hTop.x, hTop.y, nullptr, endS, d - 1, 0, -1, nullptr);
+            fillBack(rowI);
+            __syncthreads();
+        }
+        double totalAbs = -INFINITY;            // total probability, absolute
+        double o0 = 0.0, o1 = 0.0, o2 = 0.0;    // backward offsets of d2, d2 + 1, d2 + 2
+        double shiftNext = 0.0;                 // rounded maximum of b(d2 + 1), valid on the step that enters a new group
+        int32_t postMod = 0;
+        int4 hUp = make_int4(0, -1, 0, 0), hUp2 = make_int4(0, -1, 0, 0), hCur = make_int4(0, -1, 0, 0);
+        bool pend = false;
+        int32_t pendD = 0, pendXlo = 0, pendW = 0, pendOff = 0;
+        float pendAdj = 0.f;
+        auto flush = [&]() {
+            if (warp == NW - 1) {
+                const int32_t nWords = (pendW + 31) >> 5;
+                {
+                    unsigned any = 0u;
+                    for (int32_t c = lane; c < nWords; c += 32) any |= S.hitW[(pendD & 1) * 3 * S.nCh + c];
+                    if (!__any_sync(0xffffffffu, any != 0u)) { pend = false; return; }
+                }
+                const float *rowM = ringF + pendOff;
+                const int32_t jb = K::jbase(pendD, H);
+                const float *bM = stateF(S, pendD & 1);
+                int64_t base = nPairs;
+                for (int32_t c0 = 0; c0 < nWords; c0 += 32) {
+                    const int32_t c = c0 + lane;
+                    unsigned wv = c < nWords ? S.hitW[(pendD & 1) * 3 * S.nCh + c] : 0u;
+                    const int cnt = __popc(wv);
+                    int inc = cnt;
+#pragma unroll
+                    for (int o = 1; o < 32; o <<= 1) {
+                        const int q = __shfl_up_sync(0xffffffffu, inc, o);
+                        if (lane >= o) inc += q;
+                    }
+                    int64_t w = base + (inc - cnt);
+                    while (wv) {
+                        const int bit = __ffs(wv) - 1;
+                        wv &= wv - 1;
+                        const int32_t i = c * 32 + bit, x = pendXlo + i;
+                        const double pp = exp((double) ((rowM[i] + bM[3 * ((x + jb) & S.mask)]) + pendAdj));
+                        if (w < I.pairCap) {
+                            sa_pair_t o;
+                            o.p = (int32_t) floor((pp > 1.0 ? 1.0 : pp) * 10000000.0);
+                            o.x = x - 1; o.y = pendD - x - 1;
+                            o.kmerIdx = P.kmerIdx[I.kmerOff + x - 1];
+                            P.pairs[I.pairOff + w] = o;
+                        }
+                        w++;
+                    }
+                    base += __shfl_sync(0xffffffffu, inc, 31);
+                }
+                nPairs = base;
+            }
+            pend = false;
+        };
+        for (int32_t d2 = d; d2 > tracedBackTo; d2--) {
+            int32_t q = tTop - d2;
+            if (q == BT) {
+                fillBack(rowI);
+                tTop = d2; q = 0;
+                __syncthreads();
+            }
+            hCur = S.descB[q];
+            const int32_t bxlo = hCur.x, bxhi = hCur.y, w = bxhi - bxlo + 1, par = d2 & 1, jb = K::jbase(d2, H);
+            const bool post = d2 <= tracedBackFrom;
+            float *cur = stateF(S, par);                  // b(d2 + 2) -> b(d2)
+            const float *prv = stateF(S, par ^ 1);        // b(d2 + 1)
+            const float *row = ringF + hCur.z;
+            const double oF0 = offF[d2 >> 4];
+            {
+                const bool up = hUp.y >= hUp.x;
+                const int32_t cl = up ? min(bxlo, hUp.x) : bxlo, ch = up ? max(bxhi + 1, hUp.y) : bxhi + 1;
+                const int32_t el = up ? min(d2 - bxhi, d2 + 1 - hUp.y) : d2 - bxhi;
+                const int32_t eh = up ? max(d2 - bxlo + 1, d2 + 1 - hUp.x) : d2 - bxlo + 1;
+                ensureRings(P, I, S, t, NT, cl, el, max(ch - cl, eh - el), false, cLo, eLo);
+            }
+            // backward offset of this diagonal
+            if (d2 < d) {
+                o2 = o1; o1 = o0;
+                if ((d2 & 15) == 15 && d2 < d - 1) o0 = o1 + shiftNext;
+            }
+            const float e1 = (float) (o1 - o0), e2 = (float) (o2 - o0);
+            const bool newTotal = post && postMod == 0;
+            if (post) postMod = postMod == 9 ? 0 : postMod + 1;
+            const bool inlinePost = post && !newTotal;
+            float adj = 0.f;
+            if (inlinePost) adj = (float) ((oF0 + o0) - totalAbs);
+            const bool wantMax = (d2 & 15) == 0;      // the next step enters a new group of 16: it needs this diagonal's maximum
+            float tmax = -INFINITY;
+            if (d2 < d) {
+                const float cM0 = tMM + e2, cM1 = tXM + e2, cM2 = tYM + e2, cY0 = tMY + e1, cY1 = tYY + e1;
+                const float cOXe = cOX + e1, cEXe = cEX + e1;
+                const int32_t nChunks = (w + 31) >> 5;
+                for (int32_t c = warp; c < nChunks; c += NW) {
+                    const int32_t i = c * 32 + lane;
+                    bool cand = false;
+                    float arg = 0.f;
+                    if (i < w) {
+                        const int32_t x = bxlo + i, y = d2 - x;
+                        const int32_t j = (x + jb) & S.mask, sq = (j - 1 + par) & S.mask, sl = (sq + 1) & S.mask;
+                        const float aM = cur[3 * j], qY = prv[3 * sq + 2], lX = prv[3 * sl + 1];
+                        const float aE = emissionM(S, x + 1, y + 1), qE = emissionY(S, x, y + 1);
+                        const float M = sa_logAddF(sa_logAddF(aM + (aE + cM0), qY + (qE + cY0)), lX + cOXe);
+                        const float X = sa_logAddF(aM + (aE + cM1), lX + cEXe);
+                        const float Y = sa_logAddF(aM + (aE + cM2), qY + (qE + cY1));
+                        cur[3 * j] = M; cur[3 * j + 1] = X; cur[3 * j + 2] = Y;
+                        if (wantMax) tmax = fmaxf(tmax, fmaxf(M, fmaxf(X, Y)));
+                        if (inlinePost) {
+                            arg = (row[i] + M) + adj;
+                            cand = x > 0 && y > 0 && arg >= gate;
+                        }
+                    }
+                    if (inlinePost) {
+                        bool hit = false;
+                        if (__any_sync(0xffffffffu, cand)) hit = cand && exp((double) arg) >= P.threshold;
+                        const unsigned m = __ballot_sync(0xffffffffu, hit);
+                        if (lane == 0) S.hitW[par * 3 * S.nCh + c] = m;
+                    }
+                }
+                if (hUp2.y >= hUp2.x) {
+                    const int32_t jb2 = jb - 1;
+                    const int32_t nLow = max(0, min(hUp2.y, bxlo) - hUp2.x + 1);
+                    const int32_t hiStart = max(hUp2.x, bxhi + 2);
+                    const int32_t nHigh = max(0, hUp2.y - hiStart + 1);
+                    for (int32_t k = NT - 1 - t; k < nLow + nHigh; k += NT) {
+                        const int32_t xq = k < nLow ? hUp2.x + k : hiStart + (k - nLow);
+                        const int32_t s = (xq + jb2) & S.mask;
+                        cur[3 * s] = -INFINITY; cur[3 * s + 1] = -INFINITY; cur[3 * s + 2] = -INFINITY;
+                    }
+                }
+            } else if (wantMax) tmax = fmaxf(endS[0], fmaxf(endS[1], endS[2]));
+            if (pend) flush();
+            if (post) {
+                if (newTotal) {
+                    // diagonalCalculationTotalProbability (reference pairwiseAligner.c:1335-1353): the terms in float, relative to
+                    // O = oF(d2) + oB(d2); the ordered fold is WideK's (double chain on the float-derived terms)
+                    const double O = oF0 + o0;
+                    const int32_t nChunks = (w + 31) >> 5;
+                    for (int32_t c = warp; c < nChunks; c += NW) {
+                        const int32_t i = c * 32 + lane;
+                        double v = -INFINITY;
+                        if (i < w) {
+                            const int32_t j = (bxlo + i + jb) & S.mask;
+                            float vf = row[i] + cur[3 * j];
+                            vf = sa_logAddF(vf, row[w + i] + cur[3 * j + 1]);
+                            vf = sa_logAddF(vf, row[2 * w + i] + cur[3 * j + 2]);
+                            v = (double) vf;
+                            S.foldv[i] = v;
+                        }
+                        K::chunkMax(S, 0, c, lane, v);
+                    }
+                    const int4 hDn = S.descB[q + 1];
+                    const int32_t w1 = hUp.y - hUp.x + 1, wD = hDn.y - hDn.x + 1;
+                    const int32_t n1 = w1 > 0 ? w1 : 0;
+                    {
+                        const float *rowD = ringF + hDn.z;
+                        const int32_t jb1 = K::jbase(d2 + 1, H);
+                        const float rel = (float) ((offF[(d2 - 1) >> 4] + o1) - O);      // f(d2 - 1) and b(d2 + 1) onto O
+                        const int32_t nChunks1 = (n1 + 31) >> 5;
+                        for (int32_t c = warp; c < nChunks1; c += NW) {
+                            const int32_t i = c * 32 + lane;
+                            double v = -INFINITY;
+                            if (i < n1) {
+                                const int32_t x = hUp.x + i, y = d2 + 1 - x, iD = x - 1 - hDn.x;
+                                float gM = -INFINITY, gX = -INFINITY, gY = -INFINITY;
+                                if (iD >= 0 && iD < wD) { gM = rowD[iD]; gX = rowD[wD + iD]; gY = rowD[2 * wD + iD]; }
+                                const float e = emissionM(S, x, y);
+                                const float m = sa_logAddF(sa_logAddF(gM + (e + tMM), gX + (e + tXM)), gY + (e + tYM));
+                                v = (double) ((m + prv[3 * ((x + jb1) & S.mask)]) + rel);
+                                S.foldv[S.NSW + i] = v;
+                            }
+                            K::chunkMax(S, 1, c, lane, v);
+                        }
+                    }
+                    __syncthreads();
+                    K::classify(S, 0, w, lane, warp, NW);
+                    K::classify(S, 1, n1, lane, warp, NW);
+                    __syncthreads();
+                    if (warp == 0) {
+                        const double tot = K::foldChains(S, w, n1, lane);
+                        if (lane == 0) *S.sTotal = tot;
+                    }
+                    __syncthreads();
+                    totalAbs = O + *S.sTotal;
+                    adj = (float) (O - totalAbs);
+                }
+                // diagonalCalculationPosteriorMatchProbs (reference pairwiseAligner.c:1355-1421)
+                const int32_t nChunks = inlinePost && d2 < d ? 0 : (w + 31) >> 5;
+                for (int32_t c = warp; c < nChunks; c += NW) {
+                    const int32_t i = c * 32 + lane, x = bxlo + i;
+                    bool cand = false;
+                    float arg = 0.f;
+                    if (i < w) {
+                        arg = (row[i] + cur[3 * ((x + jb) & S.mask)]) + adj;
+                        cand = x > 0 && d2 - x > 0 && arg >= gate;
+                    }
+                    bool hit = false;
+                    if (__any_sync(0xffffffffu, cand)) hit = cand && exp((double) arg) >= P.threshold;
+                    const unsigned m = __ballot_sync(0xffffffffu, hit);
+                    if (lane == 0) S.hitW[par * 3 * S.nCh + c] = m;
+                }
+                pend = true; pendD = d2; pendXlo = bxlo; pendW = w; pendOff = hCur.z; pendAdj = adj;
+            }
+            if (wantMax) postMax(E, tmax, lane, warp);
+            __syncthreads();                    // b(d2), the hit words and (wantMax) the maxima are complete
+            if (wantMax) shiftNext = readMax(E, NW);
+            hUp2 = hUp; hUp = hCur;
+            rowI = rowI == 0 ? cap - 1 : rowI - 1;
+        }
+        if (pend) flush();
+    }
+
+    // ------------------------------------------------------------------------------------------ one work item
+    static __device__ void run(const FParams &P, const FItem &I, int it, const Sm &S, const Extra &E, const Rows &RW, double *offF) {
+        const int t = threadIdx.x, NT = blockDim.x, lane = t & 31, warp = t >> 5, NW = NT >> 5;
+        const double *T = P.trans;
+        const int32_t nDiag = I.lX + I.lY;
+        int64_t nPairs = 0;
+        if (nDiag == 0) {
+            if (t == 0) P.pairCount[it] = 0;
+            return;
+        }
+        const int32_t *tbList = P.tb + I.tbOff;
+        const int32_t nTb = P.geo[it].nTb;
+        const int32_t H = I.lY + 2;
+        float *ringF = reinterpret_cast<float *>(RW.ring);
+        __syncthreads();
+        if (t == 0) { S.sInt[1] = 0; offF[0] = 0.0; }
+        int32_t cLo = -kSlack, eLo = -kSlack, bd0 = 1;
+        for (int32_t k = t; k < S.NSW; k += NT) {
+            fillConst1(P, I, S, cLo + k);
+            const int32_t y = eLo + k;
+            S.evs[y & S.mask] = (y >= 1 && y <= I.lY) ? P.evMean[I.evOff + y - 1] : 0.0;
+        }
+        {
+            const bool ragged = I.flags & 1;
+            const float s0[3] = {ragged ? -INFINITY : 0.f, ragged ? 0.f : -INFINITY, ragged ? 0.f : -INFINITY};
+            loadState(S, t, NT, H, 0, 0, 0, nullptr, s0, -1, 0, -1, nullptr);
+            if (t == 0) {
+                ringF[0] = s0[0]; ringF[1] = s0[1]; ringF[2] = s0[2];
+                RW.hdr[0] = make_int4(0, 0, 0, 3);
+            }
+        }
+        int32_t tracedBackTo = 0;
+        int tbI = 0;
+        int32_t nextT = nTb > 0 ? tbList[0] : nDiag;
+        int32_t curFrom = nextT - (nextT == nDiag ? 0 : P.traceBack + 1);
+        const float cOX = (float) (P.eX + T[T_GAP_OPEN_X]), cEX = (float) (P.eX + T[T_GAP_EXTEND_X]);
+        const float tMM = (float) T[T_MATCH_CONTINUE], tXM = (float) T[T_MATCH_FROM_GAP_X], tYM = (float) T[T_MATCH_FROM_GAP_Y];
+        const float tMY = (float) T[T_GAP_OPEN_Y], tYY = (float) T[T_GAP_EXTEND_Y];
+        int32_t rowI = 0;
+        int32_t wr = 3;
+        K::fillTable(P, I, S, RW, t, NT, bd0, 1, tbI, nTb, tbList, wr);
+        __syncthreads();
+        int32_t xlo1 = 0, xhi1 = 0, xlo2 = 0, xhi2 = -1;
+        double o0 = 0.0, o1 = 0.0, o2 = 0.0;    // forward offsets of d, d - 1, d - 2
+        double shiftNext = 0.0;                 // rounded maximum of f(d - 1), valid on diagonals that are multiples of 16
+        for (int32_t d = 1; d <= nDiag; d++) {
+            rowI = rowI + 1 == RW.cap ? 0 : rowI + 1;
+            if (d >= bd0 + BT) {
+                bd0 = d;
+                K::fillTable(P, I, S, RW, t, NT, bd0, rowI, tbI, nTb, tbList, wr);
+                __syncthreads();
+            }
+            const int4 D4 = S.desc[d - bd0];
+            const int32_t xlo = D4.x, xhi = D4.y, w = xhi - xlo + 1, par = d & 1, jb = K::jbase(d, H);
+            ensureRings(P, I, S, t, NT, xlo, d - xhi, w - 1, true, cLo, eLo);
+            o2 = o1; o1 = o0;
+            if ((d & 15) == 0) {
+                o0 = o1 + shiftNext;
+                if (t == 0) offF[d >> 4] = o0;
+            }
+            const float e1 = (float) (o1 - o0), e2 = (float) (o2 - o0);
+            const float cM0 = tMM + e2, cM1 = tXM + e2, cM2 = tYM + e2, cY0 = tMY + e1, cY1 = tYY + e1;
+            const float cOXe = cOX + e1, cEXe = cEX + e1;
+            const bool full = D4.w == 3;
+            const bool wantMax = ((d + 1) & 15) == 0;
+            float tmax = -INFINITY;
+            float *row = ringF + D4.z;
+            float *cur = stateF(S, par);                      // f(d - 2) -> f(d)
+            const float *prv = stateF(S, par ^ 1);            // f(d - 1)
+            const int32_t nChunks = (w + 31) >> 5;
+            for (int32_t c = warp; c < nChunks; c += NW) {
+                const int32_t i = c * 32 + lane;
+                if (i < w) {
+                    const int32_t x = xlo + i, y = d - x;
+                    const int32_t j = (x + jb) & S.mask, sl = (j - 1 + par) & S.mask, su = (sl + 1) & S.mask;
+                    float eM, eY;
+                    emissions(S, x, y, eM, eY);
+                    float *pj = cur + 3 * j;
+                    const float *pl = prv + 3 * sl, *pu = prv + 3 * su;
+                    const float n1M = pl[0], n1X = pl[1];
+                    const float f1M = pu[0], f1Y = pu[2];
+                    const float n2M = pj[0], n2X = pj[1], n2Y = pj[2];
+                    // stateMachine3_cellCalculate order (the first contribution lands on -inf)
+                    const float X = sa_logAddF(n1M + cOXe, n1X + cEXe);
+                    const float M = sa_logAddF(sa_logAddF(n2M + (eM + cM0), n2X + (eM + cM1)), n2Y + (eM + cM2));
+                    const float Y = sa_logAddF(f1M + (eY + cY0), f1Y + (eY + cY1));
+                    pj[0] = M; pj[1] = X; pj[2] = Y;
+                    row[i] = M;
+                    if (full) { row[w + i] = X; row[2 * w + i] = Y; }
+                    if (wantMax) tmax = fmaxf(tmax, fmaxf(M, fmaxf(X, Y)));
+                }
+            }
+            if (xhi2 >= xlo2) {
+                const int32_t jb2 = jb + 1;
+                const int32_t nLow = max(0, min(xhi2, xlo - 2) - xlo2 + 1);
+                const int32_t hiStart = max(xlo2, xhi);
+                const int32_t nHigh = max(0, xhi2 - hiStart + 1);
+                for (int32_t k = NT - 1 - t; k < nLow + nHigh; k += NT) {
+                    const int32_t xq = k < nLow ? xlo2 + k : hiStart + (k - nLow);
+                    float *ps = cur + 3 * ((xq + jb2) & S.mask);
+                    ps[0] = -INFINITY; ps[1] = -INFINITY; ps[2] = -INFINITY;
+                }
+            }
+            xlo2 = xlo1; xhi2 = xhi1; xlo1 = xlo; xhi1 = xhi;
+            if (wantMax) postMax(E, tmax, lane, warp);
+            __syncthreads();                    // f(d) is complete
+            if (wantMax) shiftNext = readMax(E, NW);
+            if (d != nextT) continue;
+            const bool atEnd = d == nDiag;
+            const int32_t tracedBackFrom = curFrom;
+            traceback(P, I, S, E, RW, offF, t, NT, H, d, rowI, cLo, eLo, tracedBackTo, tracedBackFrom, atEnd, cOX, cEX, nPairs);
+            tracedBackTo = tracedBackFrom;
+            tbI++;
+            nextT = tbI < nTb ? tbList[tbI] : nDiag;
+            curFrom = nextT - (nextT == nDiag ? 0 : P.traceBack + 1);
+            if (atEnd) break;
+            __syncthreads();
+            {
+                const int4 h0 = RW.hdr[rowI], h1 = RW.hdr[rowI == 0 ? RW.cap - 1 : rowI - 1];
+                const float none[3] = {-INFINITY, -INFINITY, -INFINITY};
+                loadState(S, t, NT, H, d, h0.x, h0.y, ringF + h0.z, none, d - 1, h1.x, h1.y, ringF + h1.z);
+                xlo1 = h0.x; xhi1 = h0.y; xlo2 = h1.x; xhi2 = h1.y;
+            }
+            __syncthreads();
+        }
+        if (t == NT - 1) P.pairCount[it] = nPairs;
+    }
+};
+
+// Launch: blockDim = threads of the class, dynamic shared memory = WideF<GR>::smemBytes(P.wNSW, P.wFold == nullptr)
+template <bool GR>
+__global__ void __launch_bounds__(1024, 1) sa_wide32_kernel(const __grid_constant__ FParams P) {
+    extern __shared__ __align__(16) double sa_wsm32[];
+    typename WideF<GR>::Sm S;
+    typename WideF<GR>::Extra E;
+    WideF<GR>::carve(S, E, sa_wsm32, P.wNSW, P.wFold ? P.wFold + (int64_t) blockIdx.x * 2 * P.wNSW : nullptr,
+                     GR ? P.wRings + (int64_t) blockIdx.x * 6 * P.wNSW : nullptr);
+    sa_logAdd_init();
+    typename WideF<GR>::Rows RW;
+    RW.ring = P.scratch + (int64_t) blockIdx.x * P.wRingDoubles;
+    RW.hdr = P.wHdr + (int64_t) blockIdx.x * P.wRowsCap;
+    RW.cap = P.wRowsCap;
+    RW.ringDoubles = (int32_t) P.wRingDoubles;            // the ring counts FLOATS here (same element count, half the bytes)
+    double *offF = P.wOff + (int64_t) blockIdx.x * P.wOffCap;
+    for (;;) {
+        __syncthreads();
+        if (threadIdx.x == 0) S.sInt[0] = atomicAdd(P.counter, 1);
+        __syncthreads();
+        const int n = S.sInt[0];
+        if (n >= P.nOrder) break;
+        const int it = P.order[n];
+        WideF<GR>::run(P, P.items[it], it, S, E, RW, offF);
+    }
+}
