@@ -489,33 +489,6 @@ extern "C" int sa_gpu_set_precision(int precision) {
 }
 extern "C" int sa_gpu_get_precision(void) { return currentPrecision(); }
 
-// FP32 wide kernel: rings in global memory from this window size on (SA_WIDE32_GR_FROM), shared-memory bytes, occupancy, launch
-static bool wide32GlobalRings(int c) {
-    int from = 2048;
-    if (const char *e = getenv("SA_WIDE32_GR_FROM")) from = atoi(e);
-    return kWideNSW[c] >= from || WideF<false>::smemBytes(kWideNSW[c], false) > kSmemCap;
-}
-static size_t wide32SmemBytes(bool gr, int NSW, bool foldInSmem) {
-    return gr ? WideF<true>::smemBytes(NSW, false) : WideF<false>::smemBytes(NSW, foldInSmem);
-}
-template <bool GR>
-static int wide32OccupancyT(int threads, size_t smem, int *bps) {
-    static bool raised = false;
-    if (smem > 48 * 1024 && !raised) {
-        CK(cudaFuncSetAttribute(sa_wide32_kernel<GR>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) kSmemCap));
-        raised = true;
-    }
-    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(bps, sa_wide32_kernel<GR>, threads, smem));
-    return SA_OK;
-}
-static int wide32Occupancy(bool gr, int threads, size_t smem, int *bps) {
-    return gr ? wide32OccupancyT<true>(threads, smem, bps) : wide32OccupancyT<false>(threads, smem, bps);
-}
-static void wide32Launch(bool gr, int blocks, int threads, size_t smem, cudaStream_t st, const FParams &f) {
-    if (gr) sa_wide32_kernel<true><<<blocks, threads, smem, st>>>(f);
-    else sa_wide32_kernel<false><<<blocks, threads, smem, st>>>(f);
-}
-
 // does the class keep its emission rings in global memory?  From the 2048-slot window on: with the rings in shared memory
 // one CTA of that class fills an SM (1024 threads, half of them idle on a typical diagonal); with only the DP state
 // there, two CTAs of 512 threads fit and overlap each other's barriers (+15 % on the contract pattern).
@@ -544,6 +517,41 @@ static bool wideFoldGlobal(int c, bool gr) {
     if (gr) return true;
     if (const char *e = getenv("SA_WIDE_FOLDG_FROM")) if (kWideNSW[c] >= atoi(e)) return true;
     return wideSmemBytes(false, kWideNSW[c], true) > kSmemCap;
+}
+
+// FP32 wide kernel: one instantiation per window class — <rings in global memory, window, max threads, CTAs per SM the
+// registers are held to>; the window is a compile-time constant there (immediate masks and shared-memory offsets)
+#define SA_W32_CLASSES(X) X(0, false, 256, 128, 6) X(1, false, 512, 256, 3) X(2, false, 1024, 256, 3) X(3, true, 2048, 256, 3) X(4, true, 4096, 512, 1)
+static bool wide32GlobalRings(int c) { return c >= 3; }
+static int wide32Threads(int c) {
+    static const int nt[kWideClasses] = {128, 256, 256, 256, 512};
+    const int t = wideThreads(c);                     // SA_WIDE_NT override, bounded by the instantiation's launch bound
+    return getenv("SA_WIDE_NT") ? std::min(t, nt[c]) : nt[c];
+}
+static size_t wide32SmemBytes(int c, bool foldInSmem) {
+#define X(C, GR, NSW, NT, MB) if (c == C) return WideF<GR, NSW>::smemBytes(NSW, foldInSmem);
+    SA_W32_CLASSES(X)
+#undef X
+    return 0;
+}
+static int wide32Occupancy(int c, int threads, size_t smem, int *bps) {
+    static bool raised[kWideClasses] = {false, false, false, false, false};
+#define X(C, GR, NSW, NT, MB)                                                                                                   \
+    if (c == C) {                                                                                                              \
+        if (smem > 48 * 1024 && !raised[C]) {                                                                                  \
+            CK(cudaFuncSetAttribute(sa_wide32_kernel<GR, NSW, NT, MB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) kSmemCap)); \
+            raised[C] = true;                                                                                                  \
+        }                                                                                                                      \
+        CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(bps, sa_wide32_kernel<GR, NSW, NT, MB>, threads, smem));             \
+    }
+    SA_W32_CLASSES(X)
+#undef X
+    return SA_OK;
+}
+static void wide32Launch(int c, int blocks, int threads, size_t smem, cudaStream_t st, const FParams &f) {
+#define X(C, GR, NSW, NT, MB) if (c == C) sa_wide32_kernel<GR, NSW, NT, MB><<<blocks, threads, smem, st>>>(f);
+    SA_W32_CLASSES(X)
+#undef X
 }
 
 // readBase: index of reads[0] in the caller's array (error messages name the caller's read)
@@ -1008,11 +1016,11 @@ static int prepareBatch(const sa_model_t *m, const sa_read_t *reads, int64_t nRe
         const bool hdp = m->kind == SA_EMIT_HDP;
         b->fp32 = currentPrecision() == SA_PRECISION_FP32 && !b->expectations && m->kind == SA_EMIT_GAUSS_MEANONLY_DESCALE;
         const bool gr = b->fp32 ? wide32GlobalRings(c) : wideGlobalRings(c);
-        const bool foldGlobal = b->fp32 ? (gr || wide32SmemBytes(false, kWideNSW[c], true) > kSmemCap) : wideFoldGlobal(c, gr);
-        const size_t smem = b->fp32 ? wide32SmemBytes(gr, kWideNSW[c], !foldGlobal) : wideSmemBytes(gr, kWideNSW[c], !foldGlobal);
+        const bool foldGlobal = b->fp32 ? gr : wideFoldGlobal(c, gr);
+        const size_t smem = b->fp32 ? wide32SmemBytes(c, !foldGlobal) : wideSmemBytes(gr, kWideNSW[c], !foldGlobal);
         int bps = 1;
         if (b->fp32) {
-            if ((rc = wide32Occupancy(gr, wideThreads(c), smem, &bps))) return rc;
+            if ((rc = wide32Occupancy(c, wide32Threads(c), smem, &bps))) return rc;
         } else if ((rc = wideOccupancy(gr, hdp, b->expectations, wideThreads(c), smem, &bps))) return rc;
         b->wBlocks[c] = (int) std::min<int64_t>((int64_t) nSM * std::max(1, bps), (int64_t) b->wOrder[c].size());
         b->wRows[c] += 4 + 256;      // + one descriptor table of headers written ahead
@@ -1211,9 +1219,8 @@ static int launchBatch(sa_batch_t *b) {
         f.wNSW = kWideNSW[c]; f.wRowsCap = b->wRows[c]; f.wRingDoubles = b->wRingDoubles[c];
         f.scratch = b->dWRing[c].p; f.wHdr = b->dWHdr[c].p; f.wFold = b->dWFold[c].p; f.wRings = b->dWRings[c].p;
         if (b->fp32) {
-            const bool gr = b->dWRings[c].p != nullptr;
             f.wOff = b->dWOff[c].p; f.wOffCap = b->wOffCap[c];
-            wide32Launch(gr, b->wBlocks[c], wideThreads(c), wide32SmemBytes(gr, kWideNSW[c], b->dWFold[c].p == nullptr), st, f);
+            wide32Launch(c, b->wBlocks[c], wide32Threads(c), wide32SmemBytes(c, b->dWFold[c].p == nullptr), st, f);
         } else {
             const bool gr = wideGlobalRings(c);
             wideLaunch(gr, hdp, b->expectations, b->wBlocks[c], wideThreads(c),

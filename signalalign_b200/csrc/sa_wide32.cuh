@@ -21,7 +21,9 @@
 #pragma once
 #include "sa_wide.cuh"
 
-template <bool GR>
+// NSWT: the window (slots) as a compile-time constant — every `& mask`, plane offset and shared-memory address of the hot
+// loops is then an immediate instead of a value the compiler keeps re-deriving from the kernel parameters.
+template <bool GR, int NSWT>
 struct WideF {
     using K = WideK<false, false, GR>;
     using Sm = typename K::Sm;            // same struct; st / cst hold the layouts below behind the double pointers
@@ -40,7 +42,8 @@ struct WideF {
     struct Extra {          // what the float variant adds to the shared tables
         float *red;         // [64] per-warp maxima for the offset refresh
     };
-    static __device__ __forceinline__ void carve(Sm &S, Extra &E, double *base, int NSW, double *foldGlobal, double *ringsGlobal) {
+    static __device__ __forceinline__ void carve(Sm &S, Extra &E, double *base, double *foldGlobal, double *ringsGlobal) {
+        constexpr int NSW = NSWT;
         S.NSW = NSW; S.mask = NSW - 1; S.nCh = NSW / 32;
         double *p = base;
         S.st = p; p += 3 * NSW;                              // 24 B per slot
@@ -177,7 +180,7 @@ struct WideF {
     // WideK::traceback for the structure.  b(d2) is relative to a backward offset oB(d2) (0 on the block's first diagonal,
     // moved by the rounded maximum of the previous diagonal whenever d2 enters a new group of 16); f(d2) is relative to
     // offF[d2 >> 4], written by the forward sweep.
-    static __device__ void traceback(const FParams &P, const FItem &I, const Sm &S, const Extra &E, const Rows &RW, const double *offF,
+    static __device__ __forceinline__ void traceback(const FParams &P, const FItem &I, const Sm &S, const Extra &E, const Rows &RW, const double *offF,
                                      int t, int NT, int32_t H, int32_t d, int32_t rowI, int32_t &cLo, int32_t &eLo,
                                      int32_t tracedBackTo, int32_t tracedBackFrom, bool atEnd, float cOX, float cEX,
                                      int64_t &nPairs) {
@@ -416,7 +419,7 @@ struct WideF {
     }
 
     // ------------------------------------------------------------------------------------------ one work item
-    static __device__ void run(const FParams &P, const FItem &I, int it, const Sm &S, const Extra &E, const Rows &RW, double *offF) {
+    static __device__ __forceinline__ void run(const FParams &P, const FItem &I, int it, const Sm &S, const Extra &E, const Rows &RW, double *offF) {
         const int t = threadIdx.x, NT = blockDim.x, lane = t & 31, warp = t >> 5, NW = NT >> 5;
         const double *T = P.trans;
         const int32_t nDiag = I.lX + I.lY;
@@ -544,16 +547,17 @@ struct WideF {
     }
 };
 
-// Launch: blockDim = threads of the class, dynamic shared memory = WideF<GR>::smemBytes(P.wNSW, P.wFold == nullptr)
-template <bool GR>
-__global__ void __launch_bounds__(1024, 1) sa_wide32_kernel(const __grid_constant__ FParams P) {
+// Launch: blockDim = threads of the class (<= NTMAX), dynamic shared memory = WideF<GR, NSW>::smemBytes(NSW, P.wFold == nullptr)
+template <bool GR, int NSW, int NTMAX, int MINB>
+__global__ void __launch_bounds__(NTMAX, MINB) sa_wide32_kernel(const __grid_constant__ FParams P) {
     extern __shared__ __align__(16) double sa_wsm32[];
-    typename WideF<GR>::Sm S;
-    typename WideF<GR>::Extra E;
-    WideF<GR>::carve(S, E, sa_wsm32, P.wNSW, P.wFold ? P.wFold + (int64_t) blockIdx.x * 2 * P.wNSW : nullptr,
-                     GR ? P.wRings + (int64_t) blockIdx.x * 6 * P.wNSW : nullptr);
+    using W = WideF<GR, NSW>;
+    typename W::Sm S;
+    typename W::Extra E;
+    W::carve(S, E, sa_wsm32, P.wFold ? P.wFold + (int64_t) blockIdx.x * 2 * NSW : nullptr,
+             GR ? P.wRings + (int64_t) blockIdx.x * 6 * NSW : nullptr);
     sa_logAdd_init();
-    typename WideF<GR>::Rows RW;
+    typename W::Rows RW;
     RW.ring = P.scratch + (int64_t) blockIdx.x * P.wRingDoubles;
     RW.hdr = P.wHdr + (int64_t) blockIdx.x * P.wRowsCap;
     RW.cap = P.wRowsCap;
@@ -566,6 +570,6 @@ __global__ void __launch_bounds__(1024, 1) sa_wide32_kernel(const __grid_constan
         const int n = S.sInt[0];
         if (n >= P.nOrder) break;
         const int it = P.order[n];
-        WideF<GR>::run(P, P.items[it], it, S, E, RW, offF);
+        W::run(P, P.items[it], it, S, E, RW, offF);
     }
 }
