@@ -18,7 +18,7 @@
 // fetches its coefficients with two conflict-free LDS.128.  Row 16 is all zeros: the "far" case (|x - y| >= 7.5, or an
 // operand -inf) evaluates 0 + max(x, y) through the same instructions.  Every kernel calls sa_logAdd_init() once per CTA.
 __shared__ __align__(16) double sa_lt[68];
-__shared__ __align__(16) float sa_ltf[68];      // the same table in single precision (sa_logAddF, the FP32 band kernel)
+__shared__ __align__(16) float sa_ltf[68];      // single precision, linear coefficient minus one (sa_logAddF, the FP32 band kernel)
 
 __device__ __forceinline__ void sa_logAdd_init() {
     const float c[16] = {-0.009350833524763f, 0.130659527668286f, 0.498799810682272f, 0.693203116424741f,
@@ -31,7 +31,7 @@ __device__ __forceinline__ void sa_logAdd_init() {
 #pragma unroll
         for (int q = 1; q < 16; q++) v = k == q ? c[q] : v;
         sa_lt[i] = n >= 16 ? 0.0 : (double) v;
-        sa_ltf[i] = n >= 16 ? 0.0f : v;
+        sa_ltf[i] = n >= 16 ? 0.0f : ((i & 3) == 2 ? v - 1.0f : v);
     }
     __syncthreads();
 }
@@ -63,22 +63,27 @@ __device__ __forceinline__ double sa_logAdd(double x, double y) {
     return __dadd_rn(__dadd_rn(r, cb.y), base);
 }
 
-// The same logAdd in single precision for the FP32 band kernel (sa_wide32.cuh): the reference's coefficients ARE float
-// literals, the range index ceil(2 d) comes from one FADD.RU (2 d + 2^23 rounded up leaves it in the low mantissa bits), the
-// four coefficients of a row arrive in one LDS.128, the cubic is three FFMA.  Thresholds and branches are those of the
-// reference; only the rounding differs (operands are values relative to a per-diagonal offset: see sa_wide32.cuh).
-__device__ __forceinline__ float sa_logAddF(float x, float y) {
+// The same logAdd in single precision for the FP32 band kernel (sa_wide32.cuh).  The reference returns min + P(d) with
+// d = |x - y| and P one of its four cubics for log(1 + e^d); since min = max - d this is max + (P(d) - d), and P(d) - d is
+// the same cubic with 1 taken off its linear coefficient (the table above stores it that way).  That form needs neither
+// the "far" test nor a select between the operands: d is clamped to 8 on its bit pattern (which also absorbs +-inf and the
+// NaN of -inf - -inf), ceil(2 d) = 16 from 7.5 up, and row 16 is zeros, so a far pair evaluates max + 0.  The range index
+// comes out of one FFMA.RU (2 d + 2^23 rounded up leaves it in the low mantissa bits, and shifted left by four it IS the
+// byte offset of the row once 2^23's own bits are folded into the base address), the four coefficients arrive in one
+// LDS.128, the cubic is three FFMA: 11 instructions.  Thresholds are the reference's except at the single float d == 7.5f
+// (the cubic's 5.5e-4 instead of 0), which stands for true differences on both sides of 7.5 in equal measure.
+// (sa_logAddKey: the folded base address.  The kernel parks it in shared memory and reads it back once per diagonal — a
+// value that comes out of a load is one the assembler cannot split into "base" and "constant" again at every use)
+__device__ __forceinline__ unsigned sa_logAddKey() { return (unsigned) __cvta_generic_to_shared(sa_ltf) - 0xB0000000u; }
+__device__ __forceinline__ float sa_logAddF(float x, float y, unsigned key) {
     const float diff = __fsub_rn(x, y);
-    const unsigned bits = __float_as_uint(diff), ah = bits & 0x7fffffffu;
-    const bool far = ah >= 0x40F00000u;                 // |diff| >= 7.5f, inf or NaN
-    const bool xlt = (int) bits < 0;
-    const float base = (far == xlt) ? y : x;            // far: max(x, y); else min(x, y)
-    const float d = __uint_as_float(umin(ah, 0x41000000u));
-    unsigned n = __float_as_uint(__fadd_ru(__fmul_rn(d, 2.0f), 8388608.0f)) & 0x7fffffu;
-    n = far ? 16u : n;
-    const float4 c = *reinterpret_cast<const float4 *>(sa_ltf + 4 * n);
+    const float d = __uint_as_float(umin(__float_as_uint(diff) & 0x7fffffffu, 0x41000000u));
+    const unsigned nb = __float_as_uint(__fmaf_ru(d, 2.0f, 8388608.0f));           // 0x4B000000 + ceil(2 d)
+    const unsigned addr = (nb << 4) + key;
+    float4 c;
+    asm("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(c.x), "=f"(c.y), "=f"(c.z), "=f"(c.w) : "r"(addr));
     const float r = fmaf(fmaf(fmaf(c.x, d, c.y), d, c.z), d, c.w);
-    return __fadd_rn(r, base);
+    return __fadd_rn(fmaxf(x, y), r);
 }
 
 // exp() for the expectation sums (cell_signal_updateExpectations, impl/pairwiseAligner.c:914-944): every band cell adds

@@ -36,11 +36,12 @@ struct WideF {
     static __host__ __device__ size_t smemBytes(int NSW, bool foldInSmem) {
         size_t b = (size_t) 24 * NSW + (GR ? 0 : (size_t) (24 + 8 + (foldInSmem ? 16 : 0)) * NSW) + 16;
         b += (size_t) (NSW / 32) * (2 * 8 + 2 * 4 + 2 * 4 + 6 * 4);
-        b += (size_t) (2 * BT + 2) * 16 + 3 * (BT + 1) * 4 + 16 + 16 + 64 * 4;
+        b += (size_t) (2 * BT + 2) * 16 + 3 * (BT + 1) * 4 + 16 + 16 + 64 * 4 + 8 * 4;
         return b;
     }
     struct Extra {          // what the float variant adds to the shared tables
         float *red;         // [64] per-warp maxima for the offset refresh
+        float *kc;          // [8] the transition constants in single precision: MM XM YM MY | YY (eX + openX) (eX + extendX) logAdd-key
     };
     static __device__ __forceinline__ void carve(Sm &S, Extra &E, double *base, double *foldGlobal, double *ringsGlobal) {
         constexpr int NSW = NSWT;
@@ -61,12 +62,22 @@ struct WideF {
         S.candM = u; u += 2 * S.nCh;
         S.resetM = u; u += 2 * S.nCh;
         S.hitW = u; u += 6 * S.nCh;
+        E.kc = reinterpret_cast<float *>(u); u += 8;        // (16-byte aligned: every block above is a multiple of 16 bytes)
         int32_t *q = reinterpret_cast<int32_t *>(u);
         S.aX = q; q += BT + 1;
         S.aY = q; q += BT + 1;
         S.aD = q; q += BT + 1;
         S.sInt = q; q += 4;
         E.red = reinterpret_cast<float *>(q);
+    }
+    static __device__ __forceinline__ void fillTransitions(const FParams &P, const Extra &E) {
+        const double *T = P.trans;
+        if (threadIdx.x == 0) {
+            E.kc[0] = (float) T[T_MATCH_CONTINUE]; E.kc[1] = (float) T[T_MATCH_FROM_GAP_X]; E.kc[2] = (float) T[T_MATCH_FROM_GAP_Y];
+            E.kc[3] = (float) T[T_GAP_OPEN_Y]; E.kc[4] = (float) T[T_GAP_EXTEND_Y];
+            E.kc[5] = (float) (P.eX + T[T_GAP_OPEN_X]); E.kc[6] = (float) (P.eX + T[T_GAP_EXTEND_X]);
+            E.kc[7] = __uint_as_float(sa_logAddKey());      // read back with the constants: see sa_logAddKey
+        }
     }
     static __device__ __forceinline__ float *stateF(const Sm &S, int parity) { return reinterpret_cast<float *>(S.st) + parity * 3 * S.NSW; }
 
@@ -169,10 +180,10 @@ struct WideF {
         for (int o = 16; o > 0; o >>= 1) tmax = fmaxf(tmax, __shfl_xor_sync(0xffffffffu, tmax, o));
         if (lane == 0) E.red[warp] = tmax;
     }
-    static __device__ __forceinline__ double readMax(const Extra &E, int NW) {
+    static __device__ __forceinline__ float readMax(const Extra &E, int NW) {
         float m = -INFINITY;
         for (int w = 0; w < NW; w++) m = fmaxf(m, E.red[w]);
-        return m > -INFINITY ? (double) rintf(m) : 0.0;
+        return m > -INFINITY ? rintf(m) : 0.f;
     }
 
     // ------------------------------------------------------------------------------------------ traceback
@@ -182,12 +193,9 @@ struct WideF {
     // offF[d2 >> 4], written by the forward sweep.
     static __device__ __forceinline__ void traceback(const FParams &P, const FItem &I, const Sm &S, const Extra &E, const Rows &RW, const double *offF,
                                      int t, int NT, int32_t H, int32_t d, int32_t rowI, int32_t &cLo, int32_t &eLo,
-                                     int32_t tracedBackTo, int32_t tracedBackFrom, bool atEnd, float cOX, float cEX,
-                                     int64_t &nPairs) {
+                                     int32_t tracedBackTo, int32_t tracedBackFrom, bool atEnd, int64_t &nPairs) {
         const int lane = t & 31, warp = t >> 5, NW = NT >> 5;
         const double *T = P.trans;
-        const float tMM = (float) T[T_MATCH_CONTINUE], tXM = (float) T[T_MATCH_FROM_GAP_X], tYM = (float) T[T_MATCH_FROM_GAP_Y];
-        const float tMY = (float) T[T_GAP_OPEN_Y], tYY = (float) T[T_GAP_EXTEND_Y];
         const float gate = (float) P.logThrGate;
         const int32_t cap = RW.cap;
         const float *ringF = reinterpret_cast<const float *>(RW.ring);
@@ -211,8 +219,9 @@ struct WideF {
             __syncthreads();
         }
         double totalAbs = -INFINITY;            // total probability, absolute
-        double o0 = 0.0, o1 = 0.0, o2 = 0.0;    // backward offsets of d2, d2 + 1, d2 + 2
-        double shiftNext = 0.0;                 // rounded maximum of b(d2 + 1), valid on the step that enters a new group
+        double o0 = 0.0;                        // backward offset of d2
+        float s0 = 0.f, s1 = 0.f;               // o(d2) - o(d2 + 1) and o(d2 + 1) - o(d2 + 2): integers, zero except where a group starts
+        float shiftNext = 0.f;                  // rounded maximum of b(d2 + 1), valid on the step that enters a new group
         int32_t postMod = 0;
         int4 hUp = make_int4(0, -1, 0, 0), hUp2 = make_int4(0, -1, 0, 0), hCur = make_int4(0, -1, 0, 0);
         bool pend = false;
@@ -284,10 +293,10 @@ struct WideF {
             }
             // backward offset of this diagonal
             if (d2 < d) {
-                o2 = o1; o1 = o0;
-                if ((d2 & 15) == 15 && d2 < d - 1) o0 = o1 + shiftNext;
+                s1 = s0; s0 = 0.f;
+                if ((d2 & 15) == 15 && d2 < d - 1) { s0 = shiftNext; o0 += (double) shiftNext; }
             }
-            const float e1 = (float) (o1 - o0), e2 = (float) (o2 - o0);
+            const float e1 = -s0, e2 = -(s0 + s1);
             const bool newTotal = post && postMod == 0;
             if (post) postMod = postMod == 9 ? 0 : postMod + 1;
             const bool inlinePost = post && !newTotal;
@@ -296,25 +305,29 @@ struct WideF {
             const bool wantMax = (d2 & 15) == 0;      // the next step enters a new group of 16: it needs this diagonal's maximum
             float tmax = -INFINITY;
             if (d2 < d) {
-                const float cM0 = tMM + e2, cM1 = tXM + e2, cM2 = tYM + e2, cY0 = tMY + e1, cY1 = tYY + e1;
-                const float cOXe = cOX + e1, cEXe = cEX + e1;
+                const float4 k0 = *reinterpret_cast<const float4 *>(E.kc), k1 = *reinterpret_cast<const float4 *>(E.kc + 4);
+                const float cM0 = k0.x + e2, cM1 = k0.y + e2, cM2 = k0.z + e2, cY0 = k0.w + e1, cY1 = k1.x + e1;
+                const float cOXe = k1.y + e1, cEXe = k1.z + e1;
+                const unsigned lk = __float_as_uint(k1.w);
                 const int32_t nChunks = (w + 31) >> 5;
                 for (int32_t c = warp; c < nChunks; c += NW) {
                     const int32_t i = c * 32 + lane;
                     bool cand = false;
                     float arg = 0.f;
+                    // the stored forward value comes from L2 or HBM: asked for before the cell's arithmetic, used after it
+                    const float fM = (inlinePost && i < w) ? row[i] : 0.f;
                     if (i < w) {
                         const int32_t x = bxlo + i, y = d2 - x;
                         const int32_t j = (x + jb) & S.mask, sq = (j - 1 + par) & S.mask, sl = (sq + 1) & S.mask;
                         const float aM = cur[3 * j], qY = prv[3 * sq + 2], lX = prv[3 * sl + 1];
                         const float aE = emissionM(S, x + 1, y + 1), qE = emissionY(S, x, y + 1);
-                        const float M = sa_logAddF(sa_logAddF(aM + (aE + cM0), qY + (qE + cY0)), lX + cOXe);
-                        const float X = sa_logAddF(aM + (aE + cM1), lX + cEXe);
-                        const float Y = sa_logAddF(aM + (aE + cM2), qY + (qE + cY1));
+                        const float M = sa_logAddF(sa_logAddF(aM + (aE + cM0), qY + (qE + cY0), lk), lX + cOXe, lk);
+                        const float X = sa_logAddF(aM + (aE + cM1), lX + cEXe, lk);
+                        const float Y = sa_logAddF(aM + (aE + cM2), qY + (qE + cY1), lk);
                         cur[3 * j] = M; cur[3 * j + 1] = X; cur[3 * j + 2] = Y;
                         if (wantMax) tmax = fmaxf(tmax, fmaxf(M, fmaxf(X, Y)));
                         if (inlinePost) {
-                            arg = (row[i] + M) + adj;
+                            arg = (fM + M) + adj;
                             cand = x > 0 && y > 0 && arg >= gate;
                         }
                     }
@@ -340,6 +353,7 @@ struct WideF {
             if (pend) flush();
             if (post) {
                 if (newTotal) {
+                    const unsigned lk = __float_as_uint(E.kc[7]);
                     // diagonalCalculationTotalProbability (reference pairwiseAligner.c:1335-1353): the terms in float, relative to
                     // O = oF(d2) + oB(d2); the ordered fold is WideK's (double chain on the float-derived terms)
                     const double O = oF0 + o0;
@@ -350,8 +364,8 @@ struct WideF {
                         if (i < w) {
                             const int32_t j = (bxlo + i + jb) & S.mask;
                             float vf = row[i] + cur[3 * j];
-                            vf = sa_logAddF(vf, row[w + i] + cur[3 * j + 1]);
-                            vf = sa_logAddF(vf, row[2 * w + i] + cur[3 * j + 2]);
+                            vf = sa_logAddF(vf, row[w + i] + cur[3 * j + 1], lk);
+                            vf = sa_logAddF(vf, row[2 * w + i] + cur[3 * j + 2], lk);
                             v = (double) vf;
                             S.foldv[i] = v;
                         }
@@ -363,7 +377,8 @@ struct WideF {
                     {
                         const float *rowD = ringF + hDn.z;
                         const int32_t jb1 = K::jbase(d2 + 1, H);
-                        const float rel = (float) ((offF[(d2 - 1) >> 4] + o1) - O);      // f(d2 - 1) and b(d2 + 1) onto O
+                        const float rel = (float) ((offF[(d2 - 1) >> 4] + (o0 - (double) s0)) - O);      // f(d2 - 1) and b(d2 + 1) onto O
+                        const float tMM = E.kc[0], tXM = E.kc[1], tYM = E.kc[2];
                         const int32_t nChunks1 = (n1 + 31) >> 5;
                         for (int32_t c = warp; c < nChunks1; c += NW) {
                             const int32_t i = c * 32 + lane;
@@ -373,7 +388,7 @@ struct WideF {
                                 float gM = -INFINITY, gX = -INFINITY, gY = -INFINITY;
                                 if (iD >= 0 && iD < wD) { gM = rowD[iD]; gX = rowD[wD + iD]; gY = rowD[2 * wD + iD]; }
                                 const float e = emissionM(S, x, y);
-                                const float m = sa_logAddF(sa_logAddF(gM + (e + tMM), gX + (e + tXM)), gY + (e + tYM));
+                                const float m = sa_logAddF(sa_logAddF(gM + (e + tMM), gX + (e + tXM), lk), gY + (e + tYM), lk);
                                 v = (double) ((m + prv[3 * ((x + jb1) & S.mask)]) + rel);
                                 S.foldv[S.NSW + i] = v;
                             }
@@ -421,7 +436,6 @@ struct WideF {
     // ------------------------------------------------------------------------------------------ one work item
     static __device__ __forceinline__ void run(const FParams &P, const FItem &I, int it, const Sm &S, const Extra &E, const Rows &RW, double *offF) {
         const int t = threadIdx.x, NT = blockDim.x, lane = t & 31, warp = t >> 5, NW = NT >> 5;
-        const double *T = P.trans;
         const int32_t nDiag = I.lX + I.lY;
         int64_t nPairs = 0;
         if (nDiag == 0) {
@@ -453,16 +467,14 @@ struct WideF {
         int tbI = 0;
         int32_t nextT = nTb > 0 ? tbList[0] : nDiag;
         int32_t curFrom = nextT - (nextT == nDiag ? 0 : P.traceBack + 1);
-        const float cOX = (float) (P.eX + T[T_GAP_OPEN_X]), cEX = (float) (P.eX + T[T_GAP_EXTEND_X]);
-        const float tMM = (float) T[T_MATCH_CONTINUE], tXM = (float) T[T_MATCH_FROM_GAP_X], tYM = (float) T[T_MATCH_FROM_GAP_Y];
-        const float tMY = (float) T[T_GAP_OPEN_Y], tYY = (float) T[T_GAP_EXTEND_Y];
         int32_t rowI = 0;
         int32_t wr = 3;
         K::fillTable(P, I, S, RW, t, NT, bd0, 1, tbI, nTb, tbList, wr);
         __syncthreads();
         int32_t xlo1 = 0, xhi1 = 0, xlo2 = 0, xhi2 = -1;
-        double o0 = 0.0, o1 = 0.0, o2 = 0.0;    // forward offsets of d, d - 1, d - 2
-        double shiftNext = 0.0;                 // rounded maximum of f(d - 1), valid on diagonals that are multiples of 16
+        double o0 = 0.0;                        // forward offset of d
+        float s0 = 0.f, s1 = 0.f;               // o(d) - o(d - 1) and o(d - 1) - o(d - 2): integers, zero except where a group starts
+        float shiftNext = 0.f;                  // rounded maximum of f(d - 1), valid on diagonals that are multiples of 16
         for (int32_t d = 1; d <= nDiag; d++) {
             rowI = rowI + 1 == RW.cap ? 0 : rowI + 1;
             if (d >= bd0 + BT) {
@@ -473,14 +485,16 @@ struct WideF {
             const int4 D4 = S.desc[d - bd0];
             const int32_t xlo = D4.x, xhi = D4.y, w = xhi - xlo + 1, par = d & 1, jb = K::jbase(d, H);
             ensureRings(P, I, S, t, NT, xlo, d - xhi, w - 1, true, cLo, eLo);
-            o2 = o1; o1 = o0;
+            s1 = s0; s0 = 0.f;
             if ((d & 15) == 0) {
-                o0 = o1 + shiftNext;
+                s0 = shiftNext; o0 += (double) shiftNext;
                 if (t == 0) offF[d >> 4] = o0;
             }
-            const float e1 = (float) (o1 - o0), e2 = (float) (o2 - o0);
-            const float cM0 = tMM + e2, cM1 = tXM + e2, cM2 = tYM + e2, cY0 = tMY + e1, cY1 = tYY + e1;
-            const float cOXe = cOX + e1, cEXe = cEX + e1;
+            const float e1 = -s0, e2 = -(s0 + s1);
+            const float4 k0 = *reinterpret_cast<const float4 *>(E.kc), k1 = *reinterpret_cast<const float4 *>(E.kc + 4);
+            const float cM0 = k0.x + e2, cM1 = k0.y + e2, cM2 = k0.z + e2, cY0 = k0.w + e1, cY1 = k1.x + e1;
+            const float cOXe = k1.y + e1, cEXe = k1.z + e1;
+            const unsigned lk = __float_as_uint(k1.w);
             const bool full = D4.w == 3;
             const bool wantMax = ((d + 1) & 15) == 0;
             float tmax = -INFINITY;
@@ -501,9 +515,9 @@ struct WideF {
                     const float f1M = pu[0], f1Y = pu[2];
                     const float n2M = pj[0], n2X = pj[1], n2Y = pj[2];
                     // stateMachine3_cellCalculate order (the first contribution lands on -inf)
-                    const float X = sa_logAddF(n1M + cOXe, n1X + cEXe);
-                    const float M = sa_logAddF(sa_logAddF(n2M + (eM + cM0), n2X + (eM + cM1)), n2Y + (eM + cM2));
-                    const float Y = sa_logAddF(f1M + (eY + cY0), f1Y + (eY + cY1));
+                    const float X = sa_logAddF(n1M + cOXe, n1X + cEXe, lk);
+                    const float M = sa_logAddF(sa_logAddF(n2M + (eM + cM0), n2X + (eM + cM1), lk), n2Y + (eM + cM2), lk);
+                    const float Y = sa_logAddF(f1M + (eY + cY0), f1Y + (eY + cY1), lk);
                     pj[0] = M; pj[1] = X; pj[2] = Y;
                     row[i] = M;
                     if (full) { row[w + i] = X; row[2 * w + i] = Y; }
@@ -528,7 +542,7 @@ struct WideF {
             if (d != nextT) continue;
             const bool atEnd = d == nDiag;
             const int32_t tracedBackFrom = curFrom;
-            traceback(P, I, S, E, RW, offF, t, NT, H, d, rowI, cLo, eLo, tracedBackTo, tracedBackFrom, atEnd, cOX, cEX, nPairs);
+            traceback(P, I, S, E, RW, offF, t, NT, H, d, rowI, cLo, eLo, tracedBackTo, tracedBackFrom, atEnd, nPairs);
             tracedBackTo = tracedBackFrom;
             tbI++;
             nextT = tbI < nTb ? tbList[tbI] : nDiag;
@@ -556,6 +570,7 @@ __global__ void __launch_bounds__(NTMAX, MINB) sa_wide32_kernel(const __grid_con
     typename W::Extra E;
     W::carve(S, E, sa_wsm32, P.wFold ? P.wFold + (int64_t) blockIdx.x * 2 * NSW : nullptr,
              GR ? P.wRings + (int64_t) blockIdx.x * 6 * NSW : nullptr);
+    W::fillTransitions(P, E);
     sa_logAdd_init();
     typename W::Rows RW;
     RW.ring = P.scratch + (int64_t) blockIdx.x * P.wRingDoubles;

@@ -37,6 +37,25 @@ with open(outp, "w") as f:
 here = os.path.dirname(os.path.abspath(so))
 cache = {}
 print("total warp-instructions %d" % tot)
+# stall samples by source line (all samples), with the four big reasons split out
+cols = {k: sh.index(k) for k in ("# Samples", "stall_long_sb", "stall_barrier", "stall_wait", "stall_short_sb", "stall_math", "stall_branch_resolving", "stall_no_inst") if k in sh}
+if os.environ.get("STALLS") and cols:
+    st = collections.defaultdict(lambda: collections.Counter())
+    for r, s_ in zip(data, lines):
+        for k, i in cols.items():
+            st[s_][k] += int(r[i] or 0)
+    allS = sum(v["# Samples"] for v in st.values())
+    print("samples %d: " % allS + ", ".join("%s %.1f%%" % (k, 100.0 * sum(v[k] for v in st.values()) / allS) for k in cols if k != "# Samples"))
+    for k, v in sorted(st.items(), key=lambda kv: -kv[1]["# Samples"])[:top]:
+        text = ""
+        if k:
+            p = os.path.join(os.path.dirname(os.path.abspath(so)), "csrc", k[0])
+            if os.path.exists(p):
+                L = open(p).read().split("\n")
+                text = L[k[1] - 1].strip()[:80] if k[1] - 1 < len(L) else ""
+        print("%-22s %5.1f%%  lsb %4.1f bar %4.1f wait %4.1f ssb %4.1f | %s" % ("%s:%d" % k if k else "?", 100.0 * v["# Samples"] / allS,
+              100.0 * v["stall_long_sb"] / allS, 100.0 * v["stall_barrier"] / allS, 100.0 * v["stall_wait"] / allS, 100.0 * v["stall_short_sb"] / allS, text))
+    print()
 for k, v in by.most_common(top):
     text = ""
     if k:
