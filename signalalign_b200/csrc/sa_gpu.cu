@@ -523,13 +523,14 @@ static bool wideFoldGlobal(int c, bool gr) {
 // registers are held to>; the window is a compile-time constant there (immediate masks and shared-memory offsets)
 #define SA_W32_CLASSES(X) X(0, false, 256, 128, 6) X(1, false, 512, 256, 3) X(2, false, 1024, 256, 3) X(3, true, 2048, 256, 3) X(4, true, 4096, 512, 1)
 static bool wide32GlobalRings(int c) { return c >= 3; }
-static int wide32Threads(int c) {
-    static const int nt[kWideClasses] = {128, 256, 256, 256, 512};
-    const int t = wideThreads(c);                     // SA_WIDE_NT override, bounded by the instantiation's launch bound
-    return getenv("SA_WIDE_NT") ? std::min(t, nt[c]) : nt[c];
+static int wide32Threads(int c) {                     // a template argument of the kernel, not a launch-time choice
+#define X(C, GR, NSW, NT, MB) if (c == C) return NT;
+    SA_W32_CLASSES(X)
+#undef X
+    return 0;
 }
 static size_t wide32SmemBytes(int c, bool foldInSmem) {
-#define X(C, GR, NSW, NT, MB) if (c == C) return WideF<GR, NSW>::smemBytes(NSW, foldInSmem);
+#define X(C, GR, NSW, NT, MB) if (c == C) return WideF<GR, NSW, NT>::smemBytes(NSW, foldInSmem);
     SA_W32_CLASSES(X)
 #undef X
     return 0;

@@ -23,8 +23,21 @@
 
 // NSWT: the window (slots) as a compile-time constant — every `& mask`, plane offset and shared-memory address of the hot
 // loops is then an immediate instead of a value the compiler keeps re-deriving from the kernel parameters.
-template <bool GR, int NSWT>
+// NTT: threads per CTA, likewise.  Values every diagonal needs (the thread index, the base of the row ring, the base of the
+// constant ring) go through pin(): an opaque move that the compiler cannot re-derive, so they stay in registers instead
+// of being rebuilt from special registers and kernel parameters on every diagonal.
+template <bool GR, int NSWT, int NTT>
 struct WideF {
+    template <typename T> static __device__ __forceinline__ T *pin(T *p) {
+        T *q;
+        asm volatile("mov.u64 %0, %1;" : "=l"(q) : "l"(p));
+        return q;
+    }
+    static __device__ __forceinline__ int pinnedTid() {
+        int t;
+        asm volatile("mov.u32 %0, %%tid.x;" : "=r"(t));
+        return t;
+    }
     using K = WideK<false, false, GR>;
     using Sm = typename K::Sm;            // same struct; st / cst hold the layouts below behind the double pointers
     using Rows = typename K::Rows;        // ring = floats behind the double pointer; offsets count floats
@@ -48,7 +61,7 @@ struct WideF {
         S.NSW = NSW; S.mask = NSW - 1; S.nCh = NSW / 32;
         double *p = base;
         S.st = p; p += 3 * NSW;                              // 24 B per slot
-        if (GR) { S.cst = ringsGlobal; S.evs = ringsGlobal + 3 * NSW; S.foldv = foldGlobal; }
+        if (GR) { S.cst = pin(ringsGlobal); S.evs = S.cst + 3 * NSW; S.foldv = foldGlobal; }
         else {
             S.cst = p; p += 3 * NSW;
             S.evs = p; p += NSW;
@@ -159,7 +172,7 @@ struct WideF {
                 const int32_t i = (s - jA - loA) & S.mask;
                 float v0 = -INFINITY, v1 = -INFINITY, v2 = -INFINITY;
                 if (i < wA) {
-                    if (rowA) { v0 = rowA[i]; v1 = rowA[wA + i]; v2 = rowA[2 * wA + i]; }
+                    if (rowA) { v0 = __ldcs(rowA + i); v1 = __ldcs(rowA + wA + i); v2 = __ldcs(rowA + 2 * wA + i); }
                     else { v0 = cA[0]; v1 = cA[1]; v2 = cA[2]; }
                 }
                 bufA[3 * s] = v0; bufA[3 * s + 1] = v1; bufA[3 * s + 2] = v2;
@@ -167,7 +180,7 @@ struct WideF {
             {
                 const int32_t i = (s - jB - loB) & S.mask;
                 float v0 = -INFINITY, v1 = -INFINITY, v2 = -INFINITY;
-                if (rowB && i < wB) { v0 = rowB[i]; v1 = rowB[wB + i]; v2 = rowB[2 * wB + i]; }
+                if (rowB && i < wB) { v0 = __ldcs(rowB + i); v1 = __ldcs(rowB + wB + i); v2 = __ldcs(rowB + 2 * wB + i); }
                 bufB[3 * s] = v0; bufB[3 * s + 1] = v1; bufB[3 * s + 2] = v2;
             }
         }
@@ -191,14 +204,13 @@ struct WideF {
     // WideK::traceback for the structure.  b(d2) is relative to a backward offset oB(d2) (0 on the block's first diagonal,
     // moved by the rounded maximum of the previous diagonal whenever d2 enters a new group of 16); f(d2) is relative to
     // offF[d2 >> 4], written by the forward sweep.
-    static __device__ __forceinline__ void traceback(const FParams &P, const FItem &I, const Sm &S, const Extra &E, const Rows &RW, const double *offF,
+    static __device__ __forceinline__ void traceback(const FParams &P, const FItem &I, const Sm &S, const Extra &E, const Rows &RW, const float *ringF, const double *offF,
                                      int t, int NT, int32_t H, int32_t d, int32_t rowI, int32_t &cLo, int32_t &eLo,
                                      int32_t tracedBackTo, int32_t tracedBackFrom, bool atEnd, int64_t &nPairs) {
         const int lane = t & 31, warp = t >> 5, NW = NT >> 5;
         const double *T = P.trans;
         const float gate = (float) P.logThrGate;
         const int32_t cap = RW.cap;
-        const float *ringF = reinterpret_cast<const float *>(RW.ring);
         const bool rag = atEnd && (I.flags & 2);
         const float endS[3] = {(float) (rag ? (T[T_GAP_OPEN_X] + T[T_GAP_OPEN_Y]) / 2.0 : T[T_MATCH_CONTINUE]),
                                (float) (rag ? T[T_GAP_EXTEND_X] : T[T_MATCH_FROM_GAP_X]),
@@ -315,7 +327,7 @@ struct WideF {
                     bool cand = false;
                     float arg = 0.f;
                     // the stored forward value comes from L2 or HBM: asked for before the cell's arithmetic, used after it
-                    const float fM = (inlinePost && i < w) ? row[i] : 0.f;
+                    const float fM = (inlinePost && i < w) ? __ldcs(row + i) : 0.f;
                     if (i < w) {
                         const int32_t x = bxlo + i, y = d2 - x;
                         const int32_t j = (x + jb) & S.mask, sq = (j - 1 + par) & S.mask, sl = (sq + 1) & S.mask;
@@ -363,9 +375,9 @@ struct WideF {
                         double v = -INFINITY;
                         if (i < w) {
                             const int32_t j = (bxlo + i + jb) & S.mask;
-                            float vf = row[i] + cur[3 * j];
-                            vf = sa_logAddF(vf, row[w + i] + cur[3 * j + 1], lk);
-                            vf = sa_logAddF(vf, row[2 * w + i] + cur[3 * j + 2], lk);
+                            float vf = __ldcs(row + i) + cur[3 * j];
+                            vf = sa_logAddF(vf, __ldcs(row + w + i) + cur[3 * j + 1], lk);
+                            vf = sa_logAddF(vf, __ldcs(row + 2 * w + i) + cur[3 * j + 2], lk);
                             v = (double) vf;
                             S.foldv[i] = v;
                         }
@@ -386,7 +398,7 @@ struct WideF {
                             if (i < n1) {
                                 const int32_t x = hUp.x + i, y = d2 + 1 - x, iD = x - 1 - hDn.x;
                                 float gM = -INFINITY, gX = -INFINITY, gY = -INFINITY;
-                                if (iD >= 0 && iD < wD) { gM = rowD[iD]; gX = rowD[wD + iD]; gY = rowD[2 * wD + iD]; }
+                                if (iD >= 0 && iD < wD) { gM = __ldcs(rowD + iD); gX = __ldcs(rowD + wD + iD); gY = __ldcs(rowD + 2 * wD + iD); }
                                 const float e = emissionM(S, x, y);
                                 const float m = sa_logAddF(sa_logAddF(gM + (e + tMM), gX + (e + tXM), lk), gY + (e + tYM), lk);
                                 v = (double) ((m + prv[3 * ((x + jb1) & S.mask)]) + rel);
@@ -414,7 +426,7 @@ struct WideF {
                     bool cand = false;
                     float arg = 0.f;
                     if (i < w) {
-                        arg = (row[i] + cur[3 * ((x + jb) & S.mask)]) + adj;
+                        arg = (__ldcs(row + i) + cur[3 * ((x + jb) & S.mask)]) + adj;
                         cand = x > 0 && d2 - x > 0 && arg >= gate;
                     }
                     bool hit = false;
@@ -435,7 +447,8 @@ struct WideF {
 
     // ------------------------------------------------------------------------------------------ one work item
     static __device__ __forceinline__ void run(const FParams &P, const FItem &I, int it, const Sm &S, const Extra &E, const Rows &RW, double *offF) {
-        const int t = threadIdx.x, NT = blockDim.x, lane = t & 31, warp = t >> 5, NW = NT >> 5;
+        constexpr int NT = NTT, NW = NT >> 5;
+        const int t = pinnedTid(), lane = t & 31, warp = t >> 5;
         const int32_t nDiag = I.lX + I.lY;
         int64_t nPairs = 0;
         if (nDiag == 0) {
@@ -445,7 +458,7 @@ struct WideF {
         const int32_t *tbList = P.tb + I.tbOff;
         const int32_t nTb = P.geo[it].nTb;
         const int32_t H = I.lY + 2;
-        float *ringF = reinterpret_cast<float *>(RW.ring);
+        float *ringF = pin(reinterpret_cast<float *>(RW.ring));
         __syncthreads();
         if (t == 0) { S.sInt[1] = 0; offF[0] = 0.0; }
         int32_t cLo = -kSlack, eLo = -kSlack, bd0 = 1;
@@ -519,8 +532,8 @@ struct WideF {
                     const float M = sa_logAddF(sa_logAddF(n2M + (eM + cM0), n2X + (eM + cM1), lk), n2Y + (eM + cM2), lk);
                     const float Y = sa_logAddF(f1M + (eY + cY0), f1Y + (eY + cY1), lk);
                     pj[0] = M; pj[1] = X; pj[2] = Y;
-                    row[i] = M;
-                    if (full) { row[w + i] = X; row[2 * w + i] = Y; }
+                    __stcs(row + i, M);                     // (streaming: the rows must not push the constant rings out of L1)
+                    if (full) { __stcs(row + w + i, X); __stcs(row + 2 * w + i, Y); }
                     if (wantMax) tmax = fmaxf(tmax, fmaxf(M, fmaxf(X, Y)));
                 }
             }
@@ -542,7 +555,7 @@ struct WideF {
             if (d != nextT) continue;
             const bool atEnd = d == nDiag;
             const int32_t tracedBackFrom = curFrom;
-            traceback(P, I, S, E, RW, offF, t, NT, H, d, rowI, cLo, eLo, tracedBackTo, tracedBackFrom, atEnd, nPairs);
+            traceback(P, I, S, E, RW, ringF, offF, t, NT, H, d, rowI, cLo, eLo, tracedBackTo, tracedBackFrom, atEnd, nPairs);
             tracedBackTo = tracedBackFrom;
             tbI++;
             nextT = tbI < nTb ? tbList[tbI] : nDiag;
@@ -561,11 +574,11 @@ struct WideF {
     }
 };
 
-// Launch: blockDim = threads of the class (<= NTMAX), dynamic shared memory = WideF<GR, NSW>::smemBytes(NSW, P.wFold == nullptr)
+// Launch: blockDim = NTMAX (the class's thread count), dynamic shared memory = WideF<GR, NSW>::smemBytes(NSW, P.wFold == nullptr)
 template <bool GR, int NSW, int NTMAX, int MINB>
 __global__ void __launch_bounds__(NTMAX, MINB) sa_wide32_kernel(const __grid_constant__ FParams P) {
     extern __shared__ __align__(16) double sa_wsm32[];
-    using W = WideF<GR, NSW>;
+    using W = WideF<GR, NSW, NTMAX>;
     typename W::Sm S;
     typename W::Extra E;
     W::carve(S, E, sa_wsm32, P.wFold ? P.wFold + (int64_t) blockIdx.x * 2 * NSW : nullptr,
