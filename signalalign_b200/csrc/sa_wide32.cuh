@@ -138,25 +138,31 @@ struct WideF {
         __syncthreads();
     }
 
+    // ring reads: plain shared-memory loads, or (rings in global memory) ld.global.ca — said explicitly, because a pinned
+    // pointer is opaque to the compiler, which would otherwise emit generic loads
+    static __device__ __forceinline__ double ldD(const double *p) { return GR ? __ldca(p) : *p; }
+    static __device__ __forceinline__ float2 ldF2(const double *p) {
+        return GR ? __ldca(reinterpret_cast<const float2 *>(p)) : *reinterpret_cast<const float2 *>(p);
+    }
     // match and gap-Y emission of cell (x, y): the difference in double, the rest in float
     static __device__ __forceinline__ void emissions(const Sm &S, int32_t x, int32_t y, float &eM, float &eY) {
         const double *c = S.cst + (x & S.mask) * 3;
-        const float2 qm = *reinterpret_cast<const float2 *>(c + 1), qy = *reinterpret_cast<const float2 *>(c + 2);   // (iM, cM), (iY, cY)
-        const float d0 = (float) (S.evs[y & S.mask] - c[0]);
+        const float2 qm = ldF2(c + 1), qy = ldF2(c + 2);   // (iM, cM), (iY, cY)
+        const float d0 = (float) (ldD(S.evs + (y & S.mask)) - ldD(c));
         const float aM = d0 * qm.x, aY = d0 * qy.x;
         eM = fmaf(-0.5f * aM, aM, qm.y);
         eY = fmaf(-0.5f * aY, aY, qy.y);
     }
     static __device__ __forceinline__ float emissionM(const Sm &S, int32_t x, int32_t y) {
         const double *c = S.cst + (x & S.mask) * 3;
-        const float2 q = *reinterpret_cast<const float2 *>(c + 1);
-        const float aM = (float) (S.evs[y & S.mask] - c[0]) * q.x;
+        const float2 q = ldF2(c + 1);
+        const float aM = (float) (ldD(S.evs + (y & S.mask)) - ldD(c)) * q.x;
         return fmaf(-0.5f * aM, aM, q.y);
     }
     static __device__ __forceinline__ float emissionY(const Sm &S, int32_t x, int32_t y) {
         const double *c = S.cst + (x & S.mask) * 3;
-        const float2 q = *reinterpret_cast<const float2 *>(c + 2);
-        const float aY = (float) (S.evs[y & S.mask] - c[0]) * q.x;
+        const float2 q = ldF2(c + 2);
+        const float aY = (float) (ldD(S.evs + (y & S.mask)) - ldD(c)) * q.x;
         return fmaf(-0.5f * aY, aY, q.y);
     }
 
