@@ -274,7 +274,6 @@ struct DevBuf {
 // wide band kernel classes: window slots, threads per CTA (sa_wide.cuh)
 static const int kWideClasses = 5;
 static const int kWideNSW[kWideClasses] = {256, 512, 1024, 2048, 4096};
-static const int kWideNT[kWideClasses] = {128, 256, 512, 512, 1024};
 static const size_t kSmemCap = 227 * 1024 - 1024;   // opt-in shared memory per CTA minus the kernels' static part (logAdd table)
 
 // one work item = one sub-region of one read after getSplitPoints
@@ -439,35 +438,40 @@ static void ctaLaunch(int c, bool oneCell, bool ex, bool hdp, int blocks, cudaSt
 static size_t wideSmemBytes(bool gr, int NSW, bool foldInSmem) {
     return gr ? WideK<false, false, true>::smemBytes(NSW, false) : WideK<false, false, false>::smemBytes(NSW, foldInSmem);
 }
-template <bool EX, bool HD, bool GR>
-static int wideOccupancyT(int threads, size_t smem, int *bps) {
-    static size_t allowed = 0;   // (the attribute is per function and device; raised monotonically)
-    if (smem > 48 * 1024 && smem > allowed) {
-        CK(cudaFuncSetAttribute(sa_wide_kernel<EX, HD, GR>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) kSmemCap));
-        allowed = kSmemCap;
+// One instantiation of the FP64 wide kernel per window class and (expectations, HDP) variant: <rings in global memory,
+// window, threads, CTAs per SM the registers are held to>; window and thread count are compile-time constants there.
+#define SA_W64_CLASSES(X) X(0, false, 256, 128, 5) X(1, false, 512, 256, 3) X(2, false, 1024, 512, 2) X(3, true, 2048, 512, 2) X(4, true, 4096, 1024, 1)
+template <bool EX, bool HD>
+static int wideOccupancyT(int c, size_t smem, int *bps) {
+    static bool raised[kWideClasses] = {false, false, false, false, false};
+#define X(C, GR, NSW, NT, MB)                                                                                                      \
+    if (c == C) {                                                                                                                 \
+        if (smem > 48 * 1024 && !raised[C]) {                                                                                     \
+            CK(cudaFuncSetAttribute(sa_wide_kernel<EX, HD, GR, NSW, NT, MB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) kSmemCap)); \
+            raised[C] = true;                                                                                                     \
+        }                                                                                                                         \
+        CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(bps, sa_wide_kernel<EX, HD, GR, NSW, NT, MB>, NT, smem));                \
     }
-    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(bps, sa_wide_kernel<EX, HD, GR>, threads, smem));
+    SA_W64_CLASSES(X)
+#undef X
     return SA_OK;
 }
-template <bool GR>
-static int wideOccupancyG(bool hdp, bool ex, int threads, size_t smem, int *bps) {
-    if (hdp && ex) return wideOccupancyT<true, true, GR>(threads, smem, bps);
-    if (hdp) return wideOccupancyT<false, true, GR>(threads, smem, bps);
-    return ex ? wideOccupancyT<true, false, GR>(threads, smem, bps) : wideOccupancyT<false, false, GR>(threads, smem, bps);
+static int wideOccupancy(int c, bool hdp, bool ex, size_t smem, int *bps) {
+    if (hdp && ex) return wideOccupancyT<true, true>(c, smem, bps);
+    if (hdp) return wideOccupancyT<false, true>(c, smem, bps);
+    return ex ? wideOccupancyT<true, false>(c, smem, bps) : wideOccupancyT<false, false>(c, smem, bps);
 }
-static int wideOccupancy(bool gr, bool hdp, bool ex, int threads, size_t smem, int *bps) {
-    return gr ? wideOccupancyG<true>(hdp, ex, threads, smem, bps) : wideOccupancyG<false>(hdp, ex, threads, smem, bps);
+template <bool EX, bool HD>
+static void wideLaunchT(int c, int blocks, size_t smem, cudaStream_t st, const FParams &f) {
+#define X(C, GR, NSW, NT, MB) if (c == C) sa_wide_kernel<EX, HD, GR, NSW, NT, MB><<<blocks, NT, smem, st>>>(f);
+    SA_W64_CLASSES(X)
+#undef X
 }
-template <bool GR>
-static void wideLaunchG(bool hdp, bool ex, int blocks, int threads, size_t smem, cudaStream_t st, const FParams &f) {
-    if (hdp && ex) sa_wide_kernel<true, true, GR><<<blocks, threads, smem, st>>>(f);
-    else if (hdp) sa_wide_kernel<false, true, GR><<<blocks, threads, smem, st>>>(f);
-    else if (ex) sa_wide_kernel<true, false, GR><<<blocks, threads, smem, st>>>(f);
-    else sa_wide_kernel<false, false, GR><<<blocks, threads, smem, st>>>(f);
-}
-static void wideLaunch(bool gr, bool hdp, bool ex, int blocks, int threads, size_t smem, cudaStream_t st, const FParams &f) {
-    if (gr) wideLaunchG<true>(hdp, ex, blocks, threads, smem, st, f);
-    else wideLaunchG<false>(hdp, ex, blocks, threads, smem, st, f);
+static void wideLaunch(int c, bool hdp, bool ex, int blocks, size_t smem, cudaStream_t st, const FParams &f) {
+    if (hdp && ex) wideLaunchT<true, true>(c, blocks, smem, st, f);
+    else if (hdp) wideLaunchT<false, true>(c, blocks, smem, st, f);
+    else if (ex) wideLaunchT<true, false>(c, blocks, smem, st, f);
+    else wideLaunchT<false, false>(c, blocks, smem, st, f);
 }
 // ---- precision of the wide band kernel for Gaussian alignment runs: FP64 (default, bit-faithful) or FP32 state relative to
 // per-diagonal offsets (sa_wide32.cuh; within the contract's 1e-4).  SA_PRECISION=fp32 in the environment sets the default.
@@ -492,30 +496,25 @@ extern "C" int sa_gpu_get_precision(void) { return currentPrecision(); }
 // does the class keep its emission rings in global memory?  From the 2048-slot window on: with the rings in shared memory
 // one CTA of that class fills an SM (1024 threads, half of them idle on a typical diagonal); with only the DP state
 // there, two CTAs of 512 threads fit and overlap each other's barriers (+15 % on the contract pattern).
-// SA_WIDE_GR_FROM=<slots> moves the limit (experiments).
 static bool wideGlobalRings(int c) {
-    int from = 2048;
-    if (const char *e = getenv("SA_WIDE_GR_FROM")) from = atoi(e);
-    return kWideNSW[c] >= from || wideSmemBytes(false, kWideNSW[c], false) > kSmemCap;
+#define X(C, GR, NSW, NT, MB) if (c == C) return GR;
+    SA_W64_CLASSES(X)
+#undef X
+    return false;
 }
-// threads per CTA of a class (SA_WIDE_NT=a,b,c,d,e overrides the table; experiments)
-static int wideThreads(int c) {
-    if (const char *e = getenv("SA_WIDE_NT")) {
-        int v[kWideClasses], n = 0;
-        for (const char *q = e; *q && n < kWideClasses;) {
-            char *end = nullptr;
-            long x = strtol(q, &end, 10);
-            if (end == q) break;
-            v[n++] = (int) x;
-            q = *end ? end + 1 : end;
-        }
-        if (c < n && v[c] >= 32 && v[c] <= 1024 && v[c] % 32 == 0) return v[c];
-    }
-    return kWideNT[c];
+static int wideThreads(int c) {                       // a template argument of the kernel, not a launch-time choice
+#define X(C, GR, NSW, NT, MB) if (c == C) return NT;
+    SA_W64_CLASSES(X)
+#undef X
+    return 0;
 }
+// fold terms in global memory: with the rings there, and from the 1024-slot window on (two CTAs of 512 threads per SM
+// instead of one: 25.0 -> 26.8 GCUPS on the contract pattern).  SA_WIDE_FOLDG_FROM=<slots> moves the limit (experiments).
 static bool wideFoldGlobal(int c, bool gr) {
     if (gr) return true;
-    if (const char *e = getenv("SA_WIDE_FOLDG_FROM")) if (kWideNSW[c] >= atoi(e)) return true;
+    int from = 1024;
+    if (const char *e = getenv("SA_WIDE_FOLDG_FROM")) from = atoi(e);
+    if (kWideNSW[c] >= from) return true;
     return wideSmemBytes(false, kWideNSW[c], true) > kSmemCap;
 }
 
@@ -1022,7 +1021,7 @@ static int prepareBatch(const sa_model_t *m, const sa_read_t *reads, int64_t nRe
         int bps = 1;
         if (b->fp32) {
             if ((rc = wide32Occupancy(c, wide32Threads(c), smem, &bps))) return rc;
-        } else if ((rc = wideOccupancy(gr, hdp, b->expectations, wideThreads(c), smem, &bps))) return rc;
+        } else if ((rc = wideOccupancy(c, hdp, b->expectations, smem, &bps))) return rc;
         b->wBlocks[c] = (int) std::min<int64_t>((int64_t) nSM * std::max(1, bps), (int64_t) b->wOrder[c].size());
         b->wRows[c] += 4 + 256;      // + one descriptor table of headers written ahead
         b->wRingDoubles[c] = (b->wRingDoubles[c] + 64 + 15) & ~(int64_t) 15;
@@ -1224,8 +1223,7 @@ static int launchBatch(sa_batch_t *b) {
             wide32Launch(c, b->wBlocks[c], wide32Threads(c), wide32SmemBytes(c, b->dWFold[c].p == nullptr), st, f);
         } else {
             const bool gr = wideGlobalRings(c);
-            wideLaunch(gr, hdp, b->expectations, b->wBlocks[c], wideThreads(c),
-                       wideSmemBytes(gr, kWideNSW[c], b->dWFold[c].p == nullptr), st, f);
+            wideLaunch(c, hdp, b->expectations, b->wBlocks[c], wideSmemBytes(gr, kWideNSW[c], b->dWFold[c].p == nullptr), st, f);
         }
         b->lastLaunches++;
         CK(cudaGetLastError());
@@ -1893,7 +1891,7 @@ static int setup(int dev, unsigned char **base) {
     if (!g_base[dev]) {
         unsigned char *ptr = nullptr;
         CK(cudaGetSymbolAddress((void **) &ptr, sa_noalloc_scratch));     // with device `dev` current
-        CK(cudaFuncSetAttribute(sa_wide_kernel<false, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) kSmemCap));
+        CK(cudaFuncSetAttribute(sa_wide_kernel<false, false, false, kNSW, kNT, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) kSmemCap));
         g_base[dev] = ptr;
     }
     *base = g_base[dev];
@@ -2039,7 +2037,7 @@ extern "C" int sa_gpu_align_noalloc(const sa_model_t *m, const sa_read_t *R, con
             return SA_ERR_INPUT;
         }
     }
-    sa_wide_kernel<false, false, false><<<1, kNT, WideK<false, false, false>::smemBytes(kNSW, true), st>>>(f);
+    sa_wide_kernel<false, false, false, kNSW, kNT, 3><<<1, kNT, WideK<false, false, false>::smemBytes(kNSW, true), st>>>(f);
     CK(cudaGetLastError());
     int64_t n = 0;
     CK(cudaMemcpyAsync(&n, base + oPairCount, sizeof(n), cudaMemcpyDeviceToHost, st));

@@ -37,8 +37,21 @@
 // HD: HDP emission (stateMachine3HDP_cellCalculate: one kmer density for the match and the gap-Y state);
 // GR: the emission rings and the fold terms live in a per-CTA global-memory scratch (L1 / L2 resident) instead of shared
 //     memory — the 4096-slot window, whose DP state alone takes 192 KB.
-template <bool EX, bool HD, bool GR>
+// NSWT / NTT: the window (slots) and the threads per CTA as compile-time constants (0: run-time values, for the helpers
+// sa_wide32.cuh borrows) — masks, plane offsets and shared-memory addresses of the hot loops become immediates.
+template <bool EX, bool HD, bool GR, int NSWT = 0, int NTT = 0>
 struct WideK {
+    // an opaque move: the value stays in a register instead of being rebuilt from special registers / kernel parameters
+    template <typename T> static __device__ __forceinline__ T *pin(T *p) {
+        T *q;
+        asm volatile("mov.u64 %0, %1;" : "=l"(q) : "l"(p));
+        return q;
+    }
+    static __device__ __forceinline__ int pinnedTid() {
+        int t;
+        asm volatile("mov.u32 %0, %%tid.x;" : "=r"(t));
+        return t;
+    }
     static constexpr int BT = 256;             // diagonals per descriptor table
     static constexpr double kExpZero = -50.0;  // expectation terms below e^-50 are not evaluated (see sa_cta.cuh)
     static constexpr int PL = HD ? 4 : 3;      // planes of a full stored row (HDP: + the cell's log density)
@@ -70,11 +83,12 @@ struct WideK {
         b += (size_t) (2 * BT + 2) * 16 + 3 * (BT + 1) * 4 + 16 + 16;
         return b;
     }
-    static __device__ __forceinline__ void carve(Sm &S, double *base, int NSW, double *foldGlobal, double *ringsGlobal) {
+    static __device__ __forceinline__ void carve(Sm &S, double *base, int NSWarg, double *foldGlobal, double *ringsGlobal) {
+        const int NSW = NSWT ? NSWT : NSWarg;
         S.NSW = NSW; S.mask = NSW - 1; S.nCh = NSW / 32;
         double *p = base;
         S.st = p; p += 6 * NSW;
-        if (GR) { S.cst = ringsGlobal; S.evs = ringsGlobal + 5 * NSW; S.foldv = foldGlobal; }
+        if (GR) { S.cst = pin(ringsGlobal); S.evs = S.cst + 5 * NSW; S.foldv = foldGlobal; }
         else {
             S.cst = p; p += 5 * NSW;
             S.evs = p; p += NSW;
@@ -420,7 +434,7 @@ struct WideK {
 
     // ------------------------------------------------------------------------------------------ traceback
     // blocked traceback from diagonal d down to tracedBackTo + 1 (reference impl/pairwiseAligner.c:1500-1570)
-    static __device__ void traceback(const FParams &P, const FItem &I, const Sm &S, const Rows &RW, int t, int NT, int32_t H,
+    static __device__ __forceinline__ void traceback(const FParams &P, const FItem &I, const Sm &S, const Rows &RW, int t, int NT, int32_t H,
                                      int32_t d, int32_t rowI, int32_t &cLo, int32_t &eLo, int32_t tracedBackTo,
                                      int32_t tracedBackFrom, bool atEnd, double cOX, double cEX, int64_t &nPairs,
                                      double (&acc)[7], double &lik, bool &yxNaN) {
@@ -578,6 +592,8 @@ struct WideK {
                     const int32_t i = c * 32 + lane;
                     bool cand = false;
                     double arg = 0.0;
+                    // the stored forward value comes from L2 or HBM: asked for before the cell's arithmetic, used after it
+                    const double fM = (inlinePost && i < w) ? __ldcs(row + i) : 0.0;
                     if (i < w) {
                         const int32_t x = bxlo + i, y = d2 - x;
                         const int32_t j = (x + jb) & S.mask, sq = (j - 1 + par) & S.mask, sl = (sq + 1) & S.mask;
@@ -600,7 +616,7 @@ struct WideK {
                         const double Y = sa_logAdd(aM + (aE + T[T_MATCH_FROM_GAP_Y]), qY + (qE + T[T_GAP_EXTEND_Y]));
                         cur[3 * j] = M; cur[3 * j + 1] = X; cur[3 * j + 2] = Y;
                         if (inlinePost) {
-                            arg = (row[i] + M) - total;
+                            arg = (fM + M) - total;
                             cand = x > 0 && y > 0 && arg >= P.logThrGate;
                         }
                     }
@@ -770,8 +786,11 @@ struct WideK {
     }
 
     // ------------------------------------------------------------------------------------------ one work item
-    static __device__ void run(const FParams &P, const FItem &I, int it, const Sm &S, const Rows &RW) {
-        const int t = threadIdx.x, NT = blockDim.x, lane = t & 31, warp = t >> 5, NW = NT >> 5;
+    static __device__ __forceinline__ void run(const FParams &P, const FItem &I, int it, const Sm &S, const Rows &RWin) {
+        const int NT = NTT ? NTT : (int) blockDim.x, NW = NT >> 5;
+        const int t = pinnedTid(), lane = t & 31, warp = t >> 5;
+        Rows RW = RWin;
+        RW.ring = pin(RWin.ring);
         const double *T = P.trans;
         const int32_t nDiag = I.lX + I.lY;
         int64_t nPairs = 0;
@@ -851,9 +870,9 @@ struct WideK {
                                                n2Y + (eM + T[T_MATCH_FROM_GAP_Y]));
                     const double Y = sa_logAdd(f1M + (eY + T[T_GAP_OPEN_Y]), f1Y + (eY + T[T_GAP_EXTEND_Y]));
                     pj[0] = M; pj[1] = X; pj[2] = Y;
-                    row[i] = M;
-                    if (full) { row[w + i] = X; row[2 * w + i] = Y; }
-                    if (HD) row[(D4.w - 1) * w + i] = eM;
+                    __stcs(row + i, M);                 // (streaming: the rows must not push the constant rings out of L1)
+                    if (full) { __stcs(row + w + i, X); __stcs(row + 2 * w + i, Y); }
+                    if (HD) __stcs(row + (D4.w - 1) * w + i, eM);
                 }
             }
             // slots of d - 2 whose cell (x', .) has no successor (x' + 1, .) on d: back to -inf
@@ -924,16 +943,17 @@ struct WideK {
     }
 };
 
-// Persistent grid, items pulled heaviest-first from an atomic queue.  Launch: blockDim = threads of the class, dynamic
-// shared memory = WideK::smemBytes(P.wNSW, P.wFold == nullptr).
-template <bool EX, bool HD, bool GR>
-__global__ void __launch_bounds__(1024, 1) sa_wide_kernel(const __grid_constant__ FParams P) {
+// Persistent grid, items pulled heaviest-first from an atomic queue.  Launch: blockDim = NT, dynamic shared memory =
+// WideK::smemBytes(NSW, P.wFold == nullptr).  One instantiation per window class (sa_gpu.cu: SA_W64_CLASSES).
+template <bool EX, bool HD, bool GR, int NSW, int NT, int MINB>
+__global__ void __launch_bounds__(NT, MINB) sa_wide_kernel(const __grid_constant__ FParams P) {
     extern __shared__ __align__(16) double sa_wsm[];
-    typename WideK<EX, HD, GR>::Sm S;
-    WideK<EX, HD, GR>::carve(S, sa_wsm, P.wNSW, P.wFold ? P.wFold + (int64_t) blockIdx.x * 2 * P.wNSW : nullptr,
-                             GR ? P.wRings + (int64_t) blockIdx.x * 6 * P.wNSW : nullptr);
+    using W = WideK<EX, HD, GR, NSW, NT>;
+    typename W::Sm S;
+    W::carve(S, sa_wsm, NSW, P.wFold ? P.wFold + (int64_t) blockIdx.x * 2 * NSW : nullptr,
+             GR ? P.wRings + (int64_t) blockIdx.x * 6 * NSW : nullptr);
     sa_logAdd_init();
-    typename WideK<EX, HD, GR>::Rows RW;
+    typename W::Rows RW;
     RW.ring = P.scratch + (int64_t) blockIdx.x * P.wRingDoubles;
     RW.hdr = P.wHdr + (int64_t) blockIdx.x * P.wRowsCap;
     RW.cap = P.wRowsCap;
@@ -945,6 +965,6 @@ __global__ void __launch_bounds__(1024, 1) sa_wide_kernel(const __grid_constant_
         const int n = S.sInt[0];
         if (n >= P.nOrder) break;
         const int it = P.order[n];
-        WideK<EX, HD, GR>::run(P, P.items[it], it, S, RW);
+        W::run(P, P.items[it], it, S, RW);
     }
 }
