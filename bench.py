@@ -52,6 +52,11 @@ def parse():
     ap.add_argument("--seed", type=int, default=20261104)
     ap.add_argument("--anchors", default=ANCHOR_PATTERN, choices=sorted(ANCHOR_PATTERNS),
                     help="guide-anchor pattern of the synthetic reads (default: SURVEY 8d's)")
+    ap.add_argument("--precision", default="fp32", choices=["fp32", "fp64"],
+                    help="arithmetic of the band kernel on the alignment path (config 3): fp32 = DP state and logAdd in single "
+                         "precision relative to per-diagonal integer offsets (within the contract's 1e-4; sa_gpu_set_precision), "
+                         "fp64 = the reference's double arithmetic bit for bit.  Expectations and HDP runs are always fp64")
+    ap.add_argument("--no-other-precision", action="store_true", help="skip the secondary figure in the other precision")
     ap.add_argument("--no-dense", action="store_true", help="skip the secondary figure on round 1's dense anchor pattern")
     ap.add_argument("--strong", action="store_true",
                     help="strong scaling: ONE read set of --reads reads (same seed on every rank) split across the ranks by "
@@ -248,6 +253,8 @@ def main():
         reads_d = [reads_d[i] for i in parts[rank]]
     if expect:
         a.no_dense = a.no_expectations = True
+    prec = a.precision if a.workload == "config3" else "fp64"
+    sa.set_precision(prec)
     p = sa.default_params(threshold=THRESHOLD, expansion=EXPANSION, trace_back=TRACE_BACK, min_diags=MIN_DIAGS)
     reads = [sa.Read(r["target"], r["events"], r["anchors"], r["scale"], r["shift"], r["var"]) for r in reads_d]
     events = sum(r.events.shape[0] for r in reads)
@@ -294,6 +301,27 @@ def main():
     else:
         pairs_digest = [int(res.pairs[:, c].astype(np.int64).sum()) for c in range(4)]   # p, x, y, kmer column sums
     batch.close()
+
+    # ---- secondary, labelled: the same batch, resident, in the other precision
+    other = None
+    if a.workload == "config3" and not a.no_other_precision:
+        oprec = "fp64" if prec == "fp32" else "fp32"
+        sa.set_precision(oprec)
+        ob = sa.Batch(model, reads, p)
+        ob.run()
+        oms = []
+        for _ in range(2):
+            flush.fill_(1)
+            torch.cuda.synchronize()
+            ob.run()
+            oms.append(sum(ob.timing()[0]))
+        ores = ob.fetch()
+        other = {"precision": oprec, "gcups": ob.band_cells / (min(oms) * 1e-3) / 1e9, "events_per_s": events / (min(oms) * 1e-3),
+                 "ms_per_step": min(oms), "aligned_pairs": int(ores.pair_offsets[-1]),
+                 "pairs_column_sums": [int(ores.pairs[:, c].astype(np.int64).sum()) for c in range(4)]}
+        del ores
+        ob.close()
+        sa.set_precision(prec)
 
     # ---- secondary, labelled: the same resident measurement on round 1's dense anchor pattern (every kmer an anchor)
     dense = None
@@ -397,37 +425,48 @@ def main():
         peak_src = "measured (MEASURED_PEAKS.json)" if "hbm_gbs" in peaks else "fallback (B200_PROFILING.md)"
         # algorithmic bytes per band cell of the DP kernel: forward match plane written + read (16 B), X/Y
         # planes on 2 of 10 rows (6.4 B), inputs / outputs 0.4 B
-        alg_bytes_per_cell = 22.8
+        alg_bytes_per_cell = 22.8 if prec == "fp64" else 11.6      # (fp32: 4-byte planes)
         achieved_gbs = cells * alg_bytes_per_cell / (float(np.mean(kern_ms)) * 1e-3) / 1e9
         # measured DRAM traffic of the kernel (one ncu --set full capture, profiles/): bytes per band cell x this launch's cells
         traffic = None
         try:
-            traffic = json.load(open(os.path.join(ROOT, "profiles", "r2_dram_per_cell.json")))[a.anchors]["bytes_per_cell"] * cells
+            traffic = json.load(open(os.path.join(ROOT, "profiles", "r2_dram_per_cell.json")))[a.anchors][prec]["bytes_per_cell"] * cells
         except Exception:
             pass
         sm_mhz = (clocks or {}).get("sm_mhz") or 1965.0
         # FP64 pipe: ~150 algorithmic FP64 lane-instructions per band cell; peak = measured DFMA/DADD/DMUL
         # issue rate of this pool's B200 (tools/peak_fp.cu -> profiles/r1_peak_fp.jsonl), else 64 lanes/SM/clk nominal
         fp64_per_cell = 150.0
+        # FP32 mode: 122 algorithmic FP32 lane-instructions per band cell (forward 53, backward 67,
+        # posterior 2); peak = measured FFMA issue rate
+        fp32_per_cell = 122.0
+        fp32_peak, fp32_src = 148 * 128 * 1.965e9, "nominal 128 lanes/SM/clk at 1965 MHz"
         fp64_peak, fp64_src = 148 * 64 * 1.965e9, "nominal 64 lanes/SM/clk at 1965 MHz"
         try:
             for line in open(os.path.join(ROOT, "profiles", "r1_peak_fp.jsonl")):
                 rec = json.loads(line)
                 if rec.get("pipe") == "dadd":
                     fp64_peak, fp64_src = rec["lane_instr_per_s"], "measured (profiles/r1_peak_fp.jsonl, tools/peak_fp.cu)"
+                if rec.get("pipe") == "ffma":
+                    fp32_peak, fp32_src = rec["lane_instr_per_s"], "measured (profiles/r1_peak_fp.jsonl, tools/peak_fp.cu)"
         except Exception:
             pass
         out = {
             "metric": "events_aligned_per_sec", "value": events_all / (step_ms_max * 1e-3), "unit": "events/s",
             "n_gpus": world, "steps": a.steps, "warmup": a.warmup, "ms_per_step": step_ms_max,
-            "higher_is_better": True, "scaling": "strong" if a.strong else "weak", "vs_baseline": None, "dtype": "f64",
-            "data": "synthetic",
+            "higher_is_better": True, "scaling": "strong" if a.strong else "weak", "vs_baseline": None,
+            "dtype": "f32" if prec == "fp32" else "f64", "data": "synthetic",
             "config": {"strong_scaling_shards": shard_info,
                        "workload": {"config3": WORKLOAD if a.anchors == ANCHOR_PATTERN else "config3-synthetic, anchor pattern " + a.anchors,
                                     "config4": "config4-synthetic: expectations pass (getExpectationsUsingAnchors) over config 3's reads",
                                     "config5": "config5-synthetic: ACGT 5-mer table, HDP emission (1024 rows x 1200 grid points), "
                                                "log-normal read lengths (median ~20k events, clipped at 400k), -x 100"}[a.workload],
                        "anchor_pattern": {"name": a.anchors, **ANCHOR_PATTERNS[a.anchors]},
+                       "precision": {"fp32": "fp32: DP state, stored rows and logAdd in single precision relative to per-diagonal "
+                                             "integer offsets; emission differences, offsets and total probability in double "
+                                             "(posteriors within 1e-4 of the reference, tests/test_gpu_wide32.py)",
+                                     "fp64": "fp64: the reference's double arithmetic, bit for bit"}[prec],
+                       "other_precision_rank0": other,
                        "mean_band_width_rank0": cells / n_diag, "dense_pattern_rank0": dense,
                        "reads_per_gpu_per_step": a.reads, "host_threads_per_rank": host_threads, "events_per_step": events_all,
                        "band_cells_per_step": cells_all, "l2": "flushed between steps (256 MiB write) and inputs > L2",
@@ -452,11 +491,18 @@ def main():
                     "d2h_bytes_per_step": int(d2h), "gcups": cells_all / e2e_max / 1e9,
                     "ms_each_call_rank0": [round(1e3 * t, 1) for t in e2e_t]},
             # the binding roofline of the band kernels is the FP64 pipe; HBM is the secondary object
-            "roofline": {"bound": "fp64_pipe", "achieved": cells * fp64_per_cell / (float(np.mean(kern_ms)) * 1e-3),
-                         "peak": fp64_peak, "peak_source": fp64_src, "unit": "FP64 lane-instr/s",
-                         "frac": cells * fp64_per_cell / (float(np.mean(kern_ms)) * 1e-3) / fp64_peak,
-                         "per_cell": fp64_per_cell, "clock_mhz": sm_mhz, "traffic": traffic,
-                         "note": "not a contraction (no tensor cores) and not HBM bound: FP64 cubic logAdd, see roofline_hbm"},
+            "roofline": ({"bound": "fp32_pipe", "achieved": cells * fp32_per_cell / (float(np.mean(kern_ms)) * 1e-3),
+                          "peak": fp32_peak, "peak_source": fp32_src, "unit": "FP32 lane-instr/s",
+                          "frac": cells * fp32_per_cell / (float(np.mean(kern_ms)) * 1e-3) / fp32_peak,
+                          "per_cell": fp32_per_cell, "clock_mhz": sm_mhz, "traffic": traffic,
+                          "note": "not a contraction (no tensor cores) and not HBM bound: single-precision cubic logAdd; the "
+                                  "kernel is issue bound (FP32 is a quarter of its instruction mix, profiles/), see roofline_hbm"}
+                         if prec == "fp32" else
+                         {"bound": "fp64_pipe", "achieved": cells * fp64_per_cell / (float(np.mean(kern_ms)) * 1e-3),
+                          "peak": fp64_peak, "peak_source": fp64_src, "unit": "FP64 lane-instr/s",
+                          "frac": cells * fp64_per_cell / (float(np.mean(kern_ms)) * 1e-3) / fp64_peak,
+                          "per_cell": fp64_per_cell, "clock_mhz": sm_mhz, "traffic": traffic,
+                          "note": "not a contraction (no tensor cores) and not HBM bound: FP64 cubic logAdd, see roofline_hbm"}),
             "roofline_hbm": {"bound": "hbm", "achieved": achieved_gbs, "peak": hbm_peak, "unit": "GB/s",
                              "frac": achieved_gbs / hbm_peak, "traffic": traffic, "algorithmic_bytes": alg_bytes_per_cell * cells,
                              "peak_source": peak_src},

@@ -242,7 +242,24 @@ struct DevBuf {
         n = count;
         s = st;
         if (count == 0) return SA_OK;
-        CK(cudaMallocAsync((void **) &p, count * sizeof(T), st));
+        cudaError_t e = cudaMallocAsync((void **) &p, count * sizeof(T), st);
+        if (e == cudaErrorMemoryAllocation) {
+            // the pool keeps what earlier batches freed (release threshold lifted); blocks of other sizes fragment it.  Let the
+            // pending frees land, hand the unused blocks back to the driver and ask once more.
+            (void) cudaGetLastError();
+            int dev = 0;
+            cudaMemPool_t pool;
+            if (cudaDeviceSynchronize() == cudaSuccess && cudaGetDevice(&dev) == cudaSuccess &&
+                cudaDeviceGetDefaultMemPool(&pool, dev) == cudaSuccess)
+                cudaMemPoolTrimTo(pool, 0);
+            e = cudaMallocAsync((void **) &p, count * sizeof(T), st);
+        }
+        if (e != cudaSuccess) {
+            p = nullptr;
+            sa_set_error("CUDA error cudaMallocAsync(%zu bytes) at %s:%d: %s", count * sizeof(T), __FILE__, __LINE__, cudaGetErrorString(e));
+            (void) cudaGetLastError();
+            return SA_ERR_CUDA;
+        }
         return SA_OK;
     }
     int upload(const std::vector<T> &v, cudaStream_t s, int64_t *bytes) {
@@ -554,6 +571,15 @@ static void wide32Launch(int c, int blocks, int threads, size_t smem, cudaStream
 #undef X
 }
 
+// widest three-diagonal span the register-resident kernel takes; wider items go to the wide kernel.  126 = the 128-slot
+// class <2,2>: the 256-slot class <4,2> (four warps behind one mailbox barrier) runs at half its rate — 14.4 GCUPS on the
+// long-runs / trim-14 pattern against 22.5 for the wide kernel's 256-slot window on the same reads.
+// (SA_REG_MAX_SPAN=<columns> moves the limit; experiments)
+static int regMaxSpan() {
+    if (const char *e = getenv("SA_REG_MAX_SPAN")) return atoi(e);
+    return 126;
+}
+
 // readBase: index of reads[0] in the caller's array (error messages name the caller's read)
 // chunkCount: how many sub-batches of this size the caller runs back to back (scales the latency-class decision)
 static int prepareBatch(const sa_model_t *m, const sa_read_t *reads, int64_t nReads, const sa_params_t *p,
@@ -852,6 +878,7 @@ static int prepareBatch(const sa_model_t *m, const sa_read_t *reads, int64_t nRe
         if ((rc = b->dFItems.upload(b->fItems, st, &b->h2dBytes))) return rc;
         if ((rc = b->dTb.alloc(std::max<int64_t>(1, tbTotal), st))) return rc;
         if ((rc = b->dGeo.alloc(n, st))) return rc;
+        b->fp32 = currentPrecision() == SA_PRECISION_FP32 && !b->expectations && m->kind == SA_EMIT_GAUSS_MEANONLY_DESCALE;
         f.items = b->dFItems.p; f.nItems = (int32_t) n;
         f.evMean = b->dEvMean.p; f.kmerIdx = b->dPathKmer.p; f.anchors = b->dAnchors.p;
         f.tb = b->dTb.p; f.geo = b->dGeo.p; f.ft = m->dev->ft;
@@ -873,7 +900,7 @@ static int prepareBatch(const sa_model_t *m, const sa_read_t *reads, int64_t nRe
         }
         f.wPlanes = m->kind == SA_EMIT_HDP ? 4 : 3;
         f.wAllFull = b->expectations ? 1 : 0;
-        f.wGeoAlways = getenv("SA_WIDE_ONLY") != nullptr ? 1 : 0;
+        f.wGeoAlways = (getenv("SA_WIDE_ONLY") != nullptr || regMaxSpan() < 254) ? 1 : 0;
         sa_geometry_kernel<<<(unsigned) n, 32, 0, st>>>(f);
         CK(cudaGetLastError());
         CK(cudaMemcpyAsync(geo.data(), b->dGeo.p, sizeof(FGeo) * n, cudaMemcpyDeviceToHost, st));
@@ -886,6 +913,7 @@ static int prepareBatch(const sa_model_t *m, const sa_read_t *reads, int64_t nRe
     // and the band never moves backwards; else the wide kernel, in the narrowest window class that holds them plus the
     // slack of its emission rings (SA_WIDE_ONLY: every item, A/B runs); the general kernel only beyond 4096 slots.
     const bool wideOnly = getenv("SA_WIDE_ONLY") != nullptr, noWide = getenv("SA_NO_WIDE") != nullptr;
+    const int regSpan = regMaxSpan();
     int wideMax = kWideClasses;
     while (wideMax > 0 && wideSmemBytes(true, kWideNSW[wideMax - 1], false) > kSmemCap) wideMax--;
     for (int64_t i = 0; i < n; i++) {
@@ -894,8 +922,8 @@ static int prepareBatch(const sa_model_t *m, const sa_read_t *reads, int64_t nRe
         if (fastModel && it.maxP == 1 && geo[i].nTb <= b->fItems[i].nTbCap) {
             if (geo[i].monotone && !wideOnly)
                 for (int c = 0; c < 4 && !it.kernel; c++)
-                    if (geo[i].maxSpan <= 32 * kW[c] - 2) it.kernel = kW[c];
-            if (!it.kernel && !noWide && (geo[i].maxSpan > 254 || wideOnly))
+                    if (geo[i].maxSpan <= 32 * kW[c] - 2 && (noWide || geo[i].maxSpan <= regSpan)) it.kernel = kW[c];
+            if (!it.kernel && !noWide)
                 for (int c = 0; c < wideMax && !it.kernel; c++)
                     if (geo[i].maxSpan + 24 <= kWideNSW[c]) it.kernel = 100 + c;
         }
@@ -1014,9 +1042,8 @@ static int prepareBatch(const sa_model_t *m, const sa_read_t *reads, int64_t nRe
         if ((rc = b->dWOrder[c].upload(b->wOrder[c], st, &b->h2dBytes))) return rc;
         if (b->wOrder[c].empty()) continue;
         const bool hdp = m->kind == SA_EMIT_HDP;
-        b->fp32 = currentPrecision() == SA_PRECISION_FP32 && !b->expectations && m->kind == SA_EMIT_GAUSS_MEANONLY_DESCALE;
         const bool gr = b->fp32 ? wide32GlobalRings(c) : wideGlobalRings(c);
-        const bool foldGlobal = b->fp32 ? gr : wideFoldGlobal(c, gr);
+        const bool foldGlobal = b->fp32 ? (gr || kWideNSW[c] >= 1024) : wideFoldGlobal(c, gr);   // (fp32, 1024 slots: three CTAs per SM instead of two)
         const size_t smem = b->fp32 ? wide32SmemBytes(c, !foldGlobal) : wideSmemBytes(gr, kWideNSW[c], !foldGlobal);
         int bps = 1;
         if (b->fp32) {
@@ -1029,7 +1056,15 @@ static int prepareBatch(const sa_model_t *m, const sa_read_t *reads, int64_t nRe
             sa_set_error("sa_batch_prepare: a traceback block needs %.1f GB of forward rows (band too wide)", b->wRingDoubles[c] * 8e-9);
             return SA_ERR_INPUT;
         }
-        if ((rc = b->dWRing[c].alloc((size_t) b->wBlocks[c] * b->wRingDoubles[c], st))) return rc;
+        // (the FP32 kernel's ring holds floats: the same element count in half the bytes; wRingDoubles is a multiple of 16)
+        const size_t ringStride = (size_t) (b->fp32 ? b->wRingDoubles[c] / 2 : b->wRingDoubles[c]);
+        {   // a class's rings take at most a fifth of the device (the one-shot call keeps several chunks in flight)
+            size_t freeB = 0, totalB = 0;
+            CK(cudaMemGetInfo(&freeB, &totalB));
+            const int64_t fit = (int64_t) ((double) totalB * 0.2 / ((double) ringStride * 8.0));
+            if (fit < b->wBlocks[c]) b->wBlocks[c] = (int) std::max<int64_t>(1, fit);
+        }
+        if ((rc = b->dWRing[c].alloc((size_t) b->wBlocks[c] * ringStride, st))) return rc;
         if ((rc = b->dWHdr[c].alloc((size_t) b->wBlocks[c] * b->wRows[c], st))) return rc;
         if (foldGlobal && (rc = b->dWFold[c].alloc((size_t) b->wBlocks[c] * 2 * kWideNSW[c], st))) return rc;
         // a stream of its own per window class: the classes are separate persistent grids, and on one stream each would

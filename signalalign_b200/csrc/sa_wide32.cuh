@@ -592,10 +592,10 @@ __global__ void __launch_bounds__(NTMAX, MINB) sa_wide32_kernel(const __grid_con
     W::fillTransitions(P, E);
     sa_logAdd_init();
     typename W::Rows RW;
-    RW.ring = P.scratch + (int64_t) blockIdx.x * P.wRingDoubles;
+    RW.ring = P.scratch + (int64_t) blockIdx.x * (P.wRingDoubles >> 1);      // P.wRingDoubles FLOATS per CTA
     RW.hdr = P.wHdr + (int64_t) blockIdx.x * P.wRowsCap;
     RW.cap = P.wRowsCap;
-    RW.ringDoubles = (int32_t) P.wRingDoubles;            // the ring counts FLOATS here (same element count, half the bytes)
+    RW.ringDoubles = (int32_t) P.wRingDoubles;            // the ring counts floats here (same element count, half the bytes)
     double *offF = P.wOff + (int64_t) blockIdx.x * P.wOffCap;
     for (;;) {
         __syncthreads();
