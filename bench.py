@@ -37,6 +37,26 @@ from signalalign_b200.synth import ANCHOR_PATTERNS  # noqa: E402  (numpy only)
 GEN = dict(ANCHOR_PATTERNS[ANCHOR_PATTERN])
 
 
+def compare_pairs(ra, rb):
+    """posterior agreement of two results on the same reads (the two precisions): pairs matched on (read, x, y)"""
+    def keys(r):
+        n = np.diff(r.pair_offsets)
+        rid = np.repeat(np.arange(len(n), dtype=np.int64), n)
+        return (rid << 42) | (r.pairs[:, 1].astype(np.int64) << 21) | r.pairs[:, 2].astype(np.int64)
+    ka, kb = keys(ra), keys(rb)
+    if ka.shape == kb.shape and np.array_equal(ka, kb):
+        ia = ib = slice(None)
+        only = np.zeros(0, dtype=np.int64)
+    else:
+        _, ia, ib = np.intersect1d(ka, kb, assume_unique=True, return_indices=True)
+        only = np.concatenate([np.delete(ra.pairs[:, 0], ia), np.delete(rb.pairs[:, 0], ib)]).astype(np.int64)
+    dp = np.abs(ra.pairs[ia, 0].astype(np.int64) - rb.pairs[ib, 0].astype(np.int64))
+    return {"pairs_compared": int(dp.shape[0]), "max_abs_dp": float(dp.max()) / 1e7 if dp.size else 0.0,
+            "dp_above_1e-4": int((dp > 1000).sum()), "dp_above_1e-5": int((dp > 100).sum()),
+            "kmer_mismatches": int((ra.pairs[ia, 3] != rb.pairs[ib, 3]).sum()),
+            "pairs_in_one_only": int(only.shape[0]), "largest_p_of_those": float(only.max()) / 1e7 if only.size else None}
+
+
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -295,6 +315,7 @@ def main():
     clocks = sampler.stop() if rank == 0 else None
     step_ms = float(np.sum(dev_ms)) / a.steps
     res = batch.fetch()
+    res_keep = res if (a.workload == "config3" and not a.no_other_precision) else None
     n_pairs = int(res.pair_offsets[-1])
     if expect:        # the expectations pass returns 9 transition sums + the likelihood per read
         pairs_digest = [float(v) for v in res.transitions.sum(0)] + [float(res.likelihood.sum())]
@@ -318,8 +339,10 @@ def main():
         ores = ob.fetch()
         other = {"precision": oprec, "gcups": ob.band_cells / (min(oms) * 1e-3) / 1e9, "events_per_s": events / (min(oms) * 1e-3),
                  "ms_per_step": min(oms), "aligned_pairs": int(ores.pair_offsets[-1]),
-                 "pairs_column_sums": [int(ores.pairs[:, c].astype(np.int64).sum()) for c in range(4)]}
+                 "pairs_column_sums": [int(ores.pairs[:, c].astype(np.int64).sum()) for c in range(4)],
+                 "agreement_with_headline": compare_pairs(res_keep, ores)}
         del ores
+        res_keep = None
         ob.close()
         sa.set_precision(prec)
 

@@ -1058,10 +1058,18 @@ static int prepareBatch(const sa_model_t *m, const sa_read_t *reads, int64_t nRe
         }
         // (the FP32 kernel's ring holds floats: the same element count in half the bytes; wRingDoubles is a multiple of 16)
         const size_t ringStride = (size_t) (b->fp32 ? b->wRingDoubles[c] / 2 : b->wRingDoubles[c]);
-        {   // a class's rings take at most a fifth of the device (the one-shot call keeps several chunks in flight)
+        {   // a class's rings take at most a fifth of the device and 40 % of what is available now (the one-shot call keeps
+            // several chunks in flight, each with up to five classes): fewer resident CTAs rather than a failed call
             size_t freeB = 0, totalB = 0;
             CK(cudaMemGetInfo(&freeB, &totalB));
-            const int64_t fit = (int64_t) ((double) totalB * 0.2 / ((double) ringStride * 8.0));
+            cudaMemPool_t pool;
+            uint64_t reserved = 0, used = 0;
+            if (cudaDeviceGetDefaultMemPool(&pool, dev) == cudaSuccess &&
+                cudaMemPoolGetAttribute(pool, cudaMemPoolAttrReservedMemCurrent, &reserved) == cudaSuccess &&
+                cudaMemPoolGetAttribute(pool, cudaMemPoolAttrUsedMemCurrent, &used) == cudaSuccess && reserved > used)
+                freeB += (size_t) (reserved - used);
+            const double budget = std::min((double) totalB * 0.2, (double) freeB * 0.4);
+            const int64_t fit = (int64_t) (budget / ((double) ringStride * 8.0));
             if (fit < b->wBlocks[c]) b->wBlocks[c] = (int) std::max<int64_t>(1, fit);
         }
         if ((rc = b->dWRing[c].alloc((size_t) b->wBlocks[c] * ringStride, st))) return rc;
