@@ -1689,6 +1689,14 @@ static int alignPipelined(const sa_model_t *m, const sa_read_t *reads, int64_t n
                           const sa_ambig_t *ambig, sa_result_t **out) {
     *out = nullptr;
     int64_t nch = nReads >= 2048 ? 4 : (nReads >= 512 ? 2 : 1);
+    {   // heavy-tailed lengths: a read is one CTA's sequential sweep, and every chunk would carry its own longest reads,
+        // which only start once the previous chunk's persistent CTAs leave — the makespans add up.  One chunk then.
+        int64_t sumEv = 0, maxEv = 0;
+        for (int64_t i = 0; i < nReads; i++) { sumEv += reads[i].nEvents; maxEv = std::max(maxEv, reads[i].nEvents); }
+        int nSM = 148, dev = 0;
+        if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&nSM, cudaDevAttrMultiProcessorCount, dev);
+        if ((double) maxEv * nSM > 0.25 * (double) sumEv) nch = 1;
+    }
     if (const char *e = getenv("SA_CHUNKS")) nch = std::max<int64_t>(1, std::min<int64_t>(atoll(e), std::max<int64_t>(1, nReads)));
     PhaseTimer timer("align");
     std::vector<std::unique_ptr<sa_batch>> bs;
