@@ -250,7 +250,7 @@ def main():
         # RNA-like: ~1.3 events per nt, median 20 k events; the RNA .nhdp of BASELINE config 5 is absent from the reference
         # snapshot: spline tables of the same shape (one row per kmer, 1200 grid points, two-component mixtures)
         if a.reads == 4736:
-            a.reads = 768
+            a.reads = 3072
         reads_d, table = synth.make_batch(a.reads, seed=a.seed + 1 + 1000 * rank, alphabet="ACGT", k=5, ref_len=3_000_000,
                                           mean_len=15400, sigma_len=1.35, min_len=770, max_len=300000,
                                           n_probs=(0.05, 0.70, 0.18, 0.07), **GEN)
