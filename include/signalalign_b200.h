@@ -192,6 +192,36 @@ typedef struct {                   /* NanoporeReadAdjustmentParameters (inc/nano
 int sa_gpu_estimate_params_batch(const sa_model_t *m, sa_strand_t *strands, int64_t nStrands, int adjustEvents,
                                  sa_scaling_t *out);
 
+/* SURVEY.md 8f N3 — variant calls of aligned pairs and their per-position marginals, on the device.
+ * Replaces writePosteriorProbsVC (impl/signalMachine.c:161-232: one TSV row per ambiguity character X of the reference
+ * kmer of every aligned pair) followed by MarginalizeVariants.get_data (src/signalalign/variantCaller.py:37-89: per
+ * reference position the posterior mass of every called base normalised over the bases, per read the mean over its
+ * positions), the TSV round trip between the two included: with roundLikeTsv != 0 every posterior is first rounded to
+ * the six decimals a "%f" field carries.  One entry per (read, strand); variants = the bases to track, e.g. "CE"
+ * (columns come out in sorted order, as the reference sorts them).  A called base outside `variants` is an error
+ * (the reference raises).  Positions come out ascending; positions no pair reports on are absent, as in the reference. */
+typedef struct {
+    const sa_pair_t *pairs;        /* the read's aligned pairs as sa_result_t holds them (kmerIdx = the path kmer) */
+    int64_t nPairs;
+    const char *target;            /* the sequence the strand was aligned to, X at the ambiguous positions */
+    int64_t targetLength;
+    int32_t strandIsComplement;    /* Strand: template 0, complement 1 */
+    int32_t forward;               /* the `forward` flag signalMachine passes to its writers */
+    int64_t referenceSequenceOffset;
+} sa_variant_read_t;
+typedef struct {
+    int64_t nReads;
+    int32_t nVariants;
+    char variants[32];             /* sorted, NUL-terminated: the column order of probs / perRead */
+    int64_t *positionOffsets;      /* nReads + 1: read i owns positions[positionOffsets[i] .. positionOffsets[i + 1]) */
+    int64_t *positions;            /* reference positions, ascending within a read */
+    double *probs;                 /* [total positions][nVariants] */
+    double *perRead;               /* [nReads][nVariants]: mean of the read's rows of probs (zeros for a read without positions) */
+} sa_marginals_t;
+int sa_gpu_marginalize_variants(const sa_model_t *m, const sa_variant_read_t *reads, int64_t nReads, const char *variants,
+                                int roundLikeTsv, sa_marginals_t **out);
+void sa_marginals_free(sa_marginals_t *r);
+
 /* ONE read, NO device allocation.  This entry point has no counterpart in the reference: it was added
  * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,
  * harnesses that forbid it).  Same result as sa_gpu_align_batch on that read (the wide band kernel, 512-slot window):

@@ -290,3 +290,59 @@ def estimate_params(match_table, alphabet, k, read, event_map, events, adjust_ev
                               int(adjust_events), _f64(out))
     names = ["scale", "shift", "var", "shift_sd", "scale_sd", "var_sd", "drift"]
     return dict(zip(names, out)), ev, int(n)
+
+
+# ---------------------------------------------------------------------------------------------------- SURVEY 8f N3
+# variant calls of one strand of one read and their per-position marginals (plain Python / numpy: small cases only)
+_RC = {"A": "T", "C": "G", "G": "C", "T": "A", "a": "t", "c": "g", "g": "c", "t": "a", "M": "K", "K": "M", "R": "Y", "Y": "R",
+       "B": "V", "V": "B", "D": "H", "H": "D", "m": "k", "k": "m", "r": "y", "y": "r", "b": "v", "v": "b", "d": "h", "h": "d"}
+
+
+def tsv_round6(p):
+    """the value a `%f` field carries (the reference's pipeline passes every posterior through the TSV text)"""
+    return float("%f" % p)
+
+
+def variant_rows(pairs, target, k, kmer_strings, strand_complement=False, forward=True, event_offset=0, ref_offset=0, rna=False):
+    """writePosteriorProbsVC (reference impl/signalMachine.c:161-232): for every aligned pair (p*1e7, x, y, kmer) whose
+    reference kmer holds the ambiguity character X (AMBIG_BASE, inc/pairwiseAligner.h:32; path_findDegeneratePositions
+    impl/pairwiseAligner.c:577-592) one row per X: (event index, reference position, called base, p).
+    pairs: int array [n, 4]; kmer_strings[i]: the path kmer of pair i.  Rows in the writer's order."""
+    ref_len = len(target)
+    ref_len_kmers = ref_len - k
+    same = (not strand_complement and forward) or (strand_complement and not forward)      # :57, :65, :82
+    rows = []
+    for (p, x, y, _), path_kmer in zip(pairs, kmer_strings):
+        k_i = target[x:x + k]
+        ref_kmer = k_i if same else "".join(_RC.get(c, c) for c in reversed(k_i))            # makeReferenceKmer :64-70
+        q_pos = [i for i, c in enumerate(ref_kmer) if c == "X"]
+        if not q_pos:
+            continue
+        x_adj = x + ref_offset if same else ref_len_kmers - (x + (ref_len - ref_offset))     # adjustReferenceCoordinate :54-62
+        for q in q_pos:
+            qq = q if same else (k - 1) - q                                                  # adjustQueryPosition :81-87
+            rows.append((int(y) + event_offset, x_adj + q, path_kmer[qq], int(p) / 1e7))
+    return rows
+
+
+def marginalize_variants(rows, variants, round_like_tsv=True):
+    """MarginalizeVariants.get_data for one (strand, mapping) group (reference src/signalalign/variantCaller.py:37-89):
+    per reference position the posterior mass of every called base, normalised over the bases; per read the mean over the
+    positions.  Returns (sorted positions, probs [n, len(variants)] in sorted(variants) order, per-read means)."""
+    vs = sorted(variants)
+    mass = {}
+    for _, pos, base, p in rows:
+        if round_like_tsv:
+            p = tsv_round6(p)
+        mass.setdefault(pos, {}).setdefault(base, []).append(p)
+    positions = sorted(mass)
+    probs = np.zeros((len(positions), len(vs)))
+    for i, pos in enumerate(positions):
+        sums = {b: sum(v) for b, v in mass[pos].items()}          # Python's left-to-right sum, as the reference's sum()
+        total = 0.0
+        for b in sums:
+            total += sums[b]
+        for b, s in sums.items():
+            probs[i, vs.index(b)] = s / total                     # (a base outside `variants` raises, as the reference does)
+    per_read = probs.sum(0) / max(1, len(positions))
+    return np.array(positions, dtype=np.int64), probs, per_read

@@ -49,6 +49,16 @@ class SaScaling(C.Structure):
                 ("scale_sd", C.c_double), ("var_sd", C.c_double), ("drift", C.c_double), ("nAssignments", C.c_int64)]
 
 
+class SaVariantRead(C.Structure):
+    _fields_ = [("pairs", C.POINTER(SaPair)), ("nPairs", C.c_int64), ("target", C.c_char_p), ("targetLength", C.c_int64),
+                ("strandIsComplement", C.c_int32), ("forward", C.c_int32), ("referenceSequenceOffset", C.c_int64)]
+
+
+class SaMarginals(C.Structure):
+    _fields_ = [("nReads", C.c_int64), ("nVariants", C.c_int32), ("variants", C.c_char * 32), ("positionOffsets", c_i64p),
+                ("positions", c_i64p), ("probs", c_f64p), ("perRead", c_f64p)]
+
+
 class SaResult(C.Structure):
     _fields_ = [("nReads", C.c_int64), ("pairOffsets", c_i64p), ("pairs", C.POINTER(SaPair)),
                 ("transitions", c_f64p), ("likelihood", c_f64p), ("assignOffsets", c_i64p),
@@ -68,6 +78,7 @@ EXPORTS = [
     "sa_debug_split_points", "sa_debug_kmer_paths", "sa_last_call_stats", "sa_set_host_threads",
     "sa_gpu_comm_unique_id", "sa_gpu_comm_init", "sa_gpu_comm_from_nccl", "sa_gpu_comm_free",
     "sa_gpu_allreduce_expectations", "sa_gpu_allgather_assignments", "sa_gpu_align_noalloc", "sa_gpu_estimate_params_batch", "sa_gpu_set_precision", "sa_gpu_get_precision",
+    "sa_gpu_marginalize_variants", "sa_marginals_free",
 ]
 
 _lib = None
@@ -137,6 +148,10 @@ def lib():
     L.sa_batch_free.argtypes = [C.c_void_p]
     L.sa_gpu_align_noalloc.argtypes = [C.c_void_p, C.POINTER(SaRead), C.POINTER(SaParams), C.POINTER(SaPair), C.c_int64, c_i64p]
     L.sa_gpu_estimate_params_batch.argtypes = [C.c_void_p, C.POINTER(SaStrand), C.c_int64, C.c_int, C.POINTER(SaScaling)]
+    L.sa_gpu_marginalize_variants.argtypes = [C.c_void_p, C.POINTER(SaVariantRead), C.c_int64, C.c_char_p, C.c_int,
+                                              C.POINTER(C.POINTER(SaMarginals))]
+    L.sa_marginals_free.restype = None
+    L.sa_marginals_free.argtypes = [C.POINTER(SaMarginals)]
     L.sa_gpu_comm_unique_id.argtypes = [C.c_void_p]
     L.sa_gpu_comm_init.argtypes = [C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_void_p)]
     L.sa_gpu_comm_from_nccl.argtypes = [C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_void_p)]
@@ -414,6 +429,35 @@ def estimate_params_batch(model, strands, adjust_events=True):
     names = ["scale", "shift", "var", "shift_sd", "scale_sd", "var_sd", "drift"]
     params = [dict({k: getattr(out[i], k) for k in names}, n_assignments=out[i].nAssignments) for i in range(len(strands))]
     return params, [k[2] for k in keep]
+
+
+def marginalize_variants(model, reads, variants, round_like_tsv=True):
+    """Variant calls of aligned pairs and their per-position marginals (sa_gpu_marginalize_variants).
+
+    reads = [(pairs int32 [n, 4] as Result.read_pairs returns them, target string with X at the ambiguous positions,
+    strand_is_complement, forward, reference_sequence_offset)].  Returns (sorted variants, list of
+    (positions int64 [m], probs float64 [m, len(variants)], per_read float64 [len(variants)]))."""
+    keep, arr = [], (SaVariantRead * max(1, len(reads)))()
+    for i, (pairs, target, comp, fwd, off) in enumerate(reads):
+        pr = np.ascontiguousarray(pairs, np.int32).reshape(-1, 4)
+        tg = target.encode() if isinstance(target, str) else bytes(target)
+        keep.append((pr, tg))
+        arr[i] = SaVariantRead(pr.ctypes.data_as(C.POINTER(SaPair)), pr.shape[0], tg, len(tg), int(bool(comp)), int(bool(fwd)), int(off))
+    out = C.POINTER(SaMarginals)()
+    vb = variants.encode() if isinstance(variants, str) else bytes(variants)
+    _check(lib().sa_gpu_marginalize_variants(model.h, arr, len(reads), vb, int(bool(round_like_tsv)), C.byref(out)))
+    try:
+        r = out.contents
+        V = r.nVariants
+        offs = np.ctypeslib.as_array(r.positionOffsets, (len(reads) + 1,)).copy()
+        tot = int(offs[-1])
+        pos = np.ctypeslib.as_array(r.positions, (max(1, tot),))[:tot].copy()
+        probs = np.ctypeslib.as_array(r.probs, (max(1, tot) * V,))[:tot * V].reshape(tot, V).copy()
+        per = np.ctypeslib.as_array(r.perRead, (max(1, len(reads)) * V,)).reshape(-1, V)[:len(reads)].copy()
+        res = [(pos[offs[i]:offs[i + 1]], probs[offs[i]:offs[i + 1]], per[i]) for i in range(len(reads))]
+        return r.variants.decode(), res
+    finally:
+        lib().sa_marginals_free(out)
 
 
 def expectations_batch(model, reads, params=None, ambig=None):

@@ -19,6 +19,7 @@
 #include "sa_wide.cuh"
 #include "sa_wide32.cuh"
 #include "sa_estimate.cuh"
+#include "sa_variants.cuh"
 
 #define CK(call)                                                                                   \
     do {                                                                                           \
@@ -1896,6 +1897,154 @@ extern "C" int sa_gpu_estimate_params_batch(const sa_model_t *m, sa_strand_t *st
         for (int64_t i = 0; i < n; i++)
             for (int64_t y = 0; y < strands[i].nEvents; y++) strands[i].events[4 * y] = hMean[(size_t) (es[(size_t) i].evOff + y)];
     }
+    return SA_OK;
+}
+
+// ================================================================================================ SURVEY 8f N3
+// sa_gpu_marginalize_variants: variant calls of aligned pairs -> per-position marginals (sa_variants.cuh)
+extern "C" void sa_marginals_free(sa_marginals_t *r) {
+    if (!r) return;
+    free(r->positionOffsets); free(r->positions); free(r->probs); free(r->perRead);
+    free(r);
+}
+extern "C" int sa_gpu_marginalize_variants(const sa_model_t *m, const sa_variant_read_t *reads, int64_t n, const char *variants,
+                                           int roundLikeTsv, sa_marginals_t **out) {
+    *out = nullptr;
+    if (sa_gpu_device_count() == 0) {
+        sa_set_error("sa_gpu_marginalize_variants: no CUDA device available; libsagpu has no CPU fallback");
+        return SA_ERR_CUDA;
+    }
+    std::string vs(variants ? variants : "");
+    std::sort(vs.begin(), vs.end());
+    vs.erase(std::unique(vs.begin(), vs.end()), vs.end());
+    if (vs.empty() || vs.size() > 31 || m->k > 15) {
+        sa_set_error("sa_gpu_marginalize_variants: need 1..31 distinct variant characters and a kmer length <= 15");
+        return SA_ERR_INPUT;
+    }
+    const int V = (int) vs.size();
+    int rc = poolInit();
+    if (rc) return rc;
+    std::vector<VarRead> vr((size_t) std::max<int64_t>(1, n));
+    int64_t pairTot = 0, rankTot = 0, massTot = 0;
+    for (int64_t i = 0; i < n; i++) {
+        const sa_variant_read_t &R = reads[i];
+        if (R.nPairs < 0 || R.targetLength < 0 || (R.nPairs > 0 && !R.pairs) || (R.targetLength > 0 && !R.target)) {
+            sa_set_error("sa_gpu_marginalize_variants: read %lld: bad sizes", (long long) i);
+            return SA_ERR_INPUT;
+        }
+        VarRead &q = vr[(size_t) i];
+        q.pairOff = pairTot; q.nPairs = R.nPairs; q.rankOff = rankTot; q.targetLen = R.targetLength; q.massOff = massTot;
+        int32_t nX = 0;
+        for (int64_t t = 0; t < R.targetLength; t++) nX += R.target[t] == 'X';
+        q.nX = nX; q.pad = 0;
+        pairTot += R.nPairs; rankTot += R.targetLength; massTot += (int64_t) nX * V;
+    }
+    PinVec<sa_pair_t> hPairs;
+    PinVec<int32_t> hRank;
+    PinVec<double> hMass;
+    if (!hPairs.resize((size_t) std::max<int64_t>(1, pairTot)) || !hRank.resize((size_t) std::max<int64_t>(1, rankTot)) ||
+        !hMass.resize((size_t) std::max<int64_t>(1, massTot))) {
+        sa_set_error("sa_gpu_marginalize_variants: cannot allocate pinned staging memory");
+        return SA_ERR_CUDA;
+    }
+#pragma omp parallel for schedule(dynamic, 8)
+    for (int64_t i = 0; i < n; i++) {
+        const sa_variant_read_t &R = reads[i];
+        const VarRead &q = vr[(size_t) i];
+        if (R.nPairs) memcpy(hPairs.data() + q.pairOff, R.pairs, sizeof(sa_pair_t) * (size_t) R.nPairs);
+        int32_t r = 0;
+        for (int64_t t = 0; t < R.targetLength; t++) hRank[(size_t) (q.rankOff + t)] = R.target[t] == 'X' ? r++ : -1;
+    }
+    sa_marginals_t *res = (sa_marginals_t *) calloc(1, sizeof(sa_marginals_t));
+    res->nReads = n; res->nVariants = V;
+    memcpy(res->variants, vs.c_str(), vs.size() + 1);
+    res->positionOffsets = (int64_t *) calloc((size_t) n + 1, sizeof(int64_t));
+    res->perRead = (double *) calloc((size_t) std::max<int64_t>(1, n) * V, sizeof(double));
+    if (n > 0 && massTot > 0) {
+        cudaStream_t st;
+        CK(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
+        struct StreamGuard { cudaStream_t s; ~StreamGuard() { cudaStreamSynchronize(s); cudaStreamDestroy(s); } } guard{st};
+        DevBuf<VarRead> dR;
+        DevBuf<sa_pair_t> dPairs;
+        DevBuf<int32_t> dRank, dErr;
+        DevBuf<double> dMass;
+        int64_t bytes = 0;
+        if ((rc = dR.upload(vr, st, &bytes)) || (rc = dPairs.upload(hPairs, st, &bytes)) || (rc = dRank.upload(hRank, st, &bytes)) ||
+            (rc = dMass.alloc((size_t) massTot, st)) || (rc = dErr.alloc(1, st))) {
+            sa_marginals_free(res);
+            return rc;
+        }
+        CK(cudaMemsetAsync(dErr.p, 0, sizeof(int32_t), st));
+        CK(cudaMemsetAsync(dMass.p, 0, sizeof(double) * massTot, st));
+        VarParams P;
+        memset(&P, 0, sizeof(P));
+        P.reads = dR.p; P.pairs = dPairs.p; P.xRank = dRank.p; P.mass = dMass.p; P.err = dErr.p;
+        P.A = m->A; P.k = m->k; P.V = V; P.roundLikeTsv = roundLikeTsv ? 1 : 0;
+        for (int d = 0; d < 256; d++) {
+            P.digitToVariant[d] = -1;
+            if (d < m->A) {
+                const size_t j = vs.find(m->alphabet[(size_t) d]);
+                if (j != std::string::npos) P.digitToVariant[d] = (int32_t) j;
+            }
+        }
+        sa_variant_mass_kernel<256><<<(unsigned) n, 256, 0, st>>>(P);
+        CK(cudaGetLastError());
+        int32_t err = 0;
+        CK(cudaMemcpyAsync(hMass.data(), dMass.p, sizeof(double) * massTot, cudaMemcpyDeviceToHost, st));
+        CK(cudaMemcpyAsync(&err, dErr.p, sizeof(err), cudaMemcpyDeviceToHost, st));
+        CK(cudaStreamSynchronize(st));
+        if (err) {
+            sa_set_error(err == 1 ? "sa_gpu_marginalize_variants: a pair calls a base that is not among the variants (the reference "
+                                    "raises in MarginalizeVariants.get_data, variantCaller.py:74)"
+                                  : "sa_gpu_marginalize_variants: an aligned pair lies outside its target sequence");
+            sa_marginals_free(res);
+            return SA_ERR_INPUT;
+        }
+    }
+    // normalise and compact (a few hundred positions per read): positions with no row are absent, order ascending
+    int64_t nPosTot = 0;
+    std::vector<int64_t> nPos((size_t) std::max<int64_t>(1, n), 0);
+    for (int64_t i = 0; i < n; i++) {
+        const VarRead &q = vr[(size_t) i];
+        for (int32_t r = 0; r < q.nX; r++) {
+            double tot = 0;
+            for (int v = 0; v < V; v++) tot += hMass[(size_t) (q.massOff + (int64_t) r * V + v)];
+            nPos[(size_t) i] += tot > 0;
+        }
+        res->positionOffsets[i + 1] = res->positionOffsets[i] + nPos[(size_t) i];
+        nPosTot += nPos[(size_t) i];
+    }
+    res->positions = (int64_t *) calloc((size_t) std::max<int64_t>(1, nPosTot), sizeof(int64_t));
+    res->probs = (double *) calloc((size_t) std::max<int64_t>(1, nPosTot) * V, sizeof(double));
+    for (int64_t i = 0; i < n; i++) {
+        const sa_variant_read_t &R = reads[i];
+        const VarRead &q = vr[(size_t) i];
+        const bool same = (!R.strandIsComplement && R.forward) || (R.strandIsComplement && !R.forward);
+        int64_t w = res->positionOffsets[i];
+        // ranks ascend with t; the reported position ascends with t (same orientation) or descends (mirrored)
+        std::vector<int64_t> tOf((size_t) q.nX);
+        {
+            int32_t r = 0;
+            for (int64_t t = 0; t < R.targetLength; t++)
+                if (R.target[t] == 'X') tOf[(size_t) r++] = t;
+        }
+        for (int32_t rr = 0; rr < q.nX; rr++) {
+            const int32_t r = same ? rr : q.nX - 1 - rr;
+            const double *ms = hMass.data() + q.massOff + (int64_t) r * V;
+            double tot = 0;
+            for (int v = 0; v < V; v++) tot += ms[v];
+            if (!(tot > 0)) continue;
+            res->positions[w] = same ? tOf[(size_t) r] + R.referenceSequenceOffset : R.referenceSequenceOffset - 1 - tOf[(size_t) r];
+            for (int v = 0; v < V; v++) {
+                res->probs[w * V + v] = ms[v] / tot;
+                res->perRead[i * V + v] += ms[v] / tot;
+            }
+            w++;
+        }
+        if (nPos[(size_t) i] > 0)
+            for (int v = 0; v < V; v++) res->perRead[i * V + v] /= (double) nPos[(size_t) i];
+    }
+    *out = res;
     return SA_OK;
 }
 
