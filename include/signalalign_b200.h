@@ -222,6 +222,33 @@ int sa_gpu_marginalize_variants(const sa_model_t *m, const sa_variant_read_t *re
                                 int roundLikeTsv, sa_marginals_t **out);
 void sa_marginals_free(sa_marginals_t *r);
 
+/* SURVEY.md 8f N4 — adaptive banded event -> kmer alignment, on the device.
+ * Replaces adaptive_banded_simple_event_align2 (impl/eventAligner.c:899-1235; band of 100 cells moved by Suzuki's rule,
+ * Viterbi over step / stay / skip with the ..._MeanOnly emission, trim states, backtrack, QC) and, with useMom != 0, the
+ * scalings of estimate_scalings_using_mom (:792-842) — what load_from_raw2 (:1240-1301) runs between event detection and
+ * the embedding of the event table.  The aligned (kmer, event) pairs are bit-identical to the reference's; a read its QC
+ * rejects (average log emission < -5.2, not spanning the kmers, a gap > 50, more than 5 events per kmer) comes back with
+ * zero pairs and failed = 1, as the reference returns an empty list.  Models with the Gaussian match table only. */
+typedef struct {
+    const char *sequence;          /* nucleotides; U is read as T */
+    int64_t sequenceLength;
+    const float *eventMean;        /* event_t.mean of the detected events (scrappie_structures.h:8-15), in signal order */
+    int64_t nEvents;
+    int32_t rna;                   /* kmers reversed, as build_kmer_list does for RNA (eventAligner.c:774-790) */
+    int32_t useMom;                /* scale / shift by the method of moments (var = 1); else the three below */
+    double scale, shift, var;
+} sa_event_read_t;
+typedef struct {
+    int64_t nReads;
+    int64_t *pairOffsets;          /* nReads + 1 */
+    int32_t *kmerIdx, *eventIdx;   /* aligned pairs in the reference's order (ascending) */
+    double *scale, *shift, *var;   /* per read, as the alignment used them */
+    double *avgLogEmission;        /* per read QC figures (also for failed reads) */
+    int32_t *maxGap, *spanned, *failed, *nAlignedBeforeQc;
+} sa_event_alignment_t;
+int sa_gpu_event_align_batch(const sa_model_t *m, const sa_event_read_t *reads, int64_t nReads, sa_event_alignment_t **out);
+void sa_event_alignment_free(sa_event_alignment_t *r);
+
 /* ONE read, NO device allocation.  This entry point has no counterpart in the reference: it was added
  * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,
  * harnesses that forbid it).  Same result as sa_gpu_align_batch on that read (the wide band kernel, 512-slot window):

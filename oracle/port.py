@@ -346,3 +346,134 @@ def marginalize_variants(rows, variants, round_like_tsv=True):
             probs[i, vs.index(b)] = s / total                     # (a base outside `variants` raises, as the reference does)
     per_read = probs.sum(0) / max(1, len(positions))
     return np.array(positions, dtype=np.int64), probs, per_read
+
+
+# ---------------------------------------------------------------------------------------------------- SURVEY 8f N4
+def mom_scalings(match_table, kmer_ids, event_means):
+    """estimate_scalings_using_mom (reference impl/eventAligner.c:792-842): shift and scale by the method of moments (the
+    events are C floats, the sums sequential doubles); var = 1"""
+    ev = np.asarray(event_means, np.float32).astype(np.float64)
+    lm = np.asarray(match_table, np.float64).reshape(-1, 5)[np.asarray(kmer_ids), 0]
+    s = 0.0
+    for v in ev:
+        s += v
+    ks = ksq = 0.0
+    for v in lm:
+        ks += v
+        ksq += v * v              # pow(levelMean, 2.0)
+    shift = s / len(ev) - ks / len(lm)
+    sq = 0.0
+    for v in ev:
+        sq += (v - shift) * (v - shift)
+    scale = (sq / len(ev)) / (ksq / len(lm))
+    return scale, shift, 1.0
+
+
+def event_align(match_table, kmer_ids, event_means, scale, shift, var):
+    """adaptive_banded_simple_event_align2 (reference impl/eventAligner.c:899-1235): Suzuki-Kasahara adaptive band of 100
+    cells over (event, kmer), Viterbi with step / stay / skip, trim states, backtrack and the reference's QC.  One numpy
+    pass per band.  Returns (aligned (kmer, event) pairs int64 [n, 2] — empty when QC fails —, dict of QC figures)."""
+    tbl = np.asarray(match_table, np.float64).reshape(-1, 5)
+    kid = np.asarray(kmer_ids, np.int64)
+    ev = np.asarray(event_means, np.float32).astype(np.float64)
+    n_kmers, n_events = len(kid), len(ev)
+    mu, sigma = tbl[kid, 0], tbl[kid, 1]
+    c1 = -0.91893853320467267 - np.log(sigma)            # log_inv_sqrt_2pi - l_sigma (stateMachine.c:296-306)
+    log_inv_var = np.log(1 / var)
+
+    def emission(e_idx, k_idx):                          # ..._MeanOnly (stateMachine.c:557-605), operation order kept
+        m, s = mu[k_idx], sigma[k_idx]
+        x = (ev[e_idx] + var * m - scale * m - shift) / var
+        a = (x - m) / s
+        return log_inv_var + (c1[k_idx] + (-0.5 * a * a))
+
+    FROM_D, FROM_U, FROM_L = 0, 1, 2
+    bw, half = 100, 50
+    events_per_kmer = n_events / n_kmers
+    p_stay = 1 - (1 / (events_per_kmer + 1))
+    lp_skip = np.log(1e-10)
+    lp_stay = np.log(p_stay)
+    lp_step = np.log(1.0 - np.exp(lp_skip) - np.exp(lp_stay))
+    lp_trim = np.log(0.01)
+    n_bands = (n_events + 1) + (n_kmers + 1)
+    bands = np.full((n_bands, bw), -np.inf)
+    trace = np.zeros((n_bands, bw), np.uint8)
+    ll_e = np.zeros(n_bands, np.int64)
+    ll_k = np.zeros(n_bands, np.int64)
+    ll_e[0], ll_k[0] = half - 1, -1 - half
+    ll_e[1], ll_k[1] = ll_e[0] + 1, ll_k[0]
+    bands[0, -1 - ll_k[0]] = 0.0
+    o = ll_e[1] - 0
+    bands[1, o] = lp_trim
+    trace[1, o] = FROM_U
+    off = np.arange(bw)
+    f32 = lambda a: np.asarray(a, np.float64).astype(np.float32).astype(np.float64)
+    for b in range(2, n_bands):
+        ll, ur = bands[b - 1, 0], bands[b - 1, bw - 1]
+        if ll == -np.inf and ur == -np.inf:
+            right = b % 2 == 1
+        else:
+            right = ll < ur
+        ll_e[b], ll_k[b] = (ll_e[b - 1], ll_k[b - 1] + 1) if right else (ll_e[b - 1] + 1, ll_k[b - 1])
+        t_off = -1 - ll_k[b]
+        if 0 <= t_off < bw:
+            e_idx = ll_e[b] - t_off
+            if 0 <= e_idx < n_events:
+                bands[b, t_off] = lp_trim * (e_idx + 1)
+                trace[b, t_off] = FROM_U
+            else:
+                bands[b, t_off] = -np.inf
+        lo = max(0 - ll_k[b], ll_e[b] - (n_events - 1), 0)
+        hi = min(n_kmers - ll_k[b], ll_e[b] - (-1), bw)
+        if hi <= lo:
+            continue
+        o = off[lo:hi]
+        e_idx, k_idx = ll_e[b] - o, ll_k[b] + o
+        o_up = ll_e[b - 1] - (e_idx - 1)
+        o_left = (k_idx - 1) - ll_k[b - 1]
+        o_diag = (k_idx - 1) - ll_k[b - 2]
+
+        def fetch(row, oo):
+            ok = (oo >= 0) & (oo < bw)
+            return np.where(ok, f32(bands[row, np.clip(oo, 0, bw - 1)]), -np.inf)       # float up / left / diag
+        up, left, diag = fetch(b - 1, o_up), fetch(b - 1, o_left), fetch(b - 2, o_diag)
+        lp = emission(e_idx, k_idx)
+        with np.errstate(invalid="ignore"):
+            s_d, s_u, s_l = f32(diag + lp_step + lp), f32(up + lp_stay + lp), f32(left + lp_skip)
+        mx = s_d.copy()
+        fr = np.full(len(o), FROM_D, np.uint8)
+        mx = np.where(s_u > mx, s_u, mx)
+        fr = np.where(mx == s_u, FROM_U, fr)
+        mx = np.where(s_l > mx, s_l, mx)
+        fr = np.where(mx == s_l, FROM_L, fr)
+        bands[b, lo:hi] = mx
+        trace[b, lo:hi] = fr
+    # backtrack
+    k_cur = n_kmers - 1
+    best, e_cur = np.float32(-np.inf), 0
+    for e_idx in range(n_events):
+        b = (e_idx + 1) + (k_cur + 1)
+        oo = ll_e[b] - e_idx
+        if 0 <= oo < bw:
+            s = np.float32(bands[b, oo] + (n_events - e_idx) * lp_trim)
+            if s > best:
+                best, e_cur = s, e_idx
+    out, sum_em, n_al, gap, max_gap = [], 0.0, 0.0, 0, 0
+    while k_cur >= 0 and e_cur >= 0:
+        out.append((k_cur, e_cur))
+        sum_em += float(emission(np.array([e_cur]), np.array([k_cur]))[0])
+        n_al += 1
+        b = (e_cur + 1) + (k_cur + 1)
+        fr = trace[b, ll_e[b] - e_cur]
+        if fr == FROM_D:
+            k_cur -= 1; e_cur -= 1; gap = 0
+        elif fr == FROM_U:
+            e_cur -= 1; gap = 0
+        else:
+            k_cur -= 1; gap += 1; max_gap = max(gap, max_gap)
+    out.reverse()
+    avg = sum_em / n_al
+    spanned = out[0][0] == 0 and out[-1][0] == n_kmers - 1
+    failed = avg < -5.2 or not spanned or max_gap > 50 or events_per_kmer > 5.0
+    qc = dict(avg_log_emission=avg, spanned=bool(spanned), max_gap=int(max_gap), failed=bool(failed), n_aligned=len(out))
+    return (np.zeros((0, 2), np.int64) if failed else np.array(out, np.int64)), qc

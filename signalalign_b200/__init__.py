@@ -59,6 +59,17 @@ class SaMarginals(C.Structure):
                 ("positions", c_i64p), ("probs", c_f64p), ("perRead", c_f64p)]
 
 
+class SaEventRead(C.Structure):
+    _fields_ = [("sequence", C.c_char_p), ("sequenceLength", C.c_int64), ("eventMean", C.POINTER(C.c_float)), ("nEvents", C.c_int64),
+                ("rna", C.c_int32), ("useMom", C.c_int32), ("scale", C.c_double), ("shift", C.c_double), ("var", C.c_double)]
+
+
+class SaEventAlignment(C.Structure):
+    _fields_ = [("nReads", C.c_int64), ("pairOffsets", c_i64p), ("kmerIdx", c_i32p), ("eventIdx", c_i32p), ("scale", c_f64p),
+                ("shift", c_f64p), ("var", c_f64p), ("avgLogEmission", c_f64p), ("maxGap", c_i32p), ("spanned", c_i32p),
+                ("failed", c_i32p), ("nAlignedBeforeQc", c_i32p)]
+
+
 class SaResult(C.Structure):
     _fields_ = [("nReads", C.c_int64), ("pairOffsets", c_i64p), ("pairs", C.POINTER(SaPair)),
                 ("transitions", c_f64p), ("likelihood", c_f64p), ("assignOffsets", c_i64p),
@@ -78,7 +89,7 @@ EXPORTS = [
     "sa_debug_split_points", "sa_debug_kmer_paths", "sa_last_call_stats", "sa_set_host_threads",
     "sa_gpu_comm_unique_id", "sa_gpu_comm_init", "sa_gpu_comm_from_nccl", "sa_gpu_comm_free",
     "sa_gpu_allreduce_expectations", "sa_gpu_allgather_assignments", "sa_gpu_align_noalloc", "sa_gpu_estimate_params_batch", "sa_gpu_set_precision", "sa_gpu_get_precision",
-    "sa_gpu_marginalize_variants", "sa_marginals_free",
+    "sa_gpu_marginalize_variants", "sa_marginals_free", "sa_gpu_event_align_batch", "sa_event_alignment_free",
 ]
 
 _lib = None
@@ -151,6 +162,9 @@ def lib():
     L.sa_gpu_marginalize_variants.argtypes = [C.c_void_p, C.POINTER(SaVariantRead), C.c_int64, C.c_char_p, C.c_int,
                                               C.POINTER(C.POINTER(SaMarginals))]
     L.sa_marginals_free.restype = None
+    L.sa_gpu_event_align_batch.argtypes = [C.c_void_p, C.POINTER(SaEventRead), C.c_int64, C.POINTER(C.POINTER(SaEventAlignment))]
+    L.sa_event_alignment_free.restype = None
+    L.sa_event_alignment_free.argtypes = [C.POINTER(SaEventAlignment)]
     L.sa_marginals_free.argtypes = [C.POINTER(SaMarginals)]
     L.sa_gpu_comm_unique_id.argtypes = [C.c_void_p]
     L.sa_gpu_comm_init.argtypes = [C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_void_p)]
@@ -458,6 +472,39 @@ def marginalize_variants(model, reads, variants, round_like_tsv=True):
         return r.variants.decode(), res
     finally:
         lib().sa_marginals_free(out)
+
+
+def event_align_batch(model, reads):
+    """Adaptive banded event -> kmer alignment (sa_gpu_event_align_batch).
+
+    reads = [dict(sequence=str, event_mean=float32 array, rna=False, scalings=None | (scale, shift, var))]; scalings None =
+    the reference's method of moments.  Returns a list of dicts: pairs int32 [n, 2] = (kmer, event), scale, shift, var,
+    avg_log_emission, max_gap, spanned, failed, n_aligned_before_qc."""
+    keep, arr = [], (SaEventRead * max(1, len(reads)))()
+    for i, r in enumerate(reads):
+        sq = r["sequence"].encode() if isinstance(r["sequence"], str) else bytes(r["sequence"])
+        ev = np.ascontiguousarray(r["event_mean"], np.float32)
+        keep.append((sq, ev))
+        sc = r.get("scalings")
+        arr[i] = SaEventRead(sq, len(sq), ev.ctypes.data_as(C.POINTER(C.c_float)), ev.shape[0], int(bool(r.get("rna"))),
+                             int(sc is None), *(sc if sc is not None else (1.0, 0.0, 1.0)))
+    out = C.POINTER(SaEventAlignment)()
+    _check(lib().sa_gpu_event_align_batch(model.h, arr, len(reads), C.byref(out)))
+    try:
+        r = out.contents
+        n = len(reads)
+        offs = np.ctypeslib.as_array(r.pairOffsets, (n + 1,)).copy()
+        tot = int(offs[-1])
+        km = np.ctypeslib.as_array(r.kmerIdx, (max(1, tot),))[:tot].copy()
+        ei = np.ctypeslib.as_array(r.eventIdx, (max(1, tot),))[:tot].copy()
+        col = lambda p, t=np.float64: np.ctypeslib.as_array(p, (max(1, n),))[:n].copy()
+        sc, sh, va, av = col(r.scale), col(r.shift), col(r.var), col(r.avgLogEmission)
+        mg, sp, fl, na = col(r.maxGap), col(r.spanned), col(r.failed), col(r.nAlignedBeforeQc)
+        return [dict(pairs=np.stack([km[offs[i]:offs[i + 1]], ei[offs[i]:offs[i + 1]]], 1), scale=float(sc[i]), shift=float(sh[i]),
+                     var=float(va[i]), avg_log_emission=float(av[i]), max_gap=int(mg[i]), spanned=bool(sp[i]), failed=bool(fl[i]),
+                     n_aligned_before_qc=int(na[i])) for i in range(n)]
+    finally:
+        lib().sa_event_alignment_free(out)
 
 
 def expectations_batch(model, reads, params=None, ambig=None):

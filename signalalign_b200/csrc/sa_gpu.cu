@@ -20,6 +20,7 @@
 #include "sa_wide32.cuh"
 #include "sa_estimate.cuh"
 #include "sa_variants.cuh"
+#include "sa_eventalign.cuh"
 
 #define CK(call)                                                                                   \
     do {                                                                                           \
@@ -519,12 +520,6 @@ static bool wideGlobalRings(int c) {
     SA_W64_CLASSES(X)
 #undef X
     return false;
-}
-static int wideThreads(int c) {                       // a template argument of the kernel, not a launch-time choice
-#define X(C, GR, NSW, NT, MB) if (c == C) return NT;
-    SA_W64_CLASSES(X)
-#undef X
-    return 0;
 }
 // fold terms in global memory: with the rings there, and from the 1024-slot window on (two CTAs of 512 threads per SM
 // instead of one: 25.0 -> 26.8 GCUPS on the contract pattern).  SA_WIDE_FOLDG_FROM=<slots> moves the limit (experiments).
@@ -2043,6 +2038,171 @@ extern "C" int sa_gpu_marginalize_variants(const sa_model_t *m, const sa_variant
         }
         if (nPos[(size_t) i] > 0)
             for (int v = 0; v < V; v++) res->perRead[i * V + v] /= (double) nPos[(size_t) i];
+    }
+    *out = res;
+    return SA_OK;
+}
+
+// ================================================================================================ SURVEY 8f N4
+// sa_gpu_event_align_batch: adaptive banded event -> kmer alignment (sa_eventalign.cuh)
+extern "C" void sa_event_alignment_free(sa_event_alignment_t *r) {
+    if (!r) return;
+    free(r->pairOffsets); free(r->kmerIdx); free(r->eventIdx); free(r->scale); free(r->shift); free(r->var);
+    free(r->avgLogEmission); free(r->maxGap); free(r->spanned); free(r->failed); free(r->nAlignedBeforeQc);
+    free(r);
+}
+extern "C" int sa_gpu_event_align_batch(const sa_model_t *m, const sa_event_read_t *reads, int64_t n, sa_event_alignment_t **out) {
+    *out = nullptr;
+    if (sa_gpu_device_count() == 0) {
+        sa_set_error("sa_gpu_event_align_batch: no CUDA device available; libsagpu has no CPU fallback");
+        return SA_ERR_CUDA;
+    }
+    if (m->match.size() != (size_t) m->K * 5) {
+        sa_set_error("sa_gpu_event_align_batch: the model has no Gaussian match table");
+        return SA_ERR_INPUT;
+    }
+    int rc = uploadModel(m);
+    if (rc) return rc;
+    if (!m->dev->raw) {
+        CK(cudaMalloc(&m->dev->raw, sizeof(double) * m->match.size()));
+        CK(cudaMemcpy(m->dev->raw, m->match.data(), sizeof(double) * m->match.size(), cudaMemcpyHostToDevice));
+    }
+    if ((rc = poolInit())) return rc;
+    const int k = m->k;
+    std::vector<EaRead> er((size_t) std::max<int64_t>(1, n));
+    int64_t kTot = 0, eTot = 0, bTot = 0, pTot = 0;
+    for (int64_t i = 0; i < n; i++) {
+        const sa_event_read_t &R = reads[i];
+        const int64_t nK = R.sequenceLength - k + 1;
+        if (nK < 1 || R.nEvents < 1 || nK > 0x3fffffff || R.nEvents > 0x3fffffff || !R.sequence || !R.eventMean) {
+            sa_set_error("sa_gpu_event_align_batch: read %lld: needs at least one kmer and one event", (long long) i);
+            return SA_ERR_INPUT;
+        }
+        EaRead &q = er[(size_t) i];
+        q.kmerOff = kTot; q.evOff = eTot; q.bandOff = bTot; q.traceOff = bTot * kEaBand; q.pairOff = 2 * pTot;
+        q.nKmers = (int32_t) nK; q.nEvents = (int32_t) R.nEvents;
+        kTot += nK; eTot += R.nEvents; bTot += nK + R.nEvents + 2; pTot += nK + R.nEvents;
+    }
+    PinVec<int32_t> hKid, hPairs;
+    PinVec<float> hEv;
+    PinVec<double> hQc;
+    if (!hKid.resize((size_t) std::max<int64_t>(1, kTot)) || !hEv.resize((size_t) std::max<int64_t>(1, eTot)) ||
+        !hPairs.resize((size_t) std::max<int64_t>(1, 2 * pTot)) || !hQc.resize((size_t) std::max<int64_t>(1, n) * 4)) {
+        sa_set_error("sa_gpu_event_align_batch: cannot allocate pinned staging memory");
+        return SA_ERR_CUDA;
+    }
+    int32_t code[256];
+    for (int c = 0; c < 256; c++) {
+        const size_t j = m->alphabet.find((char) c);
+        code[c] = (c != 0 && j != std::string::npos) ? (int32_t) j : -1;
+    }
+    code[(unsigned char) 'U'] = code[(unsigned char) 'T'];        // build_kmer_list: stString_replace(sequence, "U", "T")
+    bool bad = false;
+#pragma omp parallel for schedule(dynamic, 4) reduction(|| : bad)
+    for (int64_t i = 0; i < n; i++) {
+        const sa_event_read_t &R = reads[i];
+        EaRead &q = er[(size_t) i];
+        for (int64_t x = 0; x < q.nKmers; x++) {
+            int64_t id = 0;
+            for (int j = 0; j < k; j++) {
+                const int32_t c = code[(unsigned char) R.sequence[R.rna ? x + k - 1 - j : x + j]];     // RNA: the kmer reversed
+                bad = bad || c < 0;
+                id = id * m->A + (c < 0 ? 0 : c);
+            }
+            hKid[(size_t) (q.kmerOff + x)] = (int32_t) id;
+        }
+        memcpy(hEv.data() + q.evOff, R.eventMean, sizeof(float) * (size_t) R.nEvents);
+        if (R.useMom) {            // estimate_scalings_using_mom (impl/eventAligner.c:792-842): sequential double sums
+            double evSum = 0.0, kSum = 0.0, kSq = 0.0, evSq = 0.0;
+            for (int64_t y = 0; y < R.nEvents; y++) evSum += (double) R.eventMean[y];
+            for (int64_t x = 0; x < q.nKmers; x++) {
+                const double lm = m->match[(size_t) hKid[(size_t) (q.kmerOff + x)] * 5];
+                kSum += lm;
+                kSq += lm * lm;
+            }
+            const double shift = evSum / (double) R.nEvents - kSum / (double) q.nKmers;
+            for (int64_t y = 0; y < R.nEvents; y++) {
+                const double dlt = (double) R.eventMean[y] - shift;
+                evSq += dlt * dlt;
+            }
+            q.scale = (evSq / (double) R.nEvents) / (kSq / (double) q.nKmers);
+            q.shift = shift;
+            q.var = 1.0;
+        } else {
+            q.scale = R.scale; q.shift = R.shift; q.var = R.var;
+        }
+        q.logInvVar = log(1 / q.var);
+        q.eventsPerKmer = (double) R.nEvents / (double) q.nKmers;
+        const double pStay = 1 - (1 / (q.eventsPerKmer + 1));
+        q.lpSkip = log(1e-10);
+        q.lpStay = log(pStay);
+        q.lpStep = log(1.0 - exp(q.lpSkip) - exp(q.lpStay));
+        q.lpTrim = log(0.01);
+    }
+    if (bad) {
+        sa_set_error("sa_gpu_event_align_batch: a sequence contains a character outside the model's alphabet");
+        return SA_ERR_INPUT;
+    }
+    std::vector<double> c1((size_t) m->K);
+    for (int64_t j = 0; j < m->K; j++) c1[(size_t) j] = -0.91893853320467267 - log(m->match[(size_t) j * 5 + 1]);
+    sa_event_alignment_t *res = (sa_event_alignment_t *) calloc(1, sizeof(sa_event_alignment_t));
+    const size_t nn = (size_t) std::max<int64_t>(1, n);
+    res->nReads = n;
+    res->pairOffsets = (int64_t *) calloc((size_t) n + 1, sizeof(int64_t));
+    res->scale = (double *) calloc(nn, sizeof(double)); res->shift = (double *) calloc(nn, sizeof(double));
+    res->var = (double *) calloc(nn, sizeof(double)); res->avgLogEmission = (double *) calloc(nn, sizeof(double));
+    res->maxGap = (int32_t *) calloc(nn, sizeof(int32_t)); res->spanned = (int32_t *) calloc(nn, sizeof(int32_t));
+    res->failed = (int32_t *) calloc(nn, sizeof(int32_t)); res->nAlignedBeforeQc = (int32_t *) calloc(nn, sizeof(int32_t));
+    if (n > 0) {
+        cudaStream_t st;
+        CK(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
+        struct StreamGuard { cudaStream_t s; ~StreamGuard() { cudaStreamSynchronize(s); cudaStreamDestroy(s); } } guard{st};
+        DevBuf<EaRead> dR;
+        DevBuf<int32_t> dKid, dLlE, dLlK, dPairs;
+        DevBuf<float> dEv;
+        DevBuf<double> dC1, dLast, dQc;
+        DevBuf<uint8_t> dTrace;
+        int64_t bytes = 0;
+        if ((rc = dR.upload(er, st, &bytes)) || (rc = dKid.upload(hKid, st, &bytes)) || (rc = dEv.upload(hEv, st, &bytes)) ||
+            (rc = dC1.upload(c1, st, &bytes)) || (rc = dLlE.alloc((size_t) bTot, st)) || (rc = dLlK.alloc((size_t) bTot, st)) ||
+            (rc = dTrace.alloc((size_t) bTot * kEaBand, st)) || (rc = dLast.alloc((size_t) eTot, st)) ||
+            (rc = dPairs.alloc((size_t) 2 * pTot, st)) || (rc = dQc.alloc((size_t) n * 4, st))) {
+            sa_event_alignment_free(res);
+            return rc;
+        }
+        EaParams P;
+        memset(&P, 0, sizeof(P));
+        P.reads = dR.p; P.kmerId = dKid.p; P.ev = dEv.p; P.table = m->dev->raw; P.c1 = dC1.p; P.trace = dTrace.p;
+        P.llE = dLlE.p; P.llK = dLlK.p; P.lastCol = dLast.p; P.pairs = dPairs.p; P.qc = dQc.p;
+        sa_event_align_kernel<<<(unsigned) n, 128, 0, st>>>(P);
+        CK(cudaGetLastError());
+        CK(cudaMemcpyAsync(hPairs.data(), dPairs.p, sizeof(int32_t) * 2 * pTot, cudaMemcpyDeviceToHost, st));
+        CK(cudaMemcpyAsync(hQc.data(), dQc.p, sizeof(double) * n * 4, cudaMemcpyDeviceToHost, st));
+        CK(cudaStreamSynchronize(st));
+    }
+    for (int64_t i = 0; i < n; i++) {
+        const EaRead &q = er[(size_t) i];
+        const double *qc = hQc.data() + i * 4;
+        const int64_t na = (int64_t) qc[0];
+        const double avg = qc[1] / qc[0];               // sum_emission / n_aligned_events (:1199)
+        res->scale[i] = q.scale; res->shift[i] = q.shift; res->var[i] = q.var;
+        res->avgLogEmission[i] = avg; res->maxGap[i] = (int32_t) qc[2]; res->spanned[i] = qc[3] != 0.0;
+        res->nAlignedBeforeQc[i] = (int32_t) na;
+        res->failed[i] = (avg < -5.2 || !(qc[3] != 0.0) || qc[2] > 50 || q.eventsPerKmer > 5.0) ? 1 : 0;      // :1205
+        res->pairOffsets[i + 1] = res->pairOffsets[i] + (res->failed[i] ? 0 : na);
+    }
+    const size_t tot = (size_t) std::max<int64_t>(1, res->pairOffsets[n]);
+    res->kmerIdx = (int32_t *) calloc(tot, sizeof(int32_t));
+    res->eventIdx = (int32_t *) calloc(tot, sizeof(int32_t));
+    for (int64_t i = 0; i < n; i++) {
+        if (res->failed[i]) continue;
+        const EaRead &q = er[(size_t) i];
+        const int64_t na = res->nAlignedBeforeQc[i], cap = (int64_t) q.nKmers + q.nEvents;
+        const int32_t *pp = hPairs.data() + q.pairOff + 2 * (cap - na);
+        for (int64_t j = 0; j < na; j++) {
+            res->kmerIdx[res->pairOffsets[i] + j] = pp[2 * j];
+            res->eventIdx[res->pairOffsets[i] + j] = pp[2 * j + 1];
+        }
     }
     *out = res;
     return SA_OK;
