@@ -15,7 +15,8 @@ ref_codes = rng.integers(0, 4, 2_000_000).astype(np.int64)
 reads = []
 for _ in range(n):
     r = synth.make_read(rng, ref_codes, table, "ACGT", 6)
-    reads.append(dict(sequence=r["target"], event_mean=r["events"][:, 0].astype(np.float32), rna=False, scalings=None))
+    reads.append(dict(sequence=r["target"], event_mean=r["events"][:, 0].astype(np.float32), rna=False,
+                      scalings=(r["scale"], r["shift"], r["var"])))
 ev = sum(len(r["event_mean"]) for r in reads)
 cells = sum((len(r["event_mean"]) + len(r["sequence"]) - 4) * 100 for r in reads)
 sa.event_align_batch(model, reads[:8])
