@@ -2,7 +2,7 @@
 # round-2 evidence run: bench lines (no profiler), then the ncu launch list of the bench command, DRAM bytes per cell in
 # both precisions, and one --set full capture of the dominant kernel in each precision
 mkdir -p gpurun_out
-T=${1:-r2x}
+T=${1:-evidence}
 timeout 900 python bench.py --impl reference --steps 2 --warmup 1 > gpurun_out/${T}_bench_reference.json 2> gpurun_out/${T}_bench_reference.err
 timeout 900 python bench.py --workload config4 --steps 3 --warmup 3 > gpurun_out/${T}_bench_config4.json 2> gpurun_out/${T}_bench_config4.err
 timeout 1200 python bench.py --workload config5 --steps 2 --warmup 1 > gpurun_out/${T}_bench_config5.json 2> gpurun_out/${T}_bench_config5.err

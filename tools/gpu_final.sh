@@ -1,6 +1,6 @@
 #!/bin/bash
 mkdir -p gpurun_out
-T=${1:-r3c}
+T=${1:-final}
 timeout 2400 python -m pytest tests -m gpu -x -q 2>&1 | tail -8 > gpurun_out/${T}_pytest.txt; tail -4 gpurun_out/${T}_pytest.txt
 timeout 300 python -c "import __graft_entry__ as g; g.smoke()" 2>&1 | tail -2
 timeout 600 python tools/ea_quick.py 1184 2>&1 | tail -1 | tee gpurun_out/${T}_ea_quick.txt

@@ -1,6 +1,6 @@
 #!/bin/bash
 mkdir -p gpurun_out
-T=${1:-r2n2}
+T=${1:-n2}
 nproc
 timeout 1500 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29517 bench.py --gpus 2 --steps 3 --warmup 3 > gpurun_out/${T}_bench_n2.json 2> gpurun_out/${T}_bench_n2.err; tail -c 300 gpurun_out/${T}_bench_n2.err
 python - <<PY
