@@ -84,7 +84,7 @@ def parse():
                     help="strong scaling: ONE read set of --reads reads (same seed on every rank) split across the ranks by "
                          "signalalign_b200.shard.partition_lpt (longest-processing-time-first on estimated band cells); the "
                          "default is weak scaling (every rank its own --reads reads)")
-    ap.add_argument("--workload", default="config3", choices=["config3", "config4", "config5"],
+    ap.add_argument("--workload", default="config3", choices=["config2", "config3", "config4", "config5"],
                     help="config3 (default, BASELINE's headline): alignment of ~10k-event reads, 6-mer Gaussian table; config4: "
                          "the expectations pass (getExpectationsUsingAnchors) on the same reads; config5: 5-mer table, HDP "
                          "emission (synthetic spline tables), log-normal read lengths (median ~20k events, tail to 400k)")
@@ -260,6 +260,33 @@ def main():
         pp = 0.7 * np.exp(-0.5 * ((grid[None, :] - mu[:, None]) / 2.0) ** 2) / (2.0 * np.sqrt(2 * np.pi)) + \
             0.3 * np.exp(-0.5 * ((grid[None, :] - mu[:, None] - 3.0) / 4.0) ** 2) / (4.0 * np.sqrt(2 * np.pi))
         model.set_hdp(grid, np.arange(table.shape[0], dtype=np.int32), pp, np.gradient(pp, grid, axis=1))
+        a.no_cpu = a.no_dense = a.no_expectations = True
+    elif a.workload == "config2":
+        # cytosine-variant calling: ACEGT 6-mer table (E = 5mC: the C kmer's level shifted by 1.5 pA per E), config 3's reads,
+        # 10 % of the reference's C replaced by the two-way ambiguity code P (C/E, create_ambig_bases
+        # impl/pairwiseAligner.c:32-65) -> multi-path cells (general kernel)
+        if a.reads == 4736:
+            a.reads = 592
+        reads_d, t4 = synth.make_batch(a.reads, seed=a.seed + 2 + 1000 * rank, **GEN)
+        K5 = 5 ** 6
+        digits = np.zeros((K5, 6), np.int64)
+        v = np.arange(K5)
+        for j in range(5, -1, -1):
+            digits[:, j] = v % 5
+            v //= 5
+        to4 = np.array([0, 1, 1, 2, 3])
+        twin = np.zeros(K5, np.int64)
+        for j in range(6):
+            twin = twin * 4 + to4[digits[:, j]]
+        table = t4[twin].copy()
+        table[:, 0] += 1.5 * (digits == 2).sum(1)
+        model = sa.Model.from_tables("ACEGT", 6, trans, table)
+        rng2 = np.random.default_rng(a.seed + 11 + rank)
+        for r in reads_d:
+            t = np.frombuffer(r["target"].encode(), np.uint8).copy()
+            c = np.nonzero(t == ord("C"))[0]
+            t[c[rng2.random(len(c)) < 0.1]] = ord("P")
+            r["target"] = t.tobytes().decode()
         a.no_cpu = a.no_dense = a.no_expectations = True
     else:
         reads_d, table = synth.make_batch(a.reads, seed=a.seed + (0 if a.strong else 1000 * rank), **GEN)
@@ -482,7 +509,9 @@ def main():
             "higher_is_better": True, "scaling": "strong" if a.strong else "weak", "vs_baseline": None,
             "dtype": "f32" if prec == "fp32" else "f64", "data": "synthetic",
             "config": {"strong_scaling_shards": shard_info,
-                       "workload": {"config3": WORKLOAD if a.anchors == ANCHOR_PATTERN else "config3-synthetic, anchor pattern " + a.anchors,
+                       "workload": {"config2": "config2-synthetic: ACEGT 6-mer table, config 3's reads with 10 % of the reference's C "
+                                               "flagged as the C/E ambiguity code P (multi-path cells, general kernel)",
+                                    "config3": WORKLOAD if a.anchors == ANCHOR_PATTERN else "config3-synthetic, anchor pattern " + a.anchors,
                                     "config4": "config4-synthetic: expectations pass (getExpectationsUsingAnchors) over config 3's reads",
                                     "config5": "config5-synthetic: ACGT 5-mer table, HDP emission (1024 rows x 1200 grid points), "
                                                "log-normal read lengths (median ~20k events, clipped at 400k), -x 100"}[a.workload],

@@ -284,39 +284,42 @@ struct WideK {
         return log(I.invVar * dens);
     }
     // match and gap-Y emission of cell (x, y) from the rings
+    // ring read: a shared-memory load, or (rings in global memory) ld.global.ca said explicitly — the pinned base pointer is
+    // opaque to the compiler, which would otherwise emit generic loads
+    static __device__ __forceinline__ double ldR(const double *p) { return GR ? __ldca(p) : *p; }
     static __device__ __forceinline__ void emissions(const FParams &P, const FItem &I, const Sm &S, int32_t x, int32_t y,
                                                      double &eM, double &eY) {
         const double *c = S.cst + (x & S.mask) * 5;
-        const double ev = S.evs[y & S.mask];
+        const double ev = ldR(S.evs + (y & S.mask));
         if (HD) {
-            const long long row = __double_as_longlong(c[2]);
-            const double q = (((ev + c[0]) - c[1]) - I.shift) * I.invVar;
+            const long long row = __double_as_longlong(ldR(c + 2));
+            const double q = (((ev + ldR(c)) - ldR(c + 1)) - I.shift) * I.invVar;
             double e = SA_NEG_INF;
             if (row >= 0) e = hdpLogDensity(P, I, row, q);
             eM = e; eY = e;
             return;
         }
-        const double d0 = ev - c[0];
-        const double aM = d0 * c[1], aY = d0 * c[3];
-        eM = fma(-0.5 * aM, aM, c[2]);
-        eY = fma(-0.5 * aY, aY, c[4]);
+        const double d0 = ev - ldR(c);
+        const double aM = d0 * ldR(c + 1), aY = d0 * ldR(c + 3);
+        eM = fma(-0.5 * aM, aM, ldR(c + 2));
+        eY = fma(-0.5 * aY, aY, ldR(c + 4));
     }
     static __device__ __forceinline__ double emissionM(const FParams &P, const FItem &I, const Sm &S, int32_t x, int32_t y) {
         const double *c = S.cst + (x & S.mask) * 5;
-        const double ev = S.evs[y & S.mask];
+        const double ev = ldR(S.evs + (y & S.mask));
         if (HD) {
-            const long long row = __double_as_longlong(c[2]);
-            const double q = (((ev + c[0]) - c[1]) - I.shift) * I.invVar;
+            const long long row = __double_as_longlong(ldR(c + 2));
+            const double q = (((ev + ldR(c)) - ldR(c + 1)) - I.shift) * I.invVar;
             return row >= 0 ? hdpLogDensity(P, I, row, q) : SA_NEG_INF;
         }
-        const double aM = (ev - c[0]) * c[1];
-        return fma(-0.5 * aM, aM, c[2]);
+        const double aM = (ev - ldR(c)) * ldR(c + 1);
+        return fma(-0.5 * aM, aM, ldR(c + 2));
     }
     static __device__ __forceinline__ double emissionY(const FParams &P, const FItem &I, const Sm &S, int32_t x, int32_t y) {
         if (HD) return emissionM(P, I, S, x, y);
         const double *c = S.cst + (x & S.mask) * 5;
-        const double aY = (S.evs[y & S.mask] - c[0]) * c[3];
-        return fma(-0.5 * aY, aY, c[4]);
+        const double aY = (ldR(S.evs + (y & S.mask)) - ldR(c)) * ldR(c + 3);
+        return fma(-0.5 * aY, aY, ldR(c + 4));
     }
 
     // ------------------------------------------------------------------------------------------ state helpers
