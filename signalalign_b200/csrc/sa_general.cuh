@@ -37,6 +37,8 @@ struct GParams {
     int32_t *counter;
     const int32_t *pathOff;
     const int32_t *pathKmer;
+    const int32_t *pcCol;    // column of every path-cell (same indexing as pathKmer): spares the search for it (sa_mp_kernel)
+    int32_t mpCap;           // sa_mp_kernel: path-cells per diagonal its shared-memory working set holds (0: it stays in global memory)
     const double *evMean, *evNoise, *evLogNoise;
     const int32_t *bandL, *bandW;
     const int64_t *bandOff;  // prefix of path-cells over the diagonals of the item
@@ -73,10 +75,13 @@ struct GCtx {
     const GItem *I;
     const int32_t *pathOff;   // item-local
     const int32_t *pathKmer;
+    const int32_t *pcCol;     // item-local (sa_mp_kernel)
     const int32_t *bandL, *bandW;
     const int64_t *bandOff;
     double *F, *B, *vals;
+    double *E;                // sa_mp_kernel: match / gap-Y emission of every path-cell of the forward ring (2 per path-cell)
     int64_t ringMask;
+    int64_t bStride;          // path-cells per diagonal buffer of B (maxDiagPC, or sa_mp_kernel's shared-memory capacity)
 };
 
 // (A non-inlined single copy of this function was tried against the instruction-cache stalls ncu shows: 5208 instead of
@@ -167,7 +172,7 @@ __device__ __forceinline__ double *g_F(const GCtx &c, const GDiag &g, int64_t pc
     return c.F + ((g.off + pc) & c.ringMask) * 3;
 }
 __device__ __forceinline__ double *g_B(const GCtx &c, int64_t d, int64_t pc) {
-    return c.B + ((d % 3) * c.P->maxDiagPC + pc) * 3;
+    return c.B + ((d % 3) * c.bStride + pc) * 3;
 }
 
 // Work is dealt out per PATH-CELL, not per cell: thread j of a diagonal takes the j-th (cell, path) pair, so a warp that
@@ -576,6 +581,7 @@ __global__ void SA_GEN_BOUNDS sa_general_kernel(const GParams P) {
         c.B = c.F + P.ringSize * 3;
         c.vals = c.B + 3 * P.maxDiagPC * 3;
         c.ringMask = P.ringSize - 1;
+        c.bStride = P.maxDiagPC;
         const int64_t nDiag = (int64_t) I.lX + I.lY;
         int64_t nPairs = 0, nAssign = 0;
         double acc9[9];
@@ -663,5 +669,256 @@ __global__ void SA_GEN_BOUNDS sa_general_kernel(const GParams P) {
         } else if (threadIdx.x == 0) {
             P.pairCount[it] = nPairs;
         }
+    }
+}
+
+
+// =====================================================================================================================
+// sa_mp_kernel — the alignment pass of the general kernel with its WORKING SET out of global memory.
+//
+// Same inputs, same arithmetic, same order of every logAdd as sa_general_kernel<false> (the results are byte-identical);
+// what changes is where the sweep's neighbours live and how a thread finds its cell:
+//   * the three most recent diagonals of the sweep in flight (f(d-1), f(d-2) and the one being written; b(d+1), b(d+2)
+//     and the one being written during a traceback) are ONE set of three buffers indexed by path-cell within the
+//     diagonal — in shared memory when the widest diagonal of the batch fits (GParams.mpCap), else in the per-CTA
+//     global slab the general kernel uses for its backward ring.  The forward ring in global memory is still written on
+//     every diagonal (the traceback reads f from it) but no longer read by the forward sweep; after a traceback the two
+//     newest forward diagonals are copied back from it;
+//   * thread j of a diagonal owns path-cell j; its column comes from the per-path-cell array pcCol (one load) instead of
+//     a bisection over the column prefix; neighbours are located by column (32-bit), not by x - y arithmetic in 64 bits;
+//   * band descriptors of d, d-1, d-2 are carried from step to step instead of being re-read three times per step;
+//   * 256 threads per CTA.
+// Expectations (and the HDP assignment lists) stay on sa_general_kernel<true>.
+struct MDiag {
+    int32_t x0, W, pc0, nPC;     // first column, cells, item-local index of its first path-cell, path-cells
+    int64_t off;                 // path-cells of the item before this diagonal (forward ring position)
+};
+__device__ __forceinline__ MDiag m_diag(const GCtx &c, int64_t d) {
+    MDiag g;
+    const int32_t L = c.bandL[d];
+    g.W = c.bandW[d]; g.off = c.bandOff[d];
+    g.x0 = (int32_t) ((d + L) / 2);
+    g.pc0 = c.pathOff[g.x0];
+    g.nPC = c.pathOff[g.x0 + g.W] - g.pc0;
+    return g;
+}
+__device__ __forceinline__ double *m_W(const GCtx &c, int64_t d, int32_t pc) {      // working set, as g_B addresses it
+    return c.B + ((int64_t) (d % 3) * c.bStride + pc) * 3;
+}
+__device__ __forceinline__ double *m_F(const GCtx &c, const MDiag &g, int32_t pc) {
+    return c.F + ((g.off + pc) & c.ringMask) * 3;
+}
+__device__ __forceinline__ double *m_E(const GCtx &c, const MDiag &g, int32_t pc) {
+    return c.E + ((g.off + pc) & c.ringMask) * 2;
+}
+// path-cell (within diagonal g) of column x's first path, -1 when the column is outside the band of g
+__device__ __forceinline__ int32_t m_colPC(const GCtx &c, const MDiag &g, int32_t x) {
+    return (x >= g.x0 && x < g.x0 + g.W) ? c.pathOff[x] - g.pc0 : -1;
+}
+
+__device__ __forceinline__ void m_forwardDiag(const GCtx &c, int64_t d, const MDiag &g, const MDiag &g1, const MDiag &g2, bool has2) {
+    const double *T = c.P->trans;
+    const bool swX = T[T_GAP_SWITCH_TO_X] > SA_NEG_INF || T[T_GAP_SWITCH_TO_X] != T[T_GAP_SWITCH_TO_X];
+    for (int32_t j = threadIdx.x; j < g.nPC; j += blockDim.x) {
+        const int32_t x = c.pcCol[g.pc0 + j], y = (int32_t) d - x;
+        const int32_t colPC = c.pathOff[x] - g.pc0, nP = c.pathOff[x + 1] - c.pathOff[x];
+        const int32_t pl = m_colPC(c, g1, x - 1), pu = m_colPC(c, g1, x), pm = has2 ? m_colPC(c, g2, x - 1) : -1;
+        const int32_t *kC = c.pathKmer + c.pathOff[x];
+        const int32_t kp = kC[j - colPC];
+        // both emissions of the path-cell, kept beside the forward ring: the backward sweep reads them back instead of
+        // evaluating the two divisions again (same kmer, same event: the same bits)
+        const double eMv = g_emit(c, kp, y, true), eYv = g_emit(c, kp, y, false);
+        {
+            double *e = m_E(c, g, j);
+            e[0] = eMv; e[1] = eYv;
+        }
+        double M = SA_NEG_INF, X = SA_NEG_INF, Y = SA_NEG_INF;
+        if (pl >= 0) {
+            const int32_t nQ = c.pathOff[x] - c.pathOff[x - 1];
+            const int32_t *kQ = c.pathKmer + c.pathOff[x - 1];
+            const double eP = g_gapX(c, kp);
+            for (int32_t q = 0; q < nQ; q++)
+                if (g_legal(c, kQ[q], kp)) {
+                    const double *f = m_W(c, d - 1, pl + q);
+                    X = sa_logAdd(X, __dadd_rn(f[0], __dadd_rn(eP, T[T_GAP_OPEN_X])));
+                    X = sa_logAdd(X, __dadd_rn(f[1], __dadd_rn(eP, T[T_GAP_EXTEND_X])));
+                    if (swX) X = sa_logAdd(X, __dadd_rn(f[2], __dadd_rn(eP, T[T_GAP_SWITCH_TO_X])));
+                }
+        }
+        if (pm >= 0) {
+            const int32_t nQ = c.pathOff[x] - c.pathOff[x - 1];
+            const int32_t *kQ = c.pathKmer + c.pathOff[x - 1];
+            const double eP = eMv;
+            for (int32_t q = 0; q < nQ; q++)
+                if (g_legal(c, kQ[q], kp)) {
+                    const double *f = m_W(c, d - 2, pm + q);
+                    M = sa_logAdd(M, __dadd_rn(f[0], __dadd_rn(eP, T[T_MATCH_CONTINUE])));
+                    M = sa_logAdd(M, __dadd_rn(f[1], __dadd_rn(eP, T[T_MATCH_FROM_GAP_X])));
+                    M = sa_logAdd(M, __dadd_rn(f[2], __dadd_rn(eP, T[T_MATCH_FROM_GAP_Y])));
+                }
+        }
+        if (pu >= 0) {
+            const double eP = eYv;
+            for (int32_t q = 0; q < nP; q++)
+                if (kC[q] == kp) {
+                    const double *f = m_W(c, d - 1, pu + q);
+                    Y = sa_logAdd(Y, __dadd_rn(f[0], __dadd_rn(eP, T[T_GAP_OPEN_Y])));
+                    Y = sa_logAdd(Y, __dadd_rn(f[2], __dadd_rn(eP, T[T_GAP_EXTEND_Y])));
+                }
+        }
+        double *o = m_W(c, d, j);
+        o[0] = M; o[1] = X; o[2] = Y;
+        double *r = m_F(c, g, j);
+        r[0] = M; r[1] = X; r[2] = Y;
+    }
+}
+
+// b(d) by gathering from b(d+1) / b(d+2) in the working set (g_backwardDiag's order)
+__device__ __forceinline__ void m_backwardDiag(const GCtx &c, int64_t d, const MDiag &g, const MDiag &g1, const MDiag &g2,
+                                               bool has1, bool has2) {
+    const double *T = c.P->trans;
+    const bool swX = T[T_GAP_SWITCH_TO_X] > SA_NEG_INF || T[T_GAP_SWITCH_TO_X] != T[T_GAP_SWITCH_TO_X];
+    for (int32_t j = threadIdx.x; j < g.nPC; j += blockDim.x) {
+        const int32_t x = c.pcCol[g.pc0 + j], y = (int32_t) d - x;
+        const int32_t colPC = c.pathOff[x] - g.pc0, nQ = c.pathOff[x + 1] - c.pathOff[x];
+        const int32_t pa = has2 ? m_colPC(c, g2, x + 1) : -1;      // (x+1, y+1): this cell is its "middle"
+        const int32_t pu = has1 ? m_colPC(c, g1, x) : -1;          // (x,   y+1): this cell is its "upper"
+        const int32_t pl = has1 ? m_colPC(c, g1, x + 1) : -1;      // (x+1, y  ): this cell is its "lower"
+        const int32_t *kZ = c.pathKmer + c.pathOff[x];
+        const int32_t kq = kZ[j - colPC];
+        double M = SA_NEG_INF, X = SA_NEG_INF, Y = SA_NEG_INF;
+        if (pa >= 0) {
+            const int32_t nP = c.pathOff[x + 2] - c.pathOff[x + 1];
+            const int32_t *kP = c.pathKmer + c.pathOff[x + 1];
+            for (int32_t p = 0; p < nP; p++)
+                if (g_legal(c, kq, kP[p])) {
+                    const double eP = m_E(c, g2, pa + p)[0];          // g_emit(c, kP[p], y + 1, true), as the forward sweep left it
+                    const double a = m_W(c, d + 2, pa + p)[0];
+                    M = sa_logAdd(M, __dadd_rn(a, __dadd_rn(eP, T[T_MATCH_CONTINUE])));
+                    X = sa_logAdd(X, __dadd_rn(a, __dadd_rn(eP, T[T_MATCH_FROM_GAP_X])));
+                    Y = sa_logAdd(Y, __dadd_rn(a, __dadd_rn(eP, T[T_MATCH_FROM_GAP_Y])));
+                }
+        }
+        if (pu >= 0) {
+            for (int32_t p = 0; p < nQ; p++)
+                if (kZ[p] == kq) {
+                    const double eP = m_E(c, g1, pu + p)[1];          // g_emit(c, kq, y + 1, false): same kmer, same event
+                    const double a = m_W(c, d + 1, pu + p)[2];
+                    M = sa_logAdd(M, __dadd_rn(a, __dadd_rn(eP, T[T_GAP_OPEN_Y])));
+                    Y = sa_logAdd(Y, __dadd_rn(a, __dadd_rn(eP, T[T_GAP_EXTEND_Y])));
+                }
+        }
+        if (pl >= 0) {
+            const int32_t nP = c.pathOff[x + 2] - c.pathOff[x + 1];
+            const int32_t *kP = c.pathKmer + c.pathOff[x + 1];
+            for (int32_t p = 0; p < nP; p++)
+                if (g_legal(c, kq, kP[p])) {
+                    const double eP = g_gapX(c, kP[p]);
+                    const double a = m_W(c, d + 1, pl + p)[1];
+                    M = sa_logAdd(M, __dadd_rn(a, __dadd_rn(eP, T[T_GAP_OPEN_X])));
+                    X = sa_logAdd(X, __dadd_rn(a, __dadd_rn(eP, T[T_GAP_EXTEND_X])));
+                    if (swX) Y = sa_logAdd(Y, __dadd_rn(a, __dadd_rn(eP, T[T_GAP_SWITCH_TO_X])));
+                }
+        }
+        double *o = m_W(c, d, j);
+        o[0] = M; o[1] = X; o[2] = Y;
+    }
+}
+
+// Launch: 256 threads, dynamic shared memory = 3 * mpCap * 3 doubles (0 when the working set stays in global memory)
+__global__ void __launch_bounds__(256) sa_mp_kernel(const GParams P) {
+    extern __shared__ __align__(16) double sa_mpsm[];
+    __shared__ int sItem;
+    __shared__ double sTotal;
+    __shared__ int sWarp[8];
+    sa_logAdd_init();
+    for (;;) {
+        __syncthreads();
+        if (threadIdx.x == 0) sItem = atomicAdd(P.counter, 1);
+        __syncthreads();
+        if (sItem >= P.nItems) break;
+        const int it = P.order[sItem];
+        const GItem &I = P.items[it];
+        GCtx c;
+        c.P = &P; c.I = &I;
+        c.pathOff = P.pathOff + I.pathOffOff;
+        c.pathKmer = P.pathKmer + I.pathKmerOff;
+        c.pcCol = P.pcCol + I.pathKmerOff;
+        c.bandL = P.bandL + I.diagOff; c.bandW = P.bandW + I.diagOff; c.bandOff = P.bandOff + I.diagOff;
+        c.F = P.scratch + (int64_t) blockIdx.x * P.slabDoubles;
+        double *slabB = c.F + P.ringSize * 3;
+        c.B = P.mpCap > 0 ? sa_mpsm : slabB;
+        c.bStride = P.mpCap > 0 ? P.mpCap : P.maxDiagPC;
+        c.vals = slabB + 3 * P.maxDiagPC * 3;
+        c.E = c.vals + 2 * P.maxWidth;
+        c.ringMask = P.ringSize - 1;
+        const int64_t nDiag = (int64_t) I.lX + I.lY;
+        int64_t nPairs = 0;
+        if (nDiag > 0) {
+            MDiag g1 = m_diag(c, 0), g2 = g1;       // d - 1, d - 2
+            {
+                const bool ragged = I.flags & 1;
+                for (int32_t j = threadIdx.x; j < g1.nPC; j += blockDim.x) {
+                    double *o = m_W(c, 0, j), *r = m_F(c, g1, j);
+                    o[0] = r[0] = ragged ? SA_NEG_INF : 0.0;
+                    o[1] = r[1] = ragged ? 0.0 : SA_NEG_INF;
+                    o[2] = r[2] = ragged ? 0.0 : SA_NEG_INF;
+                }
+            }
+            int64_t tracedBackTo = 0;
+            for (int64_t d = 1; d <= nDiag; d++) {
+                __syncthreads();
+                const MDiag g = m_diag(c, d);
+                m_forwardDiag(c, d, g, g1, g2, d >= 2);
+                const bool atEnd = d == nDiag;
+                const bool tbPoint = d >= tracedBackTo + P.minDiags && (int64_t) g.W <= P.expansion * 2 + 1;
+                if (!(atEnd || tbPoint)) { g2 = g1; g1 = g; continue; }
+                __syncthreads();
+                {   // end / ragged end state on the traceback start diagonal (stateMachine.c:1147-1173)
+                    const bool rag = atEnd && (I.flags & 2);
+                    const double e0 = rag ? __ddiv_rn(__dadd_rn(P.trans[T_GAP_OPEN_X], P.trans[T_GAP_OPEN_Y]), 2.0) : P.trans[T_MATCH_CONTINUE];
+                    const double e1 = rag ? P.trans[T_GAP_EXTEND_X] : P.trans[T_MATCH_FROM_GAP_X];
+                    const double e2 = rag ? P.trans[T_GAP_EXTEND_Y] : P.trans[T_MATCH_FROM_GAP_Y];
+                    for (int32_t j = threadIdx.x; j < g.nPC; j += blockDim.x) {
+                        double *o = m_W(c, d, j);
+                        o[0] = e0; o[1] = e1; o[2] = e2;
+                    }
+                }
+                const int64_t tracedBackFrom = d - (atEnd ? 0 : P.traceBack + 1);
+                double total = SA_NEG_INF;
+                int64_t nPost = 0;
+                MDiag b0 = g, b1 = g, b2 = g;       // d2 - 1, d2, d2 + 1 while the loop runs (b1 = current callback diagonal)
+                for (int64_t d2 = d; d2 > tracedBackTo; d2--) {
+                    __syncthreads();
+                    const bool post = d2 <= tracedBackFrom;
+                    if (post && nPost++ % 10 == 0) {
+                        g_totalProbability(c, d2, d, &sTotal);
+                        total = sTotal;
+                    }
+                    if (d2 - 1 > tracedBackTo) {
+                        b0 = m_diag(c, d2 - 1);
+                        m_backwardDiag(c, d2 - 1, b0, b1, b2, true, d2 + 1 <= d);
+                    }
+                    if (post) g_posteriorDiag(c, d2, total, &nPairs, sWarp);
+                    b2 = b1; b1 = b0;
+                }
+                tracedBackTo = tracedBackFrom;
+                if (!atEnd) {       // the forward sweep goes on: f(d), f(d - 1) back into the working set
+                    __syncthreads();
+                    for (int32_t j = threadIdx.x; j < g.nPC; j += blockDim.x) {
+                        const double *r = m_F(c, g, j);
+                        double *o = m_W(c, d, j);
+                        o[0] = r[0]; o[1] = r[1]; o[2] = r[2];
+                    }
+                    for (int32_t j = threadIdx.x; j < g1.nPC; j += blockDim.x) {
+                        const double *r = m_F(c, g1, j);
+                        double *o = m_W(c, d - 1, j);
+                        o[0] = r[0]; o[1] = r[1]; o[2] = r[2];
+                    }
+                }
+                g2 = g1; g1 = g;
+            }
+        }
+        if (threadIdx.x == 0) P.pairCount[it] = nPairs;
     }
 }

@@ -341,7 +341,9 @@ struct sa_batch {
     std::vector<ItemRec> items;  // global item id = index
     // shared inputs
     DevBuf<double> dEvMean, dEvNoise, dEvLogNoise;
-    DevBuf<int32_t> dPathOff, dPathKmer, dAnchors;
+    DevBuf<int32_t> dPathOff, dPathKmer, dPcCol, dAnchors;
+    int mpThreads = 0;         // > 0: the alignment pass of the general items runs on sa_mp_kernel
+    size_t mpSmem = 0;
     // outputs (indexed by global item id)
     DevBuf<sa_pair_t> dPairs;
     DevBuf<int64_t> dPairCount, dAssignCount;
@@ -627,7 +629,7 @@ static int prepareBatch(const sa_model_t *m, const sa_read_t *reads, int64_t nRe
 
     const bool needNoise = m->kind == SA_EMIT_GAUSS_NOISE_SCALED || m->kind == SA_EMIT_GAUSS_NOISE_DESCALE;
     const bool fastModel = modelFastEligible(m, b->expectations) && getenv("SA_FORCE_GENERAL") == nullptr;
-    PinVec<int32_t> pathOff, pathKmer, anchors32;
+    PinVec<int32_t> pathOff, pathKmer, pcCol, anchors32;
     PinVec<double> evMean, evNoise, evLogNoise;
     std::vector<ItemRec> &items = b->items;
 
@@ -743,7 +745,7 @@ static int prepareBatch(const sa_model_t *m, const sa_read_t *reads, int64_t nRe
         sa_set_error("sa_batch_prepare: batch too large (more than 2^31 kmer paths); split it");
         return SA_ERR_INPUT;
     }
-    bool pinOk = evMean.resize(evTot) && pathOff.resize(poTot) && pathKmer.resize(pkTot) && anchors32.resize(anTot * 2);
+    bool pinOk = evMean.resize(evTot) && pathOff.resize(poTot) && pathKmer.resize(pkTot) && pcCol.resize(pkTot) && anchors32.resize(anTot * 2);
     if (needNoise) pinOk = pinOk && evNoise.resize(evTot) && evLogNoise.resize(evTot);
     if (!pinOk) {
         sa_set_error("sa_batch_prepare: cannot allocate pinned staging memory");
@@ -776,8 +778,10 @@ static int prepareBatch(const sa_model_t *m, const sa_read_t *reads, int64_t nRe
             // kmer paths per matrix column (column 0 = NULL kmer)
             int32_t *po = pathOff.data() + it.pathOffOff;
             int32_t *pk = pathKmer.data() + it.pathKmerOff;
+            int32_t *pcc = pcCol.data() + it.pathKmerOff;      // column of every path-cell (sa_mp_kernel)
             int64_t w = 0;
             po[0] = 0;
+            pcc[w] = 0;
             pk[w++] = -1;
             po[1] = 1;
             int64_t roll = -1;
@@ -793,11 +797,12 @@ static int prepareBatch(const sa_model_t *m, const sa_read_t *reads, int64_t nRe
                         roll = 0;
                         for (int q = 0; q < m->k; q++) roll = roll * m->A + charCode[(unsigned char) km[q]];
                     }
+                    pcc[w] = (int32_t) x;
                     pk[w++] = (int32_t) roll;
                 } else {
                     roll = -1;
                     sa_kmer_paths(km, *m, *ambig, pathsL);  // characters were validated in phase A
-                    for (int32_t v : pathsL) pk[w++] = v;
+                    for (int32_t v : pathsL) { pcc[w] = (int32_t) x; pk[w++] = v; }
                 }
                 po[x + 1] = (int32_t) w;
                 nAmbInWin -= charAmbig[(unsigned char) km[0]];
@@ -815,6 +820,7 @@ static int prepareBatch(const sa_model_t *m, const sa_read_t *reads, int64_t nRe
     if ((rc = b->dEvLogNoise.upload(evLogNoise, st, &b->h2dBytes))) return rc;
     if ((rc = b->dPathOff.upload(pathOff, st, &b->h2dBytes))) return rc;
     if ((rc = b->dPathKmer.upload(pathKmer, st, &b->h2dBytes))) return rc;
+
     if ((rc = b->dAnchors.upload(anchors32, st, &b->h2dBytes))) return rc;
     if ((rc = b->dCounters.alloc(16, st))) return rc;
 
@@ -1144,7 +1150,8 @@ static int prepareBatch(const sa_model_t *m, const sa_read_t *reads, int64_t nRe
         if ((rc = b->dBandW.upload(bandW, st, &b->h2dBytes))) return rc;
         if ((rc = b->dBandOff.upload(bandOff, st, &b->h2dBytes))) return rc;
         int64_t ring = nextPow2(ringNeedMax);
-        int64_t slab = ring * 3 + 9 * maxDiagPC + 2 * maxWidth;
+        const bool mpKernel = !b->expectations && getenv("SA_NO_MP") == nullptr;
+        int64_t slab = ring * 3 + 9 * maxDiagPC + 2 * maxWidth + (mpKernel ? ring * 2 : 0);   // (+ the emission ring of sa_mp_kernel)
         size_t freeB = 0, totalB = 0;
         CK(cudaMemGetInfo(&freeB, &totalB));
         {   // memory the stream-ordered pool holds but does not use (the release threshold is lifted) is available too
@@ -1166,6 +1173,23 @@ static int prepareBatch(const sa_model_t *m, const sa_read_t *reads, int64_t nRe
         if ((rc = b->dGScratch.alloc((size_t) b->gCta * slab, st))) return rc;
         g.items = b->dGItems.p; g.order = b->dGOrder.p; g.nItems = (int32_t) b->gOrder.size();
         g.pathOff = b->dPathOff.p; g.pathKmer = b->dPathKmer.p;
+        // alignment runs: sa_mp_kernel (working set in shared memory when the widest diagonal fits; SA_NO_MP keeps the old one)
+        if (mpKernel) {
+            if ((rc = b->dPcCol.upload(pcCol, st, &b->h2dBytes))) return rc;
+            g.pcCol = b->dPcCol.p;
+            const size_t need = (size_t) 3 * maxDiagPC * 3 * sizeof(double);
+            g.mpCap = need <= kSmemCap - 2048 ? (int32_t) maxDiagPC : 0;
+            b->mpSmem = g.mpCap > 0 ? need : 0;
+            b->mpThreads = 256;
+            static size_t raised = 0;
+            if (b->mpSmem > 48 * 1024 && b->mpSmem > raised) {
+                CK(cudaFuncSetAttribute(sa_mp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) kSmemCap));
+                raised = kSmemCap;
+            }
+            int bps = 1;
+            CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, sa_mp_kernel, 256, b->mpSmem));
+            b->gCta = std::min(b->gCta, nSM * std::max(1, bps));
+        }
         g.evMean = b->dEvMean.p; g.evNoise = b->dEvNoise.p; g.evLogNoise = b->dEvLogNoise.p;
         g.bandL = b->dBandL.p; g.bandW = b->dBandW.p; g.bandOff = b->dBandOff.p;
         g.kt = m->dev->kt; g.gapX = m->dev->gapX;
@@ -1290,6 +1314,7 @@ static int launchBatch(sa_batch_t *b) {
         GParams g = b->gp;
         g.counter = b->dCounters.p + 4;
         if (b->expectations) sa_general_kernel<true><<<b->gCta, 128, 0, st>>>(g);
+        else if (b->mpThreads) sa_mp_kernel<<<b->gCta, b->mpThreads, b->mpSmem, st>>>(g);
         else sa_general_kernel<false><<<b->gCta, 128, 0, st>>>(g);
         b->lastLaunches++;
         CK(cudaGetLastError());
