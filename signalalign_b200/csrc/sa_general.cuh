@@ -380,7 +380,9 @@ __device__ void g_totalProbability(const GCtx &c, int64_t d, int64_t top, double
         // below the running maximum is an exact no-op (the accumulator stays within 0.1 of that maximum: each logAdd
         // returns at least max - 5e-4, and |x - y| >= 7.5 returns the larger operand unchanged), so it is skipped
         // without touching the dependent chain — as the band kernel's fold does (sa_cta.cuh, orderedFold2).
-        const bool skipOk = g.W <= 256 && (!hasMatch || gb.W <= 256);
+        // (any width: the accumulator never falls below the running maximum — logAdd returns at least its larger operand —,
+        // which is the rule the wide kernel's fold applies to windows of up to 4096 cells with byte-identical results)
+        const bool skipOk = true;
         const int32_t nB = hasMatch ? gb.W : 0, nMax = g.W > nB ? g.W : nB;
         const double *vb = c.vals + c.P->maxWidth;
         double tot = SA_NEG_INF, t2 = SA_NEG_INF, mx = SA_NEG_INF, mx2 = SA_NEG_INF;
@@ -403,14 +405,17 @@ __device__ void g_totalProbability(const GCtx &c, int64_t d, int64_t top, double
 }
 
 // exclusive block scan of one int per thread; returns the thread's offset, *total = block sum
-__device__ __forceinline__ int g_blockScan(int v, int *sWarp, int *total) {
+// (sWarp holds two sets of per-warp sums used alternately — `phase` counts the calls, identically in every thread —, so
+// that one barrier per call is enough: a set is rewritten two calls, i.e. at least one barrier, after its last reader)
+__device__ __forceinline__ int g_blockScan(int v, int *sWarpBase, int *total, int &phase) {
     int lane = threadIdx.x & 31, w = threadIdx.x >> 5, nW = (blockDim.x + 31) >> 5;
     int inc = v;
     for (int o = 1; o < 32; o <<= 1) {
         int t = __shfl_up_sync(0xffffffffu, inc, o);
         if (lane >= o) inc += t;
     }
-    __syncthreads();  // protect sWarp from the previous use
+    int *sWarp = sWarpBase + 8 * (phase & 1);
+    phase++;
     if (lane == 31) sWarp[w] = inc;
     __syncthreads();
     int base = 0, tot = 0;
@@ -423,7 +428,7 @@ __device__ __forceinline__ int g_blockScan(int v, int *sWarp, int *total) {
 }
 
 // diagonalCalculationPosteriorMatchProbs (pairwiseAligner.c:1355-1421), pairs written in the reference's order
-__device__ void g_posteriorDiag(const GCtx &c, int64_t d, double total, int64_t *nPairs, int *sWarp) {
+__device__ void g_posteriorDiag(const GCtx &c, int64_t d, double total, int64_t *nPairs, int *sWarp, int &phase) {
     GDiag g = g_diag(c, d);
     for (int32_t base = 0; base < g.W; base += blockDim.x) {
         int32_t ci = base + threadIdx.x;
@@ -445,7 +450,7 @@ __device__ void g_posteriorDiag(const GCtx &c, int64_t d, double total, int64_t 
             }
         }
         int tot;
-        int off = g_blockScan(cnt, sWarp, &tot);
+        int off = g_blockScan(cnt, sWarp, &tot, phase);
         if (cnt > 0) {
             const int32_t *kC = c.pathKmer + c.pathOff[x];
             int64_t w = *nPairs + off;
@@ -474,7 +479,7 @@ __device__ void g_posteriorDiag(const GCtx &c, int64_t d, double total, int64_t 
 // `floorDiag` = tracedBackTo of the running block: forward diagonals below it have been freed by the reference
 // (pairwiseAligner.c:1556-1569), so their cells are NULL to the callback.
 __device__ void g_expectationsDiag(const GCtx &c, int64_t d, double total, int64_t floorDiag, double *acc9,
-                                   int64_t *nAssign, int *sWarp) {
+                                   int64_t *nAssign, int *sWarp, int &phase) {
     const double *T = c.P->trans;
     const bool hdp = c.P->kind == SA_EMIT_HDP;
     GDiag g = g_diag(c, d), g1 = g, g2 = g;
@@ -488,7 +493,7 @@ __device__ void g_expectationsDiag(const GCtx &c, int64_t d, double total, int64
             int64_t w = 0;
             if (pass == 1) {
                 int tot;
-                int off = g_blockScan(cnt, sWarp, &tot);
+                int off = g_blockScan(cnt, sWarp, &tot, phase);
                 w = *nAssign + off;
                 *nAssign += tot;
             }
@@ -562,9 +567,10 @@ template <bool EXPECT>
 __global__ void SA_GEN_BOUNDS sa_general_kernel(const GParams P) {
     __shared__ int sItem;
     __shared__ double sTotal;
-    __shared__ int sWarp[8];
+    __shared__ int sWarp[16];
     __shared__ double sAcc[8][9];
     sa_logAdd_init();
+    int scanPhase = 0;                    // g_blockScan's call count (which of its two sets of warp sums is next)
     for (;;) {
         __syncthreads();
         if (threadIdx.x == 0) sItem = atomicAdd(P.counter, 1);
@@ -638,9 +644,9 @@ __global__ void SA_GEN_BOUNDS sa_general_kernel(const GParams P) {
                     if (post) {
                         if (EXPECT) {
                             likelihood += total;
-                            g_expectationsDiag(c, d2, total, tracedBackTo, acc9, &nAssign, sWarp);
+                            g_expectationsDiag(c, d2, total, tracedBackTo, acc9, &nAssign, sWarp, scanPhase);
                         } else {
-                            g_posteriorDiag(c, d2, total, &nPairs, sWarp);
+                            g_posteriorDiag(c, d2, total, &nPairs, sWarp, scanPhase);
                         }
                     }
                 }
@@ -779,7 +785,7 @@ __device__ __forceinline__ void m_backwardDiag(const GCtx &c, int64_t d, const M
     const double *T = c.P->trans;
     const bool swX = T[T_GAP_SWITCH_TO_X] > SA_NEG_INF || T[T_GAP_SWITCH_TO_X] != T[T_GAP_SWITCH_TO_X];
     for (int32_t j = threadIdx.x; j < g.nPC; j += blockDim.x) {
-        const int32_t x = c.pcCol[g.pc0 + j], y = (int32_t) d - x;
+        const int32_t x = c.pcCol[g.pc0 + j];
         const int32_t colPC = c.pathOff[x] - g.pc0, nQ = c.pathOff[x + 1] - c.pathOff[x];
         const int32_t pa = has2 ? m_colPC(c, g2, x + 1) : -1;      // (x+1, y+1): this cell is its "middle"
         const int32_t pu = has1 ? m_colPC(c, g1, x) : -1;          // (x,   y+1): this cell is its "upper"
@@ -830,8 +836,9 @@ __global__ void __launch_bounds__(256) sa_mp_kernel(const GParams P) {
     extern __shared__ __align__(16) double sa_mpsm[];
     __shared__ int sItem;
     __shared__ double sTotal;
-    __shared__ int sWarp[8];
+    __shared__ int sWarp[16];
     sa_logAdd_init();
+    int scanPhase = 0;                    // g_blockScan's call count (which of its two sets of warp sums is next)
     for (;;) {
         __syncthreads();
         if (threadIdx.x == 0) sItem = atomicAdd(P.counter, 1);
@@ -899,7 +906,7 @@ __global__ void __launch_bounds__(256) sa_mp_kernel(const GParams P) {
                         b0 = m_diag(c, d2 - 1);
                         m_backwardDiag(c, d2 - 1, b0, b1, b2, true, d2 + 1 <= d);
                     }
-                    if (post) g_posteriorDiag(c, d2, total, &nPairs, sWarp);
+                    if (post) g_posteriorDiag(c, d2, total, &nPairs, sWarp, scanPhase);
                     b2 = b1; b1 = b0;
                 }
                 tracedBackTo = tracedBackFrom;
